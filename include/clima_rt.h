@@ -1,0 +1,233 @@
+/*
+ * clima_rt.h -- C ABI of the B200-native radiative-transfer hot path of Clima.
+ *
+ * This is the drop-in boundary.  Every entry point below replaces (for a batch of
+ * atmospheric columns) one piece of the reference's Fortran path and follows the
+ * reference's own C-ABI conventions (clima/fortran/clima_c_api.f90:5,57-69 and
+ * clima/fortran/Radtran.f90:77-107):
+ *
+ *   - every export is a plain C function returning void ("bind(c) subroutine");
+ *   - the first argument of a method is the opaque handle, by value;
+ *   - ALL scalars are passed by reference (int32_t*, double*, bool as int32_t*);
+ *   - arrays are column-major (Fortran order) doubles, preceded by their dims;
+ *   - the last argument is `char err[CLIMA_RT_ERR_LEN+1]`: "" on success, otherwise a
+ *     NUL-terminated message (the Cython layer raises ClimaException when
+ *     len(err.strip()) > 0, clima/cython/AdiabatClimate.pyx:190-192).
+ *
+ * There are no torch types, no C++ types and no CUDA types in any signature: host
+ * pointers in, host pointers out (the `_device` variants take raw device pointers).
+ * There is NO CPU fallback: every compute entry fails with an err message if no
+ * CUDA device is usable.
+ *
+ * Layout conventions (identical to the reference):
+ *   - inputs are ground-first (index 0 = bottom layer), pressures in bar, number
+ *     densities in molecules/cm^3, dz in cm  (src/radtran/clima_radtran.f90:221-233);
+ *   - batched arrays put the column index LAST (slowest): T(nz,ncol),
+ *     densities(nz,ng,ncol), ... so one column's block is exactly the array the
+ *     reference's single-column `radiate` takes;
+ *   - outputs are ground-first, level index nz (0-based) = top of atmosphere
+ *     (src/radtran/clima_radtran_radiate.f90:138-154).
+ */
+#ifndef CLIMA_RT_H
+#define CLIMA_RT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CLIMA_RT_ERR_LEN 1024 /* clima/fortran/clima_c_api.f90:5 (err_len) */
+
+/* status bits written per column into clima_rt_out.status */
+#define CLIMA_RT_STATUS_RADIUS_CLAMPED 1 /* particle radius outside table: the reference fails the
+                                            whole call (clima_radtran_types.f90:972-976,773-776) */
+#define CLIMA_RT_STATUS_NONFINITE 2      /* a non-finite flux was produced */
+
+/* ---------------------------------------------------------------------------------
+ * Read-only opacity tables.  Mirrors `type OpticalProperties` and its members
+ * (src/radtran/clima_radtran_types.f90:23-141) after `create_OpticalProperties` has
+ * rebinned everything onto the opacity grid
+ * (src/radtran/clima_radtran_types_create.f90:272-645).  All indices are 1-based
+ * species indices exactly as the Fortran holds them (sp_ind, p_ind, LH2O).
+ * All pointers are HOST pointers; clima_rt_create copies them to the device.
+ * ------------------------------------------------------------------------------- */
+typedef struct clima_rt_tables {
+  /* opacity grid: OpticalProperties%wavl (nm, ascending), freq = c/(wavl*1e-9) */
+  int32_t nw;
+  const double *wavl; /* (nw+1) */
+
+  int32_t ng; /* Radtran%ng: gases in the model   (clima_radtran.f90:33) */
+  int32_t np; /* Radtran%np: particles in the model (clima_radtran.f90:36) */
+
+  /* k-distributions: type Ktable (clima_radtran_types.f90:23-38); all tables share
+     `weights` within 1e-12 (clima_radtran_types_create.f90:379-389); Ksettings wbin/wbin_e/wxy
+     are derived from them as in create_Ksettings (:191-224). */
+  int32_t nk;
+  int32_t ngauss;
+  const double *weights;         /* (ngauss) of the first table */
+  const int32_t *k_sp_ind;       /* (nk) */
+  const int32_t *k_npress;       /* (nk) */
+  const int32_t *k_ntemp;        /* (nk) */
+  const double *const *k_log10P; /* nk pointers, each (npress) log10(bar), strictly increasing */
+  const double *const *k_temp;   /* nk pointers, each (ntemp) K, strictly increasing */
+  const double *const *k_log10k; /* nk pointers, each (ngauss,npress,ntemp,nw) column-major,
+                                    log10(cm^2/molecule)  (types_create.f90:1291-1358) */
+
+  /* CIA: type Xsection with xs_type=CIAXsection (clima_radtran_types.f90:44-55).
+     dim 1: data = log10 xs (ntemp,nw) column-major, interpolated linearly in clamped T;
+     dim 0: data = xs_0d (nw). */
+  int32_t ncia;
+  const int32_t *cia_sp_ind; /* (2,ncia) column-major */
+  const int32_t *cia_dim;    /* (ncia) 0 or 1 */
+  const int32_t *cia_ntemp;  /* (ncia) (ignored for dim 0) */
+  const double *const *cia_temp;
+  const double *const *cia_data;
+
+  /* Rayleigh: xs_0d per species (types_create.f90:1048-1088) */
+  int32_t nray;
+  const int32_t *ray_sp_ind; /* (nray) */
+  const double *ray_xs;      /* (nw,nray) column-major */
+
+  /* photolysis / absorption cross sections: same layout as CIA with one species each */
+  int32_t npxs;
+  const int32_t *pxs_sp_ind; /* (npxs) */
+  const int32_t *pxs_dim;
+  const int32_t *pxs_ntemp;
+  const double *const *pxs_temp;
+  const double *const *pxs_data;
+
+  /* water continuum: type WaterContinuum (clima_radtran_types.f90:68-77) */
+  int32_t has_cont;
+  int32_t cont_LH2O;
+  int32_t cont_ntemp;
+  const double *cont_temp;          /* (ntemp) */
+  const double *cont_log10_H2O;     /* (ntemp,nw) column-major */
+  const double *cont_log10_foreign; /* (ntemp,nw) */
+
+  /* particles: type ParticleXsection (clima_radtran_types.f90:57-66) */
+  int32_t npart;
+  const int32_t *part_p_ind; /* (npart) */
+  const int32_t *part_nrad;  /* (npart) */
+  const double *const *part_radii; /* each (nrad) cm, strictly increasing */
+  const double *const *part_w0;    /* each (nrad,nw) */
+  const double *const *part_qext;  /* each (nrad,nw) */
+  const double *const *part_gt;    /* each (nrad,nw) */
+
+  /* channels: type RTChannel (clima_radtran_types.f90:263-269): 1-based inclusive bin ranges
+     into the opacity grid (types_create.f90:250-268). */
+  int32_t ir_ind_start, ir_ind_end;
+  int32_t sol_ind_start, sol_ind_end;
+
+  /* Radtran%photons_sol (nw_sol) mW/m^2/Hz (clima_radtran.f90:63-65) */
+  const double *photons_sol;
+} clima_rt_tables;
+
+/* ---------------------------------------------------------------------------------
+ * Run-time knobs: the public members of `type Radtran` (clima_radtran.f90:51-68).
+ * ------------------------------------------------------------------------------- */
+typedef struct clima_rt_params {
+  double diurnal_fac;         /* default 0.5 */
+  double photon_scale_factor; /* default 1.0 */
+  double ir_tau_min;          /* default 1e-6 */
+  int32_t has_hard_surface;   /* default 1 */
+  int32_t nzenith;
+  const double *zenith_u;       /* (nzenith) cos(zenith) */
+  const double *zenith_weights; /* (nzenith) */
+  const double *surface_albedo;     /* (nw_sol) */
+  const double *surface_emissivity; /* (nw_ir) */
+} clima_rt_params;
+
+/* ---------------------------------------------------------------------------------
+ * Result pointers: `type ClimaRadtranWrk` for both channels + f_total
+ * (clima_radtran.f90:11-25,70-72) + TOA_fluxes' ISR/OLR (:339-340), per column.
+ * Mandatory: fup_n_*, fdn_n_*, f_total, ISR, OLR.  Any spectral pointer may be NULL.
+ * ------------------------------------------------------------------------------- */
+typedef struct clima_rt_out {
+  double *fup_n_ir;  /* (nz+1,ncol) mW/m^2 */
+  double *fdn_n_ir;  /* (nz+1,ncol) */
+  double *fup_n_sol; /* (nz+1,ncol) */
+  double *fdn_n_sol; /* (nz+1,ncol) */
+  double *f_total;   /* (nz+1,ncol) */
+  double *ISR;       /* (ncol) */
+  double *OLR;       /* (ncol) */
+  /* optional spectral outputs (NULL = not wanted) */
+  double *fup_a_ir;     /* (nz+1,nw_ir,ncol) mW/m^2/Hz */
+  double *fdn_a_ir;     /* (nz+1,nw_ir,ncol) */
+  double *tau_band_ir;  /* (nz,nw_ir,ncol) */
+  double *fup_a_sol;    /* (nz+1,nw_sol,ncol) */
+  double *fdn_a_sol;    /* (nz+1,nw_sol,ncol) */
+  double *amean_sol;    /* (nz+1,nw_sol,ncol) photons/cm^2/s */
+  double *tau_band_sol; /* (nz,nw_sol,ncol) */
+  int32_t *status;      /* (ncol) CLIMA_RT_STATUS_* bits, may be NULL */
+} clima_rt_out;
+
+/* Create / destroy.  Replaces the table-holding part of `create_Radtran_2`
+   (clima_radtran.f90:128-219): uploads the tables to device `*device` and allocates nothing
+   per-column yet.  `*handle` receives an opaque pointer (like allocate_adiabatclimate,
+   clima/fortran/AdiabatClimate.f90:7-22). */
+void clima_rt_create(const clima_rt_tables *tables, const clima_rt_params *params,
+                     const int32_t *device, void **handle, char *err);
+void clima_rt_destroy(void *handle);
+
+/* Replace the run-time knobs (setters of clima/fortran/Radtran.f90:130-300). */
+void clima_rt_set_params(void *handle, const clima_rt_params *params, char *err);
+
+/* Custom optical properties already interpolated onto the opacity grid, i.e. the state that
+   OpticalProperties_set_custom_optical_properties leaves in dtau_dz_interp/w0_interp/g0_interp
+   (clima_radtran_types.f90:504-531): log10P (nP, ascending, log10 dyn/cm^2) and (nP,nw) tables.
+   clima_rt_unset_custom_optical_properties restores the `tiny(0d0)` behaviour (:558-563). */
+void clima_rt_set_custom_optical_properties(void *handle, const int32_t *nP, const double *log10P,
+                                            const double *dtau_dz, const double *w0,
+                                            const double *g0, char *err);
+void clima_rt_unset_custom_optical_properties(void *handle);
+
+/* The batched-column entry point: `Radtran%radiate` + `Radtran%TOA_fluxes`
+   (clima_radtran.f90:221-342) for ncol independent columns.
+     T_surface(ncol), T(nz,ncol), P(nz,ncol) [bar], densities(nz,ng,ncol), dz(nz,ncol),
+     pdensities(nz,np,ncol) / radii(nz,np,ncol) (both NULL or both given; mandatory if np>0,
+     clima_radtran.f90:426-436).
+   compute_opacity=0 reuses the opacity retained in the handle: either one set per column of the
+   previous call (same ncol, single chunk) or ONE column's set broadcast to all columns (the
+   frozen-opacity Jacobian mode of src/adiabat/clima_adiabat_solve.f90:798-820).
+   compute_solar=0 reuses the stale solar fluxes in f_total (clima_radtran.f90:286-289).
+   All data pointers are HOST pointers. */
+void clima_rt_radiate_batch(void *handle, const int32_t *ncol, const int32_t *nz, const int32_t *ng,
+                            const int32_t *np, const double *T_surface, const double *T,
+                            const double *P, const double *densities, const double *dz,
+                            const double *pdensities, const double *radii,
+                            const int32_t *compute_solar, const int32_t *compute_opacity,
+                            const clima_rt_out *out, char *err);
+
+/* Same, but every data pointer (inputs and `out` members) is a DEVICE pointer on the handle's
+   device; work is enqueued on the handle's stream and the call returns after a stream sync. */
+void clima_rt_radiate_batch_device(void *handle, const int32_t *ncol, const int32_t *nz,
+                                   const int32_t *ng, const int32_t *np, const double *T_surface,
+                                   const double *T, const double *P, const double *densities,
+                                   const double *dz, const double *pdensities, const double *radii,
+                                   const int32_t *compute_solar, const int32_t *compute_opacity,
+                                   const clima_rt_out *out, char *err);
+
+/* Copy the retained opacity of column `*icol` (0-based) of the last chunk to the host:
+   tau(nz,ngauss,nw), w0(nz,ngauss,nw), g(nz,nw), tau_band(nz,nw), all TOP-first exactly like
+   `type OpticalPropertiesResult` (clima_radtran_types.f90:242-247).  Test/debug hook. */
+void clima_rt_get_opacity(void *handle, const int32_t *icol, double *tau, double *w0, double *g,
+                          double *tau_band, char *err);
+
+/* Introspection used by the bench: number of kernel launches issued by the handle so far, the
+   per-stage device time (ms, CUDA events on the handle's stream) of the last batch call
+   [0]=optics+RORR [1]=two-stream IR [2]=two-stream solar [3]=integration [4]=whole call. */
+void clima_rt_get_launch_count(void *handle, int64_t *count);
+void clima_rt_get_stage_ms(void *handle, double *ms5);
+
+/* Measured FP64 issue roof of device `*device`: runs a dependent-chain-free DFMA kernel and
+   returns TFLOP/s (FMA = 2 flops).  Used as the roofline denominator. */
+void clima_rt_measure_fp64_peak(const int32_t *device, double *tflops, char *err);
+
+/* Library version string, NUL terminated (cf. clima_version_get, clima_c_api.f90:15-19). */
+void clima_rt_version_get(char *version_c /* [101] */);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CLIMA_RT_H */
