@@ -1,0 +1,681 @@
+// capi.cu -- host side of the C ABI declared in include/clima_rt.h.
+//
+// Owns the device copy of the opacity tables, the per-chunk column buffers, the retained opacity
+// (frozen-opacity / stale-solar semantics of Radtran_radiate, src/radtran/clima_radtran.f90:221-318)
+// and the launch sequence  prep -> optics+RORR -> Planck -> two-stream IR -> two-stream solar ->
+// integrate.  Error convention: clima/fortran/clima_c_api.f90:57-69 (err string, "" = success).
+// There is NO CPU fallback: every compute entry fails with an err message if CUDA is unusable.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/clima_rt.h"
+#include "rt_kernels.h"
+
+namespace {
+
+void set_err(char *err, const std::string &s) {
+  if (!err) return;
+  const size_t n = std::min<size_t>(s.size(), CLIMA_RT_ERR_LEN);
+  std::memcpy(err, s.data(), n);
+  err[n] = 0;
+}
+
+struct CudaError {
+  std::string msg;
+};
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess)                                                                    \
+      throw CudaError{std::string("CUDA error: ") + cudaGetErrorString(e_) + " at " #call};   \
+  } while (0)
+
+struct Handle {
+  int device = 0;
+  int num_sms = 148;
+  cudaStream_t st = nullptr;
+  std::vector<void *> table_allocs;  // freed at destroy
+  DevTables tb{};
+  DevParams pr{};
+  double *d_albedo = nullptr, *d_emiss = nullptr, *d_photons = nullptr;
+  double *d_custom[4] = {nullptr, nullptr, nullptr, nullptr};
+  int nw_ir = 0, nw_sol = 0;
+
+  // chunk buffers
+  int cap_cols = 0, cap_nz = 0;
+  bool cap_mem_limited = false;
+  std::vector<void *> chunk_allocs;
+  double *d_Tsurf = nullptr, *d_T = nullptr, *d_P = nullptr, *d_dens = nullptr, *d_dz = nullptr,
+         *d_pd = nullptr, *d_rd = nullptr;
+  DevChunk ch{};
+  DevFlux fx{};
+  double *d_tmp = nullptr;  // tau_band / get_opacity staging
+  size_t tmp_bytes = 0;
+  int ts_blocks = 0;
+
+  // retained state
+  int retained_opacity_ncol = 0, retained_nz = 0;
+  int retained_solar_ncol = 0;
+
+  // introspection
+  int64_t launches = 0;
+  cudaEvent_t ev[6] = {};
+  double stage_ms[5] = {0, 0, 0, 0, 0};
+};
+
+template <typename T>
+T *upload(Handle &h, const T *src, size_t n, bool track = true) {
+  if (n == 0) n = 1;
+  T *d = nullptr;
+  CK(cudaMalloc(&d, n * sizeof(T)));
+  if (src) CK(cudaMemcpy(d, src, n * sizeof(T), cudaMemcpyHostToDevice));
+  else CK(cudaMemset(d, 0, n * sizeof(T)));
+  if (track) h.table_allocs.push_back(d);
+  return d;
+}
+
+// k-distributions ascend in g by construction; verify so that RORR may skip the row-sorting stages.
+bool rows_sorted_check(const clima_rt_tables *t) {
+  const int G = t->ngauss;
+  for (int i = 0; i < t->nk; i++) {
+    const size_t n = (size_t)t->k_npress[i] * t->k_ntemp[i] * t->nw;
+    const double *f = t->k_log10k[i];
+    for (size_t r = 0; r < n; r++)
+      for (int g = 1; g < G; g++)
+        if (f[r * G + g] < f[r * G + g - 1]) return false;
+  }
+  return true;
+}
+
+void upload_params(Handle &h, const clima_rt_params *p) {
+  if (p->nzenith < 1 || p->nzenith > RT_MAXZEN)
+    throw CudaError{"nzenith must be between 1 and " + std::to_string(RT_MAXZEN)};
+  h.pr.diurnal_fac = p->diurnal_fac;
+  h.pr.photon_scale_factor = p->photon_scale_factor;
+  h.pr.ir_tau_min = p->ir_tau_min;
+  h.pr.has_hard_surface = p->has_hard_surface;
+  h.pr.nzen = p->nzenith;
+  for (int i = 0; i < p->nzenith; i++) {
+    h.pr.zen_u[i] = p->zenith_u[i];
+    h.pr.zen_w[i] = p->zenith_weights[i];
+  }
+  CK(cudaMemcpy(h.d_albedo, p->surface_albedo, h.nw_sol * sizeof(double), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(h.d_emiss, p->surface_emissivity, h.nw_ir * sizeof(double), cudaMemcpyHostToDevice));
+  h.pr.albedo = h.d_albedo;
+  h.pr.emiss = h.d_emiss;
+  h.pr.photons_sol = h.d_photons;
+}
+
+void build_tables(Handle &h, const clima_rt_tables *t) {
+  if (t->nk < 1)
+    throw CudaError{"There are no k-distributions, yet there must be some to compute total opacity."};
+  if (t->nk > RT_MAXK || t->ncia > RT_MAXCIA || t->nray > RT_MAXRAY || t->npxs > RT_MAXPXS ||
+      t->npart > RT_MAXPART)
+    throw CudaError{"too many opacity sources for the compiled table limits (rt_device.cuh)"};
+  if (t->ngauss < 1 || t->ngauss > 32) throw CudaError{"ngauss must be between 1 and 32"};
+  DevTables &d = h.tb;
+  std::memset(&d, 0, sizeof(d));
+  d.nw = t->nw; d.ng = t->ng; d.np = t->np; d.nk = t->nk; d.G = t->ngauss;
+  d.ncia = t->ncia; d.nray = t->nray; d.npxs = t->npxs; d.npart = t->npart;
+  d.has_cont = t->has_cont; d.cont_LH2O = t->cont_LH2O; d.cont_nt = t->cont_ntemp;
+  d.ir_start = t->ir_ind_start - 1; d.ir_end = t->ir_ind_end - 1;
+  d.sol_start = t->sol_ind_start - 1; d.sol_end = t->sol_ind_end - 1;
+  h.nw_ir = d.ir_end - d.ir_start + 1;
+  h.nw_sol = d.sol_end - d.sol_start + 1;
+  if (h.nw_ir < 1 || h.nw_sol < 1 || d.ir_end >= d.nw || d.sol_end >= d.nw || d.ir_start < 0 ||
+      d.sol_start < 0)
+    throw CudaError{"channel bin ranges are outside the opacity grid"};
+  d.rows_sorted = rows_sorted_check(t) ? 1 : 0;
+  const int G = d.G, nw = d.nw;
+  for (int i = 0; i < t->nk; i++) {
+    DevK &k = d.k[i];
+    k.sp = t->k_sp_ind[i]; k.np = t->k_npress[i]; k.nt = t->k_ntemp[i];
+    if (k.np < 2 || k.nt < 2) throw CudaError{"k-table grids need at least 2 points"};
+    k.logP = upload(h, t->k_log10P[i], k.np);
+    k.T = upload(h, t->k_temp[i], k.nt);
+    k.log10k = upload(h, t->k_log10k[i], (size_t)G * k.np * k.nt * nw);
+  }
+  auto xs = [&](DevXS &x, int dim, int nt, const double *temp, const double *data) {
+    x.dim = dim; x.nt = nt;
+    if (dim == 1) {
+      x.temp = upload(h, temp, nt);
+      x.data = upload(h, data, (size_t)nt * nw);
+    } else {
+      x.temp = nullptr;
+      x.data = upload(h, data, nw);
+    }
+  };
+  for (int i = 0; i < t->ncia; i++) {
+    d.cia[i].sp1 = t->cia_sp_ind[2 * i]; d.cia[i].sp2 = t->cia_sp_ind[2 * i + 1];
+    xs(d.cia[i], t->cia_dim[i], t->cia_ntemp[i], t->cia_temp[i], t->cia_data[i]);
+  }
+  for (int i = 0; i < t->npxs; i++) {
+    d.pxs[i].sp1 = t->pxs_sp_ind[i]; d.pxs[i].sp2 = 0;
+    xs(d.pxs[i], t->pxs_dim[i], t->pxs_ntemp[i], t->pxs_temp[i], t->pxs_data[i]);
+  }
+  for (int i = 0; i < t->nray; i++) d.ray_sp[i] = t->ray_sp_ind[i];
+  d.ray_xs = upload(h, t->ray_xs, (size_t)nw * std::max(1, t->nray));
+  if (t->has_cont) {
+    d.cont_temp = upload(h, t->cont_temp, t->cont_ntemp);
+    d.cont_H2O = upload(h, t->cont_log10_H2O, (size_t)t->cont_ntemp * nw);
+    d.cont_foreign = upload(h, t->cont_log10_foreign, (size_t)t->cont_ntemp * nw);
+  }
+  for (int i = 0; i < t->npart; i++) {
+    DevPart &p = d.part[i];
+    p.p_ind = t->part_p_ind[i]; p.nr = t->part_nrad[i];
+    p.radii = upload(h, t->part_radii[i], p.nr);
+    p.w0 = upload(h, t->part_w0[i], (size_t)p.nr * nw);
+    p.qext = upload(h, t->part_qext[i], (size_t)p.nr * nw);
+    p.gt = upload(h, t->part_gt[i], (size_t)p.nr * nw);
+  }
+  d.wavl = upload(h, t->wavl, nw + 1);
+  std::vector<double> freq(nw + 1);
+  for (int i = 0; i < nw + 1; i++) freq[i] = RT_C_LIGHT / (t->wavl[i] * 1.0e-9);  // types_create.f90:360-361
+  d.freq = upload(h, freq.data(), nw + 1);
+  // create_Ksettings, types_create.f90:191-224
+  std::vector<double> wb(t->weights, t->weights + G), we(G + 1), iw(G);
+  we[0] = 0.0;
+  for (int i = 1; i < G + 1; i++) we[i] = wb[i - 1] + we[i - 1];  // weights_to_bins
+  for (int i = 0; i < G; i++) iw[i] = 1.0 / (we[i + 1] - we[i]);
+  d.wbin = upload(h, wb.data(), G);
+  d.wbin_e = upload(h, we.data(), G + 1);
+  d.inv_dw = upload(h, iw.data(), G);
+  h.d_photons = upload(h, t->photons_sol, h.nw_sol);
+  h.d_albedo = upload<double>(h, nullptr, h.nw_sol);
+  h.d_emiss = upload<double>(h, nullptr, h.nw_ir);
+}
+
+void free_chunk(Handle &h) {
+  for (void *p : h.chunk_allocs) cudaFree(p);
+  h.chunk_allocs.clear();
+  h.cap_cols = 0;
+  h.cap_nz = 0;
+  h.retained_opacity_ncol = 0;
+  h.retained_solar_ncol = 0;
+}
+
+template <typename T>
+T *calloc_dev(Handle &h, size_t n) {
+  T *d = nullptr;
+  CK(cudaMalloc(&d, std::max<size_t>(n, 1) * sizeof(T)));
+  h.chunk_allocs.push_back(d);
+  return d;
+}
+
+size_t per_col_bytes(const Handle &h, int nz) {
+  const DevTables &tb = h.tb;
+  const size_t L = nz + 1;
+  size_t b = 0;
+  b += (size_t)tb.nw * nz * tb.G * 8 * 2;            // tau, w0
+  b += (size_t)tb.nw * nz * 8 * 2;                   // gt, tband
+  b += (size_t)nz * rt_nbr(tb) * 12 + (size_t)nz * 16 + 64;  // brackets, slots, foreign_col
+  b += L * (2 * h.nw_ir + 3 * h.nw_sol) * 8;         // spectral fluxes
+  b += L * h.nw_ir * 8;                              // Planck
+  b += L * 5 * 8 + 16;                               // integrated
+  b += (size_t)nz * (3 + tb.ng + 2 * tb.np) * 8 + 8; // inputs
+  return b;
+}
+
+void ensure_chunk(Handle &h, int ncol, int nz) {
+  size_t free_b = 0, total_b = 0;
+  {
+    const char *cc0 = std::getenv("CLIMA_RT_CHUNK_COLS");
+    const int want = std::min(ncol, cc0 ? std::max(1, atoi(cc0)) : 4096);
+    if (h.cap_nz == nz && h.cap_cols > 0 && (h.cap_cols >= want || h.cap_mem_limited)) return;
+  }
+  free_chunk(h);
+  CK(cudaMemGetInfo(&free_b, &total_b));
+  const int itemsz = rt_twostream_items_per_layer();
+  const char *bps = std::getenv("CLIMA_RT_TS_BLOCKS_PER_SM");
+  const int blocks_per_sm = bps ? std::max(1, atoi(bps)) : 4;
+  h.ts_blocks = h.num_sms * blocks_per_sm;
+  const size_t nres = (size_t)h.ts_blocks * rt_twostream_block_threads();
+  const size_t scratch_b = nres * nz * itemsz * 8;
+  const size_t pcb = per_col_bytes(h, nz);
+  const double budget = 0.7 * (double)free_b - (double)scratch_b;
+  if (budget < (double)pcb) throw CudaError{"not enough device memory for one column"};
+  long long cols = (long long)(budget / (double)pcb);
+  const char *cc = std::getenv("CLIMA_RT_CHUNK_COLS");
+  long long maxc = cc ? std::max(1, atoi(cc)) : 4096;
+  h.cap_mem_limited = cols < std::min<long long>(maxc, ncol);
+  cols = std::min<long long>(cols, maxc);
+  cols = std::min<long long>(cols, ncol);
+  const int C = (int)cols;
+  const DevTables &tb = h.tb;
+  const size_t L = nz + 1;
+  h.d_Tsurf = calloc_dev<double>(h, C);
+  h.d_T = calloc_dev<double>(h, (size_t)C * nz);
+  h.d_P = calloc_dev<double>(h, (size_t)C * nz);
+  h.d_dz = calloc_dev<double>(h, (size_t)C * nz);
+  h.d_dens = calloc_dev<double>(h, (size_t)C * nz * tb.ng);
+  h.d_pd = calloc_dev<double>(h, (size_t)C * nz * std::max(tb.np, 1));
+  h.d_rd = calloc_dev<double>(h, (size_t)C * nz * std::max(tb.np, 1));
+  DevChunk &ch = h.ch;
+  ch.slot_of_layer = calloc_dev<int>(h, (size_t)C * nz);
+  ch.layer_of_slot = calloc_dev<int>(h, (size_t)C * nz);
+  ch.nslots = calloc_dev<int>(h, C);
+  ch.ibr = calloc_dev<int>(h, (size_t)C * nz * rt_nbr(tb));
+  ch.qbr = calloc_dev<double>(h, (size_t)C * nz * rt_nbr(tb));
+  ch.foreign_col = calloc_dev<double>(h, (size_t)C * nz);
+  ch.tau = calloc_dev<double>(h, (size_t)C * tb.nw * nz * tb.G);
+  ch.w0 = calloc_dev<double>(h, (size_t)C * tb.nw * nz * tb.G);
+  ch.gt = calloc_dev<double>(h, (size_t)C * tb.nw * nz);
+  ch.tband = calloc_dev<double>(h, (size_t)C * tb.nw * nz);
+  ch.status = calloc_dev<int>(h, C);
+  DevFlux &fx = h.fx;
+  fx.fup_a_ir = calloc_dev<double>(h, (size_t)C * h.nw_ir * L);
+  fx.fdn_a_ir = calloc_dev<double>(h, (size_t)C * h.nw_ir * L);
+  fx.fup_a_sol = calloc_dev<double>(h, (size_t)C * h.nw_sol * L);
+  fx.fdn_a_sol = calloc_dev<double>(h, (size_t)C * h.nw_sol * L);
+  fx.amean_sol = calloc_dev<double>(h, (size_t)C * h.nw_sol * L);
+  fx.fup_n_ir = calloc_dev<double>(h, (size_t)C * L);
+  fx.fdn_n_ir = calloc_dev<double>(h, (size_t)C * L);
+  fx.fup_n_sol = calloc_dev<double>(h, (size_t)C * L);
+  fx.fdn_n_sol = calloc_dev<double>(h, (size_t)C * L);
+  fx.f_total = calloc_dev<double>(h, (size_t)C * L);
+  fx.ISR = calloc_dev<double>(h, C);
+  fx.OLR = calloc_dev<double>(h, C);
+  fx.bpl = calloc_dev<double>(h, (size_t)C * h.nw_ir * L);
+  fx.scratch = calloc_dev<double>(h, nres * nz * itemsz);
+  fx.scratch_threads = nres;
+  fx.status = ch.status;
+  CK(cudaMemset(fx.fup_n_sol, 0, (size_t)C * L * 8));
+  CK(cudaMemset(fx.fdn_n_sol, 0, (size_t)C * L * 8));
+  h.tmp_bytes = std::max((size_t)C * nz * std::max(h.nw_ir, h.nw_sol) * 8,
+                         ((size_t)nz * tb.G * tb.nw * 2 + (size_t)nz * tb.nw * 2) * 8);
+  h.d_tmp = (double *)calloc_dev<char>(h, h.tmp_bytes);
+  h.cap_cols = C;
+  h.cap_nz = nz;
+}
+
+// Frozen-opacity broadcast with more columns than the buffers hold: keep column 0's opacity,
+// slot map and stale solar fluxes across the reallocation.
+void grow_for_bcast(Handle &h, int ncol, int nz) {
+  const char *cc0 = std::getenv("CLIMA_RT_CHUNK_COLS");
+  const int want = std::min(ncol, cc0 ? std::max(1, atoi(cc0)) : 4096);
+  if (want <= h.cap_cols || h.cap_mem_limited) return;
+  const DevTables &tb = h.tb;
+  const int cap = h.ch.nslot_cap;
+  const size_t n1 = (size_t)tb.nw * cap * tb.G, n2 = (size_t)tb.nw * cap, L = nz + 1;
+  const int rs = h.retained_solar_ncol;
+  double *sv = nullptr;
+  int *svi = nullptr;
+  CK(cudaMalloc(&sv, (2 * n1 + 2 * n2 + 2 * L) * 8));
+  CK(cudaMalloc(&svi, (size_t)nz * sizeof(int)));
+  CK(cudaMemcpy(sv, h.ch.tau, n1 * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(sv + n1, h.ch.w0, n1 * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(sv + 2 * n1, h.ch.gt, n2 * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(sv + 2 * n1 + n2, h.ch.tband, n2 * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(sv + 2 * n1 + 2 * n2, h.fx.fup_n_sol, L * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(sv + 2 * n1 + 2 * n2 + L, h.fx.fdn_n_sol, L * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(svi, h.ch.slot_of_layer, (size_t)nz * sizeof(int), cudaMemcpyDeviceToDevice));
+  ensure_chunk(h, ncol, nz);
+  CK(cudaMemcpy(h.ch.tau, sv, n1 * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(h.ch.w0, sv + n1, n1 * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(h.ch.gt, sv + 2 * n1, n2 * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(h.ch.tband, sv + 2 * n1 + n2, n2 * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(h.fx.fup_n_sol, sv + 2 * n1 + 2 * n2, L * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(h.fx.fdn_n_sol, sv + 2 * n1 + 2 * n2 + L, L * 8, cudaMemcpyDeviceToDevice));
+  CK(cudaMemcpy(h.ch.slot_of_layer, svi, (size_t)nz * sizeof(int), cudaMemcpyDeviceToDevice));
+  cudaFree(sv);
+  cudaFree(svi);
+  h.ch.nslot_cap = cap;
+  h.retained_opacity_ncol = 1;
+  h.retained_nz = nz;
+  h.retained_solar_ncol = rs == 1 ? 1 : 0;
+}
+
+struct HostIn {
+  const double *T_surface, *T, *P, *dens, *dz, *pd, *rd;
+};
+
+void record(Handle &h, int i) { CK(cudaEventRecord(h.ev[i], h.st)); }
+
+// Runs one chunk whose inputs are already on the device (h.ch input pointers set).
+void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opacity,
+               bool opacity_bcast, bool solar_bcast) {
+  DevChunk &ch = h.ch;
+  ch.ncol = ncol;
+  ch.nz = nz;
+  record(h, 0);
+  if (compute_opacity) {
+    CK(cudaMemsetAsync(ch.status, 0, ncol * sizeof(int), h.st));
+    rt_launch_prep(h.tb, ch, h.st);
+    h.launches++;
+    // tight slot capacity: max number of unique layers over the chunk
+    std::vector<int> ns(ncol);
+    CK(cudaMemcpyAsync(ns.data(), ch.nslots, ncol * sizeof(int), cudaMemcpyDeviceToHost, h.st));
+    CK(cudaStreamSynchronize(h.st));
+    ch.nslot_cap = *std::max_element(ns.begin(), ns.end());
+    rt_launch_optics_rorr(h.tb, ch, h.st);
+    h.launches++;
+  }
+  record(h, 1);
+  rt_launch_planck(h.tb, ch, h.fx, h.st);
+  rt_launch_twostream_ir(h.tb, h.pr, ch, h.fx, opacity_bcast ? 1 : 0, h.ts_blocks, h.st);
+  h.launches += 2;
+  record(h, 2);
+  if (compute_solar) {
+    rt_launch_twostream_solar(h.tb, h.pr, ch, h.fx, opacity_bcast ? 1 : 0, h.ts_blocks, h.st);
+    int z = h.pr.nzen;
+    while (z > 0) { h.launches++; z -= (z >= 4 ? 4 : (z >= 2 ? 2 : 1)); }
+  }
+  record(h, 3);
+  rt_launch_integrate(h.tb, h.pr, ch, h.fx, compute_solar ? 1 : 0, solar_bcast ? 1 : 0, h.st);
+  h.launches++;
+  record(h, 4);
+  CK(cudaGetLastError());
+}
+
+void accumulate_stage_ms(Handle &h) {
+  CK(cudaEventSynchronize(h.ev[4]));
+  for (int i = 0; i < 4; i++) {
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, h.ev[i], h.ev[i + 1]));
+    h.stage_ms[i] += ms;
+  }
+  float ms = 0.f;
+  CK(cudaEventElapsedTime(&ms, h.ev[0], h.ev[4]));
+  h.stage_ms[4] += ms;
+}
+
+std::string check_inputs(const Handle &h, int ncol, int nz, int ng, int np, const double *pd,
+                         const double *rd) {
+  // check_inputs, clima_radtran.f90:417-491
+  if ((pd && !rd) || (rd && !pd)) return "Both pdensities and radii must be arguments.";
+  if (h.tb.np > 0 && !rd)
+    return "The model contains particles but \"pdensities\" and \"radii\" are not arguments.";
+  if (ng != h.tb.ng) return "\"densities\" has the wrong input dimension.";
+  if (rd && np != h.tb.np) return "\"pdensities\" has the wrong input dimension.";
+  if (nz < 1) return "\"nz\" can not be less than 1.";
+  if (ncol < 1) return "\"ncol\" can not be less than 1.";
+  return "";
+}
+
+// device==true: all pointers are device pointers.
+void radiate_batch_impl(Handle &h, bool device, int ncol, int nz, int ng, int np, const HostIn &in,
+                        bool compute_solar, bool compute_opacity, const clima_rt_out *out) {
+  CK(cudaSetDevice(h.device));
+  const std::string e = check_inputs(h, ncol, nz, ng, np, in.pd, in.rd);
+  if (!e.empty()) throw CudaError{e};
+  if (!out || !out->fup_n_ir || !out->fdn_n_ir || !out->fup_n_sol || !out->fdn_n_sol ||
+      !out->f_total || !out->ISR || !out->OLR)
+    throw CudaError{"mandatory output pointers are NULL"};
+  const bool had_retained = h.retained_opacity_ncol > 0 && h.retained_nz == nz && h.cap_nz == nz;
+  if (!compute_opacity && !had_retained)
+    throw CudaError{"compute_opacity=.false. but no opacity with this nz is retained in the handle"};
+  if (compute_opacity) ensure_chunk(h, ncol, nz);
+  bool opacity_bcast = false, solar_bcast = false;
+  if (!compute_opacity) {
+    if (h.retained_opacity_ncol == 1) {
+      opacity_bcast = true;  // frozen-opacity Jacobian mode: every column uses column 0's opacity
+      grow_for_bcast(h, ncol, nz);
+    } else if (h.retained_opacity_ncol != ncol) {
+      throw CudaError{"compute_opacity=.false. needs the retained opacity of 1 column (broadcast) or of the same single-chunk batch"};
+    }
+  }
+  const int C = h.cap_cols;
+  if (!compute_solar) {
+    if (h.retained_solar_ncol == 1) solar_bcast = true;
+    else if (h.retained_solar_ncol != 0 && (h.retained_solar_ncol != ncol || ncol > C))
+      throw CudaError{"compute_solar=.false. needs the retained solar fluxes of 1 column (broadcast) or of the same single-chunk batch"};
+  }
+  const DevTables &tb = h.tb;
+  const size_t L = nz + 1;
+  const cudaMemcpyKind kin = device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+  const cudaMemcpyKind kout = device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+  for (int i = 0; i < 5; i++) h.stage_ms[i] = 0.0;
+  for (int c0 = 0; c0 < ncol; c0 += C) {
+    const int n = std::min(C, ncol - c0);
+    DevChunk &ch = h.ch;
+    if (device) {
+      ch.T_surface = in.T_surface + c0;
+      ch.T = in.T + (size_t)c0 * nz;
+      ch.P = in.P + (size_t)c0 * nz;
+      ch.dz = in.dz + (size_t)c0 * nz;
+      ch.dens = in.dens + (size_t)c0 * nz * ng;
+      ch.pdens = in.pd ? in.pd + (size_t)c0 * nz * np : nullptr;
+      ch.radii = in.rd ? in.rd + (size_t)c0 * nz * np : nullptr;
+    } else {
+      CK(cudaMemcpyAsync(h.d_Tsurf, in.T_surface + c0, n * 8, kin, h.st));
+      CK(cudaMemcpyAsync(h.d_T, in.T + (size_t)c0 * nz, (size_t)n * nz * 8, kin, h.st));
+      if (compute_opacity) {
+        CK(cudaMemcpyAsync(h.d_P, in.P + (size_t)c0 * nz, (size_t)n * nz * 8, kin, h.st));
+        CK(cudaMemcpyAsync(h.d_dz, in.dz + (size_t)c0 * nz, (size_t)n * nz * 8, kin, h.st));
+        CK(cudaMemcpyAsync(h.d_dens, in.dens + (size_t)c0 * nz * ng, (size_t)n * nz * ng * 8, kin, h.st));
+        if (in.pd) {
+          CK(cudaMemcpyAsync(h.d_pd, in.pd + (size_t)c0 * nz * np, (size_t)n * nz * np * 8, kin, h.st));
+          CK(cudaMemcpyAsync(h.d_rd, in.rd + (size_t)c0 * nz * np, (size_t)n * nz * np * 8, kin, h.st));
+        }
+      }
+      ch.T_surface = h.d_Tsurf; ch.T = h.d_T; ch.P = h.d_P; ch.dz = h.d_dz; ch.dens = h.d_dens;
+      ch.pdens = in.pd ? h.d_pd : nullptr;
+      ch.radii = in.rd ? h.d_rd : nullptr;
+    }
+    run_chunk(h, n, nz, compute_solar, compute_opacity, opacity_bcast, solar_bcast);
+    const DevFlux &fx = h.fx;
+    auto cp = [&](double *dst, const double *src, size_t per_col) {
+      if (dst) CK(cudaMemcpyAsync(dst + (size_t)c0 * per_col, src, (size_t)n * per_col * 8, kout, h.st));
+    };
+    cp(out->fup_n_ir, fx.fup_n_ir, L);
+    cp(out->fdn_n_ir, fx.fdn_n_ir, L);
+    cp(out->fup_n_sol, fx.fup_n_sol, L);
+    cp(out->fdn_n_sol, fx.fdn_n_sol, L);
+    cp(out->f_total, fx.f_total, L);
+    cp(out->ISR, fx.ISR, 1);
+    cp(out->OLR, fx.OLR, 1);
+    cp(out->fup_a_ir, fx.fup_a_ir, L * h.nw_ir);
+    cp(out->fdn_a_ir, fx.fdn_a_ir, L * h.nw_ir);
+    cp(out->fup_a_sol, fx.fup_a_sol, L * h.nw_sol);
+    cp(out->fdn_a_sol, fx.fdn_a_sol, L * h.nw_sol);
+    cp(out->amean_sol, fx.amean_sol, L * h.nw_sol);
+    if (out->tau_band_ir && !opacity_bcast) {
+      rt_launch_tau_band(tb, ch, 1, h.d_tmp, h.st);
+      h.launches++;
+      cp(out->tau_band_ir, h.d_tmp, (size_t)nz * h.nw_ir);
+    }
+    if (out->tau_band_sol && !opacity_bcast) {
+      rt_launch_tau_band(tb, ch, 0, h.d_tmp, h.st);
+      h.launches++;
+      cp(out->tau_band_sol, h.d_tmp, (size_t)nz * h.nw_sol);
+    }
+    if (out->status)
+      CK(cudaMemcpyAsync(out->status + c0, ch.status, n * sizeof(int), kout, h.st));
+    CK(cudaStreamSynchronize(h.st));
+    accumulate_stage_ms(h);
+    if (compute_opacity) {
+      h.retained_opacity_ncol = (ncol <= C) ? ncol : 0;
+      h.retained_nz = nz;
+    }
+    if (compute_solar) h.retained_solar_ncol = (ncol <= C) ? ncol : 0;
+  }
+  // particle radius outside the table: the reference fails the whole call
+  // (clima_radtran_types.f90:773-776)
+  if (compute_opacity && tb.npart > 0) {
+    std::vector<int> stv(std::min(ncol, C));
+    CK(cudaMemcpy(stv.data(), h.ch.status, stv.size() * sizeof(int), cudaMemcpyDeviceToHost));
+    for (int s : stv)
+      if (s & CLIMA_RT_STATUS_RADIUS_CLAMPED)
+        throw CudaError{"Opacity computation failed in one or more wavelength bins."};
+  }
+}
+
+}  // namespace
+
+// =============================================================================================
+extern "C" {
+
+void clima_rt_create(const clima_rt_tables *tables, const clima_rt_params *params,
+                     const int32_t *device, void **handle, char *err) {
+  set_err(err, "");
+  if (handle) *handle = nullptr;
+  Handle *h = nullptr;
+  try {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
+      throw CudaError{"clima_rt: no usable CUDA device (there is no CPU fallback)"};
+    const int dev = device ? *device : 0;
+    if (dev < 0 || dev >= ndev) throw CudaError{"clima_rt: device index out of range"};
+    CK(cudaSetDevice(dev));
+    h = new Handle;
+    h->device = dev;
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, dev));
+    h->num_sms = prop.multiProcessorCount;
+    CK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
+    for (auto &e : h->ev) CK(cudaEventCreate(&e));
+    build_tables(*h, tables);
+    upload_params(*h, params);
+    *handle = h;
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+    if (h) clima_rt_destroy(h);
+  }
+}
+
+void clima_rt_destroy(void *handle) {
+  if (!handle) return;
+  Handle *h = static_cast<Handle *>(handle);
+  cudaSetDevice(h->device);
+  free_chunk(*h);
+  for (void *p : h->table_allocs) cudaFree(p);
+  for (auto &p : h->d_custom) if (p) cudaFree(p);
+  for (auto &e : h->ev) if (e) cudaEventDestroy(e);
+  if (h->st) cudaStreamDestroy(h->st);
+  delete h;
+}
+
+void clima_rt_set_params(void *handle, const clima_rt_params *params, char *err) {
+  set_err(err, "");
+  try {
+    Handle &h = *static_cast<Handle *>(handle);
+    CK(cudaSetDevice(h.device));
+    upload_params(h, params);
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_set_custom_optical_properties(void *handle, const int32_t *nP, const double *log10P,
+                                            const double *dtau_dz, const double *w0,
+                                            const double *g0, char *err) {
+  set_err(err, "");
+  try {
+    Handle &h = *static_cast<Handle *>(handle);
+    CK(cudaSetDevice(h.device));
+    if (*nP < 2) throw CudaError{"custom optical properties need at least 2 pressure points"};
+    for (auto &p : h.d_custom) { if (p) cudaFree(p); p = nullptr; }
+    const size_t n = (size_t)(*nP) * h.tb.nw;
+    h.d_custom[0] = upload(h, log10P, *nP, false);
+    h.d_custom[1] = upload(h, dtau_dz, n, false);
+    h.d_custom[2] = upload(h, w0, n, false);
+    h.d_custom[3] = upload(h, g0, n, false);
+    h.tb.has_custom = 1;
+    h.tb.custom_nP = *nP;
+    h.tb.c_log10P = h.d_custom[0]; h.tb.c_dtau = h.d_custom[1];
+    h.tb.c_w0 = h.d_custom[2]; h.tb.c_g0 = h.d_custom[3];
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_unset_custom_optical_properties(void *handle) {
+  Handle &h = *static_cast<Handle *>(handle);
+  h.tb.has_custom = 0;
+}
+
+void clima_rt_radiate_batch(void *handle, const int32_t *ncol, const int32_t *nz, const int32_t *ng,
+                            const int32_t *np, const double *T_surface, const double *T,
+                            const double *P, const double *densities, const double *dz,
+                            const double *pdensities, const double *radii,
+                            const int32_t *compute_solar, const int32_t *compute_opacity,
+                            const clima_rt_out *out, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle) throw CudaError{"clima_rt: NULL handle"};
+    HostIn in{T_surface, T, P, densities, dz, pdensities, radii};
+    radiate_batch_impl(*static_cast<Handle *>(handle), false, *ncol, *nz, *ng, *np, in,
+                       *compute_solar != 0, *compute_opacity != 0, out);
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_radiate_batch_device(void *handle, const int32_t *ncol, const int32_t *nz,
+                                   const int32_t *ng, const int32_t *np, const double *T_surface,
+                                   const double *T, const double *P, const double *densities,
+                                   const double *dz, const double *pdensities, const double *radii,
+                                   const int32_t *compute_solar, const int32_t *compute_opacity,
+                                   const clima_rt_out *out, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle) throw CudaError{"clima_rt: NULL handle"};
+    HostIn in{T_surface, T, P, densities, dz, pdensities, radii};
+    radiate_batch_impl(*static_cast<Handle *>(handle), true, *ncol, *nz, *ng, *np, in,
+                       *compute_solar != 0, *compute_opacity != 0, out);
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_get_opacity(void *handle, const int32_t *icol, double *tau, double *w0, double *g,
+                          double *tau_band, char *err) {
+  set_err(err, "");
+  try {
+    Handle &h = *static_cast<Handle *>(handle);
+    CK(cudaSetDevice(h.device));
+    if (h.retained_opacity_ncol < 1 || *icol < 0 || *icol >= h.retained_opacity_ncol)
+      throw CudaError{"clima_rt_get_opacity: column not retained"};
+    const int nz = h.retained_nz;
+    const size_t n1 = (size_t)nz * h.tb.G * h.tb.nw, n2 = (size_t)nz * h.tb.nw;
+    double *d = h.d_tmp;
+    h.ch.nz = nz;
+    rt_launch_expand_opacity(h.tb, h.ch, *icol, d, d + n1, d + 2 * n1, d + 2 * n1 + n2, h.st);
+    h.launches++;
+    CK(cudaMemcpyAsync(tau, d, n1 * 8, cudaMemcpyDeviceToHost, h.st));
+    CK(cudaMemcpyAsync(w0, d + n1, n1 * 8, cudaMemcpyDeviceToHost, h.st));
+    CK(cudaMemcpyAsync(g, d + 2 * n1, n2 * 8, cudaMemcpyDeviceToHost, h.st));
+    CK(cudaMemcpyAsync(tau_band, d + 2 * n1 + n2, n2 * 8, cudaMemcpyDeviceToHost, h.st));
+    CK(cudaStreamSynchronize(h.st));
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_get_launch_count(void *handle, int64_t *count) {
+  *count = static_cast<Handle *>(handle)->launches;
+}
+
+void clima_rt_get_stage_ms(void *handle, double *ms5) {
+  Handle &h = *static_cast<Handle *>(handle);
+  for (int i = 0; i < 5; i++) ms5[i] = h.stage_ms[i];
+}
+
+void clima_rt_measure_fp64_peak(const int32_t *device, double *tflops, char *err) {
+  set_err(err, "");
+  try {
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1)
+      throw CudaError{"clima_rt: no usable CUDA device"};
+    CK(cudaSetDevice(*device));
+    *tflops = rt_measure_fp64_tflops(*device, nullptr);
+    if (*tflops <= 0.0) throw CudaError{"clima_rt: FP64 peak measurement failed"};
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_version_get(char *version_c) {
+  const char *v = "clima_rt_b200 0.1.0";
+  std::strncpy(version_c, v, 100);
+  version_c[100] = 0;
+}
+
+}  // extern "C"

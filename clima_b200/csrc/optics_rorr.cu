@@ -1,0 +1,419 @@
+// optics_rorr.cu -- optical-property assembly + random overlap with resorting and rebinning.
+//
+// Replaces the body of the per-bin loop of OpticalProperties_compute_opacity
+// (src/radtran/clima_radtran_types.f90:638-771) and k_rorr (:780-888) for a batch of columns.
+//
+// Work unit = (column, wavelength bin l, unique layer slot).  A unit is owned by LPU = P*P/32
+// lanes of one warp (P = ngauss rounded up to a power of two: 8 lanes at ngauss=16, 4 units per
+// warp).  Per unit:
+//   1. continua (Rayleigh, CIA, photolysis xs, H2O continuum, custom, particles)  -- A.3
+//   2. for each k-gas: bilinear log10k(P,T) interpolation, lane per g-point       -- A.2
+//   3. RORR merge of the running mixture a(1..G) with the new gas b(1..G):
+//        keys(i,j) = a_i + b_j.  The G x G keys live in REGISTERS, 32 per lane, as FP64 bit
+//        patterns whose low 2*log2(P) mantissa bits are replaced by the element index (i,j):
+//        one 64-bit compare then orders (value, index) lexicographically, i.e. a STABLE rank like
+//        mrgrnk (futils), needs no payload, and perturbs only the ORDER of keys closer than
+//        2^-44 relative -- the exact tau is re-formed from (i,j) after the sort.
+//        Rows are already ascending because k-distributions ascend in g (checked at table load,
+//        `rows_sorted`), so the bitonic network starts at merge stage log2(P)+1: 26 of the 36
+//        compare-exchange steps at P=16, 20 of them in-register, 6 through warp shuffles.
+//   4. weights_to_bins + rebin (clima_eqns.f90:43-54, futils rebin): per-lane running edge over
+//        its 32 sorted elements, monotone output-bin pointer, deterministic per-lane partials in
+//        shared memory (no atomics: bit-reproducible run to run).
+//   5. total tau, w0 clamp, band tau (:856-886).
+#include "rt_device.cuh"
+#include "rt_kernels.h"
+
+namespace {
+
+template <int P>
+struct Cfg {
+  static constexpr int LOGP = (P == 8 ? 3 : (P == 16 ? 4 : 5));
+  static constexpr int N = P * P;
+  static constexpr int KPL = 32;       // keys per lane
+  static constexpr int LPU = N / KPL;  // lanes per unit: 2, 8, 32
+  static constexpr int GPL = P / LPU;  // g-points per lane in the interpolation: 4, 2, 1
+  static constexpr int UPB = 128 / LPU;  // units per 128-thread block
+  static constexpr unsigned long long IDXMASK = (unsigned long long)(N - 1);
+};
+
+__device__ __forceinline__ double shfl_xor_d(double v, int lanemask) {
+  return __shfl_xor_sync(0xffffffffu, v, lanemask);
+}
+
+// compare-exchange, ascending (keys are distinct by construction)
+__device__ __forceinline__ void ce(double &a, double &b) {
+  const bool p = a < b;
+  const double lo = p ? a : b;
+  const double hi = p ? b : a;
+  a = lo;
+  b = hi;
+}
+
+// Bitonic sort network over positions pos = ul*32 + r, all runs ascending ("flip" variant: the first
+// step of stage k pairs pos with pos ^ (2^k-1), the remaining steps pos with pos ^ d).  Stages
+// below `kfirst` are skipped (rows pre-sorted).
+template <int P>
+__device__ __forceinline__ void bitonic_network(double (&x)[32], const int ul, const int kfirst) {
+  using C = Cfg<P>;
+#pragma unroll
+  for (int k = 1; k <= 2 * C::LOGP; k++) {
+    if (k < kfirst) continue;
+    // ---- flip step
+    if (k <= 5) {
+      const int m = (1 << k) - 1;
+#pragma unroll
+      for (int r = 0; r < 32; r++)
+        if ((r & (1 << (k - 1))) == 0) ce(x[r], x[r ^ m]);
+    } else {
+      const int lm = ((1 << k) - 1) >> 5;
+      const bool keepmin = (ul & ((lm + 1) >> 1)) == 0;
+#pragma unroll
+      for (int r = 0; r < 16; r++) {
+        const double y1 = shfl_xor_d(x[r ^ 31], lm);
+        const double y2 = shfl_xor_d(x[r], lm);
+        x[r] = ((x[r] < y1) == keepmin) ? x[r] : y1;
+        x[r ^ 31] = ((x[r ^ 31] < y2) == keepmin) ? x[r ^ 31] : y2;
+      }
+    }
+    // ---- half-cleaner steps
+#pragma unroll
+    for (int s = k - 2; s >= 0; s--) {
+      const int d = 1 << s;
+      if (d < 32) {
+#pragma unroll
+        for (int r = 0; r < 32; r++)
+          if ((r & d) == 0) ce(x[r], x[r | d]);
+      } else {
+        const int lm = d >> 5;
+        const bool keepmin = (ul & lm) == 0;
+#pragma unroll
+        for (int r = 0; r < 32; r++) {
+          const double y = shfl_xor_d(x[r], lm);
+          x[r] = ((x[r] < y) == keepmin) ? x[r] : y;
+        }
+      }
+    }
+  }
+}
+
+template <int P>
+__global__ void __launch_bounds__(128)
+optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevChunk ch) {
+  using C = Cfg<P>;
+  constexpr int LPU = C::LPU, UPB = C::UPB, LOGP = C::LOGP;
+  constexpr int AST = P + 1;              // padded strides: units of one warp hit distinct banks
+  constexpr int PST = P * LPU + 1;
+  __shared__ double s_w[P];               // wbin, zero padded
+  __shared__ double s_E[P + 1];           // wbin_e
+  __shared__ double s_ib[P];              // 1/(wbin_e(g+1)-wbin_e(g))
+  __shared__ double s_a[UPB * AST];       // running mixture tau_k(g)
+  __shared__ double s_b[UPB * AST];       // new gas k*col (g)
+  __shared__ double s_part[UPB * PST];    // rebin partials [g][lane]
+
+  const int G = tb.G, nw = tb.nw, nz = ch.nz, ng = tb.ng;
+  for (int i = threadIdx.x; i < P; i += blockDim.x) {
+    s_w[i] = i < G ? tb.wbin[i] : 0.0;
+    s_ib[i] = i < G ? tb.inv_dw[i] : 0.0;
+  }
+  for (int i = threadIdx.x; i < P + 1; i += blockDim.x) s_E[i] = tb.wbin_e[i < G ? i : G];
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31;
+  const int ul = lane & (LPU - 1);     // lane within unit
+  const int ub = threadIdx.x / LPU;    // unit within block
+  const long long uid = (long long)blockIdx.x * UPB + ub;
+  const int cap = ch.nslot_cap;
+  int slot = (int)(uid % cap);
+  int l = (int)((uid / cap) % nw);
+  long long cl = uid / ((long long)cap * nw);
+  bool active = cl < ch.ncol;
+  int c = active ? (int)cl : ch.ncol - 1;
+  const int nsl = ch.nslots[c];
+  if (slot >= nsl) {
+    active = false;
+    slot = nsl - 1;
+  }
+  if (__all_sync(0xffffffffu, !active)) return;
+
+  double *sa = s_a + ub * AST, *sb = s_b + ub * AST, *sp = s_part + ub * PST;
+  const int k = ch.layer_of_slot[(size_t)c * nz + slot];  // ground-first layer index
+  const double *dens = ch.dens + (size_t)c * nz * ng + k;  // dens[i*nz]
+  const double dzk = ch.dz[(size_t)c * nz + k];
+  const int nbr = rt_nbr(tb);
+  const int *ib = ch.ibr + ((size_t)c * nz + slot) * nbr;
+  const double *qb = ch.qbr + ((size_t)c * nz + slot) * nbr;
+  int rbase = 2 * tb.nk;
+
+  // ------------------------------------------------------------------ 1. continua (A.3)
+  // Rayleigh (:686-693)
+  double tausg = 0.0;
+  for (int i = 0; i < tb.nray; i++) {
+    const double col = dens[(size_t)(tb.ray_sp[i] - 1) * nz] * dzk;
+    tausg = tausg + tb.ray_xs[l + (size_t)i * nw] * col;
+  }
+  // CIA (:696-704), photolysis (:707-713)
+  double taua = 0.0;
+  for (int i = 0; i < tb.ncia + tb.npxs; i++) {
+    const bool is_cia = i < tb.ncia;
+    const DevXS &x = is_cia ? tb.cia[i] : tb.pxs[i - tb.ncia];
+    double xs;
+    if (x.dim == 0) {
+      xs = x.data[l];
+    } else {
+      const int it = ib[rbase + i];
+      const double q1 = qb[rbase + i], p1 = 1.0 - q1;
+      const double *f = x.data + (size_t)l * x.nt;
+      xs = rt_ten2power(p1 * f[it] + q1 * f[it + 1]);
+    }
+    if (is_cia)
+      taua = taua + xs * dens[(size_t)(x.sp1 - 1) * nz] * dens[(size_t)(x.sp2 - 1) * nz] * dzk;
+    else
+      taua = taua + xs * (dens[(size_t)(x.sp1 - 1) * nz] * dzk);
+  }
+  rbase += tb.ncia + tb.npxs;
+  // water continuum (:716-723)
+  if (tb.has_cont) {
+    const int it = ib[rbase];
+    const double q1 = qb[rbase], p1 = 1.0 - q1;
+    const double *fh = tb.cont_H2O + (size_t)l * tb.cont_nt;
+    const double *ff = tb.cont_foreign + (size_t)l * tb.cont_nt;
+    const double H2O = rt_ten2power(p1 * fh[it] + q1 * fh[it + 1]);
+    const double foreign = rt_ten2power(p1 * ff[it] + q1 * ff[it + 1]);
+    const double dw = dens[(size_t)(tb.cont_LH2O - 1) * nz];
+    taua = taua + H2O * dw * (dw * dzk) + foreign * dw * ch.foreign_col[(size_t)c * nz + slot];
+  }
+  rbase += 1;
+  // particles (:733-744)
+  double tausp = 0.0, taup = 0.0;
+  double tausp_1[RT_MAXPART], gtp[RT_MAXPART];
+  if (tb.npart > 0) {
+    const double *rad = ch.radii + (size_t)c * nz * tb.np + k;
+    const double *pdn = ch.pdens + (size_t)c * nz * tb.np + k;
+    for (int i = 0; i < tb.npart; i++) {
+      const DevPart &p = tb.part[i];
+      const int ir = ib[rbase + i];
+      const double q1 = qb[rbase + i], p1 = 1.0 - q1;
+      const size_t o = (size_t)l * p.nr + ir;
+      const double w0p = p1 * p.w0[o] + q1 * p.w0[o + 1];
+      const double qext = p1 * p.qext[o] + q1 * p.qext[o + 1];
+      gtp[i] = p1 * p.gt[o] + q1 * p.gt[o + 1];
+      const double r = rad[(size_t)(p.p_ind - 1) * nz];
+      const double taup_1 = qext * RT_PI * (r * r) * pdn[(size_t)(p.p_ind - 1) * nz] * dzk;
+      taup = taup + taup_1;
+      tausp_1[i] = w0p * taup_1;
+      tausp = tausp + tausp_1[i];
+    }
+  }
+  rbase += tb.npart;
+  // custom optical properties (:726-730, 546-572)
+  double tauc = RT_TINY, w0c = RT_TINY, g0c = RT_TINY;
+  if (tb.has_custom) {
+    const int ip = ib[rbase];
+    const double q1 = qb[rbase], p1 = 1.0 - q1;
+    const size_t o = (size_t)l * tb.custom_nP + ip;
+    tauc = (p1 * tb.c_dtau[o] + q1 * tb.c_dtau[o + 1]) * dzk;
+    w0c = p1 * tb.c_w0[o] + q1 * tb.c_w0[o + 1];
+    g0c = p1 * tb.c_g0[o] + q1 * tb.c_g0[o + 1];
+  }
+  const double tausc = w0c * tauc;
+  // asymmetry (:746-757)
+  double gt = 0.0;
+  {
+    const double den = fmax(RT_TAU_MIN, (tausp + tausg + tausc));
+    for (int i = 0; i < tb.npart; i++) gt = gt + gtp[i] * tausp_1[i] / den;
+    gt = gt + g0c * tausc / den;
+    gt = fmin(gt, RT_MAX_GT);
+  }
+
+  // ------------------------------------------------------------------ 2+3+4. k-gases and RORR
+  const int kfirst = tb.rows_sorted ? LOGP + 1 : 1;
+  for (int jj = 0; jj < tb.nk; jj++) {
+    const DevK &kt = tb.k[jj];
+    const int ix = ib[2 * jj], iy = ib[2 * jj + 1];
+    const double q1 = qb[2 * jj], q2 = qb[2 * jj + 1];
+    const double p1 = 1.0 - q1, p2 = 1.0 - q2;
+    const double col = dens[(size_t)(kt.sp - 1) * nz] * dzk;  // cols(j,sp) :607
+    const double *f = kt.log10k + (size_t)G * (ix + (size_t)kt.np * (iy + (size_t)kt.nt * l));
+    const size_t sy = (size_t)G * kt.np;
+    double *dst = jj == 0 ? sa : sb;
+#pragma unroll
+    for (int t = 0; t < C::GPL; t++) {
+      const int g = ul + LPU * t;
+      if (g < G) {
+        // interp_2d, linear_interpolation_module.F90:322-335
+        const double fx1 = p1 * f[g] + q1 * f[g + G];
+        const double fx2 = p1 * f[g + sy] + q1 * f[g + sy + G];
+        const double v = p2 * fx1 + q2 * fx2;
+        dst[g] = rt_ten2power(v) * col;  // :660, :816-819 / :828
+      } else {
+        dst[g] = 0.0;
+      }
+    }
+    __syncwarp();
+    if (jj == 0) continue;
+
+    // ---- keys: pos = ul*32 + r ;  i = pos >> LOGP (running mixture), j = pos & (P-1) (new gas)
+    double x[32];
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+      const int pos = ul * 32 + r;
+      const int i = pos >> LOGP, j = pos & (P - 1);
+      const bool valid = (i < G) && (j < G);
+      const double v = sa[i] + sb[j];  // :828 tau_xy
+      const unsigned long long bits =
+          valid ? (unsigned long long)__double_as_longlong(v) : 0x7fe0000000000000ull;  // huge, finite
+      x[r] = __longlong_as_double((long long)((bits & ~C::IDXMASK) | (unsigned long long)pos));
+    }
+    bitonic_network<P>(x, ul, kfirst);
+
+    // ---- weights_to_bins + rebin (:843-849)
+    // lane total weight
+    double tot = 0.0;
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+      const unsigned idx = (unsigned)((unsigned long long)__double_as_longlong(x[r]) & C::IDXMASK);
+      tot += s_w[idx >> LOGP] * s_w[idx & (P - 1)];
+    }
+    double off = tot;  // inclusive scan over the unit's lanes -> exclusive
+#pragma unroll
+    for (int d = 1; d < LPU; d <<= 1) {
+      const double t = __shfl_up_sync(0xffffffffu, off, d, LPU);
+      if (ul >= d) off += t;
+    }
+    off -= tot;
+    for (int g = 0; g < G; g++) sp[g * LPU + ul] = 0.0;
+    int g = 0;
+#pragma unroll
+    for (int s = P / 2; s > 0; s >>= 1)
+      if (g + s <= G - 1 && s_E[g + s] <= off) g += s;
+    double n0 = s_E[g], n1 = s_E[g + 1], ibw = s_ib[g];
+    double acc = 0.0, o0 = off;
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+      const unsigned idx = (unsigned)((unsigned long long)__double_as_longlong(x[r]) & C::IDXMASK);
+      const int i = idx >> LOGP, j = idx & (P - 1);
+      const double w = s_w[i] * s_w[j];  // wxy, clima_radtran_types_create.f90:216-222
+      if (w > 0.0) {
+        const double tv = sa[i] + sb[j];  // exact tau_xy of the sorted element
+        const double o1 = o0 + w;
+        double lo = o0;
+        while (o1 > n1 && g < G - 1) {  // old bin crosses the right edge of new bin g
+          acc += (lo <= n0) ? tv : ((n1 - lo) * ibw) * tv;
+          sp[g * LPU + ul] = acc;
+          acc = 0.0;
+          g++;
+          n0 = n1;
+          lo = n1;
+          n1 = s_E[g + 1];
+          ibw = s_ib[g];
+        }
+        const double hi = fmin(o1, n1);
+        if (hi > lo) acc += (lo <= n0 && hi >= n1) ? tv : ((hi - lo) * ibw) * tv;
+        o0 = o1;
+      }
+    }
+    sp[g * LPU + ul] = acc;
+    __syncwarp();
+#pragma unroll
+    for (int t = 0; t < C::GPL; t++) {
+      const int gg = ul + LPU * t;
+      double s = 0.0;
+      if (gg < G) {
+#pragma unroll
+        for (int q = 0; q < LPU; q++) s += sp[gg * LPU + q];
+      }
+      sa[gg] = s;
+    }
+    __syncwarp();
+  }
+
+  // ------------------------------------------------------------------ 5. totals (:856-886)
+  const size_t obase = (((size_t)c * nw + l) * cap + slot);
+#pragma unroll
+  for (int t = 0; t < C::GPL; t++) {
+    const int gg = ul + LPU * t;
+    if (gg < G) {
+      const double tau = tausg + taua + taup + sa[gg] + tauc;
+      double w0 = 0.0;
+      if (!(tau <= RT_TAU_MIN)) w0 = fmin(RT_MAX_W0, (tausg + tausp + tausc) / tau);
+      sb[gg] = tau;
+      if (active) {
+        ch.tau[obase * G + gg] = tau;
+        ch.w0[obase * G + gg] = w0;
+      }
+    }
+  }
+  __syncwarp();
+  if (ul == 0 && active) {
+    double tbnd = 0.0;
+    for (int gg = 0; gg < G; gg++) tbnd = tbnd + sb[gg] * s_w[gg];
+    ch.tband[obase] = tbnd;
+    ch.gt[obase] = gt;
+  }
+}
+
+// Expand the slot-indexed opacity of one column into the reference's OpticalPropertiesResult layout
+// tau(nz,G,nw), w0(nz,G,nw), g(nz,nw), tau_band(nz,nw), top-first (clima_radtran_types.f90:242-247).
+__global__ void expand_opacity_kernel(const DevTables tb, const DevChunk ch, int c, double *tau,
+                                      double *w0, double *g, double *tband) {
+  const int nz = ch.nz, G = tb.G, nw = tb.nw, cap = ch.nslot_cap;
+  const size_t total = (size_t)nz * G * nw;
+  for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const int n = (int)(t % nz);
+    const int gg = (int)((t / nz) % G);
+    const int l = (int)(t / ((size_t)nz * G));
+    const int k = nz - 1 - n;
+    const int slot = ch.slot_of_layer[(size_t)c * nz + k];
+    const size_t o = (((size_t)c * nw + l) * cap + slot);
+    tau[t] = ch.tau[o * G + gg];
+    w0[t] = ch.w0[o * G + gg];
+    if (gg == 0) {
+      g[n + (size_t)l * nz] = ch.gt[o];
+      tband[n + (size_t)l * nz] = ch.tband[o];
+    }
+  }
+}
+
+// tau_band of one channel, ground-first (nz,nw_ch,ncol) (clima_radtran_radiate.f90:151-154)
+__global__ void tau_band_kernel(const DevTables tb, const DevChunk ch, int ind_start, int nwch,
+                                double *out) {
+  const int nz = ch.nz, nw = tb.nw, cap = ch.nslot_cap;
+  const size_t total = (size_t)nz * nwch * ch.ncol;
+  for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const int i = (int)(t % nz);
+    const int ll = (int)((t / nz) % nwch);
+    const int c = (int)(t / ((size_t)nz * nwch));
+    const int slot = ch.slot_of_layer[(size_t)c * nz + i];
+    out[t] = ch.tband[((size_t)c * nw + (ind_start + ll)) * cap + slot];
+  }
+}
+
+}  // namespace
+
+void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, cudaStream_t st) {
+  const long long units = (long long)ch.ncol * tb.nw * ch.nslot_cap;
+  if (tb.G <= 8) {
+    const long long nb = (units + Cfg<8>::UPB - 1) / Cfg<8>::UPB;
+    optics_rorr_kernel<8><<<(unsigned)nb, 128, 0, st>>>(tb, ch);
+  } else if (tb.G <= 16) {
+    const long long nb = (units + Cfg<16>::UPB - 1) / Cfg<16>::UPB;
+    optics_rorr_kernel<16><<<(unsigned)nb, 128, 0, st>>>(tb, ch);
+  } else {
+    const long long nb = (units + Cfg<32>::UPB - 1) / Cfg<32>::UPB;
+    optics_rorr_kernel<32><<<(unsigned)nb, 128, 0, st>>>(tb, ch);
+  }
+}
+
+void rt_launch_expand_opacity(const DevTables &tb, const DevChunk &ch, int icol, double *tau,
+                              double *w0, double *g, double *tband, cudaStream_t st) {
+  expand_opacity_kernel<<<592, 256, 0, st>>>(tb, ch, icol, tau, w0, g, tband);
+}
+
+void rt_launch_tau_band(const DevTables &tb, const DevChunk &ch, int is_ir, double *out,
+                        cudaStream_t st) {
+  const int s = is_ir ? tb.ir_start : tb.sol_start, e = is_ir ? tb.ir_end : tb.sol_end;
+  tau_band_kernel<<<592, 256, 0, st>>>(tb, ch, s, e - s + 1, out);
+}

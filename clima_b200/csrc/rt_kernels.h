@@ -1,0 +1,40 @@
+// rt_kernels.h -- host-callable launchers of the RT kernels (internal; the public surface is
+// include/clima_rt.h).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "rt_device.cuh"
+
+// Outputs of the two-stream + integration stages for one chunk.
+struct DevFlux {
+  // spectral, ground-first, [col][ll][level]
+  double *fup_a_ir, *fdn_a_ir, *fup_a_sol, *fdn_a_sol, *amean_sol;
+  // integrated [col][level]
+  double *fup_n_ir, *fdn_n_ir, *fup_n_sol, *fdn_n_sol, *f_total;
+  double *ISR, *OLR;       // [col]
+  double *bpl;             // [col][ll_ir][nz+1] Planck, top-first
+  double *scratch;         // two-stream forward-sweep storage, [layer][item][resident thread]
+  size_t scratch_threads;  // resident threads the scratch was sized for
+  int *status;
+};
+
+// prep.cu
+void rt_launch_prep(const DevTables &tb, const DevChunk &ch, cudaStream_t st);
+// optics_rorr.cu
+void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, cudaStream_t st);
+// twostream.cu.  `ocol_bcast`: every column reads the opacity of column 0 (frozen-opacity mode).
+void rt_launch_planck(const DevTables &tb, const DevChunk &ch, const DevFlux &fx, cudaStream_t st);
+void rt_launch_twostream_ir(const DevTables &tb, const DevParams &pr, const DevChunk &ch,
+                            const DevFlux &fx, int ocol_bcast, int nblocks, cudaStream_t st);
+void rt_launch_twostream_solar(const DevTables &tb, const DevParams &pr, const DevChunk &ch,
+                               const DevFlux &fx, int ocol_bcast, int nblocks, cudaStream_t st);
+void rt_launch_integrate(const DevTables &tb, const DevParams &pr, const DevChunk &ch,
+                         const DevFlux &fx, int compute_solar, int sol_bcast, cudaStream_t st);
+void rt_launch_tau_band(const DevTables &tb, const DevChunk &ch, int is_ir, double *out,
+                        cudaStream_t st);
+void rt_launch_expand_opacity(const DevTables &tb, const DevChunk &ch, int icol, double *tau,
+                              double *w0, double *g, double *tband, cudaStream_t st);
+int rt_twostream_block_threads();
+int rt_twostream_items_per_layer();
+// fp64_peak.cu
+double rt_measure_fp64_tflops(int device, cudaStream_t st);

@@ -1,0 +1,521 @@
+// twostream.cu -- Toon-89 two-stream solver (IR + solar), Planck source, g/zenith weighting.
+//
+// Replaces two_stream_ir / two_stream_solar / tridiag
+// (src/radtran/clima_radtran_twostream.f90:10-316) and the per-bin loop of `radiate`
+// (src/radtran/clima_radtran_radiate.f90:50-158) for a batch of columns.
+//
+// Mapping: one THREAD per (column, channel bin ll, g-point): the 2nz x 2nz tridiagonal system is
+// solved by the same Thomas recurrence, in the same row order, as `tridiag` (:297-316), so the
+// result tracks the reference to rounding.  The P (= ngauss rounded to a power of two) threads of
+// one (column, bin) are adjacent lanes: tau/w0 loads are full 8*G-byte lines and the g-weighted
+// sum (radiate.f90:122-126) is a sub-warp shuffle reduction.
+//
+// The forward sweep streams layer by layer and keeps only the previous layer in registers; what
+// the back substitution needs per layer (c', d' of its two rows, Gamma, exp(-lambda tau), C+(tau),
+// C-(tau)) goes to a global scratch laid out [layer][item][resident thread] (coalesced 8-byte
+// accesses; the kernel is persistent so the scratch is sized by resident threads, not by work).
+//
+// Work skipped because it is provably invariant:
+//   * duplicated layers (same slot as the previous layer) reuse gamma/lambda/Gamma/exp;
+//   * solar: the matrix (A,B,D) does not depend on the zenith angle (A.5), so it is factored once
+//     and the zenith quadrature is folded into the right-hand side: back substitution and flux
+//     reconstruction are linear in the RHS, hence sum_z w_z flux_z is obtained from ONE back
+//     substitution of D' = sum_z w_z d'_z (and sum_z w_z C+-_z, sum_z w_z direct_z);
+//   * the direct beam exp(-tauc/u0) is carried as a running product (one exp per layer and zenith
+//     instead of two, :75-76).
+#include "rt_device.cuh"
+#include "rt_kernels.h"
+
+namespace {
+
+constexpr int TS_THREADS = 128;
+constexpr int IR_ITEMS = 8;
+constexpr int SOL_ITEMS = 10;
+
+template <int P>
+__device__ __forceinline__ double group_sum(double v) {
+#pragma unroll
+  for (int m = P / 2; m >= 1; m >>= 1) v += __shfl_xor_sync(0xffffffffu, v, m);
+  return v;
+}
+
+__global__ void planck_kernel(const DevTables tb, const DevChunk ch, double *bpl) {
+  const int nz = ch.nz, nw_ir = tb.ir_end - tb.ir_start + 1;
+  const size_t total = (size_t)ch.ncol * nw_ir * (nz + 1);
+  for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const int n = (int)(t % (nz + 1));
+    const int ll = (int)((t / (nz + 1)) % nw_ir);
+    const int c = (int)(t / ((size_t)(nz + 1) * nw_ir));
+    const int l = tb.ir_start + ll;
+    const double avg_freq = 0.5 * (tb.freq[l] + tb.freq[l + 1]);  // radiate.f90:64
+    const double T = (n == nz) ? ch.T_surface[c] : ch.T[(size_t)c * nz + (nz - 1 - n)];  // :65-69
+    bpl[t] = rt_planck(avg_freq, T);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ IR
+template <int P>
+__global__ void __launch_bounds__(TS_THREADS)
+twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevParams pr,
+                    const __grid_constant__ DevChunk ch, const __grid_constant__ DevFlux fx,
+                    const int ocol_bcast) {
+  constexpr int GPB = TS_THREADS / P;  // (col,bin) groups per block
+  const int G = tb.G, nw = tb.nw, nz = ch.nz, cap = ch.nslot_cap;
+  const int nw_ir = tb.ir_end - tb.ir_start + 1;
+  const long long ngroups = (long long)ch.ncol * nw_ir;
+  const size_t nres = (size_t)gridDim.x * TS_THREADS;
+  const size_t rtid = (size_t)blockIdx.x * TS_THREADS + threadIdx.x;
+  double *scr = fx.scratch + rtid;
+  const int gl = threadIdx.x % P;
+  const int gq = gl < G ? gl : G - 1;
+  const double wg = gl < G ? tb.wbin[gq] : 0.0;
+  const double norm = 2.0 * RT_PI * 0.5;  // twostream.f90:185-186 (u1 = 0.5)
+  const bool hard = pr.has_hard_surface != 0;
+  const double tmin = pr.ir_tau_min;
+
+  for (long long w = blockIdx.x; w * GPB < ngroups; w += gridDim.x) {
+    long long gid = w * GPB + threadIdx.x / P;
+    const bool gactive = gid < ngroups;
+    if (!gactive) gid = ngroups - 1;
+    const int c = (int)(gid / nw_ir), ll = (int)(gid % nw_ir);
+    const int l = tb.ir_start + ll;
+    const int oc = ocol_bcast ? 0 : c;
+    const size_t ob = ((size_t)oc * nw + l) * cap;
+    const double *tau_p = ch.tau + ob * G + gq;
+    const double *w0_p = ch.w0 + ob * G + gq;
+    const double *gt_p = ch.gt + ob;
+    const int *sol = ch.slot_of_layer + (size_t)oc * nz;
+    const double *bp = fx.bpl + ((size_t)c * nw_ir + ll) * (nz + 1);
+    const double emis = pr.emiss[ll];
+    const double Rsfc = hard ? 1.0 - emis : 0.0;
+
+    // ---- forward sweep (top layer first)
+    double e1, e2, e3, e4, cpb, cmb, cgam, wrk;  // layer i
+    double tau_i, g12;                           // layer i
+    double cprev, dprev;                         // c', d' of row 2i
+    double cp0_top;
+    int slot = sol[nz - 1];
+    {
+      const double tau = tau_p[(size_t)slot * G], w0 = w0_p[(size_t)slot * G], gt = gt_p[slot];
+      const double gam1 = 2.0 - w0 * (1.0 + gt), gam2 = w0 * (1.0 - gt);  // :195-196
+      const double lam = sqrt(gam1 * gam1 - gam2 * gam2);                 // :199
+      cgam = gam2 / (gam1 + lam);                                         // :200
+      wrk = exp(-lam * tau);                                              // :206
+      e1 = 1.0 + cgam * wrk; e2 = 1.0 - cgam * wrk; e3 = cgam + wrk; e4 = cgam - wrk;
+      g12 = 1.0 / (gam1 + gam2);
+      tau_i = tau;
+      double b0, b1;  // :216-227
+      const double Bt = bp[0], Bb = bp[1];
+      if (tau <= tmin) { b0 = 0.5 * (Bt + Bb); b1 = 0.0; } else { b0 = Bt; b1 = (Bb - b0) / tau; }
+      const double cp0 = norm * (b0 + b1 * g12);
+      cpb = norm * (b0 + b1 * (tau + g12));
+      const double cm0 = norm * (b0 + b1 * (-g12));
+      cmb = norm * (b0 + b1 * (tau - g12));
+      cp0_top = cp0;
+      // row 1 (:251-254) and its Thomas step (:302-303)
+      cprev = (-e2) / e1;
+      dprev = (0.0 - cm0) / e1;
+    }
+    for (int i = 0; i < nz; i++) {
+      double c1, d1;              // row 2i+1 (0-based)
+      double cn = 0.0, dn = 0.0;  // row 2i+2
+      double e1n = 0, e2n = 0, e3n = 0, e4n = 0, cpbn = 0, cmbn = 0, cgamn = 0, wrkn = 0, taun = 0, g12n = 0;
+      if (i < nz - 1) {
+        const int slotn = sol[nz - 2 - i];
+        if (slotn == slot) {
+          cgamn = cgam; wrkn = wrk; e1n = e1; e2n = e2; e3n = e3; e4n = e4; taun = tau_i; g12n = g12;
+        } else {
+          const double tau = tau_p[(size_t)slotn * G], w0 = w0_p[(size_t)slotn * G], gt = gt_p[slotn];
+          const double gam1 = 2.0 - w0 * (1.0 + gt), gam2 = w0 * (1.0 - gt);
+          const double lam = sqrt(gam1 * gam1 - gam2 * gam2);
+          cgamn = gam2 / (gam1 + lam);
+          wrkn = exp(-lam * tau);
+          e1n = 1.0 + cgamn * wrkn; e2n = 1.0 - cgamn * wrkn; e3n = cgamn + wrkn; e4n = cgamn - wrkn;
+          g12n = 1.0 / (gam1 + gam2);
+          taun = tau;
+          slot = slotn;
+        }
+        double b0, b1;
+        const double Bt = bp[i + 1], Bb = bp[i + 2];
+        if (taun <= tmin) { b0 = 0.5 * (Bt + Bb); b1 = 0.0; } else { b0 = Bt; b1 = (Bb - b0) / taun; }
+        const double cp0n = norm * (b0 + b1 * g12n);
+        cpbn = norm * (b0 + b1 * (taun + g12n));
+        const double cm0n = norm * (b0 + b1 * (-g12n));
+        cmbn = norm * (b0 + b1 * (taun - g12n));
+        // even Fortran row l=2i (:266-270) -> 0-based row 2i+1
+        {
+          const double A = e2n * e1 - e3 * e4n;
+          const double B = e2 * e2n - e4 * e4n;
+          const double D = e1n * e4n - e2n * e3n;
+          const double E = e2n * (cp0n - cpb) - e4n * (cm0n - cmb);
+          const double den = B - A * cprev;
+          c1 = D / den;
+          d1 = (E - A * dprev) / den;
+        }
+        // odd Fortran row l=2i+1 (:257-262) -> 0-based row 2i+2
+        {
+          const double A = e2 * e3 - e4 * e1;
+          const double B = e1 * e1n - e3 * e3n;
+          const double D = e3 * e4n - e1 * e2n;
+          const double E = e3 * (cp0n - cpb) + e1 * (cmb - cm0n);
+          const double den = B - A * c1;
+          cn = D / den;
+          dn = (E - A * d1) / den;
+        }
+      } else {
+        // last row (:272-275); surface terms (:236-247)
+        double Ssfc;
+        if (hard) {
+          Ssfc = emis * RT_PI * bp[nz];
+        } else {
+          double b1_bot = 0.0;
+          if (!(tau_i <= tmin)) b1_bot = (bp[nz] - bp[nz - 1]) / tau_i;
+          Ssfc = RT_PI * (bp[nz] + 0.5 * b1_bot);
+        }
+        const double A = e1 - Rsfc * e3;
+        const double B = e2 - Rsfc * e4;
+        const double E = Ssfc - cpb + Rsfc * cmb;
+        c1 = 0.0;
+        d1 = (E - A * dprev) / (B - A * cprev);
+      }
+      double *s = scr + (size_t)i * IR_ITEMS * nres;
+      s[0] = cprev; s[nres] = dprev; s[2 * nres] = c1; s[3 * nres] = d1;
+      s[4 * nres] = cgam; s[5 * nres] = wrk; s[6 * nres] = cpb; s[7 * nres] = cmb;
+      e1 = e1n; e2 = e2n; e3 = e3n; e4 = e4n; cpb = cpbn; cmb = cmbn; cgam = cgamn; wrk = wrkn;
+      tau_i = taun; g12 = g12n; cprev = cn; dprev = dn;
+    }
+
+    // ---- back substitution (:311-313) + fluxes (:288-293) + g-weights (radiate.f90:122-126)
+    double *fup_o = fx.fup_a_ir + ((size_t)c * nw_ir + ll) * (nz + 1);
+    double *fdn_o = fx.fdn_a_ir + ((size_t)c * nw_ir + ll) * (nz + 1);
+    const bool writer = gactive && gl == 0;
+    double xnext = 0.0;
+    double y1 = 0, y2 = 0, ee3 = 0, ee4 = 0;
+    for (int i = nz - 1; i >= 0; i--) {
+      const double *s = scr + (size_t)i * IR_ITEMS * nres;
+      const double c0 = s[0], d0 = s[nres], c1 = s[2 * nres], d1 = s[3 * nres];
+      const double cg = s[4 * nres], wk = s[5 * nres], pb = s[6 * nres], mb = s[7 * nres];
+      const double x1 = d1 - c1 * xnext;  // c1 == 0 for the last row
+      const double x0 = d0 - c0 * x1;
+      y1 = x0; y2 = x1;
+      const double ee1 = 1.0 + cg * wk, ee2 = 1.0 - cg * wk;
+      ee3 = cg + wk; ee4 = cg - wk;
+      const double fup = (y1 * ee1 + y2 * ee2 + pb);
+      const double fdn = (y1 * ee3 + y2 * ee4 + mb);
+      const double su = group_sum<P>(fup * wg), sd = group_sum<P>(fdn * wg);
+      if (writer) { fup_o[nz - 1 - i] = su; fdn_o[nz - 1 - i] = sd; }
+      xnext = x0;
+    }
+    {
+      const double fup = ((y1 * ee3 - y2 * ee4) + cp0_top);  // :288
+      const double su = group_sum<P>(fup * wg);
+      if (writer) { fup_o[nz] = su; fdn_o[nz] = 0.0; }
+    }
+  }
+}
+
+// --------------------------------------------------------------------------------------- solar
+template <int P, int ZC>
+__global__ void __launch_bounds__(TS_THREADS)
+twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevParams pr,
+                       const __grid_constant__ DevChunk ch, const __grid_constant__ DevFlux fx,
+                       const int ocol_bcast, const int zbeg, const int accumulate) {
+  constexpr int GPB = TS_THREADS / P;
+  const int G = tb.G, nw = tb.nw, nz = ch.nz, cap = ch.nslot_cap;
+  const int nw_sol = tb.sol_end - tb.sol_start + 1;
+  const long long ngroups = (long long)ch.ncol * nw_sol;
+  const size_t nres = (size_t)gridDim.x * TS_THREADS;
+  const size_t rtid = (size_t)blockIdx.x * TS_THREADS + threadIdx.x;
+  double *scr = fx.scratch + rtid;
+  const int gl = threadIdx.x % P;
+  const int gq = gl < G ? gl : G - 1;
+  const double wg = gl < G ? tb.wbin[gq] : 0.0;
+  const double sq3 = sqrt(3.0);
+  const double u1i = 1.0 / (1.0 / sqrt(3.0));  // (1/u1), u1 = 1/sqrt(3)  (:30,:135)
+
+  double u0[ZC], iu0[ZC], iu02[ZC], wz[ZC];
+#pragma unroll
+  for (int z = 0; z < ZC; z++) {
+    const bool on = zbeg + z < pr.nzen;
+    u0[z] = on ? pr.zen_u[zbeg + z] : 1.0;
+    wz[z] = on ? pr.zen_w[zbeg + z] : 0.0;
+    iu0[z] = 1.0 / u0[z];
+    iu02[z] = 1.0 / (u0[z] * u0[z]);
+  }
+
+  for (long long w = blockIdx.x; w * GPB < ngroups; w += gridDim.x) {
+    long long gid = w * GPB + threadIdx.x / P;
+    const bool gactive = gid < ngroups;
+    if (!gactive) gid = ngroups - 1;
+    const int c = (int)(gid / nw_sol), ll = (int)(gid % nw_sol);
+    const int l = tb.sol_start + ll;
+    const int oc = ocol_bcast ? 0 : c;
+    const size_t ob = ((size_t)oc * nw + l) * cap;
+    const double *tau_p = ch.tau + ob * G + gq;
+    const double *w0_p = ch.w0 + ob * G + gq;
+    const double *gt_p = ch.gt + ob;
+    const int *sol = ch.slot_of_layer + (size_t)oc * nz;
+    const double Rsfc = pr.albedo[ll];
+
+    // layer i state (zenith independent)
+    double e1, e2, e3, e4, cgam, wrk;
+    // per-zenith layer coefficients (reused by duplicated layers) and running state
+    double fp[ZC], fm[ZC], ex[ZC];  // facp/denom, facm/denom, exp(-tau'/u0)
+    double et[ZC];                  // exp(-tauc/u0) at the top of layer i
+    double cpb[ZC], cmb[ZC], dprev[ZC];
+    double cprev;
+    double CP0_top = 0.0, FDN_top = 0.0, AM_top = 0.0;
+    int slot = -1;
+
+    auto layer_coeffs = [&](const int s) {
+      const double tau_in = tau_p[(size_t)s * G], w0_in = w0_p[(size_t)s * G], gt_in = gt_p[s];
+      // delta-Eddington scaling (:38-40)
+      const double f = 1.0 - w0_in * gt_in * gt_in;
+      const double tau = tau_in * f;
+      const double w0 = w0_in * (1.0 - gt_in * gt_in) / f;
+      const double gt = gt_in / (1.0 + gt_in);
+      // quadrature coefficients (:43-46)
+      const double gam1 = sq3 * (2.0 - w0 * (1.0 + gt)) / 2.0;
+      const double gam2 = sq3 * w0 * (1.0 - gt) / 2.0;
+      const double lam = sqrt(gam1 * gam1 - gam2 * gam2);  // :50
+      cgam = gam2 / (gam1 + lam);                          // :51
+      wrk = exp(-lam * tau);                               // :56
+      e1 = 1.0 + cgam * wrk; e2 = 1.0 - cgam * wrk; e3 = cgam + wrk; e4 = cgam - wrk;
+#pragma unroll
+      for (int z = 0; z < ZC; z++) {
+        const double gam3 = (1.0 - sq3 * gt * u0[z]) / 2.0;  // :45
+        const double gam4 = 1.0 - gam3;
+        const double facp = w0 * ((gam1 - iu0[z]) * gam3 + gam4 * gam2);  // :76
+        const double facm = w0 * ((gam1 + iu0[z]) * gam4 + gam2 * gam3);  // :77
+        const double rden = 1.0 / (lam * lam - iu02[z]);                  // :80
+        fp[z] = facp * rden;
+        fm[z] = facm * rden;
+        ex[z] = exp(-tau * iu0[z]);
+      }
+    };
+
+    // ---- top layer and row 1
+    slot = sol[nz - 1];
+    layer_coeffs(slot);
+    double Dprev = 0.0;  // sum_z w_z d'_z of row 2i
+#pragma unroll
+    for (int z = 0; z < ZC; z++) {
+      const double etb = ex[z];  // et0 = exp(-tauc(1)/u0) = 1
+      const double cp0 = fp[z], cm0 = fm[z];
+      cpb[z] = etb * fp[z];
+      cmb[z] = etb * fm[z];
+      et[z] = etb;
+      dprev[z] = (0.0 - cm0) / e1;  // rows :93-96, Thomas :302-303
+      Dprev += wz[z] * dprev[z];
+      CP0_top += wz[z] * cp0;
+      FDN_top += wz[z] * u0[z];  // direct(1) = u0*Fs_pi (:73)
+      AM_top += wz[z];           // direct(1)/u0
+    }
+    cprev = (-e2) / e1;
+
+    for (int i = 0; i < nz; i++) {
+      // layer i ("o"ld) values; layer_coeffs() overwrites e1..e4/cgam/wrk/fp/fm/ex with layer i+1
+      const double e1o = e1, e2o = e2, e3o = e3, e4o = e4, cgo = cgam, wko = wrk;
+      double c1, cn = 0.0, D1 = 0.0, Dn = 0.0;
+      double CPB = 0.0, CMB = 0.0, DIR = 0.0, DIRU = 0.0;
+#pragma unroll
+      for (int z = 0; z < ZC; z++) {
+        CPB += wz[z] * cpb[z];
+        CMB += wz[z] * cmb[z];
+        DIR += wz[z] * (u0[z] * et[z]);  // direct(i+1) = u0*etb(i) (:84)
+        DIRU += wz[z] * et[z];           // direct(i+1)/u0
+      }
+      if (i < nz - 1) {
+        const int slotn = sol[nz - 2 - i];
+        if (slotn != slot) {
+          layer_coeffs(slotn);
+          slot = slotn;
+        }
+        // even Fortran row l=2i (:107-112) -> 0-based row 2i+1 ; (e1..e4 = layer i+1)
+        const double A1 = e2 * e1o - e3o * e4, B1 = e2o * e2 - e4o * e4, Dd1 = e1 * e4 - e2 * e3;
+        const double r1 = 1.0 / (B1 - A1 * cprev);
+        c1 = Dd1 * r1;
+        // odd Fortran row l=2i+1 (:99-104) -> 0-based row 2i+2
+        const double A2 = e2o * e3o - e4o * e1o, B2 = e1o * e1 - e3o * e3, Dd2 = e3o * e4 - e1o * e2;
+        const double r2 = 1.0 / (B2 - A2 * c1);
+        cn = Dd2 * r2;
+#pragma unroll
+        for (int z = 0; z < ZC; z++) {
+          const double etb = et[z] * ex[z];
+          const double cp0n = et[z] * fp[z], cm0n = et[z] * fm[z];
+          const double E1 = e2 * (cp0n - cpb[z]) - e4 * (cm0n - cmb[z]);
+          const double d1 = (E1 - A1 * dprev[z]) * r1;
+          const double E2 = e3o * (cp0n - cpb[z]) + e1o * (cmb[z] - cm0n);
+          const double dn = (E2 - A2 * d1) * r2;
+          D1 += wz[z] * d1;
+          Dn += wz[z] * dn;
+          dprev[z] = dn;
+          cpb[z] = etb * fp[z];
+          cmb[z] = etb * fm[z];
+          et[z] = etb;
+        }
+      } else {
+        const double A = e1o - Rsfc * e3o, B = e2o - Rsfc * e4o;  // :114-117
+        const double r1 = 1.0 / (B - A * cprev);
+        c1 = 0.0;
+#pragma unroll
+        for (int z = 0; z < ZC; z++) {
+          const double Ssfc = Rsfc * (u0[z] * et[z]);  // :90
+          const double E = Ssfc - cpb[z] + Rsfc * cmb[z];
+          D1 += wz[z] * ((E - A * dprev[z]) * r1);
+        }
+      }
+      double *s = scr + (size_t)i * SOL_ITEMS * nres;
+      s[0] = cprev; s[nres] = Dprev; s[2 * nres] = c1; s[3 * nres] = D1;
+      s[4 * nres] = cgo; s[5 * nres] = wko; s[6 * nres] = CPB; s[7 * nres] = CMB;
+      s[8 * nres] = DIR; s[9 * nres] = DIRU;
+      cprev = cn;
+      Dprev = Dn;
+    }
+
+    // ---- ONE back substitution for the zenith-weighted solution, fluxes (:135-148), g-weights
+    const size_t obase = ((size_t)c * nw_sol + ll) * (nz + 1);
+    double *fup_o = fx.fup_a_sol + obase, *fdn_o = fx.fdn_a_sol + obase, *am_o = fx.amean_sol + obase;
+    const bool writer = gactive && gl == 0;
+    // scale factors applied after the g/zenith sums (radiate.f90:167-180)
+    const double ps = pr.photons_sol[ll] * pr.photon_scale_factor;  // clima_radtran.f90:302
+    const double avg_freq = 0.5 * (tb.freq[l] + tb.freq[l + 1]);
+    const double avg_wavl = 1.0e9 * RT_C_LIGHT / avg_freq;
+    const double am1 = (avg_freq / avg_wavl);
+    const double am2 = (avg_wavl / (RT_PLANK * RT_C_LIGHT * 1.0e16));
+    const double dwl = (tb.wavl[l + 1] - tb.wavl[l]);
+    auto emit = [&](const int ig, double fup, double fdn, double am) {
+      const double su = group_sum<P>(fup * wg), sd = group_sum<P>(fdn * wg), sa = group_sum<P>(am * wg);
+      if (writer) {
+        double a = su * ps * pr.diurnal_fac, b = sd * ps * pr.diurnal_fac, m = sa * ps * pr.diurnal_fac;
+        m = m * am1;
+        m = m * am2 * dwl;
+        if (accumulate) { a += fup_o[ig]; b += fdn_o[ig]; m += am_o[ig]; }
+        fup_o[ig] = a; fdn_o[ig] = b; am_o[ig] = m;
+      }
+    };
+    double xnext = 0.0, y1 = 0, y2 = 0, ee3 = 0, ee4 = 0;
+    for (int i = nz - 1; i >= 0; i--) {
+      const double *s = scr + (size_t)i * SOL_ITEMS * nres;
+      const double c0 = s[0], d0 = s[nres], c1 = s[2 * nres], d1 = s[3 * nres];
+      const double cg = s[4 * nres], wk = s[5 * nres], pb = s[6 * nres], mb = s[7 * nres];
+      const double dir = s[8 * nres], diru = s[9 * nres];
+      const double x1 = d1 - c1 * xnext;
+      const double x0 = d0 - c0 * x1;
+      y1 = x0; y2 = x1;
+      const double ee1 = 1.0 + cg * wk, ee2 = 1.0 - cg * wk;
+      ee3 = cg + wk; ee4 = cg - wk;
+      const double am = u1i * (y1 * (ee1 + ee3) + y2 * (ee2 + ee4) + pb + mb) + diru;  // :137-139
+      const double fup = (y1 * ee1 + y2 * ee2 + pb);                                 // :146
+      const double fdn = (y1 * ee3 + y2 * ee4 + mb) + dir;                           // :147
+      emit(nz - 1 - i, fup, fdn, am);
+      xnext = x0;
+    }
+    {
+      const double up = (y1 * ee3 - y2 * ee4) + CP0_top;  // :143
+      emit(nz, up, FDN_top, u1i * up + AM_top);           // :135, :144
+    }
+  }
+}
+
+// ------------------------------------------------------------------------- frequency integration
+// radiate.f90:184-192 + clima_radtran.f90:286-289,316 + TOA_fluxes (:339-340).
+// One thread per (column, level); the sum over bins runs in the reference's order.
+__global__ void integrate_kernel(const DevTables tb, const DevChunk ch, const DevFlux fx,
+                                 const int compute_solar, const int sol_bcast) {
+  const int nz = ch.nz, L = nz + 1;
+  const int nw_ir = tb.ir_end - tb.ir_start + 1, nw_sol = tb.sol_end - tb.sol_start + 1;
+  const size_t total = (size_t)ch.ncol * L;
+  for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const int i = (int)(t % L);
+    const int c = (int)(t / L);
+    double up = 0.0, dn = 0.0;
+    for (int ll = 0; ll < nw_ir; ll++) {
+      const int l = tb.ir_start + ll;
+      const double dfreq = tb.freq[l] - tb.freq[l + 1];
+      up = up + fx.fup_a_ir[((size_t)c * nw_ir + ll) * L + i] * dfreq;
+      dn = dn + fx.fdn_a_ir[((size_t)c * nw_ir + ll) * L + i] * dfreq;
+    }
+    fx.fup_n_ir[t] = up;
+    fx.fdn_n_ir[t] = dn;
+    double sup, sdn;
+    if (compute_solar) {
+      sup = 0.0; sdn = 0.0;
+      for (int ll = 0; ll < nw_sol; ll++) {
+        const int l = tb.sol_start + ll;
+        const double dfreq = tb.freq[l] - tb.freq[l + 1];
+        sup = sup + fx.fup_a_sol[((size_t)c * nw_sol + ll) * L + i] * dfreq;
+        sdn = sdn + fx.fdn_a_sol[((size_t)c * nw_sol + ll) * L + i] * dfreq;
+      }
+      fx.fup_n_sol[t] = sup;
+      fx.fdn_n_sol[t] = sdn;
+    } else {
+      // stale solar fluxes of the previous call (clima_radtran.f90:286-289)
+      const size_t ts = sol_bcast ? (size_t)i : t;
+      sup = fx.fup_n_sol[ts];
+      sdn = fx.fdn_n_sol[ts];
+      if (sol_bcast && c > 0) { fx.fup_n_sol[t] = sup; fx.fdn_n_sol[t] = sdn; }
+    }
+    fx.f_total[t] = (sdn - sup) + (dn - up);
+    if (i == nz) {
+      fx.ISR[c] = (sdn - sup);
+      fx.OLR[c] = -(dn - up);
+      if (!(isfinite(sdn) && isfinite(sup) && isfinite(dn) && isfinite(up))) atomicOr(fx.status + c, 2);
+    }
+  }
+}
+
+}  // namespace
+
+int rt_twostream_block_threads() { return TS_THREADS; }
+int rt_twostream_items_per_layer() { return SOL_ITEMS > IR_ITEMS ? SOL_ITEMS : IR_ITEMS; }
+
+void rt_launch_planck(const DevTables &tb, const DevChunk &ch, const DevFlux &fx, cudaStream_t st) {
+  planck_kernel<<<1184, 256, 0, st>>>(tb, ch, fx.bpl);
+}
+
+void rt_launch_twostream_ir(const DevTables &tb, const DevParams &pr, const DevChunk &ch,
+                            const DevFlux &fx, int ocol_bcast, int nblocks, cudaStream_t st) {
+  if (tb.G <= 8) twostream_ir_kernel<8><<<nblocks, TS_THREADS, 0, st>>>(tb, pr, ch, fx, ocol_bcast);
+  else if (tb.G <= 16) twostream_ir_kernel<16><<<nblocks, TS_THREADS, 0, st>>>(tb, pr, ch, fx, ocol_bcast);
+  else twostream_ir_kernel<32><<<nblocks, TS_THREADS, 0, st>>>(tb, pr, ch, fx, ocol_bcast);
+}
+
+template <int P>
+static void launch_solar_p(const DevTables &tb, const DevParams &pr, const DevChunk &ch,
+                           const DevFlux &fx, int ocol_bcast, int nblocks, cudaStream_t st) {
+  // zenith angles in passes of at most 4 (register budget); later passes accumulate
+  int zbeg = 0;
+  while (zbeg < pr.nzen) {
+    const int left = pr.nzen - zbeg;
+    const int acc = zbeg > 0;
+    if (left >= 4) {
+      twostream_solar_kernel<P, 4><<<nblocks, TS_THREADS, 0, st>>>(tb, pr, ch, fx, ocol_bcast, zbeg, acc);
+      zbeg += 4;
+    } else if (left >= 2) {
+      twostream_solar_kernel<P, 2><<<nblocks, TS_THREADS, 0, st>>>(tb, pr, ch, fx, ocol_bcast, zbeg, acc);
+      zbeg += 2;
+    } else {
+      twostream_solar_kernel<P, 1><<<nblocks, TS_THREADS, 0, st>>>(tb, pr, ch, fx, ocol_bcast, zbeg, acc);
+      zbeg += 1;
+    }
+  }
+}
+
+void rt_launch_twostream_solar(const DevTables &tb, const DevParams &pr, const DevChunk &ch,
+                               const DevFlux &fx, int ocol_bcast, int nblocks, cudaStream_t st) {
+  if (tb.G <= 8) launch_solar_p<8>(tb, pr, ch, fx, ocol_bcast, nblocks, st);
+  else if (tb.G <= 16) launch_solar_p<16>(tb, pr, ch, fx, ocol_bcast, nblocks, st);
+  else launch_solar_p<32>(tb, pr, ch, fx, ocol_bcast, nblocks, st);
+}
+
+void rt_launch_integrate(const DevTables &tb, const DevParams &pr, const DevChunk &ch,
+                         const DevFlux &fx, int compute_solar, int sol_bcast, cudaStream_t st) {
+  (void)pr;
+  const size_t total = (size_t)ch.ncol * (ch.nz + 1);
+  int nb = (int)((total + 255) / 256);
+  if (nb > 4736) nb = 4736;
+  integrate_kernel<<<nb, 256, 0, st>>>(tb, ch, fx, compute_solar, sol_bcast);
+}

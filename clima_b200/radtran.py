@@ -1,0 +1,210 @@
+"""Host-side mirror of the reference's `Radtran` interface over the CUDA C-ABI library.
+
+Same method names, argument meaning and error behaviour as `type Radtran`
+(src/radtran/clima_radtran.f90:31-85: `radiate`, `TOA_fluxes`, `set_custom_optical_properties`,
+`unset_custom_optical_properties`, public knobs `diurnal_fac`, `surface_albedo`, ...), plus the
+batched-column entry point `radiate_batch` / `TOA_fluxes_batch` that the north star adds.
+Errors follow the Cython layer (clima/cython/_clima.pyx:11,48-49): a non-empty `err` raises
+`ClimaException`.
+
+All compute goes through `libclima_rt.so` (include/clima_rt.h).  There is no CPU fallback: if the
+library is missing or no CUDA device is usable, construction raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Dict, Optional
+
+import numpy as np
+
+from ._abi import (COut, CParams, CTables, ERR_LEN, OpacityTables, RadtranParams, alloc_out,
+                   c_double_p, dptr)
+
+_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libclima_rt.so")
+_lib = None
+
+EXPORTS = ["clima_rt_create", "clima_rt_destroy", "clima_rt_set_params",
+           "clima_rt_set_custom_optical_properties", "clima_rt_unset_custom_optical_properties",
+           "clima_rt_radiate_batch", "clima_rt_radiate_batch_device", "clima_rt_get_opacity",
+           "clima_rt_get_launch_count", "clima_rt_get_stage_ms", "clima_rt_measure_fp64_peak",
+           "clima_rt_version_get"]
+
+
+class ClimaException(Exception):
+    """clima/cython/_clima.pyx:11"""
+
+
+def load_library() -> C.CDLL:
+    """Loads the CUDA C-ABI library.  Fails loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_LIB_PATH):
+            raise ClimaException(
+                f"{_LIB_PATH} is missing: build it with `python -m clima_b200.build` "
+                "(there is no CPU fallback)")
+        _lib = C.CDLL(_LIB_PATH)
+        for name in EXPORTS:
+            getattr(_lib, name).restype = None
+    return _lib
+
+
+def _i(v):
+    return C.byref(C.c_int32(int(v)))
+
+
+def _check(err):
+    if len(err.value.strip()) > 0:
+        raise ClimaException(err.value.decode())
+
+
+def measure_fp64_peak(device: int = 0) -> float:
+    lib = load_library()
+    out = C.c_double(0.0)
+    err = C.create_string_buffer(ERR_LEN + 1)
+    lib.clima_rt_measure_fp64_peak(_i(device), C.byref(out), err)
+    _check(err)
+    return out.value
+
+
+def version() -> str:
+    buf = C.create_string_buffer(101)
+    load_library().clima_rt_version_get(buf)
+    return buf.value.decode()
+
+
+class ClimaRadtranWrk:
+    """`type ClimaRadtranWrk` (clima_radtran.f90:11-25) of one column."""
+
+    def __init__(self, fup_a, fdn_a, fup_n, fdn_n, amean, tau_band):
+        self.fup_a, self.fdn_a, self.fup_n, self.fdn_n = fup_a, fdn_a, fup_n, fdn_n
+        self.amean, self.tau_band = amean, tau_band
+
+
+class Radtran:
+    def __init__(self, tables: OpacityTables, params: RadtranParams, device: int = 0):
+        self._lib = load_library()
+        self.tables = tables
+        self._params = params
+        self._ct, self._keep_t = tables.to_c()
+        cp, self._keep_p = params.to_c()
+        self._h = C.c_void_p()
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self._lib.clima_rt_create(C.byref(self._ct), C.byref(cp), _i(device), C.byref(self._h), err)
+        _check(err)
+        self.device = device
+        self.wrk_ir: Optional[ClimaRadtranWrk] = None
+        self.wrk_sol: Optional[ClimaRadtranWrk] = None
+        self.f_total: Optional[np.ndarray] = None
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                self._lib.clima_rt_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    # ---- run-time knobs (public members of type Radtran, clima_radtran.f90:51-68)
+    @property
+    def params(self) -> RadtranParams:
+        return self._params
+
+    @params.setter
+    def params(self, p: RadtranParams):
+        cp, keep = p.to_c()
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self._lib.clima_rt_set_params(self._h, C.byref(cp), err)
+        _check(err)
+        self._params, self._keep_p = p, keep
+
+    def set_custom_optical_properties(self, log10P, dtau_dz, w0, g0):
+        """State after OpticalProperties_set_custom_optical_properties
+        (clima_radtran_types.f90:504-531): tables already on the opacity grid."""
+        arrs = [np.ascontiguousarray(np.asarray(a, dtype=np.float64).ravel(order="F"))
+                for a in (log10P, dtau_dz, w0, g0)]
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self._lib.clima_rt_set_custom_optical_properties(self._h, _i(len(arrs[0])),
+                                                         *(dptr(a) for a in arrs), err)
+        _check(err)
+
+    def unset_custom_optical_properties(self):
+        self._lib.clima_rt_unset_custom_optical_properties(self._h)
+
+    # ---- the batched-column entry point
+    def radiate_batch(self, cols: Dict, compute_solar=True, compute_opacity=True, spectral=False,
+                      out=None):
+        """`radiate` + `TOA_fluxes` for cols['ncol'] columns.  `cols` holds Fortran-ordered
+        T_surface(ncol), T(nz,ncol), P(nz,ncol) [bar], densities(nz,ng,ncol), dz(nz,ncol) and
+        optionally pdensities/radii(nz,np,ncol).  Returns a dict of result arrays."""
+        nz, ng, npp, ncol = cols["nz"], cols["ng"], cols["np"], cols["ncol"]
+        if out is None:
+            out = alloc_out(nz, ncol, self.tables.nw_ir, self.tables.nw_sol, spectral)
+        o, arrs = out
+        err = C.create_string_buffer(ERR_LEN + 1)
+        pd = dptr(cols["pdensities"]) if "pdensities" in cols else c_double_p()
+        rd = dptr(cols["radii"]) if "radii" in cols else c_double_p()
+        self._lib.clima_rt_radiate_batch(self._h, _i(ncol), _i(nz), _i(ng), _i(npp),
+                                         dptr(cols["T_surface"]), dptr(cols["T"]), dptr(cols["P"]),
+                                         dptr(cols["densities"]), dptr(cols["dz"]), pd, rd,
+                                         _i(compute_solar), _i(compute_opacity), C.byref(o), err)
+        _check(err)
+        return arrs
+
+    def TOA_fluxes_batch(self, cols: Dict):
+        r = self.radiate_batch(cols)
+        return r["ISR"], r["OLR"]
+
+    # ---- the reference's single-column API (clima_radtran.f90:221-342)
+    def radiate(self, T_surface, T, P, densities, dz, pdensities=None, radii=None,
+                compute_solar=True, compute_opacity=True):
+        T = np.ascontiguousarray(T, dtype=np.float64)
+        nz = T.shape[0]
+        dens = np.asfortranarray(densities, dtype=np.float64)
+        cols = dict(ncol=1, nz=nz, ng=dens.shape[1] if dens.ndim > 1 else 1,
+                    np=0 if pdensities is None else np.asarray(pdensities).reshape(nz, -1).shape[1],
+                    T_surface=np.array([float(T_surface)]), T=T,
+                    P=np.ascontiguousarray(P, dtype=np.float64),
+                    densities=np.ascontiguousarray(dens.ravel(order="F")),
+                    dz=np.ascontiguousarray(dz, dtype=np.float64))
+        if pdensities is not None:
+            cols["pdensities"] = np.ascontiguousarray(np.asfortranarray(pdensities, dtype=np.float64).ravel(order="F"))
+        if radii is not None:
+            cols["radii"] = np.ascontiguousarray(np.asfortranarray(radii, dtype=np.float64).ravel(order="F"))
+        if (pdensities is None) != (radii is None):
+            raise ClimaException("Both pdensities and radii must be arguments.")
+        r = self.radiate_batch(cols, compute_solar, compute_opacity, spectral=True)
+        self.wrk_ir = ClimaRadtranWrk(r["fup_a_ir"][..., 0], r["fdn_a_ir"][..., 0], r["fup_n_ir"][:, 0],
+                                      r["fdn_n_ir"][:, 0], np.zeros_like(r["fup_a_ir"][..., 0]),
+                                      r["tau_band_ir"][..., 0])
+        self.wrk_sol = ClimaRadtranWrk(r["fup_a_sol"][..., 0], r["fdn_a_sol"][..., 0], r["fup_n_sol"][:, 0],
+                                       r["fdn_n_sol"][:, 0], r["amean_sol"][..., 0], r["tau_band_sol"][..., 0])
+        self.f_total = r["f_total"][:, 0]
+        self._last = r
+        return r
+
+    def TOA_fluxes(self, T_surface, T, P, densities, dz, pdensities=None, radii=None):
+        r = self.radiate(T_surface, T, P, densities, dz, pdensities, radii)
+        return float(r["ISR"][0]), float(r["OLR"][0])
+
+    # ---- introspection / test hooks
+    def get_opacity(self, nz: int, icol: int = 0):
+        G, nw = self.tables.ngauss, self.tables.nw
+        tau = np.zeros((nz, G, nw), order="F")
+        w0 = np.zeros((nz, G, nw), order="F")
+        g = np.zeros((nz, nw), order="F")
+        tb = np.zeros((nz, nw), order="F")
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self._lib.clima_rt_get_opacity(self._h, _i(icol), dptr(tau), dptr(w0), dptr(g), dptr(tb), err)
+        _check(err)
+        return tau, w0, g, tb
+
+    def launch_count(self) -> int:
+        n = C.c_int64(0)
+        self._lib.clima_rt_get_launch_count(self._h, C.byref(n))
+        return n.value
+
+    def stage_ms(self):
+        a = (C.c_double * 5)()
+        self._lib.clima_rt_get_stage_ms(self._h, a)
+        return list(a)

@@ -1,0 +1,60 @@
+"""Shared parity cases: small synthetic tables/columns that the oracle finishes in seconds."""
+import numpy as np
+
+from clima_b200 import synth
+
+TOL = 1.0e-9  # north_star: 1e-9 relative on layer fluxes and OLR (FP64)
+
+
+def small_case(G=16, nw=12, nz=10, ncol=3, nk=3, npart=0, nzen=4, seed=1, doubled=True, **kw):
+    n_sol = max(2, (2 * nw) // 3)
+    ir_start = max(1, nw // 3)
+    tb = synth.make_tables(nw=nw, G=G, nk=nk, ncia=6, nray=3, npxs=2, cont=True, npart=npart,
+                           npress=8, ntemp=6, n_sol=n_sol, ir_start=ir_start, seed=seed)
+    pr = synth.default_params(tb, nzenith=nzen, **kw)
+    cols = synth.make_columns(ncol, nz=nz, seed=seed, doubled=doubled, npart=npart)
+    return tb, pr, cols
+
+
+def rel_err(a, b):
+    """max |a-b| / max|b| (flux arrays span many decades; the scale is the array maximum)."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    s = np.max(np.abs(b))
+    if s == 0.0:
+        return float(np.max(np.abs(a)))
+    return float(np.max(np.abs(a - b)) / s)
+
+
+def elem_rel_err(a, b, floor=1e-6):
+    """max elementwise relative error over elements with |b| > floor*max|b|."""
+    a = np.asarray(a, dtype=np.float64)
+    b = np.asarray(b, dtype=np.float64)
+    s = np.max(np.abs(b))
+    m = np.abs(b) > floor * s
+    if not m.any():
+        return 0.0
+    return float(np.max(np.abs(a[m] - b[m]) / np.abs(b[m])))
+
+
+FLUX_KEYS = ["fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol"]
+SPEC_KEYS = ["fup_a_ir", "fdn_a_ir", "tau_band_ir", "fup_a_sol", "fdn_a_sol", "amean_sol", "tau_band_sol"]
+
+
+def compare(r_gpu, r_ref, spectral=True, tol=TOL, verbose=False):
+    worst = {}
+    for k in FLUX_KEYS + (SPEC_KEYS if spectral else []):
+        worst[k] = rel_err(r_gpu[k], r_ref[k])
+    for k in FLUX_KEYS:
+        worst[k + "_elem"] = elem_rel_err(r_gpu[k], r_ref[k])
+    for k in ("ISR", "OLR"):
+        worst[k] = float(np.max(np.abs(r_gpu[k] - r_ref[k]) / np.abs(r_ref[k])))
+    # f_total is a difference of four large numbers: absolute tolerance vs max |flux|
+    scale = max(np.max(np.abs(r_ref[k])) for k in FLUX_KEYS)
+    worst["f_total"] = float(np.max(np.abs(r_gpu["f_total"] - r_ref["f_total"])) / scale)
+    if verbose:
+        for k, v in worst.items():
+            print(f"  {k:16s} {v:.3e}")
+    bad = {k: v for k, v in worst.items() if not (v <= tol)}
+    assert not bad, f"parity failure (tol {tol}): {bad}"
+    return worst

@@ -1,0 +1,202 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same seeded
+inputs.  Tolerance 1e-9 relative (north_star), FP64."""
+import numpy as np
+import pytest
+
+from cases import TOL, compare, rel_err, small_case
+from clima_b200 import synth
+from clima_b200.radtran import ClimaException, Radtran
+from oracle_lib import OracleRadtran
+
+pytestmark = pytest.mark.gpu
+
+
+def run_both(tb, pr, cols, spectral=True, **kw):
+    g = Radtran(tb, pr)
+    o = OracleRadtran(tb, pr, kind="parity")
+    rg = g.radiate_batch(cols, spectral=spectral, **kw)
+    ro = o.radiate_batch(cols, spectral=spectral, nthreads=8, **kw)
+    return g, o, rg, ro
+
+
+@pytest.mark.parametrize("G", [16, 8, 20, 32, 5])
+def test_small_parity_ngauss(G):
+    tb, pr, cols = small_case(G=G, nw=10, nz=8, ncol=3)
+    g, o, rg, ro = run_both(tb, pr, cols)
+    compare(rg, ro)
+    assert np.all(rg["status"] == 0)
+
+
+def test_opacity_parity():
+    """tau, w0, g, tau_band of OpticalPropertiesResult (clima_radtran_types.f90:242-247)."""
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=2)
+    g = Radtran(tb, pr)
+    o = OracleRadtran(tb, pr)
+    g.radiate_batch(cols)
+    o.radiate(cols, icol=1)
+    tg = g.get_opacity(cols["nz"], icol=1)
+    to = o.get_opacity(cols["nz"])
+    for a, b, name in zip(tg, to, ("tau", "w0", "g", "tau_band")):
+        m = np.abs(b) > 0
+        e = np.max(np.abs(a[m] - b[m]) / np.abs(b[m])) if m.any() else 0.0
+        assert e < 1e-11, (name, e)
+
+
+@pytest.mark.parametrize("nzen", [1, 3, 8])
+def test_zenith_passes(nzen):
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=2, nzen=nzen)
+    _, _, rg, ro = run_both(tb, pr, cols)
+    compare(rg, ro)
+
+
+def test_undoubled_odd_nz_and_no_hard_surface():
+    tb, pr, cols = small_case(G=16, nw=10, nz=9, ncol=2, doubled=False, has_hard_surface=False)
+    _, _, rg, ro = run_both(tb, pr, cols)
+    compare(rg, ro)
+
+
+def test_emissivity_albedo_vectors():
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=2)
+    rng = np.random.default_rng(3)
+    pr.surface_albedo = rng.uniform(0.05, 0.6, tb.nw_sol)
+    pr.surface_emissivity = rng.uniform(0.7, 1.0, tb.nw_ir)
+    pr.photon_scale_factor = 0.4286
+    _, _, rg, ro = run_both(tb, pr, cols)
+    compare(rg, ro)
+
+
+def test_particles_and_custom_opacity():
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=2, npart=2)
+    g = Radtran(tb, pr)
+    o = OracleRadtran(tb, pr)
+    compare(g.radiate_batch(cols, spectral=True), o.radiate_batch(cols, spectral=True))
+    # custom optical properties (clima_radtran_types.f90:504-572)
+    rng = np.random.default_rng(5)
+    nP = 7
+    log10P = np.linspace(0.5, 6.5, nP)
+    dtau = np.asfortranarray(10.0 ** rng.uniform(-9, -6, (nP, tb.nw)))
+    w0 = np.asfortranarray(rng.uniform(0.1, 0.9, (nP, tb.nw)))
+    g0 = np.asfortranarray(rng.uniform(0.0, 0.8, (nP, tb.nw)))
+    g.set_custom_optical_properties(log10P, dtau, w0, g0)
+    o.set_custom(log10P, dtau, w0, g0)
+    r1 = g.radiate_batch(cols, spectral=True)
+    compare(r1, o.radiate_batch(cols, spectral=True))
+    # all-zero custom opacity must not change fluxes (tests/test_radtran.f90:86-104)
+    z = np.zeros((nP, tb.nw), order="F")
+    g.set_custom_optical_properties(log10P, z, z, z)
+    o.set_custom(log10P, z, z, z)
+    r0 = g.radiate_batch(cols, spectral=True)
+    compare(r0, o.radiate_batch(cols, spectral=True))
+    g.unset_custom_optical_properties()
+    o.unset_custom()
+    r2 = g.radiate_batch(cols, spectral=True)
+    compare(r2, o.radiate_batch(cols, spectral=True))
+    assert rel_err(r0["fup_n_ir"], r2["fup_n_ir"]) < 1e-12
+
+
+def test_particle_radius_out_of_range_fails_like_reference():
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=2, npart=1)
+    cols["radii"][:] = 1.0  # 1 cm: outside the Mie table
+    g = Radtran(tb, pr)
+    with pytest.raises(ClimaException, match="Opacity computation failed"):
+        g.radiate_batch(cols)
+
+
+def test_frozen_opacity_jacobian_mode():
+    """compute_opacity=.false., compute_solar=.false. (clima_adiabat_solve.f90:798-820): perturbed
+    temperatures re-use ONE column's opacity and the stale solar fluxes."""
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=1, nzen=1)
+    g = Radtran(tb, pr)
+    o = OracleRadtran(tb, pr)
+    rg0 = g.radiate_batch(cols, spectral=False)
+    ro0 = o.radiate(cols, 0, spectral=False)
+    compare(rg0, ro0, spectral=False)
+    nz = cols["nz"]
+    npert = 5
+    pert = {k: v for k, v in cols.items()}
+    pert["ncol"] = npert
+    pert["T_surface"] = np.repeat(cols["T_surface"], npert) * (1 + 1e-2 * np.arange(npert))
+    T = np.repeat(cols["T"], npert, axis=1).copy(order="F")
+    for c in range(npert):
+        T[c % nz:, c] *= 1.01
+    pert["T"] = T
+    for k in ("P", "dz"):
+        pert[k] = np.asfortranarray(np.repeat(cols[k], npert, axis=1))
+    pert["densities"] = np.asfortranarray(np.repeat(cols["densities"], npert, axis=2))
+    rg = g.radiate_batch(pert, compute_solar=False, compute_opacity=False)
+    for c in range(npert):
+        ro = o.radiate(pert, c, compute_solar=False, compute_opacity=False, spectral=False)
+        sub = {k: (v[..., c:c + 1] if v.ndim > 1 else v[c:c + 1]) for k, v in rg.items()}
+        compare(sub, ro, spectral=False)
+
+
+def test_same_batch_frozen_opacity():
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=3)
+    g = Radtran(tb, pr)
+    r1 = g.radiate_batch(cols)
+    r2 = g.radiate_batch(cols, compute_opacity=False)
+    for k in ("fup_n_ir", "fup_n_sol", "f_total"):
+        assert np.array_equal(r1[k], r2[k])
+
+
+def test_single_column_api_matches_batch():
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=2)
+    g = Radtran(tb, pr)
+    rb = g.radiate_batch(cols)
+    isr, olr = g.TOA_fluxes(cols["T_surface"][1], cols["T"][:, 1], cols["P"][:, 1],
+                            cols["densities"][:, :, 1], cols["dz"][:, 1])
+    assert isr == rb["ISR"][1] and olr == rb["OLR"][1]
+    assert np.array_equal(g.f_total, rb["f_total"][:, 1])
+    assert g.wrk_ir.fup_a.shape == (cols["nz"] + 1, tb.nw_ir)
+
+
+def test_error_convention():
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=2)
+    g = Radtran(tb, pr)
+    bad = dict(cols)
+    bad["ng"] = cols["ng"] - 1
+    with pytest.raises(ClimaException, match="densities"):
+        g.radiate_batch(bad)
+    with pytest.raises(ClimaException, match="retained"):
+        Radtran(tb, pr).radiate_batch(cols, compute_opacity=False)
+
+
+def test_chunking_is_transparent(monkeypatch):
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=7)
+    r1 = Radtran(tb, pr).radiate_batch(cols, spectral=True)
+    monkeypatch.setenv("CLIMA_RT_CHUNK_COLS", "3")
+    r2 = Radtran(tb, pr).radiate_batch(cols, spectral=True)
+    for k in r1:
+        assert np.array_equal(r1[k], r2[k]), k
+
+
+def test_bit_reproducible():
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=4)
+    g = Radtran(tb, pr)
+    r1 = g.radiate_batch(cols, spectral=True)
+    r2 = g.radiate_batch(cols, spectral=True)
+    for k in r1:
+        assert np.array_equal(r1[k], r2[k]), k
+
+
+def test_scanon_full_size_parity():
+    """S-canon dimensions (nw=100, G=16, K=5, nz_r=202, Z=4), a few columns of the cfg2 sweep."""
+    tb = synth.make_tables()
+    pr = synth.default_params(tb)
+    cols = synth.make_columns(6, nz=100)
+    g = Radtran(tb, pr)
+    o = OracleRadtran(tb, pr, kind="parity")
+    rg = g.radiate_batch(cols, spectral=True)
+    ro = o.radiate_batch(cols, spectral=True, nthreads=8)
+    w = compare(rg, ro, verbose=True)
+    assert w["OLR"] < TOL and w["ISR"] < TOL
+
+
+def test_modern_earth_like_single_column():
+    """cfg1 shape: nz=200 undoubled, 8 zenith angles, albedo 0.15 (tests/test_radtran.f90:33-38)."""
+    tb = synth.make_tables()
+    pr = synth.default_params(tb, nzenith=8, albedo=0.15)
+    cols = synth.make_columns(1, nz=200, doubled=False, T_surf_range=(288.0, 288.0))
+    g = Radtran(tb, pr)
+    o = OracleRadtran(tb, pr, kind="parity")
+    compare(g.radiate_batch(cols, spectral=True), o.radiate_batch(cols, spectral=True), verbose=True)
