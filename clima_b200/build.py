@@ -41,7 +41,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(f"--- {s}\n{out}\n")
         if p.returncode != 0:
             raise RuntimeError(f"nvcc failed on {s}")
-    cmd = [NVCC, "-shared", "-o", LIB] + objs + ["-lcudart"]
+    cmd = [NVCC, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB] + objs + ["-lcudart"]
     subprocess.run(cmd, check=True)
     return LIB
 

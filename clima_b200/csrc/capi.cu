@@ -67,7 +67,7 @@ struct Handle {
   // introspection
   int64_t launches = 0;
   cudaEvent_t ev[6] = {};
-  double stage_ms[5] = {0, 0, 0, 0, 0};
+  double stage_ms[6] = {0, 0, 0, 0, 0, 0};
 };
 
 template <typename T>
@@ -345,6 +345,7 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
   ch.ncol = ncol;
   ch.nz = nz;
   record(h, 0);
+  if (!compute_opacity) record(h, 5);
   if (compute_opacity) {
     CK(cudaMemsetAsync(ch.status, 0, ncol * sizeof(int), h.st));
     rt_launch_prep(h.tb, ch, h.st);
@@ -354,6 +355,7 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     CK(cudaMemcpyAsync(ns.data(), ch.nslots, ncol * sizeof(int), cudaMemcpyDeviceToHost, h.st));
     CK(cudaStreamSynchronize(h.st));
     ch.nslot_cap = *std::max_element(ns.begin(), ns.end());
+    record(h, 5);
     rt_launch_optics_rorr(h.tb, ch, h.st);
     h.launches++;
   }
@@ -376,12 +378,15 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
 
 void accumulate_stage_ms(Handle &h) {
   CK(cudaEventSynchronize(h.ev[4]));
-  for (int i = 0; i < 4; i++) {
-    float ms = 0.f;
+  float ms = 0.f;
+  for (int i = 1; i < 4; i++) {
     CK(cudaEventElapsedTime(&ms, h.ev[i], h.ev[i + 1]));
     h.stage_ms[i] += ms;
   }
-  float ms = 0.f;
+  CK(cudaEventElapsedTime(&ms, h.ev[5], h.ev[1]));
+  h.stage_ms[0] += ms;  // the optics+RORR kernel alone
+  CK(cudaEventElapsedTime(&ms, h.ev[0], h.ev[5]));
+  h.stage_ms[5] += ms;  // prep kernel + slot-count readback
   CK(cudaEventElapsedTime(&ms, h.ev[0], h.ev[4]));
   h.stage_ms[4] += ms;
 }
@@ -431,7 +436,7 @@ void radiate_batch_impl(Handle &h, bool device, int ncol, int nz, int ng, int np
   const size_t L = nz + 1;
   const cudaMemcpyKind kin = device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
   const cudaMemcpyKind kout = device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
-  for (int i = 0; i < 5; i++) h.stage_ms[i] = 0.0;
+  for (int i = 0; i < 6; i++) h.stage_ms[i] = 0.0;
   for (int c0 = 0; c0 < ncol; c0 += C) {
     const int n = std::min(C, ncol - c0);
     DevChunk &ch = h.ch;
@@ -653,9 +658,13 @@ void clima_rt_get_launch_count(void *handle, int64_t *count) {
   *count = static_cast<Handle *>(handle)->launches;
 }
 
-void clima_rt_get_stage_ms(void *handle, double *ms5) {
+void clima_rt_get_stream(void *handle, void **stream) {
+  *stream = (void *)static_cast<Handle *>(handle)->st;
+}
+
+void clima_rt_get_stage_ms(void *handle, double *ms6) {
   Handle &h = *static_cast<Handle *>(handle);
-  for (int i = 0; i < 5; i++) ms5[i] = h.stage_ms[i];
+  for (int i = 0; i < 6; i++) ms6[i] = h.stage_ms[i];
 }
 
 void clima_rt_measure_fp64_peak(const int32_t *device, double *tflops, char *err) {

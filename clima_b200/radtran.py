@@ -27,7 +27,7 @@ _lib = None
 EXPORTS = ["clima_rt_create", "clima_rt_destroy", "clima_rt_set_params",
            "clima_rt_set_custom_optical_properties", "clima_rt_unset_custom_optical_properties",
            "clima_rt_radiate_batch", "clima_rt_radiate_batch_device", "clima_rt_get_opacity",
-           "clima_rt_get_launch_count", "clima_rt_get_stage_ms", "clima_rt_measure_fp64_peak",
+           "clima_rt_get_launch_count", "clima_rt_get_stage_ms", "clima_rt_get_stream", "clima_rt_measure_fp64_peak",
            "clima_rt_version_get"]
 
 
@@ -151,6 +151,26 @@ class Radtran:
         _check(err)
         return arrs
 
+    def radiate_batch_device(self, ncol, nz, ng, npp, inp: Dict[str, int], outp: Dict[str, int],
+                             compute_solar=True, compute_opacity=True):
+        """Same call with raw DEVICE addresses (integers, e.g. `tensor.data_ptr()`): `inp` has
+        T_surface, T, P, densities, dz (and pdensities, radii); `outp` any member of
+        `clima_rt_out` (the seven integrated results are mandatory)."""
+        from ._abi import OUT_FIELDS, c_int32_p
+        o = COut()
+        for n in OUT_FIELDS:
+            setattr(o, n, C.cast(C.c_void_p(outp.get(n, 0) or None), c_double_p))
+        o.status = C.cast(C.c_void_p(outp.get("status", 0) or None), c_int32_p)
+
+        def dp(k):
+            return C.cast(C.c_void_p(inp.get(k, 0) or None), c_double_p)
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self._lib.clima_rt_radiate_batch_device(self._h, _i(ncol), _i(nz), _i(ng), _i(npp),
+                                                dp("T_surface"), dp("T"), dp("P"), dp("densities"),
+                                                dp("dz"), dp("pdensities"), dp("radii"),
+                                                _i(compute_solar), _i(compute_opacity), C.byref(o), err)
+        _check(err)
+
     def TOA_fluxes_batch(self, cols: Dict):
         r = self.radiate_batch(cols)
         return r["ISR"], r["OLR"]
@@ -204,7 +224,13 @@ class Radtran:
         self._lib.clima_rt_get_launch_count(self._h, C.byref(n))
         return n.value
 
+    def stream(self) -> int:
+        """cudaStream_t (as an integer) the handle launches on."""
+        p = C.c_void_p()
+        self._lib.clima_rt_get_stream(self._h, C.byref(p))
+        return p.value or 0
+
     def stage_ms(self):
-        a = (C.c_double * 5)()
+        a = (C.c_double * 6)()
         self._lib.clima_rt_get_stage_ms(self._h, a)
         return list(a)

@@ -1,0 +1,60 @@
+"""Algorithmic work of the RT hot path per column (restated in DESIGN.md).
+
+Counting convention: every +,-,*,/,sqrt,exp,compare counts 1; an FMA-able a*b+c counts 2; a
+comparison sort of n keys counts n*log2(n); work that is provably invariant is counted once
+(duplicated layers of the doubled grid, zenith-independent two-stream terms)."""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+
+
+@dataclass
+class Dims:
+    nw: int      # opacity-grid bins
+    L_ir: int    # IR channel bins
+    L_sol: int   # solar channel bins
+    G: int       # ngauss
+    K: int       # k-distribution gases
+    C: int       # CIA pairs
+    R: int       # Rayleigh species
+    X: int       # photolysis cross sections
+    Z: int       # zenith angles
+    nz: int      # RT layers (nz_r)
+    U: int       # unique layers
+    ng: int      # gases in the model
+
+
+def stage_ops(d: Dims) -> dict:
+    G2 = d.G * d.G
+    ops = {
+        "k_interp": d.nw * d.U * d.K * d.G * 11,
+        "continua": d.nw * d.U * (10 * d.C + 2 * d.R + 2 * d.X + 18) + d.nw * d.nz * 10 * d.G,
+        "rorr": d.nw * d.U * (d.K - 1) * (G2 * (5 + 2 * math.log2(d.G)) + 2 * d.G),
+        "ir": d.L_ir * d.G * d.nz * 88 + d.L_ir * (d.nz + 1) * 5,
+        "solar": d.L_sol * d.G * d.nz * (55 + 70 * d.Z),
+        "integrate": (4 * d.L_ir + 6 * d.L_sol * d.Z) * d.G * (d.nz + 1)
+                     + 4 * (d.L_ir + d.L_sol) * (d.nz + 1),
+    }
+    ops["total"] = sum(ops.values())
+    return ops
+
+
+def column_bytes(d: Dims) -> dict:
+    """Algorithmic HBM bytes per column: inputs once in, integrated flux profiles once out."""
+    inp = d.nz * (3 + d.ng) * 8 + 8
+    out = 5 * (d.nz + 1) * 8 + 16
+    return {"in": inp, "out": out, "total": inp + out}
+
+
+def dims_of(tables, params, cols) -> Dims:
+    import numpy as np
+    nz = cols["nz"]
+    # unique layers of column 0 (consecutive duplicates share a slot, csrc/prep.cu)
+    T, P, dz = cols["T"][:, 0], cols["P"][:, 0], cols["dz"][:, 0]
+    dens = cols["densities"][:, :, 0]
+    same = (T[1:] == T[:-1]) & (P[1:] == P[:-1]) & (dz[1:] == dz[:-1]) & np.all(dens[1:] == dens[:-1], axis=1)
+    U = int(nz - np.count_nonzero(same))
+    return Dims(nw=tables.nw, L_ir=tables.nw_ir, L_sol=tables.nw_sol, G=tables.ngauss, K=len(tables.k),
+                C=len(tables.cia), R=len(tables.ray_sp_ind), X=len(tables.pxs), Z=len(params.zenith_u),
+                nz=nz, U=U, ng=tables.ng)

@@ -216,9 +216,15 @@ void clima_rt_get_opacity(void *handle, const int32_t *icol, double *tau, double
 
 /* Introspection used by the bench: number of kernel launches issued by the handle so far, the
    per-stage device time (ms, CUDA events on the handle's stream) of the last batch call
-   [0]=optics+RORR [1]=two-stream IR [2]=two-stream solar [3]=integration [4]=whole call. */
+   [0]=optics+RORR kernel [1]=Planck + two-stream IR [2]=two-stream solar [3]=integration
+   [4]=whole call (kernels only, without the host<->device copies) [5]=prep kernel. */
 void clima_rt_get_launch_count(void *handle, int64_t *count);
-void clima_rt_get_stage_ms(void *handle, double *ms5);
+void clima_rt_get_stage_ms(void *handle, double *ms6);
+
+/* The CUDA stream (a cudaStream_t, returned as an opaque pointer) every kernel of the handle is
+   launched on, so that a caller can bracket calls with its own CUDA events on the launching
+   stream or order its own work (e.g. an NCCL all-gather of the flux profiles) after them. */
+void clima_rt_get_stream(void *handle, void **stream);
 
 /* Measured FP64 issue roof of device `*device`: runs a dependent-chain-free DFMA kernel and
    returns TFLOP/s (FMA = 2 flops).  Used as the roofline denominator. */
