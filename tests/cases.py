@@ -41,7 +41,7 @@ FLUX_KEYS = ["fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol"]
 SPEC_KEYS = ["fup_a_ir", "fdn_a_ir", "tau_band_ir", "fup_a_sol", "fdn_a_sol", "amean_sol", "tau_band_sol"]
 
 
-def compare(r_gpu, r_ref, spectral=True, tol=TOL, verbose=False):
+def compare(r_gpu, r_ref, spectral=True, tol=TOL, verbose=False, elem_tol=None):
     worst = {}
     for k in FLUX_KEYS + (SPEC_KEYS if spectral else []):
         worst[k] = rel_err(r_gpu[k], r_ref[k])
@@ -55,6 +55,7 @@ def compare(r_gpu, r_ref, spectral=True, tol=TOL, verbose=False):
     if verbose:
         for k, v in worst.items():
             print(f"  {k:16s} {v:.3e}")
-    bad = {k: v for k, v in worst.items() if not (v <= tol)}
+    etol = tol if elem_tol is None else elem_tol
+    bad = {k: v for k, v in worst.items() if not (v <= (etol if k.endswith('_elem') else tol))}
     assert not bad, f"parity failure (tol {tol}): {bad}"
     return worst
