@@ -311,6 +311,7 @@ def run_ours(args):
             "stage_ms_per_step": {"optics_rorr": stage[0], "planck_ir": stage[1], "solar": stage[2],
                                   "integrate": stage[3], "kernels_total": stage[4], "prep": stage[5]},
             "wall_ms_per_step": 1e3 * t_wall / args.steps,
+            "rorr": dict(zip(("units", "exact_kernel_units", "worklist_overflows"), rt.rorr_stats())),
             "roofline": {
                 "kernel": "optics_rorr_kernel<16>", "bound": "fp64", "achieved": achieved,
                 "peak": fp64_tf, "unit": "TFLOP/s", "frac": achieved / fp64_tf,

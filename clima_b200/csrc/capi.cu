@@ -58,7 +58,13 @@ struct Handle {
   DevFlux fx{};
   double *d_tmp = nullptr;  // tau_band / get_opacity staging
   size_t tmp_bytes = 0;
-  int ts_blocks = 0;
+  int ts_blocks = 0, ts_blocks_sol = 0;
+  // RORR exact-path worklist (units the fast kernel could not certify)
+  int *d_worklist = nullptr, *d_wcount = nullptr;
+  int wcap = 0;
+  int *h_wcount = nullptr;  // pinned
+  int rorr_exact_only = 0;  // CLIMA_RT_RORR=exact
+  int64_t rorr_units = 0, rorr_exact_units = 0, rorr_overflows = 0;
 
   // retained state
   int retained_opacity_ncol = 0, retained_nz = 0;
@@ -233,10 +239,13 @@ void ensure_chunk(Handle &h, int ncol, int nz) {
   free_chunk(h);
   CK(cudaMemGetInfo(&free_b, &total_b));
   const int itemsz = rt_twostream_items_per_layer();
+  int occ_ir = 1, occ_sol = 1;
+  rt_twostream_occupancy(h.tb.G, h.pr.nzen, &occ_ir, &occ_sol);
   const char *bps = std::getenv("CLIMA_RT_TS_BLOCKS_PER_SM");
-  const int blocks_per_sm = bps ? std::max(1, atoi(bps)) : 4;
-  h.ts_blocks = h.num_sms * blocks_per_sm;
-  const size_t nres = (size_t)h.ts_blocks * rt_twostream_block_threads();
+  if (bps) occ_ir = occ_sol = std::max(1, atoi(bps));
+  h.ts_blocks = h.num_sms * occ_ir;
+  h.ts_blocks_sol = h.num_sms * occ_sol;
+  const size_t nres = (size_t)std::max(h.ts_blocks, h.ts_blocks_sol) * rt_twostream_block_threads();
   const size_t scratch_b = nres * nz * itemsz * 8;
   const size_t pcb = per_col_bytes(h, nz);
   const double budget = 0.7 * (double)free_b - (double)scratch_b;
@@ -269,6 +278,13 @@ void ensure_chunk(Handle &h, int ncol, int nz) {
   ch.gt = calloc_dev<double>(h, (size_t)C * tb.nw * nz);
   ch.tband = calloc_dev<double>(h, (size_t)C * tb.nw * nz);
   ch.status = calloc_dev<int>(h, C);
+  {
+    const long long units = (long long)C * tb.nw * nz;
+    if (units >= (1ll << 31)) throw CudaError{"chunk too large: lower CLIMA_RT_CHUNK_COLS"};
+    h.wcap = (int)std::min<long long>(units, std::max<long long>(65536, units / 8));
+    h.d_worklist = calloc_dev<int>(h, h.wcap);
+    h.d_wcount = calloc_dev<int>(h, 1);
+  }
   DevFlux &fx = h.fx;
   fx.fup_a_ir = calloc_dev<double>(h, (size_t)C * h.nw_ir * L);
   fx.fdn_a_ir = calloc_dev<double>(h, (size_t)C * h.nw_ir * L);
@@ -340,7 +356,7 @@ void record(Handle &h, int i) { CK(cudaEventRecord(h.ev[i], h.st)); }
 
 // Runs one chunk whose inputs are already on the device (h.ch input pointers set).
 void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opacity,
-               bool opacity_bcast, bool solar_bcast) {
+               bool opacity_bcast, bool solar_bcast, bool force_exact = false) {
   DevChunk &ch = h.ch;
   ch.ncol = ncol;
   ch.nz = nz;
@@ -356,8 +372,15 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     CK(cudaStreamSynchronize(h.st));
     ch.nslot_cap = *std::max_element(ns.begin(), ns.end());
     record(h, 5);
-    rt_launch_optics_rorr(h.tb, ch, h.st);
-    h.launches++;
+    const int exact = (h.rorr_exact_only || force_exact) ? 1 : 0;
+    rt_launch_optics_rorr(h.tb, ch, h.d_worklist, h.d_wcount, h.wcap, exact, h.st);
+    const bool two = !exact && h.tb.rows_sorted;
+    h.launches += two ? 2 : 1;
+    *h.h_wcount = 0;
+    if (two)
+      CK(cudaMemcpyAsync(h.h_wcount, h.d_wcount, sizeof(int), cudaMemcpyDeviceToHost, h.st));
+    h.rorr_units += (long long)ncol * h.tb.nw * ch.nslot_cap;
+    if (!two) h.rorr_exact_units += (long long)ncol * h.tb.nw * ch.nslot_cap;
   }
   record(h, 1);
   rt_launch_planck(h.tb, ch, h.fx, h.st);
@@ -365,7 +388,7 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
   h.launches += 2;
   record(h, 2);
   if (compute_solar) {
-    rt_launch_twostream_solar(h.tb, h.pr, ch, h.fx, opacity_bcast ? 1 : 0, h.ts_blocks, h.st);
+    rt_launch_twostream_solar(h.tb, h.pr, ch, h.fx, opacity_bcast ? 1 : 0, h.ts_blocks_sol, h.st);
     int z = h.pr.nzen;
     while (z > 0) { h.launches++; z -= (z >= 4 ? 4 : (z >= 2 ? 2 : 1)); }
   }
@@ -464,7 +487,8 @@ void radiate_batch_impl(Handle &h, bool device, int ncol, int nz, int ng, int np
       ch.pdens = in.pd ? h.d_pd : nullptr;
       ch.radii = in.rd ? h.d_rd : nullptr;
     }
-    run_chunk(h, n, nz, compute_solar, compute_opacity, opacity_bcast, solar_bcast);
+    for (int attempt = 0; attempt < 2; attempt++) {
+    run_chunk(h, n, nz, compute_solar, compute_opacity, opacity_bcast, solar_bcast, attempt == 1);
     const DevFlux &fx = h.fx;
     auto cp = [&](double *dst, const double *src, size_t per_col) {
       if (dst) CK(cudaMemcpyAsync(dst + (size_t)c0 * per_col, src, (size_t)n * per_col * 8, kout, h.st));
@@ -495,6 +519,14 @@ void radiate_batch_impl(Handle &h, bool device, int ncol, int nz, int ng, int np
       CK(cudaMemcpyAsync(out->status + c0, ch.status, n * sizeof(int), kout, h.st));
     CK(cudaStreamSynchronize(h.st));
     accumulate_stage_ms(h);
+    // more uncertified RORR units than the worklist holds: redo the chunk with the exact kernel
+    if (compute_opacity && attempt == 0 && *h.h_wcount > h.wcap) {
+      h.rorr_overflows++;
+      continue;
+    }
+    if (compute_opacity) h.rorr_exact_units += *h.h_wcount;
+    break;
+    }
     if (compute_opacity) {
       h.retained_opacity_ncol = (ncol <= C) ? ncol : 0;
       h.retained_nz = nz;
@@ -536,6 +568,12 @@ void clima_rt_create(const clima_rt_tables *tables, const clima_rt_params *param
     h->num_sms = prop.multiProcessorCount;
     CK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
     for (auto &e : h->ev) CK(cudaEventCreate(&e));
+    CK(cudaMallocHost(&h->h_wcount, sizeof(int)));
+    *h->h_wcount = 0;
+    {
+      const char *m = std::getenv("CLIMA_RT_RORR");
+      h->rorr_exact_only = (m && std::string(m) == "exact") ? 1 : 0;
+    }
     build_tables(*h, tables);
     upload_params(*h, params);
     *handle = h;
@@ -554,6 +592,7 @@ void clima_rt_destroy(void *handle) {
   for (auto &p : h->d_custom) if (p) cudaFree(p);
   for (auto &e : h->ev) if (e) cudaEventDestroy(e);
   if (h->st) cudaStreamDestroy(h->st);
+  if (h->h_wcount) cudaFreeHost(h->h_wcount);
   delete h;
 }
 
@@ -656,6 +695,13 @@ void clima_rt_get_opacity(void *handle, const int32_t *icol, double *tau, double
 
 void clima_rt_get_launch_count(void *handle, int64_t *count) {
   *count = static_cast<Handle *>(handle)->launches;
+}
+
+void clima_rt_get_rorr_stats(void *handle, int64_t *stats3) {
+  Handle &h = *static_cast<Handle *>(handle);
+  stats3[0] = h.rorr_units;
+  stats3[1] = h.rorr_exact_units;
+  stats3[2] = h.rorr_overflows;
 }
 
 void clima_rt_get_stream(void *handle, void **stream) {

@@ -50,6 +50,17 @@ __device__ __forceinline__ void ce(double &a, double &b) {
   b = hi;
 }
 
+// exact tau_xy of sorted element `idx` + the non-decreasing check of the fast kernel
+__device__ __forceinline__ double fa_tv(const double *sa, const double *sb, const unsigned idx,
+                                        const int LOGP, const int P, double &prev, double &first,
+                                        bool &ok, const int r) {
+  const double tv = __dadd_rn(sa[idx >> LOGP], sb[idx & (P - 1)]);
+  ok = ok && (tv >= prev);
+  prev = tv;
+  if (r == 0) first = tv;
+  return tv;
+}
+
 // Bitonic sort network over positions pos = ul*32 + r, all runs ascending ("flip" variant: the first
 // step of stage k pairs pos with pos ^ (2^k-1), the remaining steps pos with pos ^ d).  Stages
 // below `kfirst` are skipped (rows pre-sorted).
@@ -97,55 +108,25 @@ __device__ __forceinline__ void bitonic_network(double (&x)[32], const int ul, c
   }
 }
 
-template <int P>
-__global__ void __launch_bounds__(128)
-optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevChunk ch) {
-  using C = Cfg<P>;
-  constexpr int LPU = C::LPU, UPB = C::UPB, LOGP = C::LOGP;
-  constexpr int AST = P + 1;              // padded strides: units of one warp hit distinct banks
-  constexpr int PST = P * LPU + 1;
-  __shared__ double s_w[P];               // wbin, zero padded
-  __shared__ double s_E[P + 1];           // wbin_e
-  __shared__ double s_ib[P];              // 1/(wbin_e(g+1)-wbin_e(g))
-  __shared__ double s_a[UPB * AST];       // running mixture tau_k(g)
-  __shared__ double s_b[UPB * AST];       // new gas k*col (g)
-  __shared__ double s_part[UPB * PST];    // rebin partials [g][lane]
+// ---------------------------------------------------------------------------------------------
+// Pieces shared by the fast and the exact kernel.
+// ---------------------------------------------------------------------------------------------
+struct Continua {
+  double tausg, taua, taup, tausp, tauc, tausc, gt;
+};
 
-  const int G = tb.G, nw = tb.nw, nz = ch.nz, ng = tb.ng;
-  for (int i = threadIdx.x; i < P; i += blockDim.x) {
-    s_w[i] = i < G ? tb.wbin[i] : 0.0;
-    s_ib[i] = i < G ? tb.inv_dw[i] : 0.0;
-  }
-  for (int i = threadIdx.x; i < P + 1; i += blockDim.x) s_E[i] = tb.wbin_e[i < G ? i : G];
-  __syncthreads();
-
-  const int lane = threadIdx.x & 31;
-  const int ul = lane & (LPU - 1);     // lane within unit
-  const int ub = threadIdx.x / LPU;    // unit within block
-  const long long uid = (long long)blockIdx.x * UPB + ub;
-  const int cap = ch.nslot_cap;
-  int slot = (int)(uid % cap);
-  int l = (int)((uid / cap) % nw);
-  long long cl = uid / ((long long)cap * nw);
-  bool active = cl < ch.ncol;
-  int c = active ? (int)cl : ch.ncol - 1;
-  const int nsl = ch.nslots[c];
-  if (slot >= nsl) {
-    active = false;
-    slot = nsl - 1;
-  }
-  if (__all_sync(0xffffffffu, !active)) return;
-
-  double *sa = s_a + ub * AST, *sb = s_b + ub * AST, *sp = s_part + ub * PST;
-  const int k = ch.layer_of_slot[(size_t)c * nz + slot];  // ground-first layer index
+// Rayleigh, CIA, photolysis, water continuum, particles, custom opacity and the asymmetry
+// parameter of one (column c, bin l, slot) -- A.3, clima_radtran_types.f90:664-757.
+__device__ __forceinline__ Continua rt_continua(const DevTables &tb, const DevChunk &ch, const int c,
+                                                const int l, const int slot, const int k) {
+  const int nw = tb.nw, nz = ch.nz, ng = tb.ng;
   const double *dens = ch.dens + (size_t)c * nz * ng + k;  // dens[i*nz]
   const double dzk = ch.dz[(size_t)c * nz + k];
   const int nbr = rt_nbr(tb);
   const int *ib = ch.ibr + ((size_t)c * nz + slot) * nbr;
   const double *qb = ch.qbr + ((size_t)c * nz + slot) * nbr;
   int rbase = 2 * tb.nk;
-
-  // ------------------------------------------------------------------ 1. continua (A.3)
+  Continua o;
   // Rayleigh (:686-693)
   double tausg = 0.0;
   for (int i = 0; i < tb.nray; i++) {
@@ -194,10 +175,10 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
       const DevPart &p = tb.part[i];
       const int ir = ib[rbase + i];
       const double q1 = qb[rbase + i], p1 = 1.0 - q1;
-      const size_t o = (size_t)l * p.nr + ir;
-      const double w0p = p1 * p.w0[o] + q1 * p.w0[o + 1];
-      const double qext = p1 * p.qext[o] + q1 * p.qext[o + 1];
-      gtp[i] = p1 * p.gt[o] + q1 * p.gt[o + 1];
+      const size_t o2 = (size_t)l * p.nr + ir;
+      const double w0p = p1 * p.w0[o2] + q1 * p.w0[o2 + 1];
+      const double qext = p1 * p.qext[o2] + q1 * p.qext[o2 + 1];
+      gtp[i] = p1 * p.gt[o2] + q1 * p.gt[o2 + 1];
       const double r = rad[(size_t)(p.p_ind - 1) * nz];
       const double taup_1 = qext * RT_PI * (r * r) * pdn[(size_t)(p.p_ind - 1) * nz] * dzk;
       taup = taup + taup_1;
@@ -211,10 +192,10 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   if (tb.has_custom) {
     const int ip = ib[rbase];
     const double q1 = qb[rbase], p1 = 1.0 - q1;
-    const size_t o = (size_t)l * tb.custom_nP + ip;
-    tauc = (p1 * tb.c_dtau[o] + q1 * tb.c_dtau[o + 1]) * dzk;
-    w0c = p1 * tb.c_w0[o] + q1 * tb.c_w0[o + 1];
-    g0c = p1 * tb.c_g0[o] + q1 * tb.c_g0[o + 1];
+    const size_t o2 = (size_t)l * tb.custom_nP + ip;
+    tauc = (p1 * tb.c_dtau[o2] + q1 * tb.c_dtau[o2 + 1]) * dzk;
+    w0c = p1 * tb.c_w0[o2] + q1 * tb.c_w0[o2 + 1];
+    g0c = p1 * tb.c_g0[o2] + q1 * tb.c_g0[o2 + 1];
   }
   const double tausc = w0c * tauc;
   // asymmetry (:746-757)
@@ -225,31 +206,188 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     gt = gt + g0c * tausc / den;
     gt = fmin(gt, RT_MAX_GT);
   }
+  o.tausg = tausg; o.taua = taua; o.taup = taup; o.tausp = tausp; o.tauc = tauc; o.tausc = tausc;
+  o.gt = gt;
+  return o;
+}
 
-  // ------------------------------------------------------------------ 2+3+4. k-gases and RORR
-  const int kfirst = tb.rows_sorted ? LOGP + 1 : 1;
-  for (int jj = 0; jj < tb.nk; jj++) {
-    const DevK &kt = tb.k[jj];
-    const int ix = ib[2 * jj], iy = ib[2 * jj + 1];
-    const double q1 = qb[2 * jj], q2 = qb[2 * jj + 1];
-    const double p1 = 1.0 - q1, p2 = 1.0 - q2;
-    const double col = dens[(size_t)(kt.sp - 1) * nz] * dzk;  // cols(j,sp) :607
-    const double *f = kt.log10k + (size_t)G * (ix + (size_t)kt.np * (iy + (size_t)kt.nt * l));
-    const size_t sy = (size_t)G * kt.np;
-    double *dst = jj == 0 ? sa : sb;
+// k(g) * column of k-gas jj for the unit's layer: bilinear log10k(P,T) interpolation, lane per
+// g-point (A.2, :649-662 + interp_2d, linear_interpolation_module.F90:322-335), into dst[0..P).
+template <int P>
+__device__ __forceinline__ void rt_kgas(const DevTables &tb, const DevChunk &ch, const int c,
+                                        const int l, const int slot, const int k, const int jj,
+                                        const int ul, double *dst) {
+  using C = Cfg<P>;
+  const int G = tb.G, nz = ch.nz;
+  const int nbr = rt_nbr(tb);
+  const int *ib = ch.ibr + ((size_t)c * nz + slot) * nbr;
+  const double *qb = ch.qbr + ((size_t)c * nz + slot) * nbr;
+  const DevK &kt = tb.k[jj];
+  const int ix = ib[2 * jj], iy = ib[2 * jj + 1];
+  const double q1 = qb[2 * jj], q2 = qb[2 * jj + 1];
+  const double p1 = 1.0 - q1, p2 = 1.0 - q2;
+  const double col = ch.dens[(size_t)c * nz * tb.ng + k + (size_t)(kt.sp - 1) * nz] *
+                     ch.dz[(size_t)c * nz + k];  // cols(j,sp) :607
+  const double *f = kt.log10k + (size_t)G * (ix + (size_t)kt.np * (iy + (size_t)kt.nt * l));
+  const size_t sy = (size_t)G * kt.np;
 #pragma unroll
-    for (int t = 0; t < C::GPL; t++) {
-      const int g = ul + LPU * t;
-      if (g < G) {
-        // interp_2d, linear_interpolation_module.F90:322-335
-        const double fx1 = p1 * f[g] + q1 * f[g + G];
-        const double fx2 = p1 * f[g + sy] + q1 * f[g + sy + G];
-        const double v = p2 * fx1 + q2 * fx2;
-        dst[g] = rt_ten2power(v) * col;  // :660, :816-819 / :828
-      } else {
-        dst[g] = 0.0;
+  for (int t = 0; t < C::GPL; t++) {
+    const int g = ul + C::LPU * t;
+    if (g < G) {
+      const double fx1 = p1 * f[g] + q1 * f[g + G];
+      const double fx2 = p1 * f[g + sy] + q1 * f[g + sy + G];
+      const double v = p2 * fx1 + q2 * fx2;
+      dst[g] = rt_ten2power(v) * col;  // :660, :816-819 / :828
+    } else {
+      dst[g] = 0.0;
+    }
+  }
+}
+
+// weights_to_bins + rebin (:843-849) of the unit's sorted sequence.  Element m of the sequence is
+// (tau tv, weight w) delivered by `elem(r, tv, w)` for the lane's positions r = 0..31 in sorted
+// order; lanes of the unit hold consecutive runs.  The new bin values land in sa[0..P).
+// Deterministic: per-lane partials in shared memory, summed in lane order.
+#define RT_REBIN_PASS(ELEM_W, ELEM_TV)                                                          \
+  double tot = 0.0;                                                                              \
+  _Pragma("unroll") for (int r = 0; r < 32; r++) { tot = __dadd_rn(tot, (ELEM_W)); }                             \
+  double off = tot;                                                                              \
+  _Pragma("unroll") for (int d = 1; d < LPU; d <<= 1) {                                          \
+    const double t_ = __shfl_up_sync(0xffffffffu, off, d, LPU);                                  \
+    if (ul >= d) off = __dadd_rn(off, t_);                                                       \
+  }                                                                                              \
+  off = __dsub_rn(off, tot);                                                                     \
+  for (int g_ = 0; g_ < G; g_++) sp[g_ * LPU + ul] = 0.0;                                        \
+  int g = 0;                                                                                     \
+  _Pragma("unroll") for (int s_ = P / 2; s_ > 0; s_ >>= 1)                                       \
+    if (g + s_ <= G - 1 && s_E[g + s_] <= off) g += s_;                                          \
+  double n0 = s_E[g], n1 = s_E[g + 1], ibw = s_ib[g];                                            \
+  double acc = 0.0, o0 = off;                                                                    \
+  _Pragma("unroll") for (int r = 0; r < 32; r++) {                                               \
+    const double w = (ELEM_W);                                                                   \
+    if (w > 0.0) {                                                                               \
+      const double tv = (ELEM_TV);                                                               \
+      const double o1 = __dadd_rn(o0, w);                                                        \
+      double lo = o0;                                                                            \
+      while (o1 > n1 && g < G - 1) { /* old bin crosses the right edge of new bin g */           \
+        acc = __dadd_rn(acc, (lo <= n0) ? tv : __dmul_rn(__dmul_rn(__dsub_rn(n1, lo), ibw), tv)); \
+        sp[g * LPU + ul] = acc;                                                                  \
+        acc = 0.0;                                                                               \
+        g++;                                                                                     \
+        n0 = n1;                                                                                 \
+        lo = n1;                                                                                 \
+        n1 = s_E[g + 1];                                                                         \
+        ibw = s_ib[g];                                                                           \
+      }                                                                                          \
+      const double hi = fmin(o1, n1);                                                            \
+      if (hi > lo)                                                                               \
+        acc = __dadd_rn(acc, (lo <= n0 && hi >= n1) ? tv                                         \
+                                                    : __dmul_rn(__dmul_rn(__dsub_rn(hi, lo), ibw), tv)); \
+      o0 = o1;                                                                                   \
+    }                                                                                            \
+  }                                                                                              \
+  sp[g * LPU + ul] = acc;                                                                        \
+  __syncwarp();                                                                                  \
+  _Pragma("unroll") for (int t = 0; t < C::GPL; t++) {                                           \
+    const int gg = ul + LPU * t;                                                                 \
+    double s_ = 0.0;                                                                             \
+    if (gg < G) {                                                                                \
+      _Pragma("unroll") for (int q = 0; q < LPU; q++) s_ = __dadd_rn(s_, sp[gg * LPU + q]);      \
+    }                                                                                            \
+    sa[gg] = s_;                                                                                 \
+  }                                                                                              \
+  __syncwarp();
+
+// total tau, w0 clamp, band tau, asymmetry of the unit (:856-886) -> HBM (slot-indexed layout).
+template <int P>
+__device__ __forceinline__ void rt_store_unit(const DevTables &tb, const DevChunk &ch, const Continua &q,
+                                              const int c, const int l, const int slot, const int ul,
+                                              const bool active, const double *sa, double *sb,
+                                              const double *s_w) {
+  using C = Cfg<P>;
+  const int G = tb.G;
+  const size_t obase = (((size_t)c * tb.nw + l) * ch.nslot_cap + slot);
+#pragma unroll
+  for (int t = 0; t < C::GPL; t++) {
+    const int gg = ul + C::LPU * t;
+    if (gg < G) {
+      const double tau = __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(q.tausg, q.taua), q.taup), sa[gg]), q.tauc);
+      double w0 = 0.0;
+      if (!(tau <= RT_TAU_MIN)) w0 = fmin(RT_MAX_W0, (q.tausg + q.tausp + q.tausc) / tau);
+      sb[gg] = tau;
+      if (active) {
+        ch.tau[obase * G + gg] = tau;
+        ch.w0[obase * G + gg] = w0;
       }
     }
+  }
+  __syncwarp();
+  if (ul == 0 && active) {
+    double tbnd = 0.0;
+    for (int gg = 0; gg < G; gg++) tbnd = __dadd_rn(tbnd, __dmul_rn(sb[gg], s_w[gg]));
+    ch.tband[obase] = tbnd;
+    ch.gt[obase] = q.gt;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// EXACT kernel: full 64-bit (value, index) bitonic network.  Used for every unit when the tables
+// are not ascending in g, and otherwise only for the units the fast kernel could not certify
+// (`worklist`, filled by the fast kernel).
+// ---------------------------------------------------------------------------------------------
+template <int P>
+__global__ void __launch_bounds__(128)
+optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevChunk ch,
+                   const int *__restrict__ worklist, const int *__restrict__ wcount, const int wcap) {
+  using C = Cfg<P>;
+  constexpr int LPU = C::LPU, UPB = C::UPB, LOGP = C::LOGP;
+  constexpr int AST = P + 1;              // padded strides: units of one warp hit distinct banks
+  constexpr int PST = P * LPU + 1;
+  __shared__ double s_w[P];               // wbin, zero padded
+  __shared__ double s_E[P + 1];           // wbin_e
+  __shared__ double s_ib[P];              // 1/(wbin_e(g+1)-wbin_e(g))
+  __shared__ double s_a[UPB * AST];       // running mixture tau_k(g)
+  __shared__ double s_b[UPB * AST];       // new gas k*col (g)
+  __shared__ double s_part[UPB * PST];    // rebin partials [g][lane]
+
+  const int G = tb.G, nw = tb.nw, nz = ch.nz;
+  for (int i = threadIdx.x; i < P; i += blockDim.x) {
+    s_w[i] = i < G ? tb.wbin[i] : 0.0;
+    s_ib[i] = i < G ? tb.inv_dw[i] : 0.0;
+  }
+  for (int i = threadIdx.x; i < P + 1; i += blockDim.x) s_E[i] = tb.wbin_e[i < G ? i : G];
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31;
+  const int ul = lane & (LPU - 1);     // lane within unit
+  const int ub = threadIdx.x / LPU;    // unit within block
+  long long uid = (long long)blockIdx.x * UPB + ub;
+  const int cap = ch.nslot_cap;
+  bool active = true;
+  if (worklist) {
+    int n = *wcount;
+    if (n > wcap) n = wcap;
+    if (uid < n) uid = worklist[uid]; else { active = false; uid = 0; }
+  }
+  int slot = (int)(uid % cap);
+  int l = (int)((uid / cap) % nw);
+  long long cl = uid / ((long long)cap * nw);
+  if (cl >= ch.ncol) active = false;
+  int c = cl < ch.ncol ? (int)cl : ch.ncol - 1;
+  const int nsl = ch.nslots[c];
+  if (slot >= nsl) {
+    active = false;
+    slot = nsl - 1;
+  }
+  if (__all_sync(0xffffffffu, !active)) return;
+
+  double *sa = s_a + ub * AST, *sb = s_b + ub * AST, *sp = s_part + ub * PST;
+  const int k = ch.layer_of_slot[(size_t)c * nz + slot];  // ground-first layer index
+  const Continua q = rt_continua(tb, ch, c, l, slot, k);
+
+  const int kfirst = tb.rows_sorted ? LOGP + 1 : 1;
+  for (int jj = 0; jj < tb.nk; jj++) {
+    rt_kgas<P>(tb, ch, c, l, slot, k, jj, ul, jj == 0 ? sa : sb);
     __syncwarp();
     if (jj == 0) continue;
 
@@ -267,89 +405,174 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     }
     bitonic_network<P>(x, ul, kfirst);
 
-    // ---- weights_to_bins + rebin (:843-849)
-    // lane total weight
-    double tot = 0.0;
-#pragma unroll
-    for (int r = 0; r < 32; r++) {
-      const unsigned idx = (unsigned)((unsigned long long)__double_as_longlong(x[r]) & C::IDXMASK);
-      tot += s_w[idx >> LOGP] * s_w[idx & (P - 1)];
-    }
-    double off = tot;  // inclusive scan over the unit's lanes -> exclusive
-#pragma unroll
-    for (int d = 1; d < LPU; d <<= 1) {
-      const double t = __shfl_up_sync(0xffffffffu, off, d, LPU);
-      if (ul >= d) off += t;
-    }
-    off -= tot;
-    for (int g = 0; g < G; g++) sp[g * LPU + ul] = 0.0;
-    int g = 0;
-#pragma unroll
-    for (int s = P / 2; s > 0; s >>= 1)
-      if (g + s <= G - 1 && s_E[g + s] <= off) g += s;
-    double n0 = s_E[g], n1 = s_E[g + 1], ibw = s_ib[g];
-    double acc = 0.0, o0 = off;
-#pragma unroll
-    for (int r = 0; r < 32; r++) {
-      const unsigned idx = (unsigned)((unsigned long long)__double_as_longlong(x[r]) & C::IDXMASK);
-      const int i = idx >> LOGP, j = idx & (P - 1);
-      const double w = s_w[i] * s_w[j];  // wxy, clima_radtran_types_create.f90:216-222
-      if (w > 0.0) {
-        const double tv = sa[i] + sb[j];  // exact tau_xy of the sorted element
-        const double o1 = o0 + w;
-        double lo = o0;
-        while (o1 > n1 && g < G - 1) {  // old bin crosses the right edge of new bin g
-          acc += (lo <= n0) ? tv : ((n1 - lo) * ibw) * tv;
-          sp[g * LPU + ul] = acc;
-          acc = 0.0;
-          g++;
-          n0 = n1;
-          lo = n1;
-          n1 = s_E[g + 1];
-          ibw = s_ib[g];
-        }
-        const double hi = fmin(o1, n1);
-        if (hi > lo) acc += (lo <= n0 && hi >= n1) ? tv : ((hi - lo) * ibw) * tv;
-        o0 = o1;
-      }
-    }
-    sp[g * LPU + ul] = acc;
-    __syncwarp();
-#pragma unroll
-    for (int t = 0; t < C::GPL; t++) {
-      const int gg = ul + LPU * t;
-      double s = 0.0;
-      if (gg < G) {
-#pragma unroll
-        for (int q = 0; q < LPU; q++) s += sp[gg * LPU + q];
-      }
-      sa[gg] = s;
-    }
-    __syncwarp();
+#define EX_IDX(r) ((unsigned)((unsigned long long)__double_as_longlong(x[r]) & C::IDXMASK))
+    RT_REBIN_PASS(__dmul_rn(s_w[EX_IDX(r) >> LOGP], s_w[EX_IDX(r) & (P - 1)]),
+                  __dadd_rn(sa[EX_IDX(r) >> LOGP], sb[EX_IDX(r) & (P - 1)]))
+#undef EX_IDX
   }
+  rt_store_unit<P>(tb, ch, q, c, l, slot, ul, active, sa, sb, s_w);
+}
 
-  // ------------------------------------------------------------------ 5. totals (:856-886)
-  const size_t obase = (((size_t)c * nw + l) * cap + slot);
+// ---------------------------------------------------------------------------------------------
+// FAST kernel.  Same work unit and lane mapping, but the G x G sums are ranked with 32-bit keys:
+//   key = [ f : 32-2*log2(P) bits ][ element index pos : 2*log2(P) bits ],
+//   f   = (bits(tau_xy) - bits(min tau_xy)) >> shift,  shift chosen so that f of the largest sum
+//         (a_G + b_G; a and b ascend) still fits.
+// f is a monotone, order-preserving quantisation of tau_xy (IEEE-754 bit patterns of non-negative
+// doubles order like integers), so one VIMNMX.U32 orders (f, index) lexicographically and a
+// compare-exchange costs 2 instructions instead of DSETP + 4 selects, with half the registers.
+// Quantisation can only mis-order sums whose f collide; the rebin pass recomputes every EXACT
+// tau_xy from its (i,j) anyway and checks that the sequence it walks is non-decreasing.  Elements
+// with equal f sit in index order, which is the stable order of `mrgrnk` whenever they are exactly
+// equal or come from the same row; if any unit sees a decrease it is appended to `worklist` and
+// redone by the exact kernel.  The fast path therefore returns the same permutation as the
+// reference's stable merge sort or hands the unit over -- it never silently differs.
+// ---------------------------------------------------------------------------------------------
+template <int P>
+__device__ __forceinline__ void bitonic_network_u32(unsigned (&x)[32], const int ul) {
+  using C = Cfg<P>;
 #pragma unroll
-  for (int t = 0; t < C::GPL; t++) {
-    const int gg = ul + LPU * t;
-    if (gg < G) {
-      const double tau = tausg + taua + taup + sa[gg] + tauc;
-      double w0 = 0.0;
-      if (!(tau <= RT_TAU_MIN)) w0 = fmin(RT_MAX_W0, (tausg + tausp + tausc) / tau);
-      sb[gg] = tau;
-      if (active) {
-        ch.tau[obase * G + gg] = tau;
-        ch.w0[obase * G + gg] = w0;
+  for (int k = C::LOGP + 1; k <= 2 * C::LOGP; k++) {
+    // ---- flip step
+    if (k <= 5) {
+      const int m = (1 << k) - 1;
+#pragma unroll
+      for (int r = 0; r < 32; r++)
+        if ((r & (1 << (k - 1))) == 0) {
+          const unsigned lo = min(x[r], x[r ^ m]), hi = max(x[r], x[r ^ m]);
+          x[r] = lo;
+          x[r ^ m] = hi;
+        }
+    } else {
+      const int lm = ((1 << k) - 1) >> 5;
+      const bool keepmin = (ul & ((lm + 1) >> 1)) == 0;
+#pragma unroll
+      for (int r = 0; r < 16; r++) {
+        const unsigned y1 = __shfl_xor_sync(0xffffffffu, x[r ^ 31], lm);
+        const unsigned y2 = __shfl_xor_sync(0xffffffffu, x[r], lm);
+        x[r] = keepmin ? min(x[r], y1) : max(x[r], y1);
+        x[r ^ 31] = keepmin ? min(x[r ^ 31], y2) : max(x[r ^ 31], y2);
+      }
+    }
+    // ---- half-cleaner steps
+#pragma unroll
+    for (int s = k - 2; s >= 0; s--) {
+      const int d = 1 << s;
+      if (d < 32) {
+#pragma unroll
+        for (int r = 0; r < 32; r++)
+          if ((r & d) == 0) {
+            const unsigned lo = min(x[r], x[r | d]), hi = max(x[r], x[r | d]);
+            x[r] = lo;
+            x[r | d] = hi;
+          }
+      } else {
+        const int lm = d >> 5;
+        const bool keepmin = (ul & lm) == 0;
+#pragma unroll
+        for (int r = 0; r < 32; r++) {
+          const unsigned y = __shfl_xor_sync(0xffffffffu, x[r], lm);
+          x[r] = keepmin ? min(x[r], y) : max(x[r], y);
+        }
       }
     }
   }
-  __syncwarp();
-  if (ul == 0 && active) {
-    double tbnd = 0.0;
-    for (int gg = 0; gg < G; gg++) tbnd = tbnd + sb[gg] * s_w[gg];
-    ch.tband[obase] = tbnd;
-    ch.gt[obase] = gt;
+}
+
+template <int P>
+__global__ void __launch_bounds__(128, 4)
+optics_rorr_fast_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevChunk ch,
+                        int *__restrict__ worklist, int *__restrict__ wcount, const int wcap) {
+  using C = Cfg<P>;
+  constexpr int LPU = C::LPU, UPB = C::UPB, LOGP = C::LOGP;
+  constexpr int IDXBITS = 2 * LOGP, FB = 32 - IDXBITS;
+  constexpr unsigned IDXM = (unsigned)(P * P - 1);
+  constexpr int AST = P + 1;
+  constexpr int PST = P * LPU + 1;
+  __shared__ double s_w[P];
+  __shared__ double s_E[P + 1];
+  __shared__ double s_ib[P];
+  __shared__ double s_wxy[P * P];         // wxy(j + i*P) = wbin(i)*wbin(j), types_create.f90:216-222
+  __shared__ double s_a[UPB * AST];
+  __shared__ double s_b[UPB * AST];
+  __shared__ double s_part[UPB * PST];
+
+  const int G = tb.G, nw = tb.nw, nz = ch.nz;
+  for (int i = threadIdx.x; i < P; i += blockDim.x) {
+    s_w[i] = i < G ? tb.wbin[i] : 0.0;
+    s_ib[i] = i < G ? tb.inv_dw[i] : 0.0;
+  }
+  for (int i = threadIdx.x; i < P + 1; i += blockDim.x) s_E[i] = tb.wbin_e[i < G ? i : G];
+  for (int i = threadIdx.x; i < P * P; i += blockDim.x) {
+    const int a = i >> LOGP, b = i & (P - 1);
+    s_wxy[i] = (a < G && b < G) ? __dmul_rn(tb.wbin[a], tb.wbin[b]) : 0.0;
+  }
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31;
+  const int ul = lane & (LPU - 1);
+  const int ub = threadIdx.x / LPU;
+  const long long uid = (long long)blockIdx.x * UPB + ub;
+  const int cap = ch.nslot_cap;
+  int slot = (int)(uid % cap);
+  int l = (int)((uid / cap) % nw);
+  long long cl = uid / ((long long)cap * nw);
+  bool active = cl < ch.ncol;
+  int c = active ? (int)cl : ch.ncol - 1;
+  const int nsl = ch.nslots[c];
+  if (slot >= nsl) {
+    active = false;
+    slot = nsl - 1;
+  }
+  if (__all_sync(0xffffffffu, !active)) return;
+
+  double *sa = s_a + ub * AST, *sb = s_b + ub * AST, *sp = s_part + ub * PST;
+  const int k = ch.layer_of_slot[(size_t)c * nz + slot];
+  const Continua q = rt_continua(tb, ch, c, l, slot, k);
+  const unsigned umask = (LPU == 32 ? 0xffffffffu : ((1u << LPU) - 1u)) << (lane & ~(LPU - 1));
+  bool unit_ok = true;
+
+  for (int jj = 0; jj < tb.nk; jj++) {
+    rt_kgas<P>(tb, ch, c, l, slot, k, jj, ul, jj == 0 ? sa : sb);
+    __syncwarp();
+    if (jj == 0) continue;
+
+    // ---- 32-bit keys
+    const unsigned long long base = (unsigned long long)__double_as_longlong(sa[0] + sb[0]);
+    const unsigned long long top = (unsigned long long)__double_as_longlong(sa[G - 1] + sb[G - 1]);
+    const unsigned long long range = top - base;
+    const int nb = 64 - __clzll((long long)range);  // bit length (0 for range == 0)
+    const int shift = nb > FB ? nb - FB : 0;
+    unsigned x[32];
+#pragma unroll
+    for (int r = 0; r < 32; r++) {
+      const int pos = ul * 32 + r;
+      const int i = pos >> LOGP, j = pos & (P - 1);
+      const bool valid = (i < G) && (j < G);
+      const double v = sa[i] + sb[j];  // :828 tau_xy
+      const unsigned f = (unsigned)(((unsigned long long)__double_as_longlong(v) - base) >> shift);
+      x[r] = valid ? ((f << IDXBITS) | (unsigned)pos) : 0xffffffffu;
+    }
+    bitonic_network_u32<P>(x, ul);
+
+    // ---- weights_to_bins + rebin with the monotonicity certificate
+    double prev = -1.0, first = -1.0;
+    bool ok = true;
+#define FA_IDX(r) (x[r] & IDXM)
+#define FA_TV(r) fa_tv(sa, sb, FA_IDX(r), LOGP, P, prev, first, ok, r)
+    RT_REBIN_PASS(s_wxy[FA_IDX(r)], FA_TV(r))
+#undef FA_TV
+#undef FA_IDX
+    // lane boundary: this lane's first element against the previous lane's last one
+    const double plast = __shfl_up_sync(0xffffffffu, prev, 1, LPU);
+    if (ul > 0 && first >= 0.0) ok = ok && (first >= plast);
+    const unsigned bal = __ballot_sync(0xffffffffu, ok);
+    unit_ok = unit_ok && ((bal & umask) == umask);
+  }
+  rt_store_unit<P>(tb, ch, q, c, l, slot, ul, active, sa, sb, s_w);
+  if (!unit_ok && active && ul == 0) {
+    const int p = atomicAdd(wcount, 1);
+    if (p < wcap) worklist[p] = (int)uid;
   }
 }
 
@@ -393,18 +616,29 @@ __global__ void tau_band_kernel(const DevTables tb, const DevChunk ch, int ind_s
 
 }  // namespace
 
-void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, cudaStream_t st) {
+template <int P>
+static void launch_rorr_p(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount, int wcap,
+                          int exact_only, cudaStream_t st) {
   const long long units = (long long)ch.ncol * tb.nw * ch.nslot_cap;
-  if (tb.G <= 8) {
-    const long long nb = (units + Cfg<8>::UPB - 1) / Cfg<8>::UPB;
-    optics_rorr_kernel<8><<<(unsigned)nb, 128, 0, st>>>(tb, ch);
-  } else if (tb.G <= 16) {
-    const long long nb = (units + Cfg<16>::UPB - 1) / Cfg<16>::UPB;
-    optics_rorr_kernel<16><<<(unsigned)nb, 128, 0, st>>>(tb, ch);
-  } else {
-    const long long nb = (units + Cfg<32>::UPB - 1) / Cfg<32>::UPB;
-    optics_rorr_kernel<32><<<(unsigned)nb, 128, 0, st>>>(tb, ch);
+  const long long nb = (units + Cfg<P>::UPB - 1) / Cfg<P>::UPB;
+  if (exact_only || !tb.rows_sorted) {
+    optics_rorr_kernel<P><<<(unsigned)nb, 128, 0, st>>>(tb, ch, nullptr, nullptr, 0);
+    return;
   }
+  cudaMemsetAsync(wcount, 0, sizeof(int), st);
+  optics_rorr_fast_kernel<P><<<(unsigned)nb, 128, 0, st>>>(tb, ch, worklist, wcount, wcap);
+  const long long nbx = ((long long)wcap + Cfg<P>::UPB - 1) / Cfg<P>::UPB;
+  optics_rorr_kernel<P><<<(unsigned)nbx, 128, 0, st>>>(tb, ch, worklist, wcount, wcap);
+}
+
+// exact_only != 0: every unit through the 64-bit exact kernel.  Otherwise fast kernel, then the
+// exact kernel over the units the fast kernel could not certify (worklist of capacity wcap; the
+// caller checks *wcount <= wcap afterwards and re-runs with exact_only on overflow).
+void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
+                           int wcap, int exact_only, cudaStream_t st) {
+  if (tb.G <= 8) launch_rorr_p<8>(tb, ch, worklist, wcount, wcap, exact_only, st);
+  else if (tb.G <= 16) launch_rorr_p<16>(tb, ch, worklist, wcount, wcap, exact_only, st);
+  else launch_rorr_p<32>(tb, ch, worklist, wcount, wcap, exact_only, st);
 }
 
 void rt_launch_expand_opacity(const DevTables &tb, const DevChunk &ch, int icol, double *tau,

@@ -21,7 +21,8 @@ struct DevFlux {
 // prep.cu
 void rt_launch_prep(const DevTables &tb, const DevChunk &ch, cudaStream_t st);
 // optics_rorr.cu
-void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, cudaStream_t st);
+void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
+                           int wcap, int exact_only, cudaStream_t st);
 // twostream.cu.  `ocol_bcast`: every column reads the opacity of column 0 (frozen-opacity mode).
 void rt_launch_planck(const DevTables &tb, const DevChunk &ch, const DevFlux &fx, cudaStream_t st);
 void rt_launch_twostream_ir(const DevTables &tb, const DevParams &pr, const DevChunk &ch,
@@ -34,6 +35,7 @@ void rt_launch_tau_band(const DevTables &tb, const DevChunk &ch, int is_ir, doub
                         cudaStream_t st);
 void rt_launch_expand_opacity(const DevTables &tb, const DevChunk &ch, int icol, double *tau,
                               double *w0, double *g, double *tband, cudaStream_t st);
+void rt_twostream_occupancy(int G, int nzen, int *ir_blocks_per_sm, int *sol_blocks_per_sm);
 int rt_twostream_block_threads();
 int rt_twostream_items_per_layer();
 // fp64_peak.cu

@@ -469,6 +469,26 @@ __global__ void integrate_kernel(const DevTables tb, const DevChunk ch, const De
 
 }  // namespace
 
+// Resident blocks per SM of the persistent two-stream kernels (grid = SMs x this, so that every
+// block of the grid is resident at once and the grid-stride loop has no half-empty second wave).
+template <int P>
+static void occ_p(int nzen, int *ir, int *sol) {
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(ir, twostream_ir_kernel<P>, TS_THREADS, 0);
+  int a = 0, b = 0, c = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&a, twostream_solar_kernel<P, 4>, TS_THREADS, 0);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&b, twostream_solar_kernel<P, 2>, TS_THREADS, 0);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c, twostream_solar_kernel<P, 1>, TS_THREADS, 0);
+  (void)nzen;
+  *sol = a < b ? (a < c ? a : c) : (b < c ? b : c);
+}
+void rt_twostream_occupancy(int G, int nzen, int *ir_blocks_per_sm, int *sol_blocks_per_sm) {
+  if (G <= 8) occ_p<8>(nzen, ir_blocks_per_sm, sol_blocks_per_sm);
+  else if (G <= 16) occ_p<16>(nzen, ir_blocks_per_sm, sol_blocks_per_sm);
+  else occ_p<32>(nzen, ir_blocks_per_sm, sol_blocks_per_sm);
+  if (*ir_blocks_per_sm < 1) *ir_blocks_per_sm = 1;
+  if (*sol_blocks_per_sm < 1) *sol_blocks_per_sm = 1;
+}
+
 int rt_twostream_block_threads() { return TS_THREADS; }
 int rt_twostream_items_per_layer() { return SOL_ITEMS > IR_ITEMS ? SOL_ITEMS : IR_ITEMS; }
 

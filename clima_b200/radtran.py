@@ -27,7 +27,7 @@ _lib = None
 EXPORTS = ["clima_rt_create", "clima_rt_destroy", "clima_rt_set_params",
            "clima_rt_set_custom_optical_properties", "clima_rt_unset_custom_optical_properties",
            "clima_rt_radiate_batch", "clima_rt_radiate_batch_device", "clima_rt_get_opacity",
-           "clima_rt_get_launch_count", "clima_rt_get_stage_ms", "clima_rt_get_stream", "clima_rt_measure_fp64_peak",
+           "clima_rt_get_launch_count", "clima_rt_get_stage_ms", "clima_rt_get_stream", "clima_rt_get_rorr_stats", "clima_rt_measure_fp64_peak",
            "clima_rt_version_get"]
 
 
@@ -229,6 +229,12 @@ class Radtran:
         p = C.c_void_p()
         self._lib.clima_rt_get_stream(self._h, C.byref(p))
         return p.value or 0
+
+    def rorr_stats(self):
+        """(units processed, units through the exact kernel, worklist overflows)."""
+        a = (C.c_int64 * 3)()
+        self._lib.clima_rt_get_rorr_stats(self._h, a)
+        return tuple(a)
 
     def stage_ms(self):
         a = (C.c_double * 6)()

@@ -221,6 +221,12 @@ void clima_rt_get_opacity(void *handle, const int32_t *icol, double *tau, double
 void clima_rt_get_launch_count(void *handle, int64_t *count);
 void clima_rt_get_stage_ms(void *handle, double *ms6);
 
+/* RORR bookkeeping since the handle was created: [0] work units (column x bin x unique layer)
+   processed, [1] units that went through the exact 64-bit sort kernel (all of them when the
+   k-tables are not ascending in g or CLIMA_RT_RORR=exact is set; otherwise only those the 32-bit
+   fast kernel could not certify), [2] worklist overflows (whole chunk redone exactly). */
+void clima_rt_get_rorr_stats(void *handle, int64_t *stats3);
+
 /* The CUDA stream (a cudaStream_t, returned as an opaque pointer) every kernel of the handle is
    launched on, so that a caller can bracket calls with its own CUDA events on the launching
    stream or order its own work (e.g. an NCCL all-gather of the flux profiles) after them. */

@@ -200,3 +200,55 @@ def test_modern_earth_like_single_column():
     g = Radtran(tb, pr)
     o = OracleRadtran(tb, pr, kind="parity")
     compare(g.radiate_batch(cols, spectral=True), o.radiate_batch(cols, spectral=True), verbose=True)
+
+
+def test_rorr_fast_path_is_bit_identical_to_exact_path(monkeypatch):
+    """The 32-bit-key fast RORR kernel must return the permutation of the stable 64-bit sort (or
+    hand the unit to the exact kernel): results are bit-identical with CLIMA_RT_RORR=exact."""
+    tb, pr, cols = small_case(G=16, nw=12, nz=10, ncol=3)
+    g = Radtran(tb, pr)
+    r1 = g.radiate_batch(cols, spectral=True)
+    units, exact, ovf = g.rorr_stats()
+    assert units > 0 and exact < units and ovf == 0
+    monkeypatch.setenv("CLIMA_RT_RORR", "exact")
+    g2 = Radtran(tb, pr)
+    r2 = g2.radiate_batch(cols, spectral=True)
+    assert g2.rorr_stats()[1] == g2.rorr_stats()[0]
+    for k in r1:
+        assert np.array_equal(r1[k], r2[k]), k
+
+
+@pytest.mark.parametrize("G", [8, 16, 32])
+def test_rorr_near_ties_go_through_the_exact_kernel(G):
+    """k-distributions made of two tight clusters (steps of 1e-13 in log10 k, six decades apart):
+    the sums a_i + b_j collide in the 32-bit quantisation, the fast kernel must notice and defer to
+    the exact kernel, and the result must still match the oracle."""
+    tb, pr, cols = small_case(G=G, nw=6, nz=6, ncol=2)
+    for kt in tb.k[:3]:
+        gidx = np.arange(G)
+        step = np.where(gidx < G // 2, 0.0, 6.0) + 1e-13 * gidx
+        kt.log10k[...] = kt.log10k[0:1, :, :, :] + step[:, None, None, None]
+    g = Radtran(tb, pr)
+    o = OracleRadtran(tb, pr)
+    compare(g.radiate_batch(cols, spectral=True), o.radiate_batch(cols, spectral=True))
+    units, exact, ovf = g.rorr_stats()
+    assert exact > 0
+
+
+def test_rorr_worklist_overflow_falls_back_to_exact(monkeypatch):
+    """Every unit uncertified (all sums tied in the quantisation) -> worklist overflow -> the chunk
+    is redone by the exact kernel; results still match the oracle."""
+    tb, pr, cols = small_case(G=16, nw=40, nz=60, ncol=40, doubled=False)
+    for kt in tb.k:
+        gidx = np.arange(16)
+        step = np.where(gidx < 8, 0.0, 6.0) + 1e-13 * gidx
+        kt.log10k[...] = kt.log10k[0:1, :, :, :] + step[:, None, None, None]
+    g = Radtran(tb, pr)
+    rg = g.radiate_batch(cols)
+    units, exact, ovf = g.rorr_stats()
+    assert ovf >= 1
+    sub = {k: (v[..., :2] if v.ndim > 1 else v[:2]) for k, v in cols.items() if isinstance(v, np.ndarray)}
+    c2 = dict(cols, **sub); c2["ncol"] = 2
+    ro = OracleRadtran(tb, pr).radiate_batch(c2)
+    rg2 = {k: (v[..., :2] if v.ndim > 1 else v[:2]) for k, v in rg.items()}
+    compare(rg2, ro, spectral=False)
