@@ -35,6 +35,7 @@ struct Cfg {
   static constexpr int GPL = P / LPU;  // g-points per lane in the interpolation: 4, 2, 1
   static constexpr int UPB = 128 / LPU;  // units per 128-thread block
   static constexpr unsigned long long IDXMASK = (unsigned long long)(N - 1);
+  static constexpr int ISTR = N + LPU;  // u16 stride of a unit's sorted-index list (bank spread)
 };
 
 __device__ __forceinline__ double shfl_xor_d(double v, int lanemask) {
@@ -48,17 +49,6 @@ __device__ __forceinline__ void ce(double &a, double &b) {
   const double hi = p ? b : a;
   a = lo;
   b = hi;
-}
-
-// exact tau_xy of sorted element `idx` + the non-decreasing check of the fast kernel
-__device__ __forceinline__ double fa_tv(const double *sa, const double *sb, const unsigned idx,
-                                        const int LOGP, const int P, double &prev, double &first,
-                                        bool &ok, const int r) {
-  const double tv = __dadd_rn(sa[idx >> LOGP], sb[idx & (P - 1)]);
-  ok = ok && (tv >= prev);
-  prev = tv;
-  if (r == 0) first = tv;
-  return tv;
 }
 
 // Bitonic sort network over positions pos = ul*32 + r, all runs ascending ("flip" variant: the first
@@ -129,12 +119,14 @@ __device__ __forceinline__ Continua rt_continua(const DevTables &tb, const DevCh
   Continua o;
   // Rayleigh (:686-693)
   double tausg = 0.0;
+#pragma unroll 1
   for (int i = 0; i < tb.nray; i++) {
     const double col = dens[(size_t)(tb.ray_sp[i] - 1) * nz] * dzk;
     tausg = tausg + tb.ray_xs[l + (size_t)i * nw] * col;
   }
   // CIA (:696-704), photolysis (:707-713)
   double taua = 0.0;
+#pragma unroll 1
   for (int i = 0; i < tb.ncia + tb.npxs; i++) {
     const bool is_cia = i < tb.ncia;
     const DevXS &x = is_cia ? tb.cia[i] : tb.pxs[i - tb.ncia];
@@ -171,6 +163,7 @@ __device__ __forceinline__ Continua rt_continua(const DevTables &tb, const DevCh
   if (tb.npart > 0) {
     const double *rad = ch.radii + (size_t)c * nz * tb.np + k;
     const double *pdn = ch.pdens + (size_t)c * nz * tb.np + k;
+#pragma unroll 1
     for (int i = 0; i < tb.npart; i++) {
       const DevPart &p = tb.part[i];
       const int ir = ib[rbase + i];
@@ -202,6 +195,7 @@ __device__ __forceinline__ Continua rt_continua(const DevTables &tb, const DevCh
   double gt = 0.0;
   {
     const double den = fmax(RT_TAU_MIN, (tausp + tausg + tausc));
+#pragma unroll 1
     for (int i = 0; i < tb.npart; i++) gt = gt + gtp[i] * tausp_1[i] / den;
     gt = gt + g0c * tausc / den;
     gt = fmin(gt, RT_MAX_GT);
@@ -244,59 +238,90 @@ __device__ __forceinline__ void rt_kgas(const DevTables &tb, const DevChunk &ch,
   }
 }
 
-// weights_to_bins + rebin (:843-849) of the unit's sorted sequence.  Element m of the sequence is
-// (tau tv, weight w) delivered by `elem(r, tv, w)` for the lane's positions r = 0..31 in sorted
-// order; lanes of the unit hold consecutive runs.  The new bin values land in sa[0..P).
-// Deterministic: per-lane partials in shared memory, summed in lane order.
-#define RT_REBIN_PASS(ELEM_W, ELEM_TV)                                                          \
-  double tot = 0.0;                                                                              \
-  _Pragma("unroll") for (int r = 0; r < 32; r++) { tot = __dadd_rn(tot, (ELEM_W)); }                             \
-  double off = tot;                                                                              \
-  _Pragma("unroll") for (int d = 1; d < LPU; d <<= 1) {                                          \
-    const double t_ = __shfl_up_sync(0xffffffffu, off, d, LPU);                                  \
-    if (ul >= d) off = __dadd_rn(off, t_);                                                       \
-  }                                                                                              \
-  off = __dsub_rn(off, tot);                                                                     \
-  for (int g_ = 0; g_ < G; g_++) sp[g_ * LPU + ul] = 0.0;                                        \
-  int g = 0;                                                                                     \
-  _Pragma("unroll") for (int s_ = P / 2; s_ > 0; s_ >>= 1)                                       \
-    if (g + s_ <= G - 1 && s_E[g + s_] <= off) g += s_;                                          \
-  double n0 = s_E[g], n1 = s_E[g + 1], ibw = s_ib[g];                                            \
-  double acc = 0.0, o0 = off;                                                                    \
-  _Pragma("unroll") for (int r = 0; r < 32; r++) {                                               \
-    const double w = (ELEM_W);                                                                   \
-    if (w > 0.0) {                                                                               \
-      const double tv = (ELEM_TV);                                                               \
-      const double o1 = __dadd_rn(o0, w);                                                        \
-      double lo = o0;                                                                            \
-      while (o1 > n1 && g < G - 1) { /* old bin crosses the right edge of new bin g */           \
-        acc = __dadd_rn(acc, (lo <= n0) ? tv : __dmul_rn(__dmul_rn(__dsub_rn(n1, lo), ibw), tv)); \
-        sp[g * LPU + ul] = acc;                                                                  \
-        acc = 0.0;                                                                               \
-        g++;                                                                                     \
-        n0 = n1;                                                                                 \
-        lo = n1;                                                                                 \
-        n1 = s_E[g + 1];                                                                         \
-        ibw = s_ib[g];                                                                           \
-      }                                                                                          \
-      const double hi = fmin(o1, n1);                                                            \
-      if (hi > lo)                                                                               \
-        acc = __dadd_rn(acc, (lo <= n0 && hi >= n1) ? tv                                         \
-                                                    : __dmul_rn(__dmul_rn(__dsub_rn(hi, lo), ibw), tv)); \
-      o0 = o1;                                                                                   \
-    }                                                                                            \
-  }                                                                                              \
-  sp[g * LPU + ul] = acc;                                                                        \
-  __syncwarp();                                                                                  \
-  _Pragma("unroll") for (int t = 0; t < C::GPL; t++) {                                           \
-    const int gg = ul + LPU * t;                                                                 \
-    double s_ = 0.0;                                                                             \
-    if (gg < G) {                                                                                \
-      _Pragma("unroll") for (int q = 0; q < LPU; q++) s_ = __dadd_rn(s_, sp[gg * LPU + q]);      \
-    }                                                                                            \
-    sa[gg] = s_;                                                                                 \
-  }                                                                                              \
+// weights_to_bins + rebin (:843-849) of the unit's sorted sequence.  `sidx[r * LPU + ul]` holds the
+// element index (i*P + j) of sorted position ul*32 + r; the lanes of the unit own consecutive runs
+// of 32 positions.  Compact on purpose (rolled loops): the unrolled version of this pass made the
+// kernel 3x larger than the instruction cache and "no instruction" its top stall.
+//   pass 1: lane weight totals -> exclusive scan over the unit's lanes = cumulative weight at the
+//           lane's first element (weights_to_bins);
+//   pass 2: walk the 32 elements with the running edge; an element inside the current new bin adds
+//           w*tau, one that crosses a new-bin edge is split at the edge (futils rebin); every closed
+//           bin is scaled by 1/width and written to the lane's partial slot.
+// The new bin values land in sa[0..P).  Deterministic: per-lane partials, summed in lane order.
+// CERT: also certify that the exact tau_xy sequence is non-decreasing (fast kernel); returns it.
+template <int P, bool CERT>
+__device__ __forceinline__ bool rt_rebin(const unsigned short *__restrict__ sidx, double *sa,
+                                         const double *sb, double *sp, const double *s_wxy,
+                                         const double *s_E, const double *s_ib, const int G,
+                                         const int ul) {
+  using C = Cfg<P>;
+  constexpr int LPU = C::LPU, LOGP = C::LOGP;
+  double tot = 0.0;
+#pragma unroll 8
+  for (int r = 0; r < 32; r++) tot = __dadd_rn(tot, s_wxy[sidx[r * LPU + ul]]);
+  double off = tot;
+#pragma unroll
+  for (int d = 1; d < LPU; d <<= 1) {
+    const double t = __shfl_up_sync(0xffffffffu, off, d, LPU);
+    if (ul >= d) off = __dadd_rn(off, t);
+  }
+  off = __dsub_rn(off, tot);
+  for (int g = 0; g < G; g++) sp[g * LPU + ul] = 0.0;
+  int g = 0;
+#pragma unroll
+  for (int s = P / 2; s > 0; s >>= 1)
+    if (g + s <= G - 1 && s_E[g + s] <= off) g += s;
+  double n1 = s_E[g + 1];
+  double acc = 0.0, o0 = off, prev = -1.0, first = -1.0;
+  bool ok = true;
+#pragma unroll 2
+  for (int r = 0; r < 32; r++) {
+    const unsigned idx = sidx[r * LPU + ul];
+    const double w = s_wxy[idx];
+    if (w > 0.0) {  // padding elements (ngauss < P) carry zero weight
+      const double tv = __dadd_rn(sa[idx >> LOGP], sb[idx & (P - 1)]);  // exact tau_xy (:828)
+      if (CERT) {
+        ok = ok && (tv >= prev);
+        prev = tv;
+        if (r == 0) first = tv;
+      }
+      const double o1 = __dadd_rn(o0, w);
+      if (o1 > n1 && g < G - 1) {
+        double lo = o0;
+        do {  // the element crosses the right edge of new bin g
+          acc = __fma_rn(__dsub_rn(n1, lo), tv, acc);
+          sp[g * LPU + ul] = __dmul_rn(acc, s_ib[g]);
+          acc = 0.0;
+          g++;
+          lo = n1;
+          n1 = s_E[g + 1];
+        } while (o1 > n1 && g < G - 1);
+        acc = __fma_rn(__dsub_rn(o1, lo), tv, acc);
+      } else {
+        acc = __fma_rn(w, tv, acc);
+      }
+      o0 = o1;
+    }
+  }
+  sp[g * LPU + ul] = __dmul_rn(acc, s_ib[g]);
+  if (CERT) {  // lane boundary: this lane's first element against the previous lane's last one
+    const double plast = __shfl_up_sync(0xffffffffu, prev, 1, LPU);
+    if (ul > 0 && first >= 0.0) ok = ok && (first >= plast);
+  }
   __syncwarp();
+#pragma unroll
+  for (int t = 0; t < C::GPL; t++) {
+    const int gg = ul + LPU * t;
+    double sum = 0.0;
+    if (gg < G) {
+#pragma unroll
+      for (int q = 0; q < LPU; q++) sum = __dadd_rn(sum, sp[gg * LPU + q]);
+    }
+    sa[gg] = sum;
+  }
+  __syncwarp();
+  return ok;
+}
 
 // total tau, w0 clamp, band tau, asymmetry of the unit (:856-886) -> HBM (slot-indexed layout).
 template <int P>
@@ -324,6 +349,7 @@ __device__ __forceinline__ void rt_store_unit(const DevTables &tb, const DevChun
   __syncwarp();
   if (ul == 0 && active) {
     double tbnd = 0.0;
+#pragma unroll 4
     for (int gg = 0; gg < G; gg++) tbnd = __dadd_rn(tbnd, __dmul_rn(sb[gg], s_w[gg]));
     ch.tband[obase] = tbnd;
     ch.gt[obase] = q.gt;
@@ -348,7 +374,9 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   __shared__ double s_ib[P];              // 1/(wbin_e(g+1)-wbin_e(g))
   __shared__ double s_a[UPB * AST];       // running mixture tau_k(g)
   __shared__ double s_b[UPB * AST];       // new gas k*col (g)
-  __shared__ double s_part[UPB * PST];    // rebin partials [g][lane]
+  extern __shared__ double s_part[];      // [UPB * PST] rebin partials [g][lane] (dynamic: 33 KB at P=32)
+  __shared__ double s_wxy[P * P];         // wxy(j + i*P) = wbin(i)*wbin(j), types_create.f90:216-222
+  __shared__ unsigned short s_idx[UPB * C::ISTR];  // sorted element indices [r][lane] per unit
 
   const int G = tb.G, nw = tb.nw, nz = ch.nz;
   for (int i = threadIdx.x; i < P; i += blockDim.x) {
@@ -356,6 +384,10 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     s_ib[i] = i < G ? tb.inv_dw[i] : 0.0;
   }
   for (int i = threadIdx.x; i < P + 1; i += blockDim.x) s_E[i] = tb.wbin_e[i < G ? i : G];
+  for (int i = threadIdx.x; i < P * P; i += blockDim.x) {
+    const int a = i >> LOGP, b = i & (P - 1);
+    s_wxy[i] = (a < G && b < G) ? __dmul_rn(tb.wbin[a], tb.wbin[b]) : 0.0;
+  }
   __syncthreads();
 
   const int lane = threadIdx.x & 31;
@@ -405,10 +437,13 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     }
     bitonic_network<P>(x, ul, kfirst);
 
-#define EX_IDX(r) ((unsigned)((unsigned long long)__double_as_longlong(x[r]) & C::IDXMASK))
-    RT_REBIN_PASS(__dmul_rn(s_w[EX_IDX(r) >> LOGP], s_w[EX_IDX(r) & (P - 1)]),
-                  __dadd_rn(sa[EX_IDX(r) >> LOGP], sb[EX_IDX(r) & (P - 1)]))
-#undef EX_IDX
+    unsigned short *sidx = s_idx + ub * C::ISTR;
+#pragma unroll
+    for (int r = 0; r < 32; r++)
+      sidx[r * LPU + ul] =
+          (unsigned short)((unsigned long long)__double_as_longlong(x[r]) & C::IDXMASK);
+    __syncwarp();
+    rt_rebin<P, false>(sidx, sa, sb, sp, s_wxy, s_E, s_ib, G, ul);
   }
   rt_store_unit<P>(tb, ch, q, c, l, slot, ul, active, sa, sb, s_w);
 }
@@ -428,22 +463,37 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
 // redone by the exact kernel.  The fast path therefore returns the same permutation as the
 // reference's stable merge sort or hands the unit over -- it never silently differs.
 // ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void ce_u32(unsigned &a, unsigned &b) {
+  const unsigned lo = min(a, b), hi = max(a, b);  // 2 x VIMNMX.U32
+  a = lo;
+  b = hi;
+}
+
+// Merge stages LOGP+1 .. 2*LOGP of the bitonic network ("flip" variant, rows pre-sorted) over
+// positions pos = ul*32 + r.  Stages whose partners all live in the lane (k <= 5) are unrolled;
+// the cross-lane stages run as a ROLLED loop over k with the lane masks in registers, so the code
+// holds one shuffle flip block, one shuffle half-cleaner block and one 5-step in-register block
+// instead of a copy per stage (instruction-cache footprint, see rt_rebin).
 template <int P>
 __device__ __forceinline__ void bitonic_network_u32(unsigned (&x)[32], const int ul) {
   using C = Cfg<P>;
+  constexpr int K0 = C::LOGP + 1, K1 = 2 * C::LOGP;
 #pragma unroll
-  for (int k = C::LOGP + 1; k <= 2 * C::LOGP; k++) {
-    // ---- flip step
-    if (k <= 5) {
-      const int m = (1 << k) - 1;
+  for (int k = K0; k <= (K1 < 5 ? K1 : 5); k++) {
+    const int m = (1 << k) - 1;
+#pragma unroll
+    for (int r = 0; r < 32; r++)
+      if ((r & (1 << (k - 1))) == 0) ce_u32(x[r], x[r ^ m]);
+#pragma unroll
+    for (int s = k - 2; s >= 0; s--) {
 #pragma unroll
       for (int r = 0; r < 32; r++)
-        if ((r & (1 << (k - 1))) == 0) {
-          const unsigned lo = min(x[r], x[r ^ m]), hi = max(x[r], x[r ^ m]);
-          x[r] = lo;
-          x[r ^ m] = hi;
-        }
-    } else {
+        if ((r & (1 << s)) == 0) ce_u32(x[r], x[r | (1 << s)]);
+    }
+  }
+#pragma unroll 1
+  for (int k = (K0 > 6 ? K0 : 6); k <= K1; k++) {
+    {  // flip step: pos <-> pos ^ (2^k - 1): partner lane ul ^ lm, partner register r ^ 31
       const int lm = ((1 << k) - 1) >> 5;
       const bool keepmin = (ul & ((lm + 1) >> 1)) == 0;
 #pragma unroll
@@ -454,27 +504,21 @@ __device__ __forceinline__ void bitonic_network_u32(unsigned (&x)[32], const int
         x[r ^ 31] = keepmin ? min(x[r ^ 31], y2) : max(x[r ^ 31], y2);
       }
     }
-    // ---- half-cleaner steps
+#pragma unroll 1
+    for (int s = k - 2; s >= 5; s--) {  // cross-lane half-cleaners
+      const int lm = 1 << (s - 5);
+      const bool keepmin = (ul & lm) == 0;
 #pragma unroll
-    for (int s = k - 2; s >= 0; s--) {
-      const int d = 1 << s;
-      if (d < 32) {
-#pragma unroll
-        for (int r = 0; r < 32; r++)
-          if ((r & d) == 0) {
-            const unsigned lo = min(x[r], x[r | d]), hi = max(x[r], x[r | d]);
-            x[r] = lo;
-            x[r | d] = hi;
-          }
-      } else {
-        const int lm = d >> 5;
-        const bool keepmin = (ul & lm) == 0;
-#pragma unroll
-        for (int r = 0; r < 32; r++) {
-          const unsigned y = __shfl_xor_sync(0xffffffffu, x[r], lm);
-          x[r] = keepmin ? min(x[r], y) : max(x[r], y);
-        }
+      for (int r = 0; r < 32; r++) {
+        const unsigned y = __shfl_xor_sync(0xffffffffu, x[r], lm);
+        x[r] = keepmin ? min(x[r], y) : max(x[r], y);
       }
+    }
+#pragma unroll
+    for (int s = 4; s >= 0; s--) {  // in-lane half-cleaners d = 16..1
+#pragma unroll
+      for (int r = 0; r < 32; r++)
+        if ((r & (1 << s)) == 0) ce_u32(x[r], x[r | (1 << s)]);
     }
   }
 }
@@ -495,7 +539,8 @@ optics_rorr_fast_kernel(const __grid_constant__ DevTables tb, const __grid_const
   __shared__ double s_wxy[P * P];         // wxy(j + i*P) = wbin(i)*wbin(j), types_create.f90:216-222
   __shared__ double s_a[UPB * AST];
   __shared__ double s_b[UPB * AST];
-  __shared__ double s_part[UPB * PST];
+  extern __shared__ double s_part[];  // [UPB * PST]
+  __shared__ unsigned short s_idx[UPB * C::ISTR];
 
   const int G = tb.G, nw = tb.nw, nz = ch.nz;
   for (int i = threadIdx.x; i < P; i += blockDim.x) {
@@ -556,16 +601,11 @@ optics_rorr_fast_kernel(const __grid_constant__ DevTables tb, const __grid_const
     bitonic_network_u32<P>(x, ul);
 
     // ---- weights_to_bins + rebin with the monotonicity certificate
-    double prev = -1.0, first = -1.0;
-    bool ok = true;
-#define FA_IDX(r) (x[r] & IDXM)
-#define FA_TV(r) fa_tv(sa, sb, FA_IDX(r), LOGP, P, prev, first, ok, r)
-    RT_REBIN_PASS(s_wxy[FA_IDX(r)], FA_TV(r))
-#undef FA_TV
-#undef FA_IDX
-    // lane boundary: this lane's first element against the previous lane's last one
-    const double plast = __shfl_up_sync(0xffffffffu, prev, 1, LPU);
-    if (ul > 0 && first >= 0.0) ok = ok && (first >= plast);
+    unsigned short *sidx = s_idx + ub * C::ISTR;
+#pragma unroll
+    for (int r = 0; r < 32; r++) sidx[r * LPU + ul] = (unsigned short)(x[r] & IDXM);
+    __syncwarp();
+    const bool ok = rt_rebin<P, true>(sidx, sa, sb, sp, s_wxy, s_E, s_ib, G, ul);
     const unsigned bal = __ballot_sync(0xffffffffu, ok);
     unit_ok = unit_ok && ((bal & umask) == umask);
   }
@@ -621,14 +661,21 @@ static void launch_rorr_p(const DevTables &tb, const DevChunk &ch, int *worklist
                           int exact_only, cudaStream_t st) {
   const long long units = (long long)ch.ncol * tb.nw * ch.nslot_cap;
   const long long nb = (units + Cfg<P>::UPB - 1) / Cfg<P>::UPB;
+  constexpr size_t dsm = (size_t)Cfg<P>::UPB * (P * Cfg<P>::LPU + 1) * sizeof(double);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(optics_rorr_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsm);
+    cudaFuncSetAttribute(optics_rorr_fast_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsm);
+    attr_set = true;
+  }
   if (exact_only || !tb.rows_sorted) {
-    optics_rorr_kernel<P><<<(unsigned)nb, 128, 0, st>>>(tb, ch, nullptr, nullptr, 0);
+    optics_rorr_kernel<P><<<(unsigned)nb, 128, dsm, st>>>(tb, ch, nullptr, nullptr, 0);
     return;
   }
   cudaMemsetAsync(wcount, 0, sizeof(int), st);
-  optics_rorr_fast_kernel<P><<<(unsigned)nb, 128, 0, st>>>(tb, ch, worklist, wcount, wcap);
+  optics_rorr_fast_kernel<P><<<(unsigned)nb, 128, dsm, st>>>(tb, ch, worklist, wcount, wcap);
   const long long nbx = ((long long)wcap + Cfg<P>::UPB - 1) / Cfg<P>::UPB;
-  optics_rorr_kernel<P><<<(unsigned)nbx, 128, 0, st>>>(tb, ch, worklist, wcount, wcap);
+  optics_rorr_kernel<P><<<(unsigned)nbx, 128, dsm, st>>>(tb, ch, worklist, wcount, wcap);
 }
 
 // exact_only != 0: every unit through the 64-bit exact kernel.  Otherwise fast kernel, then the
