@@ -1,0 +1,23 @@
+#!/usr/bin/env python
+"""Per-source-line instruction / sample / shared-wavefront breakdown of one kernel from an ncu report.
+usage: tools/ncu_lines.py report.ncu-rep kernel_regex [topN]"""
+import csv, io, subprocess, sys
+rep, kre = sys.argv[1], sys.argv[2]
+top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass",
+                      "--kernel-name", "regex:" + kre], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(out)))
+hi = next(i for i, r in enumerate(rows) if r and r[0] == "Line No")
+hdr = rows[hi]
+ie, ismp = hdr.index("Instructions Executed"), hdr.index("# Samples")
+iw, iwi = hdr.index("L1 Wavefronts Shared"), hdr.index("L1 Wavefronts Shared Ideal")
+lines = []
+for r in rows[hi + 1:]:
+    if len(r) <= ie: continue
+    if r[0] == "Line No": break
+    if r[0].isdigit():
+        lines.append((int(r[0]), r[1].strip(), int(r[ie]), int(r[ismp]), int(r[iw]), int(r[iwi])))
+ti = sum(l[2] for l in lines); ts = sum(l[3] for l in lines); tw = sum(l[4] for l in lines)
+print(f"total inst {ti} samples {ts} shared wavefronts {tw} (ideal {sum(l[5] for l in lines)})")
+for l in sorted(lines, key=lambda l: -l[3])[:top]:
+    print(f"{l[0]:5d} inst {l[2]/ti:6.3f} smp {l[3]/ts:6.3f} wf {l[4]/max(tw,1):6.3f} (x{l[4]/max(l[5],1):4.1f}) | {l[1][:100]}")
