@@ -1,0 +1,35 @@
+// optics_rorr_exact.cu -- instantiates the exact flavour of the optics + RORR kernel (rorr_impl.cuh).
+#include "rorr_impl.cuh"
+
+namespace {
+template <int P, bool FULL>
+void launch(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount, int wcap,
+            long long units, cudaStream_t st) {
+  using C = rorr::Cfg<P>;
+  auto kern = rorr::optics_rorr_kernel<P, FULL, false>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::BLOCK_BYTES);
+    attr_set = true;
+  }
+  const long long nb = (units + C::UPB - 1) / C::UPB;
+  if (nb <= 0) return;
+  kern<<<(unsigned)nb, 128, C::BLOCK_BYTES, st>>>(tb, ch, worklist, wcount, wcap);
+}
+}  // namespace
+
+// units: number of work units to cover (all units of the chunk, or the worklist capacity).
+void rorr_launch_exact(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount, int wcap,
+                    long long units, cudaStream_t st) {
+  const int G = tb.G;
+  if (G <= 8) {
+    if (G == 8) launch<8, true>(tb, ch, worklist, wcount, wcap, units, st);
+    else launch<8, false>(tb, ch, worklist, wcount, wcap, units, st);
+  } else if (G <= 16) {
+    if (G == 16) launch<16, true>(tb, ch, worklist, wcount, wcap, units, st);
+    else launch<16, false>(tb, ch, worklist, wcount, wcap, units, st);
+  } else {
+    if (G == 32) launch<32, true>(tb, ch, worklist, wcount, wcap, units, st);
+    else launch<32, false>(tb, ch, worklist, wcount, wcap, units, st);
+  }
+}

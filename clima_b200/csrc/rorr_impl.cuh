@@ -1,0 +1,568 @@
+// rorr_impl.cuh -- optical-property assembly + random overlap with resorting and rebinning.
+//
+// Replaces the body of the per-bin loop of OpticalProperties_compute_opacity
+// (src/radtran/clima_radtran_types.f90:638-771) and k_rorr (:780-888) for a batch of columns.
+// Included by optics_rorr_fast.cu and optics_rorr_exact.cu, which instantiate the two flavours.
+//
+// Work unit = (column, wavelength bin l, unique layer slot).  A unit is owned by LPU = P*P/32
+// lanes of one warp (P = ngauss rounded up to a power of two: 8 lanes at ngauss=16, 4 units per
+// warp).  Per unit:
+//   1. continua (Rayleigh, CIA, photolysis xs, H2O continuum, custom, particles)  -- A.3
+//      the Rayleigh/CIA/xs/continuum items are dealt round-robin to the unit's lanes and the two
+//      partial sums are combined with a butterfly (deterministic, same value on every lane);
+//   2. for each k-gas: bilinear log10k(P,T) interpolation, lane per g-point       -- A.2
+//   3. RORR merge of the running mixture a(1..G) with the new gas b(1..G): the G x G sums
+//      a_i + b_j live in REGISTERS, 32 per lane, and are ranked by a bitonic MERGE network (the G
+//      rows are already ascending because k-distributions ascend in g -- checked at table load --
+//      and the mixture ascends after every rebin).
+//        FAST : 32-bit keys [quantised tau_xy | element index], compare-exchange = 2 x VIMNMX.U32;
+//               the rebin walk re-forms every exact tau_xy and certifies that the sequence it walks
+//               is non-decreasing; a unit that fails is appended to a worklist.
+//        EXACT: 64-bit keys = FP64 bit pattern with the low 2*log2(P) mantissa bits replaced by the
+//               element index: one DSETP orders (value, index), i.e. the STABLE rank of mrgrnk.
+//   4. weights_to_bins + rebin (clima_eqns.f90:43-54, futils rebin): each lane walks its 32 sorted
+//      elements with the running cumulative-weight edge and a monotone output-bin pointer.
+//      The gathers a(i), b(j) by sorted element index go to per-warp tables laid out
+//      [row][lane]: every lane owns a private COLUMN (bank = lane), so a gather with 32 different
+//      rows is conflict-free.  Weights w_i*w_j come from a 4-way replicated wxy table.
+//      Per-lane partial bin sums go to shared memory and are added in lane order (no atomics:
+//      bit-reproducible run to run).
+//   5. total tau, w0 clamp, band tau (:856-886).
+#pragma once
+#include "rt_device.cuh"
+#include "rt_kernels.h"
+
+namespace rorr {
+
+template <int P>
+struct Cfg {
+  static constexpr int LOGP = (P == 8 ? 3 : (P == 16 ? 4 : 5));
+  static constexpr int N = P * P;
+  static constexpr int KPL = 32;        // keys per lane
+  static constexpr int LPU = N / KPL;   // lanes per unit: 2, 8, 32
+  static constexpr int GPL = P / LPU;   // g-points per lane: 4, 2, 1
+  static constexpr int UPW = 32 / LPU;  // units per warp: 16, 4, 1
+  static constexpr int UPB = 4 * UPW;   // units per 128-thread block
+  static constexpr int NC = (LPU == 32 ? 16 : LPU);  // table columns of one unit
+  static constexpr int CW = (LPU == 32 ? 16 : 32);   // table columns per warp
+  static constexpr int TBL = P * CW;                 // doubles per table per warp
+  static constexpr int SPST = LPU + 1;               // partial-sum row stride (bank spread)
+  static constexpr int SPU = P * SPST;               // partial-sum doubles per unit
+  static constexpr int WXC = 4;                      // copies of the wxy table
+  static constexpr int IDXB = (N <= 256 ? 1 : 2);    // bytes per sorted-index entry
+  static constexpr unsigned IDXM = (unsigned)(N - 1);
+  // dynamic shared memory: [wxy N*WXC doubles][per warp: tA, tB, partials, idx]
+  static constexpr size_t WARP_BYTES =
+      (size_t)(2 * TBL + UPW * SPU) * sizeof(double) + (size_t)32 * 32 * IDXB;
+  static constexpr size_t BLOCK_BYTES = (size_t)N * WXC * sizeof(double) + 4 * WARP_BYTES;
+};
+
+template <int B> struct IdxT { typedef unsigned char type; };
+template <> struct IdxT<2> { typedef unsigned short type; };
+
+__device__ __forceinline__ double shfl_xor_d(double v, int lanemask) {
+  return __shfl_xor_sync(0xffffffffu, v, lanemask);
+}
+
+// compare-exchange, ascending (64-bit keys are distinct by construction)
+__device__ __forceinline__ void ce(double &a, double &b) {
+  const bool p = a < b;
+  const double lo = p ? a : b;
+  const double hi = p ? b : a;
+  a = lo;
+  b = hi;
+}
+__device__ __forceinline__ void ce(unsigned &a, unsigned &b) {
+  const unsigned lo = min(a, b), hi = max(a, b);  // 2 x VIMNMX.U32
+  a = lo;
+  b = hi;
+}
+__device__ __forceinline__ double pick(bool keepmin, double a, double y) {
+  return ((a < y) == keepmin) ? a : y;
+}
+__device__ __forceinline__ unsigned pick(bool keepmin, unsigned a, unsigned y) {
+  return keepmin ? min(a, y) : max(a, y);
+}
+__device__ __forceinline__ double shfl_x(double v, int m) { return shfl_xor_d(v, m); }
+__device__ __forceinline__ unsigned shfl_x(unsigned v, int m) {
+  return __shfl_xor_sync(0xffffffffu, v, m);
+}
+
+// Bitonic sort network over positions pos = ul*32 + r, all runs ascending ("flip" variant: the
+// first step of stage k pairs pos with pos ^ (2^k-1), the remaining steps pos with pos ^ d).
+// Stages below `kfirst` are skipped (rows pre-sorted).  Stages whose partners all live in the lane
+// (k <= 5) are unrolled; the cross-lane stages run as a ROLLED loop over k with the lane masks in
+// registers, so the code holds one shuffle flip block, one shuffle half-cleaner block and one
+// 5-step in-register block instead of a copy per stage (instruction-cache footprint).
+template <int P, typename K>
+__device__ __forceinline__ void bitonic_network(K (&x)[32], const int ul, const int kfirst) {
+  using C = Cfg<P>;
+  constexpr int K1 = 2 * C::LOGP;
+#pragma unroll
+  for (int k = 1; k <= (K1 < 5 ? K1 : 5); k++) {
+    if (k < kfirst) continue;
+    const int m = (1 << k) - 1;
+#pragma unroll
+    for (int r = 0; r < 32; r++)
+      if ((r & (1 << (k - 1))) == 0) ce(x[r], x[r ^ m]);
+#pragma unroll
+    for (int s = k - 2; s >= 0; s--) {
+#pragma unroll
+      for (int r = 0; r < 32; r++)
+        if ((r & (1 << s)) == 0) ce(x[r], x[r | (1 << s)]);
+    }
+  }
+#pragma unroll 1
+  for (int k = (kfirst > 6 ? kfirst : 6); k <= K1; k++) {
+    {  // flip step: pos <-> pos ^ (2^k - 1): partner lane ul ^ lm, partner register r ^ 31
+      const int lm = ((1 << k) - 1) >> 5;
+      const bool keepmin = (ul & ((lm + 1) >> 1)) == 0;
+#pragma unroll
+      for (int r = 0; r < 16; r++) {
+        const K y1 = shfl_x(x[r ^ 31], lm);
+        const K y2 = shfl_x(x[r], lm);
+        x[r] = pick(keepmin, x[r], y1);
+        x[r ^ 31] = pick(keepmin, x[r ^ 31], y2);
+      }
+    }
+#pragma unroll 1
+    for (int s = k - 2; s >= 5; s--) {  // cross-lane half-cleaners
+      const int lm = 1 << (s - 5);
+      const bool keepmin = (ul & lm) == 0;
+#pragma unroll
+      for (int r = 0; r < 32; r++) {
+        const K y = shfl_x(x[r], lm);
+        x[r] = pick(keepmin, x[r], y);
+      }
+    }
+#pragma unroll
+    for (int s = 4; s >= 0; s--) {  // in-lane half-cleaners d = 16..1
+#pragma unroll
+      for (int r = 0; r < 32; r++)
+        if ((r & (1 << s)) == 0) ce(x[r], x[r | (1 << s)]);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+struct Continua {
+  double tausg, taua, taup, tausp, tauc, tausc, gt;
+};
+
+template <int LPU>
+__device__ __forceinline__ double unit_sum(double v) {
+#pragma unroll
+  for (int m = LPU / 2; m >= 1; m >>= 1) v = __dadd_rn(v, shfl_xor_d(v, m));
+  return v;
+}
+
+// Rayleigh, CIA, photolysis, water continuum, particles, custom opacity and the asymmetry
+// parameter of one (column c, bin l, slot) -- A.3, clima_radtran_types.f90:664-757.
+// Items (nray Rayleigh, ncia CIA, npxs cross sections, 2 continuum terms) are dealt to the unit's
+// lanes round-robin; every lane ends with the same totals.
+template <int LPU>
+__device__ __forceinline__ Continua rt_continua(const DevTables &tb, const DevChunk &ch, const int c,
+                                                const int l, const int slot, const int k,
+                                                const int ul) {
+  const int nw = tb.nw, nz = ch.nz, ng = tb.ng;
+  const double *dens = ch.dens + (size_t)c * nz * ng + k;  // dens[i*nz]
+  const double dzk = ch.dz[(size_t)c * nz + k];
+  const int nbr = rt_nbr(tb);
+  const int *ib = ch.ibr + ((size_t)c * nz + slot) * nbr;
+  const double *qb = ch.qbr + ((size_t)c * nz + slot) * nbr;
+  const int rb_xs = 2 * tb.nk;
+  const int rb_cont = rb_xs + tb.ncia + tb.npxs;
+  const int rb_part = rb_cont + 1;
+  const int rb_cust = rb_part + tb.npart;
+  Continua o;
+  double tausg = 0.0, taua = 0.0;
+  const int n_xs = tb.ncia + tb.npxs;
+  const int nitems = tb.nray + n_xs + (tb.has_cont ? 2 : 0);
+#pragma unroll 1
+  for (int it = ul; it < nitems; it += LPU) {
+    if (it < tb.nray) {  // Rayleigh (:686-693)
+      const double col = dens[(size_t)(tb.ray_sp[it] - 1) * nz] * dzk;
+      tausg = tausg + tb.ray_xs[l + (size_t)it * nw] * col;
+    } else if (it < tb.nray + n_xs) {  // CIA (:696-704), photolysis (:707-713)
+      const int i = it - tb.nray;
+      const bool is_cia = i < tb.ncia;
+      const DevXS &x = is_cia ? tb.cia[i] : tb.pxs[i - tb.ncia];
+      double xs;
+      if (x.dim == 0) {
+        xs = x.data[l];
+      } else {
+        const int t0 = ib[rb_xs + i];
+        const double q1 = qb[rb_xs + i], p1 = 1.0 - q1;
+        const double *f = x.data + (size_t)l * x.nt;
+        xs = rt_ten2power(p1 * f[t0] + q1 * f[t0 + 1]);
+      }
+      if (is_cia)
+        taua = taua + xs * dens[(size_t)(x.sp1 - 1) * nz] * dens[(size_t)(x.sp2 - 1) * nz] * dzk;
+      else
+        taua = taua + xs * (dens[(size_t)(x.sp1 - 1) * nz] * dzk);
+    } else {  // water continuum (:716-723): self term, then foreign term
+      const bool self = (it == tb.nray + n_xs);
+      const int t0 = ib[rb_cont];
+      const double q1 = qb[rb_cont], p1 = 1.0 - q1;
+      const double *f = (self ? tb.cont_H2O : tb.cont_foreign) + (size_t)l * tb.cont_nt;
+      const double xs = rt_ten2power(p1 * f[t0] + q1 * f[t0 + 1]);
+      const double dw = dens[(size_t)(tb.cont_LH2O - 1) * nz];
+      if (self) taua = taua + xs * dw * (dw * dzk);
+      else taua = taua + xs * dw * ch.foreign_col[(size_t)c * nz + slot];
+    }
+  }
+  tausg = unit_sum<LPU>(tausg);
+  taua = unit_sum<LPU>(taua);
+  // particles (:733-744)
+  double tausp = 0.0, taup = 0.0;
+  double tausp_1[RT_MAXPART], gtp[RT_MAXPART];
+  if (tb.npart > 0) {
+    const double *rad = ch.radii + (size_t)c * nz * tb.np + k;
+    const double *pdn = ch.pdens + (size_t)c * nz * tb.np + k;
+#pragma unroll 1
+    for (int i = 0; i < tb.npart; i++) {
+      const DevPart &p = tb.part[i];
+      const int ir = ib[rb_part + i];
+      const double q1 = qb[rb_part + i], p1 = 1.0 - q1;
+      const size_t o2 = (size_t)l * p.nr + ir;
+      const double w0p = p1 * p.w0[o2] + q1 * p.w0[o2 + 1];
+      const double qext = p1 * p.qext[o2] + q1 * p.qext[o2 + 1];
+      gtp[i] = p1 * p.gt[o2] + q1 * p.gt[o2 + 1];
+      const double r = rad[(size_t)(p.p_ind - 1) * nz];
+      const double taup_1 = qext * RT_PI * (r * r) * pdn[(size_t)(p.p_ind - 1) * nz] * dzk;
+      taup = taup + taup_1;
+      tausp_1[i] = w0p * taup_1;
+      tausp = tausp + tausp_1[i];
+    }
+  }
+  // custom optical properties (:726-730, 546-572)
+  double tauc = RT_TINY, w0c = RT_TINY, g0c = RT_TINY;
+  if (tb.has_custom) {
+    const int ip = ib[rb_cust];
+    const double q1 = qb[rb_cust], p1 = 1.0 - q1;
+    const size_t o2 = (size_t)l * tb.custom_nP + ip;
+    tauc = (p1 * tb.c_dtau[o2] + q1 * tb.c_dtau[o2 + 1]) * dzk;
+    w0c = p1 * tb.c_w0[o2] + q1 * tb.c_w0[o2 + 1];
+    g0c = p1 * tb.c_g0[o2] + q1 * tb.c_g0[o2 + 1];
+  }
+  const double tausc = w0c * tauc;
+  // asymmetry (:746-757)
+  double gt = 0.0;
+  {
+    const double den = fmax(RT_TAU_MIN, (tausp + tausg + tausc));
+#pragma unroll 1
+    for (int i = 0; i < tb.npart; i++) gt = gt + gtp[i] * tausp_1[i] / den;
+    gt = gt + g0c * tausc / den;
+    gt = fmin(gt, RT_MAX_GT);
+  }
+  o.tausg = tausg; o.taua = taua; o.taup = taup; o.tausp = tausp; o.tauc = tauc; o.tausc = tausc;
+  o.gt = gt;
+  return o;
+}
+
+// Writes value v of table row g into every column of the unit.  Lane `ul` starts at column ul and
+// rotates, so the lanes of a half-warp always hit distinct banks.
+template <int P>
+__device__ __forceinline__ void tbl_put(double *t, const int g, const double v, const int colbase,
+                                        const int ul) {
+  using C = Cfg<P>;
+#pragma unroll
+  for (int cc = 0; cc < C::NC; cc++) t[g * C::CW + colbase + ((cc + ul) & (C::NC - 1))] = v;
+}
+
+// k(g) * column of k-gas jj for the unit's layer: bilinear log10k(P,T) interpolation, lane per
+// g-point (A.2, :649-662 + interp_2d, linear_interpolation_module.F90:322-335), into table `dst`.
+template <int P>
+__device__ __forceinline__ void rt_kgas(const DevTables &tb, const DevChunk &ch, const int c,
+                                        const int l, const int slot, const int k, const int jj,
+                                        const int ul, const int colbase, double *dst) {
+  using C = Cfg<P>;
+  const int G = tb.G, nz = ch.nz;
+  const int nbr = rt_nbr(tb);
+  const int *ib = ch.ibr + ((size_t)c * nz + slot) * nbr;
+  const double *qb = ch.qbr + ((size_t)c * nz + slot) * nbr;
+  const DevK &kt = tb.k[jj];
+  const int ix = ib[2 * jj], iy = ib[2 * jj + 1];
+  const double q1 = qb[2 * jj], q2 = qb[2 * jj + 1];
+  const double p1 = 1.0 - q1, p2 = 1.0 - q2;
+  const double col = ch.dens[(size_t)c * nz * tb.ng + k + (size_t)(kt.sp - 1) * nz] *
+                     ch.dz[(size_t)c * nz + k];  // cols(j,sp) :607
+  const double *f = kt.log10k + (size_t)G * (ix + (size_t)kt.np * (iy + (size_t)kt.nt * l));
+  const size_t sy = (size_t)G * kt.np;
+#pragma unroll
+  for (int t = 0; t < C::GPL; t++) {
+    const int g = ul + C::LPU * t;
+    double v = 0.0;
+    if (g < G) {
+      const double fx1 = p1 * f[g] + q1 * f[g + G];
+      const double fx2 = p1 * f[g + sy] + q1 * f[g + sy + G];
+      v = rt_ten2power(p2 * fx1 + q2 * fx2) * col;  // :660, :816-819 / :828
+    }
+    tbl_put<P>(dst, g, v, colbase, ul);
+  }
+}
+
+// weights_to_bins + rebin (:843-849) of the unit's sorted sequence.  ip[r*32] (this lane's column
+// of the warp's index buffer) holds the element index (i*P + j) of sorted position ul*32 + r; the
+// lanes of the unit own consecutive runs of 32 positions; `tot` is the lane's weight total.
+//   scan  : exclusive scan of the lane totals = cumulative weight at the lane's first element
+//           (weights_to_bins);
+//   walk  : the 32 elements with the running edge; an element inside the current new bin adds
+//           w*tau, one that crosses a new-bin edge is split at the edge (futils rebin); every closed
+//           bin is scaled by 1/width and written to the lane's partial slot.  The gathers of the
+//           next element are issued before the current one is processed.
+// The new bin values are written to table A (all columns of the unit).
+// CERT: also certify that the exact tau_xy sequence is non-decreasing (fast kernel); returns it.
+template <int P, bool FULL, bool CERT>
+__device__ __forceinline__ bool rt_rebin(const typename IdxT<Cfg<P>::IDXB>::type *__restrict__ ip,
+                                         double *tA, const double *tB, double *sp,
+                                         const double *wx, const double *s_E, const double *s_ib,
+                                         const double tot, const int G, const int ul,
+                                         const int mycol, const int colbase) {
+  using C = Cfg<P>;
+  constexpr int LPU = C::LPU, LOGP = C::LOGP, CW = C::CW, SPST = C::SPST;
+  double off = tot;
+#pragma unroll
+  for (int d = 1; d < LPU; d <<= 1) {
+    const double t = __shfl_up_sync(0xffffffffu, off, d, LPU);
+    if (ul >= d) off = __dadd_rn(off, t);
+  }
+  off = __dsub_rn(off, tot);
+  for (int g = 0; g < G; g++) sp[g * SPST + ul] = 0.0;
+  int g = 0;
+#pragma unroll
+  for (int s = P / 2; s > 0; s >>= 1)
+    if (g + s <= G - 1 && s_E[g + s] <= off) g += s;
+  double n1 = s_E[g + 1];
+  double acc = 0.0, o0 = off, prev = -1.0, first = -1.0;
+  bool ok = true;
+  const double *cA = tA + mycol;
+  const double *cB = tB + mycol;
+  unsigned idx = ip[0];
+  double na = cA[(idx >> LOGP) * CW], nb = cB[(idx & (P - 1)) * CW], nw = wx[idx * C::WXC];
+#pragma unroll 4
+  for (int r = 0; r < 32; r++) {
+    const double a = na, b = nb, w = nw;
+    if (r < 31) {
+      idx = ip[(r + 1) * 32];
+      na = cA[(idx >> LOGP) * CW];
+      nb = cB[(idx & (P - 1)) * CW];
+      nw = wx[idx * C::WXC];
+    }
+    if (FULL || w > 0.0) {  // padding elements (ngauss < P) carry zero weight
+      const double tv = __dadd_rn(a, b);  // exact tau_xy (:828)
+      if (CERT) {
+        ok = ok && (tv >= prev);
+        prev = tv;
+        if (r == 0) first = tv;
+      }
+      const double o1 = __dadd_rn(o0, w);
+      if (o1 > n1 && g < G - 1) {
+        double lo = o0;
+        do {  // the element crosses the right edge of new bin g
+          acc = __fma_rn(__dsub_rn(n1, lo), tv, acc);
+          sp[g * SPST + ul] = __dmul_rn(acc, s_ib[g]);
+          acc = 0.0;
+          g++;
+          lo = n1;
+          n1 = s_E[g + 1];
+        } while (o1 > n1 && g < G - 1);
+        acc = __fma_rn(__dsub_rn(o1, lo), tv, acc);
+      } else {
+        acc = __fma_rn(w, tv, acc);
+      }
+      o0 = o1;
+    }
+  }
+  sp[g * SPST + ul] = __dmul_rn(acc, s_ib[g]);
+  if (CERT) {  // lane boundary: this lane's first element against the previous lane's last one
+    const double plast = __shfl_up_sync(0xffffffffu, prev, 1, LPU);
+    if (ul > 0 && first >= 0.0) ok = ok && (first >= plast);
+  }
+  __syncwarp();  // partials complete; every lane is done reading tA
+  double sum[C::GPL];
+#pragma unroll
+  for (int t = 0; t < C::GPL; t++) {
+    const int gg = ul + LPU * t;
+    sum[t] = 0.0;
+    if (gg < G) {
+#pragma unroll
+      for (int q = 0; q < LPU; q++) sum[t] = __dadd_rn(sum[t], sp[gg * SPST + q]);
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < C::GPL; t++) tbl_put<P>(tA, ul + LPU * t, sum[t], colbase, ul);
+  __syncwarp();
+  return ok;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The kernel.  FAST: 32-bit quantised keys + certificate, failed units appended to `worklist`.
+// !FAST: exact 64-bit (value,index) keys; if `worklist` is given, only the listed units.
+//   key32 = [ f : 32-2*log2(P) bits ][ element index pos : 2*log2(P) bits ],
+//   f     = (bits(tau_xy) - bits(min tau_xy)) >> shift, shift chosen so that f of the largest sum
+//           (a_G + b_G; a and b ascend) still fits.
+// f is a monotone quantisation of tau_xy (IEEE-754 bit patterns of non-negative doubles order like
+// integers).  Quantisation can only mis-order sums whose f collide; elements with equal f sit in
+// index order, which is the stable order of `mrgrnk` whenever they are exactly equal or come from
+// the same row.  The walk recomputes every EXACT tau_xy and checks the sequence is non-decreasing;
+// otherwise the unit is redone by the exact kernel.  The fast path therefore returns the same
+// permutation as the reference's stable merge sort or hands the unit over.
+// ---------------------------------------------------------------------------------------------
+template <int P, bool FULL, bool FAST>
+__global__ void __launch_bounds__(128, 3)
+optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevChunk ch,
+                   int *__restrict__ worklist, int *__restrict__ wcount, const int wcap) {
+  using C = Cfg<P>;
+  typedef typename IdxT<C::IDXB>::type idx_t;
+  constexpr int LPU = C::LPU, UPB = C::UPB, LOGP = C::LOGP, CW = C::CW;
+  constexpr int IDXBITS = 2 * LOGP, FB = 32 - IDXBITS;
+  __shared__ double s_w[P];      // wbin, zero padded
+  __shared__ double s_E[P + 1];  // wbin_e
+  __shared__ double s_ib[P];     // 1/(wbin_e(g+1)-wbin_e(g))
+  extern __shared__ double s_dyn[];
+  double *s_wxy = s_dyn;  // [idx][copy]: wxy(j + i*P) = wbin(i)*wbin(j), types_create.f90:216-222
+
+  const int G = FULL ? P : tb.G, nw = tb.nw, nz = ch.nz;
+  for (int i = threadIdx.x; i < P; i += blockDim.x) {
+    s_w[i] = i < G ? tb.wbin[i] : 0.0;
+    s_ib[i] = i < G ? tb.inv_dw[i] : 0.0;
+  }
+  for (int i = threadIdx.x; i < P + 1; i += blockDim.x) s_E[i] = tb.wbin_e[i < G ? i : G];
+  for (int i = threadIdx.x; i < C::N * C::WXC; i += blockDim.x) {
+    const int e = i / C::WXC, a = e >> LOGP, b = e & (P - 1);
+    s_wxy[i] = (a < G && b < G) ? __dmul_rn(tb.wbin[a], tb.wbin[b]) : 0.0;
+  }
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int ul = lane & (LPU - 1);   // lane within unit
+  const int ub = threadIdx.x / LPU;  // unit within block
+  const int mycol = (LPU == 32) ? (lane & 15) : lane;
+  const int colbase = (LPU == 32) ? 0 : (lane - ul);
+  char *wbase = (char *)(s_dyn + C::N * C::WXC) + (size_t)warp * C::WARP_BYTES;
+  double *tA = (double *)wbase;  // running mixture a(i), [row][column]
+  double *tB = tA + C::TBL;      // new gas b(j)
+  double *sp = tB + C::TBL + (ub % C::UPW) * C::SPU;
+  idx_t *ip = (idx_t *)(tB + C::TBL + C::UPW * C::SPU) + lane;
+  const double *wx = s_wxy + (lane & (C::WXC - 1));
+
+  long long uid = (long long)blockIdx.x * UPB + ub;
+  const int cap = ch.nslot_cap;
+  bool active = true;
+  if (!FAST && worklist) {
+    int n = *wcount;
+    if (n > wcap) n = wcap;
+    if (uid < n) uid = worklist[uid]; else { active = false; uid = 0; }
+  }
+  int slot = (int)(uid % cap);
+  const int l = (int)((uid / cap) % nw);
+  const long long cl = uid / ((long long)cap * nw);
+  if (cl >= ch.ncol) active = false;
+  const int c = cl < ch.ncol ? (int)cl : ch.ncol - 1;
+  const int nsl = ch.nslots[c];
+  if (slot >= nsl) {
+    active = false;
+    slot = nsl - 1;
+  }
+  if (__all_sync(0xffffffffu, !active)) return;
+
+  const int k = ch.layer_of_slot[(size_t)c * nz + slot];  // ground-first layer index
+  const Continua q = rt_continua<LPU>(tb, ch, c, l, slot, k, ul);
+  const unsigned umask = (LPU == 32 ? 0xffffffffu : ((1u << LPU) - 1u)) << (lane & ~(LPU - 1));
+  bool unit_ok = true;
+  const int kfirst = (FAST || tb.rows_sorted) ? LOGP + 1 : 1;
+  const double *cA = tA + mycol, *cB = tB + mycol;
+
+  for (int jj = 0; jj < tb.nk; jj++) {
+    rt_kgas<P>(tb, ch, c, l, slot, k, jj, ul, colbase, jj == 0 ? tA : tB);
+    __syncwarp();
+    if (jj == 0) continue;
+
+    // ---- keys: pos = ul*32 + r ;  i = pos >> LOGP (running mixture), j = pos & (P-1) (new gas)
+    double tot = 0.0;
+    if (FAST) {
+      const unsigned long long base = (unsigned long long)__double_as_longlong(cA[0] + cB[0]);
+      const unsigned long long top =
+          (unsigned long long)__double_as_longlong(cA[(G - 1) * CW] + cB[(G - 1) * CW]);
+      const unsigned long long range = top - base;
+      const int nb = 64 - __clzll((long long)range);  // bit length (0 for range == 0)
+      const int shift = nb > FB ? nb - FB : 0;
+      unsigned x[32];
+#pragma unroll
+      for (int r = 0; r < 32; r++) {
+        const int pos = ul * 32 + r;
+        const int i = pos >> LOGP, j = pos & (P - 1);
+        const double v = cA[i * CW] + cB[j * CW];  // :828 tau_xy
+        const unsigned f = (unsigned)(((unsigned long long)__double_as_longlong(v) - base) >> shift);
+        const unsigned key = (f << IDXBITS) | (unsigned)pos;
+        x[r] = (FULL || ((i < G) && (j < G))) ? key : 0xffffffffu;
+      }
+      bitonic_network<P, unsigned>(x, ul, kfirst);
+#pragma unroll
+      for (int r = 0; r < 32; r++) {
+        const unsigned idx = x[r] & C::IDXM;
+        ip[r * 32] = (idx_t)idx;
+        tot = __dadd_rn(tot, wx[idx * C::WXC]);
+      }
+    } else {
+      double x[32];
+#pragma unroll
+      for (int r = 0; r < 32; r++) {
+        const int pos = ul * 32 + r;
+        const int i = pos >> LOGP, j = pos & (P - 1);
+        const double v = cA[i * CW] + cB[j * CW];  // :828 tau_xy
+        const unsigned long long bits = (FULL || ((i < G) && (j < G)))
+                                            ? (unsigned long long)__double_as_longlong(v)
+                                            : 0x7fe0000000000000ull;  // huge, finite
+        x[r] = __longlong_as_double(
+            (long long)((bits & ~(unsigned long long)C::IDXM) | (unsigned long long)pos));
+      }
+      bitonic_network<P, double>(x, ul, kfirst);
+#pragma unroll
+      for (int r = 0; r < 32; r++) {
+        const unsigned idx = (unsigned)((unsigned long long)__double_as_longlong(x[r])) & C::IDXM;
+        ip[r * 32] = (idx_t)idx;
+        tot = __dadd_rn(tot, wx[idx * C::WXC]);
+      }
+    }
+    __syncwarp();
+    const bool ok = rt_rebin<P, FULL, FAST>(ip, tA, tB, sp, wx, s_E, s_ib, tot, G, ul, mycol, colbase);
+    if (FAST) {
+      const unsigned bal = __ballot_sync(0xffffffffu, ok);
+      unit_ok = unit_ok && ((bal & umask) == umask);
+    }
+  }
+
+  // ---- total tau, w0 clamp, band tau, asymmetry of the unit (:856-886) -> HBM (slot-indexed)
+  const size_t obase = (((size_t)c * tb.nw + l) * ch.nslot_cap + slot);
+#pragma unroll
+  for (int t = 0; t < C::GPL; t++) {
+    const int gg = ul + LPU * t;
+    if (gg < G) {
+      const double tau =
+          __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(q.tausg, q.taua), q.taup), cA[gg * CW]), q.tauc);
+      double w0 = 0.0;
+      if (!(tau <= RT_TAU_MIN)) w0 = fmin(RT_MAX_W0, (q.tausg + q.tausp + q.tausc) / tau);
+      sp[gg] = tau;
+      if (active) {
+        ch.tau[obase * G + gg] = tau;
+        ch.w0[obase * G + gg] = w0;
+      }
+    }
+  }
+  __syncwarp();
+  if (ul == 0 && active) {
+    double tbnd = 0.0;
+#pragma unroll 4
+    for (int gg = 0; gg < G; gg++) tbnd = __dadd_rn(tbnd, __dmul_rn(sp[gg], s_w[gg]));
+    ch.tband[obase] = tbnd;
+    ch.gt[obase] = q.gt;
+  }
+  if (FAST && !unit_ok && active && ul == 0) {
+    const int p = atomicAdd(wcount, 1);
+    if (p < wcap) worklist[p] = (int)uid;
+  }
+}
+
+}  // namespace rorr
