@@ -575,6 +575,10 @@ void clima_rt_create(const clima_rt_tables *tables, const clima_rt_params *param
       h->rorr_exact_only = (m && std::string(m) == "exact") ? 1 : 0;
     }
     build_tables(*h, tables);
+    {
+      const char *m = std::getenv("CLIMA_RT_RORR_NOSKIP");  // debug: always sort (no closed-form merges)
+      if (m && m[0] == '1') h->tb.pad0 |= 1;
+    }
     upload_params(*h, params);
     *handle = h;
   } catch (const CudaError &e) {

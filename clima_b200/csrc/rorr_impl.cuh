@@ -46,12 +46,11 @@ struct Cfg {
   static constexpr int NC = (LPU == 32 ? 16 : LPU);  // table columns of one unit
   static constexpr int CW = (LPU == 32 ? 16 : 32);   // table columns per warp
   static constexpr int TBL = P * CW;                 // doubles per table per warp
-  static constexpr int SPST = LPU + 1;               // partial-sum row stride (bank spread)
-  static constexpr int SPU = P * SPST;               // partial-sum doubles per unit
+  static constexpr int SPU = P + 2;                  // edge-integral doubles per unit (G+1, padded)
   static constexpr int WXC = 4;                      // copies of the wxy table
   static constexpr int IDXB = (N <= 256 ? 1 : 2);    // bytes per sorted-index entry
   static constexpr unsigned IDXM = (unsigned)(N - 1);
-  // dynamic shared memory: [wxy N*WXC doubles][per warp: tA, tB, partials, idx]
+  // dynamic shared memory: [wxy N*WXC doubles][per warp: tA, tB, edge integrals, idx]
   static constexpr size_t WARP_BYTES =
       (size_t)(2 * TBL + UPW * SPU) * sizeof(double) + (size_t)32 * 32 * IDXB;
   static constexpr size_t BLOCK_BYTES = (size_t)N * WXC * sizeof(double) + 4 * WARP_BYTES;
@@ -307,34 +306,43 @@ __device__ __forceinline__ void rt_kgas(const DevTables &tb, const DevChunk &ch,
 // lanes of the unit own consecutive runs of 32 positions; `tot` is the lane's weight total.
 //   scan  : exclusive scan of the lane totals = cumulative weight at the lane's first element
 //           (weights_to_bins);
-//   walk  : the 32 elements with the running edge; an element inside the current new bin adds
-//           w*tau, one that crosses a new-bin edge is split at the edge (futils rebin); every closed
-//           bin is scaled by 1/width and written to the lane's partial slot.  The gathers of the
-//           next element are issued before the current one is processed.
+//   walk  : the 32 elements with the running cumulative weight o and the running integral
+//           I = sum w*tau.  The rebinned value of new bin g is (I(E_g+1) - I(E_g)) / (E_g+1 - E_g)
+//           (futils rebin: overlap-weighted mean), so the walk only has to record I at the G-1
+//           interior edges: the element that contains edge E is split there,
+//           I(E) = I_before + (E - o_before) * tau.  Every edge lies in exactly one element of one
+//           lane (lane l owns (off_l, off_l+1]), hence one writer per edge, no partial sums, no
+//           atomics.  I is lane-relative during the walk; the lane offsets come from a second scan.
+//           The gathers of the next element are issued before the current one is processed.
 // The new bin values are written to table A (all columns of the unit).
 // CERT: also certify that the exact tau_xy sequence is non-decreasing (fast kernel); returns it.
 template <int P, bool FULL, bool CERT>
 __device__ __forceinline__ bool rt_rebin(const typename IdxT<Cfg<P>::IDXB>::type *__restrict__ ip,
-                                         double *tA, const double *tB, double *sp,
+                                         double *tA, const double *tB, double *sI,
                                          const double *wx, const double *s_E, const double *s_ib,
                                          const double tot, const int G, const int ul,
                                          const int mycol, const int colbase) {
   using C = Cfg<P>;
-  constexpr int LPU = C::LPU, LOGP = C::LOGP, CW = C::CW, SPST = C::SPST;
+  constexpr int LPU = C::LPU, LOGP = C::LOGP, CW = C::CW;
   double off = tot;
 #pragma unroll
   for (int d = 1; d < LPU; d <<= 1) {
     const double t = __shfl_up_sync(0xffffffffu, off, d, LPU);
     if (ul >= d) off = __dadd_rn(off, t);
   }
-  off = __dsub_rn(off, tot);
-  for (int g = 0; g < G; g++) sp[g * SPST + ul] = 0.0;
-  int g = 0;
+  // lane l owns the edges in (off_l, off_l+1]: its last element ends exactly at the next lane's start
+  // (bit-exactly: off of lane l+1 IS off_next of lane l, otherwise an edge within rounding of a
+  // lane boundary -- common: E_8 = 0.5 = the weight of the first 8 rows -- gets two owners or none)
+  const double off_next = off;
+  off = __shfl_up_sync(0xffffffffu, off_next, 1, LPU);
+  if (ul == 0) off = 0.0;
+  int g = 0;  // largest g with E[g] < off  (E[g+1] >= off)
 #pragma unroll
   for (int s = P / 2; s > 0; s >>= 1)
-    if (g + s <= G - 1 && s_E[g + s] <= off) g += s;
+    if (g + s <= G - 1 && s_E[g + s] < off) g += s;
+  const int g_first = g;
   double n1 = s_E[g + 1];
-  double acc = 0.0, o0 = off, prev = -1.0, first = -1.0;
+  double I = 0.0, o0 = off, prev = -1.0, first = -1.0;
   bool ok = true;
   const double *cA = tA + mycol;
   const double *cB = tB + mycol;
@@ -349,49 +357,47 @@ __device__ __forceinline__ bool rt_rebin(const typename IdxT<Cfg<P>::IDXB>::type
       nb = cB[(idx & (P - 1)) * CW];
       nw = wx[idx * C::WXC];
     }
-    if (FULL || w > 0.0) {  // padding elements (ngauss < P) carry zero weight
-      const double tv = __dadd_rn(a, b);  // exact tau_xy (:828)
-      if (CERT) {
+    const double tv = __dadd_rn(a, b);  // exact tau_xy (:828); padding elements: w = 0
+    if (CERT) {
+      if (FULL || w > 0.0) {
         ok = ok && (tv >= prev);
         prev = tv;
         if (r == 0) first = tv;
       }
-      const double o1 = __dadd_rn(o0, w);
-      if (o1 > n1 && g < G - 1) {
-        double lo = o0;
-        do {  // the element crosses the right edge of new bin g
-          acc = __fma_rn(__dsub_rn(n1, lo), tv, acc);
-          sp[g * SPST + ul] = __dmul_rn(acc, s_ib[g]);
-          acc = 0.0;
-          g++;
-          lo = n1;
-          n1 = s_E[g + 1];
-        } while (o1 > n1 && g < G - 1);
-        acc = __fma_rn(__dsub_rn(o1, lo), tv, acc);
-      } else {
-        acc = __fma_rn(w, tv, acc);
-      }
-      o0 = o1;
     }
+    const double o1 = (r == 31 && ul < LPU - 1) ? off_next : __dadd_rn(o0, w);
+    while (o1 > n1 && g < G - 1) {  // the element contains the right edge of new bin g
+      g++;
+      sI[g] = __fma_rn(__dsub_rn(n1, o0), tv, I);
+      n1 = s_E[g + 1];
+    }
+    I = __fma_rn(w, tv, I);
+    o0 = o1;
   }
-  sp[g * SPST + ul] = __dmul_rn(acc, s_ib[g]);
+  // lane offsets of the integral
+  double Ioff = I;
+#pragma unroll
+  for (int d = 1; d < LPU; d <<= 1) {
+    const double t = __shfl_up_sync(0xffffffffu, Ioff, d, LPU);
+    if (ul >= d) Ioff = __dadd_rn(Ioff, t);
+  }
+  if (ul == LPU - 1) sI[G] = Ioff;  // I(E_G) = the whole integral
+  if (ul == 0) sI[0] = 0.0;
+  Ioff = __shfl_up_sync(0xffffffffu, Ioff, 1, LPU);
+  if (ul == 0) Ioff = 0.0;
+  for (int e = g_first + 1; e <= g; e++) sI[e] = __dadd_rn(sI[e], Ioff);
   if (CERT) {  // lane boundary: this lane's first element against the previous lane's last one
     const double plast = __shfl_up_sync(0xffffffffu, prev, 1, LPU);
     if (ul > 0 && first >= 0.0) ok = ok && (first >= plast);
   }
-  __syncwarp();  // partials complete; every lane is done reading tA
-  double sum[C::GPL];
+  __syncwarp();  // edge integrals complete; every lane is done reading tA
 #pragma unroll
   for (int t = 0; t < C::GPL; t++) {
     const int gg = ul + LPU * t;
-    sum[t] = 0.0;
-    if (gg < G) {
-#pragma unroll
-      for (int q = 0; q < LPU; q++) sum[t] = __dadd_rn(sum[t], sp[gg * SPST + q]);
-    }
+    double v = 0.0;
+    if (gg < G) v = __dmul_rn(__dsub_rn(sI[gg + 1], sI[gg]), s_ib[gg]);
+    tbl_put<P>(tA, gg, v, colbase, ul);
   }
-#pragma unroll
-  for (int t = 0; t < C::GPL; t++) tbl_put<P>(tA, ul + LPU * t, sum[t], colbase, ul);
   __syncwarp();
   return ok;
 }
@@ -443,7 +449,7 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   char *wbase = (char *)(s_dyn + C::N * C::WXC) + (size_t)warp * C::WARP_BYTES;
   double *tA = (double *)wbase;  // running mixture a(i), [row][column]
   double *tB = tA + C::TBL;      // new gas b(j)
-  double *sp = tB + C::TBL + (ub % C::UPW) * C::SPU;
+  double *sI = tB + C::TBL + (ub % C::UPW) * C::SPU;  // I(E_g), g = 0..G
   idx_t *ip = (idx_t *)(tB + C::TBL + C::UPW * C::SPU) + lane;
   const double *wx = s_wxy + (lane & (C::WXC - 1));
 
@@ -478,6 +484,46 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     rt_kgas<P>(tb, ch, c, l, slot, k, jj, ul, colbase, jj == 0 ? tA : tB);
     __syncwarp();
     if (jj == 0) continue;
+
+    // ---- merges that need no sort.  If the rows do not interleave (a_i + b_G <= a_i+1 + b_1 for
+    // every i) the stable sorted order IS the row-major index order, row i covers exactly the
+    // cumulative-weight interval of new bin i, and the rebin (:843-849) returns
+    // a_i * sum_j(w_j) + sum_j(w_j b_j) = a_i + <b>; symmetrically b_j + <a> when the columns do not
+    // interleave.  (The reference's result differs from the closed form only by the rounding of
+    // its 256-term cumulative weights, O(1e-15) relative.)  Taken when every unit of the warp
+    // qualifies, so that the warp skips the sort as a whole.
+    {
+      const double a1 = cA[0], aG = cA[(G - 1) * CW], b1 = cB[0], bG = cB[(G - 1) * CW];
+      bool rowmaj = true, colmaj = true;
+      double ag[C::GPL], bg[C::GPL];
+#pragma unroll
+      for (int t = 0; t < C::GPL; t++) {
+        const int g = ul + LPU * t;
+        const int gn = g + 1 < P ? g + 1 : g;
+        ag[t] = cA[g * CW];
+        bg[t] = cB[g * CW];
+        if (g < G - 1) {
+          rowmaj = rowmaj && (ag[t] + bG <= cA[gn * CW] + b1);
+          colmaj = colmaj && (bg[t] + aG <= cB[gn * CW] + a1);
+        }
+      }
+      const unsigned br = __ballot_sync(0xffffffffu, rowmaj), bc = __ballot_sync(0xffffffffu, colmaj);
+      const bool urow = (br & umask) == umask, ucol = (bc & umask) == umask;
+      if (!(tb.pad0 & 1) && __all_sync(0xffffffffu, urow || ucol)) {
+        double mean = 0.0;  // <b> or <a>, summed in g order
+        const double *cm = urow ? cB : cA;
+        for (int g = 0; g < G; g++) mean = __fma_rn(s_w[g], cm[g * CW], mean);
+        __syncwarp();
+#pragma unroll
+        for (int t = 0; t < C::GPL; t++) {
+          const int g = ul + LPU * t;
+          const double v = g < G ? __dadd_rn(urow ? ag[t] : bg[t], mean) : 0.0;
+          tbl_put<P>(tA, g, v, colbase, ul);
+        }
+        __syncwarp();
+        continue;
+      }
+    }
 
     // ---- keys: pos = ul*32 + r ;  i = pos >> LOGP (running mixture), j = pos & (P-1) (new gas)
     double tot = 0.0;
@@ -527,7 +573,7 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
       }
     }
     __syncwarp();
-    const bool ok = rt_rebin<P, FULL, FAST>(ip, tA, tB, sp, wx, s_E, s_ib, tot, G, ul, mycol, colbase);
+    const bool ok = rt_rebin<P, FULL, FAST>(ip, tA, tB, sI, wx, s_E, s_ib, tot, G, ul, mycol, colbase);
     if (FAST) {
       const unsigned bal = __ballot_sync(0xffffffffu, ok);
       unit_ok = unit_ok && ((bal & umask) == umask);
@@ -544,7 +590,7 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
           __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(q.tausg, q.taua), q.taup), cA[gg * CW]), q.tauc);
       double w0 = 0.0;
       if (!(tau <= RT_TAU_MIN)) w0 = fmin(RT_MAX_W0, (q.tausg + q.tausp + q.tausc) / tau);
-      sp[gg] = tau;
+      sI[gg] = tau;
       if (active) {
         ch.tau[obase * G + gg] = tau;
         ch.w0[obase * G + gg] = w0;
@@ -555,7 +601,7 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   if (ul == 0 && active) {
     double tbnd = 0.0;
 #pragma unroll 4
-    for (int gg = 0; gg < G; gg++) tbnd = __dadd_rn(tbnd, __dmul_rn(sp[gg], s_w[gg]));
+    for (int gg = 0; gg < G; gg++) tbnd = __dadd_rn(tbnd, __dmul_rn(sI[gg], s_w[gg]));
     ch.tband[obase] = tbnd;
     ch.gt[obase] = q.gt;
   }

@@ -252,3 +252,24 @@ def test_rorr_worklist_overflow_falls_back_to_exact(monkeypatch):
     ro = OracleRadtran(tb, pr).radiate_batch(c2)
     rg2 = {k: (v[..., :2] if v.ndim > 1 else v[:2]) for k, v in rg.items()}
     compare(rg2, ro, spectral=False)
+
+
+def test_rorr_closed_form_merges_match_the_sorted_path(monkeypatch):
+    """Merges whose rows (or columns) do not interleave skip the sort and use the closed form
+    a_i + <b> (rorr_impl.cuh).  With CLIMA_RT_RORR_NOSKIP=1 every merge is sorted and rebinned; the
+    two must agree to rounding (the sorted path carries the rounding of its 256-term cumulative
+    weights), far inside the 1e-9 contract, on a batch where both kinds of merge occur."""
+    tb, pr, cols = small_case(G=16, nw=12, nz=10, ncol=3, nk=3)
+    # make one gas negligible so that its merge is row-major for sure
+    tb.k[2].log10k[...] -= 12.0
+    g = Radtran(tb, pr)
+    r1 = g.radiate_batch(cols, spectral=True)
+    t1 = g.get_opacity(cols["nz"], icol=1)[0]
+    monkeypatch.setenv("CLIMA_RT_RORR_NOSKIP", "1")
+    g2 = Radtran(tb, pr)
+    r2 = g2.radiate_batch(cols, spectral=True)
+    t2 = g2.get_opacity(cols["nz"], icol=1)[0]
+    assert np.max(np.abs(t1 - t2) / np.abs(t2)) < 1e-12
+    assert not np.array_equal(t1, t2)  # the closed form was actually taken somewhere
+    compare(r1, r2, tol=1e-12)
+    compare(r1, OracleRadtran(tb, pr).radiate_batch(cols, spectral=True))
