@@ -32,6 +32,10 @@
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 
+#ifndef RORR_MIN_BLOCKS
+#define RORR_MIN_BLOCKS 4
+#endif
+
 namespace rorr {
 
 template <int P>
@@ -416,7 +420,7 @@ __device__ __forceinline__ bool rt_rebin(const typename IdxT<Cfg<P>::IDXB>::type
 // permutation as the reference's stable merge sort or hands the unit over.
 // ---------------------------------------------------------------------------------------------
 template <int P, bool FULL, bool FAST>
-__global__ void __launch_bounds__(128, 3)
+__global__ void __launch_bounds__(128, RORR_MIN_BLOCKS)
 optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevChunk ch,
                    int *__restrict__ worklist, int *__restrict__ wcount, const int wcap) {
   using C = Cfg<P>;
