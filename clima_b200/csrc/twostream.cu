@@ -117,16 +117,27 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
       cprev = (-e2) / e1;
       dprev = (0.0 - cm0) / e1;
     }
+    // Raw inputs are prefetched one layer ahead (slot index two layers ahead, so that the dependent
+    // tau/w0/g loads can be issued a full iteration before they are needed): the sweep was
+    // latency-bound on the chain slot -> tau -> coefficients (r1e profile: 53 % long-scoreboard).
+    auto lslot = [&](int i) { return sol[nz - 1 - (i < nz ? i : nz - 1)]; };  // slot of layer i (clamped)
+    int s1 = lslot(1), s2 = lslot(2);
+    double t1 = tau_p[(size_t)s1 * G], w1 = w0_p[(size_t)s1 * G], g1 = gt_p[s1];
+    double B1 = bp[nz >= 1 ? 1 : 0], B2 = bp[nz >= 2 ? 2 : nz];
     for (int i = 0; i < nz; i++) {
+      // issue the loads of layer i+2 / level i+3
+      const int s3 = lslot(i + 3);
+      const double t2 = tau_p[(size_t)s2 * G], w2 = w0_p[(size_t)s2 * G], g2 = gt_p[s2];
+      const double B3 = bp[i + 3 <= nz ? i + 3 : nz];
       double c1, d1;              // row 2i+1 (0-based)
       double cn = 0.0, dn = 0.0;  // row 2i+2
       double e1n = 0, e2n = 0, e3n = 0, e4n = 0, cpbn = 0, cmbn = 0, cgamn = 0, wrkn = 0, taun = 0, g12n = 0;
       if (i < nz - 1) {
-        const int slotn = sol[nz - 2 - i];
+        const int slotn = s1;
         if (slotn == slot) {
           cgamn = cgam; wrkn = wrk; e1n = e1; e2n = e2; e3n = e3; e4n = e4; taun = tau_i; g12n = g12;
         } else {
-          const double tau = tau_p[(size_t)slotn * G], w0 = w0_p[(size_t)slotn * G], gt = gt_p[slotn];
+          const double tau = t1, w0 = w1, gt = g1;
           const double gam1 = 2.0 - w0 * (1.0 + gt), gam2 = w0 * (1.0 - gt);
           const double lam = sqrt(gam1 * gam1 - gam2 * gam2);
           cgamn = gam2 / (gam1 + lam);
@@ -137,7 +148,7 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
           slot = slotn;
         }
         double b0, b1;
-        const double Bt = bp[i + 1], Bb = bp[i + 2];
+        const double Bt = B1, Bb = B2;
         if (taun <= tmin) { b0 = 0.5 * (Bt + Bb); b1 = 0.0; } else { b0 = Bt; b1 = (Bb - b0) / taun; }
         const double cp0n = norm * (b0 + b1 * g12n);
         cpbn = norm * (b0 + b1 * (taun + g12n));
@@ -184,6 +195,7 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
       s[4 * nres] = cgam; s[5 * nres] = wrk; s[6 * nres] = cpb; s[7 * nres] = cmb;
       e1 = e1n; e2 = e2n; e3 = e3n; e4 = e4n; cpb = cpbn; cmb = cmbn; cgam = cgamn; wrk = wrkn;
       tau_i = taun; g12 = g12n; cprev = cn; dprev = dn;
+      s1 = s2; s2 = s3; t1 = t2; w1 = w2; g1 = g2; B1 = B2; B2 = B3;
     }
 
     // ---- back substitution (:311-313) + fluxes (:288-293) + g-weights (radiate.f90:122-126)
@@ -192,10 +204,17 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
     const bool writer = gactive && gl == 0;
     double xnext = 0.0;
     double y1 = 0, y2 = 0, ee3 = 0, ee4 = 0;
-    for (int i = nz - 1; i >= 0; i--) {
-      const double *s = scr + (size_t)i * IR_ITEMS * nres;
-      const double c0 = s[0], d0 = s[nres], c1 = s[2 * nres], d1 = s[3 * nres];
-      const double cg = s[4 * nres], wk = s[5 * nres], pb = s[6 * nres], mb = s[7 * nres];
+    // the 8 scratch values of a layer do not depend on the recurrence: keep the loads two layers
+    // ahead of the arithmetic (rotating register buffers, loop unrolled by 3)
+    double q[3][IR_ITEMS];
+    auto ld = [&](double (&b)[IR_ITEMS], int i) {
+      const double *s = scr + (size_t)(i > 0 ? i : 0) * IR_ITEMS * nres;
+#pragma unroll
+      for (int t = 0; t < IR_ITEMS; t++) b[t] = s[(size_t)t * nres];
+    };
+    auto bk = [&](const double (&b)[IR_ITEMS], int i) {
+      const double c0 = b[0], d0 = b[1], c1 = b[2], d1 = b[3];
+      const double cg = b[4], wk = b[5], pb = b[6], mb = b[7];
       const double x1 = d1 - c1 * xnext;  // c1 == 0 for the last row
       const double x0 = d0 - c0 * x1;
       y1 = x0; y2 = x1;
@@ -206,6 +225,14 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
       const double su = group_sum<P>(fup * wg), sd = group_sum<P>(fdn * wg);
       if (writer) { fup_o[nz - 1 - i] = su; fdn_o[nz - 1 - i] = sd; }
       xnext = x0;
+    };
+    ld(q[0], nz - 1);
+    ld(q[1], nz - 2);
+    for (int i = nz - 1; i >= 0; i -= 3) {
+      ld(q[2], i - 2);
+      bk(q[0], i);
+      if (i - 1 >= 0) { ld(q[0], i - 3); bk(q[1], i - 1); }
+      if (i - 2 >= 0) { ld(q[1], i - 4); bk(q[2], i - 2); }
     }
     {
       const double fup = ((y1 * ee3 - y2 * ee4) + cp0_top);  // :288
@@ -217,7 +244,7 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
 
 // --------------------------------------------------------------------------------------- solar
 template <int P, int ZC>
-__global__ void __launch_bounds__(TS_THREADS)
+__global__ void __launch_bounds__(TS_THREADS, 3)
 twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevParams pr,
                        const __grid_constant__ DevChunk ch, const __grid_constant__ DevFlux fx,
                        const int ocol_bcast, const int zbeg, const int accumulate) {
@@ -268,8 +295,7 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
     double CP0_top = 0.0, FDN_top = 0.0, AM_top = 0.0;
     int slot = -1;
 
-    auto layer_coeffs = [&](const int s) {
-      const double tau_in = tau_p[(size_t)s * G], w0_in = w0_p[(size_t)s * G], gt_in = gt_p[s];
+    auto layer_coeffs = [&](const double tau_in, const double w0_in, const double gt_in) {
       // delta-Eddington scaling (:38-40)
       const double f = 1.0 - w0_in * gt_in * gt_in;
       const double tau = tau_in * f;
@@ -297,7 +323,11 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
 
     // ---- top layer and row 1
     slot = sol[nz - 1];
-    layer_coeffs(slot);
+    layer_coeffs(tau_p[(size_t)slot * G], w0_p[(size_t)slot * G], gt_p[slot]);
+    // raw inputs prefetched one layer ahead, slot index two layers ahead (see the IR kernel)
+    auto lslot = [&](int i) { return sol[nz - 1 - (i < nz ? i : nz - 1)]; };
+    int s1 = lslot(1), s2 = lslot(2);
+    double t1 = tau_p[(size_t)s1 * G], w1 = w0_p[(size_t)s1 * G], g1 = gt_p[s1];
     double Dprev = 0.0;  // sum_z w_z d'_z of row 2i
 #pragma unroll
     for (int z = 0; z < ZC; z++) {
@@ -315,6 +345,8 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
     cprev = (-e2) / e1;
 
     for (int i = 0; i < nz; i++) {
+      const int s3 = lslot(i + 3);
+      const double t2 = tau_p[(size_t)s2 * G], w2 = w0_p[(size_t)s2 * G], g2 = gt_p[s2];
       // layer i ("o"ld) values; layer_coeffs() overwrites e1..e4/cgam/wrk/fp/fm/ex with layer i+1
       const double e1o = e1, e2o = e2, e3o = e3, e4o = e4, cgo = cgam, wko = wrk;
       double c1, cn = 0.0, D1 = 0.0, Dn = 0.0;
@@ -327,9 +359,9 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
         DIRU += wz[z] * et[z];           // direct(i+1)/u0
       }
       if (i < nz - 1) {
-        const int slotn = sol[nz - 2 - i];
+        const int slotn = s1;
         if (slotn != slot) {
-          layer_coeffs(slotn);
+          layer_coeffs(t1, w1, g1);
           slot = slotn;
         }
         // even Fortran row l=2i (:107-112) -> 0-based row 2i+1 ; (e1..e4 = layer i+1)
@@ -372,6 +404,7 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       s[8 * nres] = DIR; s[9 * nres] = DIRU;
       cprev = cn;
       Dprev = Dn;
+      s1 = s2; s2 = s3; t1 = t2; w1 = w2; g1 = g2;
     }
 
     // ---- ONE back substitution for the zenith-weighted solution, fluxes (:135-148), g-weights
@@ -396,11 +429,17 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       }
     };
     double xnext = 0.0, y1 = 0, y2 = 0, ee3 = 0, ee4 = 0;
-    for (int i = nz - 1; i >= 0; i--) {
-      const double *s = scr + (size_t)i * SOL_ITEMS * nres;
-      const double c0 = s[0], d0 = s[nres], c1 = s[2 * nres], d1 = s[3 * nres];
-      const double cg = s[4 * nres], wk = s[5 * nres], pb = s[6 * nres], mb = s[7 * nres];
-      const double dir = s[8 * nres], diru = s[9 * nres];
+    // scratch loads two layers ahead of the arithmetic (rotating register buffers, unrolled by 3)
+    double q[3][SOL_ITEMS];
+    auto ld = [&](double (&b)[SOL_ITEMS], int i) {
+      const double *s = scr + (size_t)(i > 0 ? i : 0) * SOL_ITEMS * nres;
+#pragma unroll
+      for (int t = 0; t < SOL_ITEMS; t++) b[t] = s[(size_t)t * nres];
+    };
+    auto bk = [&](const double (&b)[SOL_ITEMS], int i) {
+      const double c0 = b[0], d0 = b[1], c1 = b[2], d1 = b[3];
+      const double cg = b[4], wk = b[5], pb = b[6], mb = b[7];
+      const double dir = b[8], diru = b[9];
       const double x1 = d1 - c1 * xnext;
       const double x0 = d0 - c0 * x1;
       y1 = x0; y2 = x1;
@@ -411,6 +450,14 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       const double fdn = (y1 * ee3 + y2 * ee4 + mb) + dir;                           // :147
       emit(nz - 1 - i, fup, fdn, am);
       xnext = x0;
+    };
+    ld(q[0], nz - 1);
+    ld(q[1], nz - 2);
+    for (int i = nz - 1; i >= 0; i -= 3) {
+      ld(q[2], i - 2);
+      bk(q[0], i);
+      if (i - 1 >= 0) { ld(q[0], i - 3); bk(q[1], i - 1); }
+      if (i - 2 >= 0) { ld(q[1], i - 4); bk(q[2], i - 2); }
     }
     {
       const double up = (y1 * ee3 - y2 * ee4) + CP0_top;  // :143

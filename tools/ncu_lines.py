@@ -4,10 +4,12 @@ usage: tools/ncu_lines.py report.ncu-rep kernel_regex [topN]"""
 import csv, io, subprocess, sys
 rep, kre = sys.argv[1], sys.argv[2]
 top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass",
-                      "--kernel-name", "regex:" + kre], capture_output=True, text=True).stdout
+import re
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"],
+                     capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
-hi = next(i for i, r in enumerate(rows) if r and r[0] == "Line No")
+fi = next(i for i, r in enumerate(rows) if r and r[0] in ("Function Name", "Kernel Name") and re.search(kre, r[1]))
+hi = next(i for i, r in enumerate(rows) if i > fi and r and r[0] == "Line No")
 hdr = rows[hi]
 ie, ismp = hdr.index("Instructions Executed"), hdr.index("# Samples")
 iw, iwi = hdr.index("L1 Wavefronts Shared"), hdr.index("L1 Wavefronts Shared Ideal")

@@ -5,11 +5,11 @@ import collections, csv, io, re, subprocess, sys
 
 rep, kre = sys.argv[1], sys.argv[2]
 nw = float(sys.argv[3]) if len(sys.argv) > 3 else None
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kre],
-                     capture_output=True, text=True).stdout
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
-# the first kernel block only
-hi = next(i for i, r in enumerate(rows) if "Source" in r and "Instructions Executed" in r)
+# the first kernel block whose "Function Name" matches the regex
+fi = next(i for i, r in enumerate(rows) if r and r[0] in ("Function Name", "Kernel Name") and re.search(kre, r[1]))
+hi = next(i for i, r in enumerate(rows) if i > fi and "Source" in r and "Instructions Executed" in r)
 hdr = rows[hi]
 ie, isrc, ismp = hdr.index("Instructions Executed"), hdr.index("Source"), hdr.index("# Samples")
 agg, smp, tot = collections.Counter(), collections.Counter(), 0
