@@ -273,3 +273,22 @@ def test_rorr_closed_form_merges_match_the_sorted_path(monkeypatch):
     assert not np.array_equal(t1, t2)  # the closed form was actually taken somewhere
     compare(r1, r2, tol=1e-12)
     compare(r1, OracleRadtran(tb, pr).radiate_batch(cols, spectral=True))
+
+
+def test_sharded_matches_single():
+    """clima_b200/shard.py with the production compute callable: the blocks of a 2-way partition,
+    computed one after the other on this GPU and re-assembled, equal the single-batch result bit for
+    bit (columns are independent units; the multi-process gather itself is covered on CPU by
+    tests/test_shard_gloo.py)."""
+    from clima_b200 import shard
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=5)
+    g = Radtran(tb, pr)
+    whole = g.radiate_batch(cols)
+    parts = [g.radiate_batch(shard.slice_columns(cols, b, e)) for b, e in shard.partition(5, 2)]
+    for k in shard.RESULT_PROFILES:
+        assert np.array_equal(np.concatenate([p[k] for p in parts], axis=1), whole[k]), k
+    for k in shard.RESULT_SCALARS:
+        assert np.array_equal(np.concatenate([p[k] for p in parts]), whole[k]), k
+    one = shard.radiate_sharded(g.radiate_batch, cols, dist=None)
+    for k in shard.RESULT_PROFILES + shard.RESULT_SCALARS:
+        assert np.array_equal(one[k], whole[k]), k
