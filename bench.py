@@ -163,7 +163,7 @@ def run_reference(args):
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    _emit(line)
     return 0
 
 
@@ -331,14 +331,27 @@ def run_ours(args):
                 "value": v, "unit": UNIT, "cores": cores, "kind": "port",
                 "sample": sample + "; C++ restatement of the reference algorithm (the Fortran binary "
                                    "cannot be built on this box)"}
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
 
 
+def _emit(line: dict):
+    """The ONE JSON line goes to the real stdout; everything else any library prints on fd 1 during
+    the run (e.g. NCCL's version banner) has been routed to stderr by main()."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)

@@ -274,11 +274,20 @@ __device__ __forceinline__ void tbl_put(double *t, const int g, const double v, 
 }
 
 // k(g) * column of k-gas jj for the unit's layer: bilinear log10k(P,T) interpolation, lane per
-// g-point (A.2, :649-662 + interp_2d, linear_interpolation_module.F90:322-335), into table `dst`.
+// g-point (A.2, :649-662 + interp_2d, linear_interpolation_module.F90:322-335).  Split in two so
+// that the table loads of the NEXT gas are in flight while the current merge builds its keys:
+//   kgas_load   issues the loads (bracket record, column amount, 4 table corners per g-point)
+//   kgas_finish interpolates, exponentiates and scales; the caller puts the values into a table.
 template <int P>
-__device__ __forceinline__ void rt_kgas(const DevTables &tb, const DevChunk &ch, const int c,
-                                        const int l, const int slot, const int k, const int jj,
-                                        const int ul, const int colbase, double *dst) {
+struct KgasRaw {
+  double f[4 * Cfg<P>::GPL];
+  double q1, q2, col;
+};
+
+template <int P>
+__device__ __forceinline__ void kgas_load(const DevTables &tb, const DevChunk &ch, const int c,
+                                          const int l, const int slot, const int k, const int jj,
+                                          const int ul, KgasRaw<P> &r) {
   using C = Cfg<P>;
   const int G = tb.G, nz = ch.nz;
   const int nbr = rt_nbr(tb);
@@ -286,22 +295,34 @@ __device__ __forceinline__ void rt_kgas(const DevTables &tb, const DevChunk &ch,
   const double *qb = ch.qbr + ((size_t)c * nz + slot) * nbr;
   const DevK &kt = tb.k[jj];
   const int ix = ib[2 * jj], iy = ib[2 * jj + 1];
-  const double q1 = qb[2 * jj], q2 = qb[2 * jj + 1];
-  const double p1 = 1.0 - q1, p2 = 1.0 - q2;
-  const double col = ch.dens[(size_t)c * nz * tb.ng + k + (size_t)(kt.sp - 1) * nz] *
-                     ch.dz[(size_t)c * nz + k];  // cols(j,sp) :607
+  r.q1 = qb[2 * jj];
+  r.q2 = qb[2 * jj + 1];
+  r.col = ch.dens[(size_t)c * nz * tb.ng + k + (size_t)(kt.sp - 1) * nz] *
+          ch.dz[(size_t)c * nz + k];  // cols(j,sp) :607
   const double *f = kt.log10k + (size_t)G * (ix + (size_t)kt.np * (iy + (size_t)kt.nt * l));
   const size_t sy = (size_t)G * kt.np;
 #pragma unroll
   for (int t = 0; t < C::GPL; t++) {
     const int g = ul + C::LPU * t;
-    double v = 0.0;
-    if (g < G) {
-      const double fx1 = p1 * f[g] + q1 * f[g + G];
-      const double fx2 = p1 * f[g + sy] + q1 * f[g + sy + G];
-      v = rt_ten2power(p2 * fx1 + q2 * fx2) * col;  // :660, :816-819 / :828
-    }
-    tbl_put<P>(dst, g, v, colbase, ul);
+    const int gc = g < G ? g : G - 1;
+    r.f[4 * t + 0] = f[gc];
+    r.f[4 * t + 1] = f[gc + G];
+    r.f[4 * t + 2] = f[gc + sy];
+    r.f[4 * t + 3] = f[gc + sy + G];
+  }
+}
+
+template <int P>
+__device__ __forceinline__ void kgas_finish(const KgasRaw<P> &r, const int G, const int ul,
+                                            double (&v)[Cfg<P>::GPL]) {
+  using C = Cfg<P>;
+  const double p1 = 1.0 - r.q1, p2 = 1.0 - r.q2;
+#pragma unroll
+  for (int t = 0; t < C::GPL; t++) {
+    const int g = ul + C::LPU * t;
+    const double fx1 = p1 * r.f[4 * t + 0] + r.q1 * r.f[4 * t + 1];
+    const double fx2 = p1 * r.f[4 * t + 2] + r.q1 * r.f[4 * t + 3];
+    v[t] = g < G ? rt_ten2power(p2 * fx1 + r.q2 * fx2) * r.col : 0.0;  // :660, :816-819 / :828
   }
 }
 
@@ -484,10 +505,26 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   const int kfirst = (FAST || tb.rows_sorted) ? LOGP + 1 : 1;
   const double *cA = tA + mycol, *cB = tB + mycol;
 
-  for (int jj = 0; jj < tb.nk; jj++) {
-    rt_kgas<P>(tb, ch, c, l, slot, k, jj, ul, colbase, jj == 0 ? tA : tB);
+  // gas 0 -> table A; gas 1 -> registers (bn), put into table B at the top of its merge
+  double bn[C::GPL];
+  {
+    KgasRaw<P> r0, r1;
+    kgas_load<P>(tb, ch, c, l, slot, k, 0, ul, r0);
+    if (tb.nk > 1) kgas_load<P>(tb, ch, c, l, slot, k, 1, ul, r1);
+    double a0[C::GPL];
+    kgas_finish<P>(r0, G, ul, a0);
+#pragma unroll
+    for (int t = 0; t < C::GPL; t++) tbl_put<P>(tA, ul + LPU * t, a0[t], colbase, ul);
+    if (tb.nk > 1) kgas_finish<P>(r1, G, ul, bn);
+  }
+  for (int jj = 1; jj < tb.nk; jj++) {
+#pragma unroll
+    for (int t = 0; t < C::GPL; t++) tbl_put<P>(tB, ul + LPU * t, bn[t], colbase, ul);
     __syncwarp();
-    if (jj == 0) continue;
+    // loads of the next gas in flight during the non-interleaving test / key construction
+    KgasRaw<P> rn;
+    const bool more = jj + 1 < tb.nk;
+    if (more) kgas_load<P>(tb, ch, c, l, slot, k, jj + 1, ul, rn);
 
     // ---- merges that need no sort.  If the rows do not interleave (a_i + b_G <= a_i+1 + b_1 for
     // every i) the stable sorted order IS the row-major index order, row i covers exactly the
@@ -496,6 +533,8 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     // interleave.  (The reference's result differs from the closed form only by the rounding of
     // its 256-term cumulative weights, O(1e-15) relative.)  Taken when every unit of the warp
     // qualifies, so that the warp skips the sort as a whole.
+    bool triv = false, urow = false;
+    double cf[C::GPL];
     {
       const double a1 = cA[0], aG = cA[(G - 1) * CW], b1 = cB[0], bG = cB[(G - 1) * CW];
       bool rowmaj = true, colmaj = true;
@@ -512,18 +551,23 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
         }
       }
       const unsigned br = __ballot_sync(0xffffffffu, rowmaj), bc = __ballot_sync(0xffffffffu, colmaj);
-      const bool urow = (br & umask) == umask, ucol = (bc & umask) == umask;
-      if (!(tb.pad0 & 1) && __all_sync(0xffffffffu, urow || ucol)) {
+      urow = (br & umask) == umask;
+      triv = !(tb.pad0 & 1) && (urow || (bc & umask) == umask);
+      // A qualifying unit ALWAYS takes the closed form, also when its warp sorts because of another
+      // unit: the result of a unit must not depend on its warp-mates (the exact kernel regroups units).
+      if (__any_sync(0xffffffffu, triv)) {
         double mean = 0.0;  // <b> or <a>, summed in g order
         const double *cm = urow ? cB : cA;
         for (int g = 0; g < G; g++) mean = __fma_rn(s_w[g], cm[g * CW], mean);
+#pragma unroll
+        for (int t = 0; t < C::GPL; t++)
+          cf[t] = (ul + LPU * t) < G ? __dadd_rn(urow ? ag[t] : bg[t], mean) : 0.0;
+      }
+      if (__all_sync(0xffffffffu, triv)) {
+        if (more) kgas_finish<P>(rn, G, ul, bn);
         __syncwarp();
 #pragma unroll
-        for (int t = 0; t < C::GPL; t++) {
-          const int g = ul + LPU * t;
-          const double v = g < G ? __dadd_rn(urow ? ag[t] : bg[t], mean) : 0.0;
-          tbl_put<P>(tA, g, v, colbase, ul);
-        }
+        for (int t = 0; t < C::GPL; t++) tbl_put<P>(tA, ul + LPU * t, cf[t], colbase, ul);
         __syncwarp();
         continue;
       }
@@ -548,6 +592,7 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
         const unsigned key = (f << IDXBITS) | (unsigned)pos;
         x[r] = (FULL || ((i < G) && (j < G))) ? key : 0xffffffffu;
       }
+      if (more) kgas_finish<P>(rn, G, ul, bn);
       bitonic_network<P, unsigned>(x, ul, kfirst);
 #pragma unroll
       for (int r = 0; r < 32; r++) {
@@ -568,6 +613,7 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
         x[r] = __longlong_as_double(
             (long long)((bits & ~(unsigned long long)C::IDXM) | (unsigned long long)pos));
       }
+      if (more) kgas_finish<P>(rn, G, ul, bn);
       bitonic_network<P, double>(x, ul, kfirst);
 #pragma unroll
       for (int r = 0; r < 32; r++) {
@@ -578,8 +624,15 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     }
     __syncwarp();
     const bool ok = rt_rebin<P, FULL, FAST>(ip, tA, tB, sI, wx, s_E, s_ib, tot, G, ul, mycol, colbase);
+    if (__any_sync(0xffffffffu, triv)) {  // closed form for the qualifying units of a sorting warp
+      if (triv) {
+#pragma unroll
+        for (int t = 0; t < C::GPL; t++) tbl_put<P>(tA, ul + LPU * t, cf[t], colbase, ul);
+      }
+      __syncwarp();
+    }
     if (FAST) {
-      const unsigned bal = __ballot_sync(0xffffffffu, ok);
+      const unsigned bal = __ballot_sync(0xffffffffu, ok || triv);
       unit_ok = unit_ok && ((bal & umask) == umask);
     }
   }
