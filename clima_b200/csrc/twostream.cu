@@ -29,8 +29,8 @@
 namespace {
 
 constexpr int TS_THREADS = 128;
-constexpr int IR_ITEMS = 8;
-constexpr int SOL_ITEMS = 10;
+constexpr int IR_ITEMS = 6;   // alpha, beta, Au, Bu, Ad, Bd
+constexpr int SOL_ITEMS = 7;  // alpha, beta, Au, Bu, Ad, Bd, K
 
 template <int P>
 __device__ __forceinline__ double group_sum(double v) {
@@ -121,6 +121,7 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
     // tau/w0/g loads can be issued a full iteration before they are needed): the sweep was
     // latency-bound on the chain slot -> tau -> coefficients (r1e profile: 53 % long-scoreboard).
     auto lslot = [&](int i) { return sol[nz - 1 - (i < nz ? i : nz - 1)]; };  // slot of layer i (clamped)
+    double Ta = 0.0, Tb = 0.0;
     int s1 = lslot(1), s2 = lslot(2);
     double t1 = tau_p[(size_t)s1 * G], w1 = w0_p[(size_t)s1 * G], g1 = gt_p[s1];
     double B1 = bp[nz >= 1 ? 1 : 0], B2 = bp[nz >= 2 ? 2 : nz];
@@ -190,9 +191,24 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
         c1 = 0.0;
         d1 = (E - A * dprev) / (B - A * cprev);
       }
-      double *s = scr + (size_t)i * IR_ITEMS * nres;
-      s[0] = cprev; s[nres] = dprev; s[2 * nres] = c1; s[3 * nres] = d1;
-      s[4 * nres] = cgam; s[5 * nres] = wrk; s[6 * nres] = cpb; s[7 * nres] = cmb;
+      // What the back substitution needs from layer i, folded into 6 numbers.  With xn = x of row
+      // 2i+2 (the solution entering the layer from below), Thomas (:311-313) gives
+      //   y2 = x1 = d1 - c1*xn ,  y1 = x0 = d0 - c0*x1 = alpha + beta*xn
+      // and the fluxes (:288-293) are affine in xn as well:
+      //   fup = y1*e1 + y2*e2 + cpb = Au + Bu*xn ,  fdn = y1*e3 + y2*e4 + cmb = Ad + Bd*xn.
+      {
+        const double c0 = cprev, d0 = dprev;
+        const double Qu = e2 - c0 * e1, Qd = e4 - c0 * e3;
+        const double al = d0 - c0 * d1, be = c0 * c1;
+        double *s = scr + (size_t)i * IR_ITEMS * nres;
+        s[0] = al; s[nres] = be;
+        s[2 * nres] = (d0 * e1 + cpb) + Qu * d1; s[3 * nres] = -(Qu * c1);
+        s[4 * nres] = (d0 * e3 + cmb) + Qd * d1; s[5 * nres] = -(Qd * c1);
+        if (i == 0) {  // top-of-atmosphere upward flux (:288): y1*e3 - y2*e4 + cp0 = Ta + Tb*xn
+          Ta = (al * e3 - d1 * e4) + cp0_top;
+          Tb = be * e3 + c1 * e4;
+        }
+      }
       e1 = e1n; e2 = e2n; e3 = e3n; e4 = e4n; cpb = cpbn; cmb = cmbn; cgam = cgamn; wrk = wrkn;
       tau_i = taun; g12 = g12n; cprev = cn; dprev = dn;
       s1 = s2; s2 = s3; t1 = t2; w1 = w2; g1 = g2; B1 = B2; B2 = B3;
@@ -202,9 +218,8 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
     double *fup_o = fx.fup_a_ir + ((size_t)c * nw_ir + ll) * (nz + 1);
     double *fdn_o = fx.fdn_a_ir + ((size_t)c * nw_ir + ll) * (nz + 1);
     const bool writer = gactive && gl == 0;
-    double xnext = 0.0;
-    double y1 = 0, y2 = 0, ee3 = 0, ee4 = 0;
-    // the 8 scratch values of a layer do not depend on the recurrence: keep the loads two layers
+    double xnext = 0.0, xtop = 0.0;
+    // the scratch values of a layer do not depend on the recurrence: keep the loads two layers
     // ahead of the arithmetic (rotating register buffers, loop unrolled by 3)
     double q[3][IR_ITEMS];
     auto ld = [&](double (&b)[IR_ITEMS], int i) {
@@ -213,18 +228,12 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
       for (int t = 0; t < IR_ITEMS; t++) b[t] = s[(size_t)t * nres];
     };
     auto bk = [&](const double (&b)[IR_ITEMS], int i) {
-      const double c0 = b[0], d0 = b[1], c1 = b[2], d1 = b[3];
-      const double cg = b[4], wk = b[5], pb = b[6], mb = b[7];
-      const double x1 = d1 - c1 * xnext;  // c1 == 0 for the last row
-      const double x0 = d0 - c0 * x1;
-      y1 = x0; y2 = x1;
-      const double ee1 = 1.0 + cg * wk, ee2 = 1.0 - cg * wk;
-      ee3 = cg + wk; ee4 = cg - wk;
-      const double fup = (y1 * ee1 + y2 * ee2 + pb);
-      const double fdn = (y1 * ee3 + y2 * ee4 + mb);
+      const double fup = b[2] + b[3] * xnext;
+      const double fdn = b[4] + b[5] * xnext;
       const double su = group_sum<P>(fup * wg), sd = group_sum<P>(fdn * wg);
       if (writer) { fup_o[nz - 1 - i] = su; fdn_o[nz - 1 - i] = sd; }
-      xnext = x0;
+      xtop = xnext;
+      xnext = b[0] + b[1] * xnext;
     };
     ld(q[0], nz - 1);
     ld(q[1], nz - 2);
@@ -235,7 +244,7 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
       if (i - 2 >= 0) { ld(q[1], i - 4); bk(q[2], i - 2); }
     }
     {
-      const double fup = ((y1 * ee3 - y2 * ee4) + cp0_top);  // :288
+      const double fup = Ta + Tb * xtop;  // :288
       const double su = group_sum<P>(fup * wg);
       if (writer) { fup_o[nz] = su; fdn_o[nz] = 0.0; }
     }
@@ -343,12 +352,13 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       AM_top += wz[z];           // direct(1)/u0
     }
     cprev = (-e2) / e1;
+    double Ta = 0.0, Tb = 0.0;
 
     for (int i = 0; i < nz; i++) {
       const int s3 = lslot(i + 3);
       const double t2 = tau_p[(size_t)s2 * G], w2 = w0_p[(size_t)s2 * G], g2 = gt_p[s2];
       // layer i ("o"ld) values; layer_coeffs() overwrites e1..e4/cgam/wrk/fp/fm/ex with layer i+1
-      const double e1o = e1, e2o = e2, e3o = e3, e4o = e4, cgo = cgam, wko = wrk;
+      const double e1o = e1, e2o = e2, e3o = e3, e4o = e4;
       double c1, cn = 0.0, D1 = 0.0, Dn = 0.0;
       double CPB = 0.0, CMB = 0.0, DIR = 0.0, DIRU = 0.0;
 #pragma unroll
@@ -398,10 +408,23 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
           D1 += wz[z] * ((E - A * dprev[z]) * r1);
         }
       }
-      double *s = scr + (size_t)i * SOL_ITEMS * nres;
-      s[0] = cprev; s[nres] = Dprev; s[2 * nres] = c1; s[3 * nres] = D1;
-      s[4 * nres] = cgo; s[5 * nres] = wko; s[6 * nres] = CPB; s[7 * nres] = CMB;
-      s[8 * nres] = DIR; s[9 * nres] = DIRU;
+      // folded back-substitution data of layer i (see the IR kernel): with xn entering from below,
+      //   y1 = alpha + beta*xn, fup = Au + Bu*xn, fdn (incl. direct beam) = Ad + Bd*xn,
+      //   amean = (1/u1)*(fup + fdn) + K,  K = direct/u0 - (1/u1)*direct   (:135-148)
+      {
+        const double c0 = cprev, d0 = Dprev;
+        const double Qu = e2o - c0 * e1o, Qd = e4o - c0 * e3o;
+        const double al = d0 - c0 * D1, be = c0 * c1;
+        double *s = scr + (size_t)i * SOL_ITEMS * nres;
+        s[0] = al; s[nres] = be;
+        s[2 * nres] = (d0 * e1o + CPB) + Qu * D1; s[3 * nres] = -(Qu * c1);
+        s[4 * nres] = ((d0 * e3o + CMB) + Qd * D1) + DIR; s[5 * nres] = -(Qd * c1);
+        s[6 * nres] = DIRU - u1i * DIR;
+        if (i == 0) {  // :143  y1*e3 - y2*e4 + cp0 = Ta + Tb*xn
+          Ta = (al * e3o - D1 * e4o) + CP0_top;
+          Tb = be * e3o + c1 * e4o;
+        }
+      }
       cprev = cn;
       Dprev = Dn;
       s1 = s2; s2 = s3; t1 = t2; w1 = w2; g1 = g2;
@@ -428,7 +451,7 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
         fup_o[ig] = a; fdn_o[ig] = b; am_o[ig] = m;
       }
     };
-    double xnext = 0.0, y1 = 0, y2 = 0, ee3 = 0, ee4 = 0;
+    double xnext = 0.0, xtop = 0.0;
     // scratch loads two layers ahead of the arithmetic (rotating register buffers, unrolled by 3)
     double q[3][SOL_ITEMS];
     auto ld = [&](double (&b)[SOL_ITEMS], int i) {
@@ -437,19 +460,12 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       for (int t = 0; t < SOL_ITEMS; t++) b[t] = s[(size_t)t * nres];
     };
     auto bk = [&](const double (&b)[SOL_ITEMS], int i) {
-      const double c0 = b[0], d0 = b[1], c1 = b[2], d1 = b[3];
-      const double cg = b[4], wk = b[5], pb = b[6], mb = b[7];
-      const double dir = b[8], diru = b[9];
-      const double x1 = d1 - c1 * xnext;
-      const double x0 = d0 - c0 * x1;
-      y1 = x0; y2 = x1;
-      const double ee1 = 1.0 + cg * wk, ee2 = 1.0 - cg * wk;
-      ee3 = cg + wk; ee4 = cg - wk;
-      const double am = u1i * (y1 * (ee1 + ee3) + y2 * (ee2 + ee4) + pb + mb) + diru;  // :137-139
-      const double fup = (y1 * ee1 + y2 * ee2 + pb);                                 // :146
-      const double fdn = (y1 * ee3 + y2 * ee4 + mb) + dir;                           // :147
+      const double fup = b[2] + b[3] * xnext;  // :146
+      const double fdn = b[4] + b[5] * xnext;  // :147
+      const double am = u1i * (fup + fdn) + b[6];  // :137-139
       emit(nz - 1 - i, fup, fdn, am);
-      xnext = x0;
+      xtop = xnext;
+      xnext = b[0] + b[1] * xnext;
     };
     ld(q[0], nz - 1);
     ld(q[1], nz - 2);
@@ -460,8 +476,8 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       if (i - 2 >= 0) { ld(q[1], i - 4); bk(q[2], i - 2); }
     }
     {
-      const double up = (y1 * ee3 - y2 * ee4) + CP0_top;  // :143
-      emit(nz, up, FDN_top, u1i * up + AM_top);           // :135, :144
+      const double up = Ta + Tb * xtop;            // :143
+      emit(nz, up, FDN_top, u1i * up + AM_top);  // :135, :144
     }
   }
 }
