@@ -29,6 +29,12 @@
 namespace {
 
 constexpr int TS_THREADS = 128;
+#ifndef TS_IR_BLOCKS
+#define TS_IR_BLOCKS 5
+#endif
+#ifndef TS_SOL_BLOCKS
+#define TS_SOL_BLOCKS 3
+#endif
 constexpr int IR_ITEMS = 6;   // alpha, beta, Au, Bu, Ad, Bd
 constexpr int SOL_ITEMS = 7;  // alpha, beta, Au, Bu, Ad, Bd, K
 
@@ -56,7 +62,7 @@ __global__ void planck_kernel(const DevTables tb, const DevChunk ch, double *bpl
 
 // ------------------------------------------------------------------------------------------ IR
 template <int P>
-__global__ void __launch_bounds__(TS_THREADS)
+__global__ void __launch_bounds__(TS_THREADS, TS_IR_BLOCKS)
 twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevParams pr,
                     const __grid_constant__ DevChunk ch, const __grid_constant__ DevFlux fx,
                     const int ocol_bcast) {
@@ -253,7 +259,7 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
 
 // --------------------------------------------------------------------------------------- solar
 template <int P, int ZC>
-__global__ void __launch_bounds__(TS_THREADS, 3)
+__global__ void __launch_bounds__(TS_THREADS, TS_SOL_BLOCKS)
 twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevParams pr,
                        const __grid_constant__ DevChunk ch, const __grid_constant__ DevFlux fx,
                        const int ocol_bcast, const int zbeg, const int accumulate) {
