@@ -1,12 +1,15 @@
 // optics_rorr_fast.cu -- instantiates the fast flavour of the optics + RORR kernel (rorr_impl.cuh).
+// keys per lane at P = 16 and a private namespace: the two flavours use different lane mappings
+#define RORR_KPL16 32
+#define RORR_NS rorr_fast
 #include "rorr_impl.cuh"
 
 namespace {
 template <int P, bool FULL>
 void launch(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount, int wcap,
             long long units, cudaStream_t st) {
-  using C = rorr::Cfg<P>;
-  auto kern = rorr::optics_rorr_kernel<P, FULL, true>;
+  using C = rorr_fast::Cfg<P>;
+  auto kern = rorr_fast::optics_rorr_kernel<P, FULL, true>;
   static bool attr_set = false;
   if (!attr_set) {
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::BLOCK_BYTES);

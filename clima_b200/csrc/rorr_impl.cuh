@@ -32,17 +32,25 @@
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 
+#ifndef RORR_KPL16
+#define RORR_KPL16 32  // keys per lane at P = 16 (64 -> 4 lanes per unit, 3 cross-lane steps instead of 6: measured slower, 168 registers + spills, r1p)
+#endif
 #ifndef RORR_MIN_BLOCKS
-#define RORR_MIN_BLOCKS 4
+#define RORR_MIN_BLOCKS (RORR_KPL16 == 64 ? 3 : 4)
 #endif
 
-namespace rorr {
+#ifndef RORR_NS
+#define RORR_NS rorr
+#endif
+
+namespace RORR_NS {
 
 template <int P>
 struct Cfg {
   static constexpr int LOGP = (P == 8 ? 3 : (P == 16 ? 4 : 5));
   static constexpr int N = P * P;
-  static constexpr int KPL = 32;        // keys per lane
+  static constexpr int KPL = (P == 16 ? RORR_KPL16 : 32);  // keys per lane
+  static constexpr int LOGK = (KPL == 32 ? 5 : 6);
   static constexpr int LPU = N / KPL;   // lanes per unit: 2, 8, 32
   static constexpr int GPL = P / LPU;   // g-points per lane: 4, 2, 1
   static constexpr int UPW = 32 / LPU;  // units per warp: 16, 4, 1
@@ -56,7 +64,7 @@ struct Cfg {
   static constexpr unsigned IDXM = (unsigned)(N - 1);
   // dynamic shared memory: [wxy N*WXC doubles][per warp: tA, tB, edge integrals, idx]
   static constexpr size_t WARP_BYTES =
-      (size_t)(2 * TBL + UPW * SPU) * sizeof(double) + (size_t)32 * 32 * IDXB;
+      (size_t)(2 * TBL + UPW * SPU) * sizeof(double) + (size_t)KPL * 32 * IDXB;
   static constexpr size_t BLOCK_BYTES = (size_t)N * WXC * sizeof(double) + 4 * WARP_BYTES;
 };
 
@@ -98,50 +106,50 @@ __device__ __forceinline__ unsigned shfl_x(unsigned v, int m) {
 // registers, so the code holds one shuffle flip block, one shuffle half-cleaner block and one
 // 5-step in-register block instead of a copy per stage (instruction-cache footprint).
 template <int P, typename K>
-__device__ __forceinline__ void bitonic_network(K (&x)[32], const int ul, const int kfirst) {
+__device__ __forceinline__ void bitonic_network(K (&x)[Cfg<P>::KPL], const int ul, const int kfirst) {
   using C = Cfg<P>;
-  constexpr int K1 = 2 * C::LOGP;
+  constexpr int K1 = 2 * C::LOGP, KPL = C::KPL, LOGK = C::LOGK;
 #pragma unroll
-  for (int k = 1; k <= (K1 < 5 ? K1 : 5); k++) {
+  for (int k = 1; k <= (K1 < LOGK ? K1 : LOGK); k++) {
     if (k < kfirst) continue;
     const int m = (1 << k) - 1;
 #pragma unroll
-    for (int r = 0; r < 32; r++)
+    for (int r = 0; r < KPL; r++)
       if ((r & (1 << (k - 1))) == 0) ce(x[r], x[r ^ m]);
 #pragma unroll
     for (int s = k - 2; s >= 0; s--) {
 #pragma unroll
-      for (int r = 0; r < 32; r++)
+      for (int r = 0; r < KPL; r++)
         if ((r & (1 << s)) == 0) ce(x[r], x[r | (1 << s)]);
     }
   }
 #pragma unroll 1
-  for (int k = (kfirst > 6 ? kfirst : 6); k <= K1; k++) {
-    {  // flip step: pos <-> pos ^ (2^k - 1): partner lane ul ^ lm, partner register r ^ 31
-      const int lm = ((1 << k) - 1) >> 5;
+  for (int k = (kfirst > LOGK + 1 ? kfirst : LOGK + 1); k <= K1; k++) {
+    {  // flip step: pos <-> pos ^ (2^k - 1): partner lane ul ^ lm, partner register r ^ (KPL-1)
+      const int lm = ((1 << k) - 1) >> LOGK;
       const bool keepmin = (ul & ((lm + 1) >> 1)) == 0;
 #pragma unroll
-      for (int r = 0; r < 16; r++) {
-        const K y1 = shfl_x(x[r ^ 31], lm);
+      for (int r = 0; r < KPL / 2; r++) {
+        const K y1 = shfl_x(x[r ^ (KPL - 1)], lm);
         const K y2 = shfl_x(x[r], lm);
         x[r] = pick(keepmin, x[r], y1);
-        x[r ^ 31] = pick(keepmin, x[r ^ 31], y2);
+        x[r ^ (KPL - 1)] = pick(keepmin, x[r ^ (KPL - 1)], y2);
       }
     }
 #pragma unroll 1
-    for (int s = k - 2; s >= 5; s--) {  // cross-lane half-cleaners
-      const int lm = 1 << (s - 5);
+    for (int s = k - 2; s >= LOGK; s--) {  // cross-lane half-cleaners
+      const int lm = 1 << (s - LOGK);
       const bool keepmin = (ul & lm) == 0;
 #pragma unroll
-      for (int r = 0; r < 32; r++) {
+      for (int r = 0; r < KPL; r++) {
         const K y = shfl_x(x[r], lm);
         x[r] = pick(keepmin, x[r], y);
       }
     }
 #pragma unroll
-    for (int s = 4; s >= 0; s--) {  // in-lane half-cleaners d = 16..1
+    for (int s = LOGK - 1; s >= 0; s--) {  // in-lane half-cleaners d = KPL/2..1
 #pragma unroll
-      for (int r = 0; r < 32; r++)
+      for (int r = 0; r < KPL; r++)
         if ((r & (1 << s)) == 0) ce(x[r], x[r | (1 << s)]);
     }
   }
@@ -374,9 +382,9 @@ __device__ __forceinline__ bool rt_rebin(const typename IdxT<Cfg<P>::IDXB>::type
   unsigned idx = ip[0];
   double na = cA[(idx >> LOGP) * CW], nb = cB[(idx & (P - 1)) * CW], nw = wx[idx * C::WXC];
 #pragma unroll 4
-  for (int r = 0; r < 32; r++) {
+  for (int r = 0; r < C::KPL; r++) {
     const double a = na, b = nb, w = nw;
-    if (r < 31) {
+    if (r < C::KPL - 1) {
       idx = ip[(r + 1) * 32];
       na = cA[(idx >> LOGP) * CW];
       nb = cB[(idx & (P - 1)) * CW];
@@ -390,7 +398,7 @@ __device__ __forceinline__ bool rt_rebin(const typename IdxT<Cfg<P>::IDXB>::type
         if (r == 0) first = tv;
       }
     }
-    const double o1 = (r == 31 && ul < LPU - 1) ? off_next : __dadd_rn(o0, w);
+    const double o1 = (r == C::KPL - 1 && ul < LPU - 1) ? off_next : __dadd_rn(o0, w);
     while (o1 > n1 && g < G - 1) {  // the element contains the right edge of new bin g
       g++;
       sI[g] = __fma_rn(__dsub_rn(n1, o0), tv, I);
@@ -582,10 +590,10 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
       const unsigned long long range = top - base;
       const int nb = 64 - __clzll((long long)range);  // bit length (0 for range == 0)
       const int shift = nb > FB ? nb - FB : 0;
-      unsigned x[32];
+      unsigned x[C::KPL];
 #pragma unroll
-      for (int r = 0; r < 32; r++) {
-        const int pos = ul * 32 + r;
+      for (int r = 0; r < C::KPL; r++) {
+        const int pos = ul * C::KPL + r;
         const int i = pos >> LOGP, j = pos & (P - 1);
         const double v = cA[i * CW] + cB[j * CW];  // :828 tau_xy
         const unsigned f = (unsigned)(((unsigned long long)__double_as_longlong(v) - base) >> shift);
@@ -595,16 +603,16 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
       if (more) kgas_finish<P>(rn, G, ul, bn);
       bitonic_network<P, unsigned>(x, ul, kfirst);
 #pragma unroll
-      for (int r = 0; r < 32; r++) {
+      for (int r = 0; r < C::KPL; r++) {
         const unsigned idx = x[r] & C::IDXM;
         ip[r * 32] = (idx_t)idx;
         tot = __dadd_rn(tot, wx[idx * C::WXC]);
       }
     } else {
-      double x[32];
+      double x[C::KPL];
 #pragma unroll
-      for (int r = 0; r < 32; r++) {
-        const int pos = ul * 32 + r;
+      for (int r = 0; r < C::KPL; r++) {
+        const int pos = ul * C::KPL + r;
         const int i = pos >> LOGP, j = pos & (P - 1);
         const double v = cA[i * CW] + cB[j * CW];  // :828 tau_xy
         const unsigned long long bits = (FULL || ((i < G) && (j < G)))
@@ -616,7 +624,7 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
       if (more) kgas_finish<P>(rn, G, ul, bn);
       bitonic_network<P, double>(x, ul, kfirst);
 #pragma unroll
-      for (int r = 0; r < 32; r++) {
+      for (int r = 0; r < C::KPL; r++) {
         const unsigned idx = (unsigned)((unsigned long long)__double_as_longlong(x[r])) & C::IDXM;
         ip[r * 32] = (idx_t)idx;
         tot = __dadd_rn(tot, wx[idx * C::WXC]);
@@ -668,4 +676,4 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   }
 }
 
-}  // namespace rorr
+}  // namespace RORR_NS
