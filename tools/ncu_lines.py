@@ -21,5 +21,6 @@ for r in rows[hi + 1:]:
         lines.append((int(r[0]), r[1].strip(), int(r[ie]), int(r[ismp]), int(r[iw]), int(r[iwi])))
 ti = sum(l[2] for l in lines); ts = sum(l[3] for l in lines); tw = sum(l[4] for l in lines)
 print(f"total inst {ti} samples {ts} shared wavefronts {tw} (ideal {sum(l[5] for l in lines)})")
-for l in sorted(lines, key=lambda l: -l[3])[:top]:
+key = (lambda l: -l[2]) if (len(sys.argv) > 4 and sys.argv[4] == "inst") else (lambda l: -l[3])
+for l in sorted(lines, key=key)[:top]:
     print(f"{l[0]:5d} inst {l[2]/ti:6.3f} smp {l[3]/ts:6.3f} wf {l[4]/max(tw,1):6.3f} (x{l[4]/max(l[5],1):4.1f}) | {l[1][:100]}")
