@@ -193,6 +193,16 @@ void build_tables(Handle &h, const clima_rt_tables *t) {
   d.wbin = upload(h, wb.data(), G);
   d.wbin_e = upload(h, we.data(), G + 1);
   d.inv_dw = upload(h, iw.data(), G);
+  {  // can one sorted element (weight w_i*w_j) contain two bin edges?  Never for Gauss-Legendre sets;
+     // otherwise the RORR kernels take the general (looping) rebin walk: DevTables::pad0 bit 1.
+    double wmax = 0.0, dmin = 1.0e300;
+    for (int i = 0; i < G; i++) {
+      wmax = std::max(wmax, wb[i]);
+      dmin = std::min(dmin, we[i + 1] - we[i]);
+    }
+    const char *gw = std::getenv("CLIMA_RT_RORR_GENERAL_WALK");
+    if (!(wmax * wmax * 1.000001 < dmin) || (gw && gw[0] == '1')) d.pad0 |= 2;
+  }
   h.d_photons = upload(h, t->photons_sol, h.nw_sol);
   h.d_albedo = upload<double>(h, nullptr, h.nw_sol);
   h.d_emiss = upload<double>(h, nullptr, h.nw_ir);
@@ -220,7 +230,7 @@ size_t per_col_bytes(const Handle &h, int nz) {
   const size_t L = nz + 1;
   size_t b = 0;
   b += (size_t)tb.nw * nz * tb.G * 8 * 2;            // tau, w0
-  b += (size_t)tb.nw * nz * 8 * 2;                   // gt, tband
+  b += (size_t)tb.nw * nz * 8 * 5;                   // gt, tband, cont[3]
   b += (size_t)nz * rt_nbr(tb) * 12 + (size_t)nz * 16 + 64;  // brackets, slots, foreign_col
   b += L * (2 * h.nw_ir + 3 * h.nw_sol) * 8;         // spectral fluxes
   b += L * h.nw_ir * 8;                              // Planck
@@ -277,6 +287,7 @@ void ensure_chunk(Handle &h, int ncol, int nz) {
   ch.w0 = calloc_dev<double>(h, (size_t)C * tb.nw * nz * tb.G);
   ch.gt = calloc_dev<double>(h, (size_t)C * tb.nw * nz);
   ch.tband = calloc_dev<double>(h, (size_t)C * tb.nw * nz);
+  ch.cont = calloc_dev<double>(h, (size_t)3 * C * tb.nw * nz);
   ch.status = calloc_dev<int>(h, C);
   {
     const long long units = (long long)C * tb.nw * nz;

@@ -1,6 +1,9 @@
 // optics_rorr.cu -- launch sequence of the optics + RORR stage and the small layout kernels around
 // it.  The kernel itself lives in rorr_impl.cuh (instantiated by optics_rorr_fast.cu /
 // optics_rorr_exact.cu).
+#include <algorithm>
+
+#include "continua_impl.cuh"
 #include "rt_device.cuh"
 #include "rt_kernels.h"
 
@@ -10,6 +13,30 @@ void rorr_launch_exact(const DevTables &tb, const DevChunk &ch, int *worklist, i
                        long long units, cudaStream_t st);
 
 namespace {
+
+// g-independent opacity terms, one thread per (column, bin, unique layer slot), slot fastest.
+// Writes the asymmetry parameter and the three numbers the RORR epilogue (:856-886) needs:
+//   cont[0*U + u] = (tausg + taua) + taup     (the leading terms of the total tau, in that order)
+//   cont[1*U + u] = tauc
+//   cont[2*U + u] = tausg + tausp + tausc     (numerator of w0)
+__global__ void __launch_bounds__(256) continua_kernel(const __grid_constant__ DevTables tb,
+                                                       const __grid_constant__ DevChunk ch) {
+  const int cap = ch.nslot_cap, nw = tb.nw, nz = ch.nz;
+  const long long U = (long long)ch.ncol * nw * cap;
+  for (long long u = blockIdx.x * (long long)blockDim.x + threadIdx.x; u < U;
+       u += (long long)gridDim.x * blockDim.x) {
+    const int slot = (int)(u % cap);
+    const int l = (int)((u / cap) % nw);
+    const int c = (int)(u / ((long long)cap * nw));
+    if (slot >= ch.nslots[c]) continue;
+    const int k = ch.layer_of_slot[(size_t)c * nz + slot];
+    const Continua q = rt_continua<1>(tb, ch, c, l, slot, k, 0);
+    ch.cont[u] = __dadd_rn(__dadd_rn(q.tausg, q.taua), q.taup);
+    ch.cont[U + u] = q.tauc;
+    ch.cont[2 * U + u] = q.tausg + q.tausp + q.tausc;
+    ch.gt[u] = q.gt;
+  }
+}
 
 // Expand the slot-indexed opacity of one column into the reference's OpticalPropertiesResult layout
 // tau(nz,G,nw), w0(nz,G,nw), g(nz,nw), tau_band(nz,nw), top-first (clima_radtran_types.f90:242-247).
@@ -57,6 +84,7 @@ __global__ void tau_band_kernel(const DevTables tb, const DevChunk ch, int ind_s
 void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
                            int wcap, int exact_only, cudaStream_t st) {
   const long long units = (long long)ch.ncol * tb.nw * ch.nslot_cap;
+  continua_kernel<<<(unsigned)std::min<long long>((units + 255) / 256, 148 * 32), 256, 0, st>>>(tb, ch);
   if (exact_only || !tb.rows_sorted) {
     rorr_launch_exact(tb, ch, nullptr, nullptr, 0, units, st);
     return;

@@ -15,6 +15,9 @@ void launch(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::BLOCK_BYTES);
     attr_set = true;
   }
+  // One group of UPB units per block (NOT a persistent grid: the kernel is instruction-cache bound
+  // and the warps of a block that start together share their instruction stream; measured r1n:
+  // a persistent grid of 592 blocks doubles the no-instruction stalls)
   const long long nb = (units + C::UPB - 1) / C::UPB;
   if (nb <= 0) return;
   kern<<<(unsigned)nb, 128, C::BLOCK_BYTES, st>>>(tb, ch, worklist, wcount, wcap);

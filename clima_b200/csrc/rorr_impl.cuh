@@ -62,11 +62,36 @@ struct Cfg {
   static constexpr int WXC = 4;                      // copies of the wxy table
   static constexpr int IDXB = (N <= 256 ? 1 : 2);    // bytes per sorted-index entry
   static constexpr unsigned IDXM = (unsigned)(N - 1);
-  // dynamic shared memory: [wxy N*WXC doubles][per warp: tA, tB, edge integrals, idx]
-  static constexpr size_t WARP_BYTES =
-      (size_t)(2 * TBL + UPW * SPU) * sizeof(double) + (size_t)KPL * 32 * IDXB;
-  static constexpr size_t BLOCK_BYTES = (size_t)N * WXC * sizeof(double) + 4 * WARP_BYTES;
+  // gather addressing: a table is TBLB bytes, aligned to TBLB, row stride 2^ROWSH bytes, so that
+  // the byte address of row `row`, column `col` is  base | (row << ROWSH) | (col << 3)  (one LOP3)
+  static constexpr int ROWSH = (CW == 32 ? 8 : 7);
+  static constexpr unsigned TBLB = (unsigned)TBL * 8u;
+  static constexpr unsigned ROWMASK = (unsigned)(P - 1) << ROWSH;
+  // dynamic shared memory: [alignment slack TBLB][4 warps x (tA, tB)][wxy N*WXC doubles]
+  //                        [4 warps x edge integrals][4 warps x sorted-index bytes (general walk)]
+  static constexpr size_t SI_BYTES = (size_t)UPW * SPU * sizeof(double);
+  static constexpr size_t IP_BYTES = (size_t)KPL * 32 * IDXB;
+  static constexpr size_t BLOCK_BYTES =
+      (size_t)TBLB * 9 + (size_t)N * WXC * sizeof(double) + 4 * (SI_BYTES + IP_BYTES);
 };
+
+__device__ __forceinline__ unsigned smem_u32(const void *p) {
+  return (unsigned)__cvta_generic_to_shared(p);
+}
+// shared-memory load by 32-bit address.  volatile: the tables are rewritten between merges, the
+// statement must never be merged with an earlier load of the same address.
+template <int B>
+__device__ __forceinline__ unsigned lds_idx(unsigned addr) {
+  unsigned v;
+  if (B == 1) asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr));
+  else asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+  double v;
+  asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+  return v;
+}
 
 template <int B> struct IdxT { typedef unsigned char type; };
 template <> struct IdxT<2> { typedef unsigned short type; };
@@ -153,122 +178,6 @@ __device__ __forceinline__ void bitonic_network(K (&x)[Cfg<P>::KPL], const int u
         if ((r & (1 << s)) == 0) ce(x[r], x[r | (1 << s)]);
     }
   }
-}
-
-// ---------------------------------------------------------------------------------------------
-struct Continua {
-  double tausg, taua, taup, tausp, tauc, tausc, gt;
-};
-
-template <int LPU>
-__device__ __forceinline__ double unit_sum(double v) {
-#pragma unroll
-  for (int m = LPU / 2; m >= 1; m >>= 1) v = __dadd_rn(v, shfl_xor_d(v, m));
-  return v;
-}
-
-// Rayleigh, CIA, photolysis, water continuum, particles, custom opacity and the asymmetry
-// parameter of one (column c, bin l, slot) -- A.3, clima_radtran_types.f90:664-757.
-// Items (nray Rayleigh, ncia CIA, npxs cross sections, 2 continuum terms) are dealt to the unit's
-// lanes round-robin; every lane ends with the same totals.
-template <int LPU>
-__device__ __forceinline__ Continua rt_continua(const DevTables &tb, const DevChunk &ch, const int c,
-                                                const int l, const int slot, const int k,
-                                                const int ul) {
-  const int nw = tb.nw, nz = ch.nz, ng = tb.ng;
-  const double *dens = ch.dens + (size_t)c * nz * ng + k;  // dens[i*nz]
-  const double dzk = ch.dz[(size_t)c * nz + k];
-  const int nbr = rt_nbr(tb);
-  const int *ib = ch.ibr + ((size_t)c * nz + slot) * nbr;
-  const double *qb = ch.qbr + ((size_t)c * nz + slot) * nbr;
-  const int rb_xs = 2 * tb.nk;
-  const int rb_cont = rb_xs + tb.ncia + tb.npxs;
-  const int rb_part = rb_cont + 1;
-  const int rb_cust = rb_part + tb.npart;
-  Continua o;
-  double tausg = 0.0, taua = 0.0;
-  const int n_xs = tb.ncia + tb.npxs;
-  const int nitems = tb.nray + n_xs + (tb.has_cont ? 2 : 0);
-#pragma unroll 1
-  for (int it = ul; it < nitems; it += LPU) {
-    if (it < tb.nray) {  // Rayleigh (:686-693)
-      const double col = dens[(size_t)(tb.ray_sp[it] - 1) * nz] * dzk;
-      tausg = tausg + tb.ray_xs[l + (size_t)it * nw] * col;
-    } else if (it < tb.nray + n_xs) {  // CIA (:696-704), photolysis (:707-713)
-      const int i = it - tb.nray;
-      const bool is_cia = i < tb.ncia;
-      const DevXS &x = is_cia ? tb.cia[i] : tb.pxs[i - tb.ncia];
-      double xs;
-      if (x.dim == 0) {
-        xs = x.data[l];
-      } else {
-        const int t0 = ib[rb_xs + i];
-        const double q1 = qb[rb_xs + i], p1 = 1.0 - q1;
-        const double *f = x.data + (size_t)l * x.nt;
-        xs = rt_ten2power(p1 * f[t0] + q1 * f[t0 + 1]);
-      }
-      if (is_cia)
-        taua = taua + xs * dens[(size_t)(x.sp1 - 1) * nz] * dens[(size_t)(x.sp2 - 1) * nz] * dzk;
-      else
-        taua = taua + xs * (dens[(size_t)(x.sp1 - 1) * nz] * dzk);
-    } else {  // water continuum (:716-723): self term, then foreign term
-      const bool self = (it == tb.nray + n_xs);
-      const int t0 = ib[rb_cont];
-      const double q1 = qb[rb_cont], p1 = 1.0 - q1;
-      const double *f = (self ? tb.cont_H2O : tb.cont_foreign) + (size_t)l * tb.cont_nt;
-      const double xs = rt_ten2power(p1 * f[t0] + q1 * f[t0 + 1]);
-      const double dw = dens[(size_t)(tb.cont_LH2O - 1) * nz];
-      if (self) taua = taua + xs * dw * (dw * dzk);
-      else taua = taua + xs * dw * ch.foreign_col[(size_t)c * nz + slot];
-    }
-  }
-  tausg = unit_sum<LPU>(tausg);
-  taua = unit_sum<LPU>(taua);
-  // particles (:733-744)
-  double tausp = 0.0, taup = 0.0;
-  double tausp_1[RT_MAXPART], gtp[RT_MAXPART];
-  if (tb.npart > 0) {
-    const double *rad = ch.radii + (size_t)c * nz * tb.np + k;
-    const double *pdn = ch.pdens + (size_t)c * nz * tb.np + k;
-#pragma unroll 1
-    for (int i = 0; i < tb.npart; i++) {
-      const DevPart &p = tb.part[i];
-      const int ir = ib[rb_part + i];
-      const double q1 = qb[rb_part + i], p1 = 1.0 - q1;
-      const size_t o2 = (size_t)l * p.nr + ir;
-      const double w0p = p1 * p.w0[o2] + q1 * p.w0[o2 + 1];
-      const double qext = p1 * p.qext[o2] + q1 * p.qext[o2 + 1];
-      gtp[i] = p1 * p.gt[o2] + q1 * p.gt[o2 + 1];
-      const double r = rad[(size_t)(p.p_ind - 1) * nz];
-      const double taup_1 = qext * RT_PI * (r * r) * pdn[(size_t)(p.p_ind - 1) * nz] * dzk;
-      taup = taup + taup_1;
-      tausp_1[i] = w0p * taup_1;
-      tausp = tausp + tausp_1[i];
-    }
-  }
-  // custom optical properties (:726-730, 546-572)
-  double tauc = RT_TINY, w0c = RT_TINY, g0c = RT_TINY;
-  if (tb.has_custom) {
-    const int ip = ib[rb_cust];
-    const double q1 = qb[rb_cust], p1 = 1.0 - q1;
-    const size_t o2 = (size_t)l * tb.custom_nP + ip;
-    tauc = (p1 * tb.c_dtau[o2] + q1 * tb.c_dtau[o2 + 1]) * dzk;
-    w0c = p1 * tb.c_w0[o2] + q1 * tb.c_w0[o2 + 1];
-    g0c = p1 * tb.c_g0[o2] + q1 * tb.c_g0[o2 + 1];
-  }
-  const double tausc = w0c * tauc;
-  // asymmetry (:746-757)
-  double gt = 0.0;
-  {
-    const double den = fmax(RT_TAU_MIN, (tausp + tausg + tausc));
-#pragma unroll 1
-    for (int i = 0; i < tb.npart; i++) gt = gt + gtp[i] * tausp_1[i] / den;
-    gt = gt + g0c * tausc / den;
-    gt = fmin(gt, RT_MAX_GT);
-  }
-  o.tausg = tausg; o.taua = taua; o.taup = taup; o.tausp = tausp; o.tauc = tauc; o.tausc = tausc;
-  o.gt = gt;
-  return o;
 }
 
 // Writes value v of table row g into every column of the unit.  Lane `ul` starts at column ul and
@@ -435,6 +344,112 @@ __device__ __forceinline__ bool rt_rebin(const typename IdxT<Cfg<P>::IDXB>::type
   return ok;
 }
 
+// Same contract as rt_rebin, specialised for weight sets in which one sorted element can contain
+// AT MOST ONE bin edge (max w_i*w_j < min wbin: true for every Gauss-Legendre set; checked on the
+// host at table load, DevTables::pad0 bit 1 selects the general walk otherwise).  Differences:
+//   * the single possible edge of an element is an if-converted block (no inner loop, no divergent
+//     branch: with 32 lanes walking, SOME lane has an edge in 85 % of the steps);
+//   * gathers by 32-bit shared address  base | row offset  (tables aligned to their size), issued
+//     one element ahead of the recurrence;
+//   * s_En = bin edges with +inf beyond the last interior edge (no g < G-1 test);
+//   * a unit with `triv` set receives `cf` (its closed-form result) instead of the rebinned values.
+// Rolled (x4): the kernel is instruction-cache bound, every unrolled copy costs more than it saves.
+template <int P, bool FULL, bool CERT>
+__device__ __forceinline__ bool rt_rebin1(const unsigned aIP, double *tA, double *sI,
+                                          const unsigned aA, const unsigned aB, const unsigned aW,
+                                          const double *s_En, const double *s_ib, const double tot,
+                                          const int G, const int ul, const int colbase,
+                                          const bool triv, const double (&cf)[Cfg<P>::GPL]) {
+  using C = Cfg<P>;
+  constexpr int LPU = C::LPU, LOGP = C::LOGP, KPL = C::KPL, ROWSH = C::ROWSH;
+  double off = tot;
+#pragma unroll
+  for (int d = 1; d < LPU; d <<= 1) {
+    const double t = __shfl_up_sync(0xffffffffu, off, d, LPU);
+    if (ul >= d) off = __dadd_rn(off, t);
+  }
+  const double off_next = off;  // bit-identically the start of the next lane (edge ownership)
+  off = __shfl_up_sync(0xffffffffu, off_next, 1, LPU);
+  if (ul == 0) off = 0.0;
+  int g = 0;  // largest g with E[g] < off
+#pragma unroll
+  for (int s = P / 2; s > 0; s >>= 1)
+    if (s_En[g + s] < off) g += s;
+  const int g_first = g;
+  double n1 = s_En[g + 1];
+  double I = 0.0, o0 = off, prev = -1.0;
+  bool ok = true;
+  unsigned idx = lds_idx<C::IDXB>(aIP);
+  double na = lds_f64(aA | ((idx << (ROWSH - LOGP)) & C::ROWMASK));
+  double nb = lds_f64(aB | ((idx << ROWSH) & C::ROWMASK));
+  double nw = lds_f64(aW + idx * (unsigned)(C::WXC * 8));
+  const double first = __dadd_rn(na, nb);
+#pragma unroll 4
+  for (int r = 0; r < KPL - 1; r++) {
+    const double a = na, b = nb, w = nw;
+    idx = lds_idx<C::IDXB>(aIP + (unsigned)(r + 1) * (32u * C::IDXB));
+    na = lds_f64(aA | ((idx << (ROWSH - LOGP)) & C::ROWMASK));
+    nb = lds_f64(aB | ((idx << ROWSH) & C::ROWMASK));
+    nw = lds_f64(aW + idx * (unsigned)(C::WXC * 8));
+    const double tv = __dadd_rn(a, b);  // exact tau_xy (:828); padding elements: w = 0
+    if (CERT) {
+      if (FULL || w > 0.0) {
+        ok = ok && (tv >= prev);
+        prev = tv;
+      }
+    }
+    const double o1 = __dadd_rn(o0, w);
+    if (o1 > n1) {  // the element contains the right edge of new bin g
+      g++;
+      sI[g] = __fma_rn(__dsub_rn(n1, o0), tv, I);
+      n1 = s_En[g + 1];
+    }
+    I = __fma_rn(w, tv, I);
+    o0 = o1;
+  }
+  {  // last element: ends bit-exactly where the next lane starts
+    const double tv = __dadd_rn(na, nb);
+    if (CERT) {
+      if (FULL || nw > 0.0) {
+        ok = ok && (tv >= prev);
+        prev = tv;
+      }
+    }
+    const double o1 = ul < LPU - 1 ? off_next : __dadd_rn(o0, nw);
+    if (o1 > n1) {
+      g++;
+      sI[g] = __fma_rn(__dsub_rn(n1, o0), tv, I);
+    }
+    I = __fma_rn(nw, tv, I);
+  }
+  // lane offsets of the integral
+  double Ioff = I;
+#pragma unroll
+  for (int d = 1; d < LPU; d <<= 1) {
+    const double t = __shfl_up_sync(0xffffffffu, Ioff, d, LPU);
+    if (ul >= d) Ioff = __dadd_rn(Ioff, t);
+  }
+  if (ul == LPU - 1) sI[G] = Ioff;  // I(E_G) = the whole integral
+  if (ul == 0) sI[0] = 0.0;
+  Ioff = __shfl_up_sync(0xffffffffu, Ioff, 1, LPU);
+  if (ul == 0) Ioff = 0.0;
+  for (int e = g_first + 1; e <= g; e++) sI[e] = __dadd_rn(sI[e], Ioff);
+  if (CERT) {  // lane boundary: this lane's first element against the previous lane's last one
+    const double plast = __shfl_up_sync(0xffffffffu, prev, 1, LPU);
+    if (ul > 0 && (FULL || prev >= 0.0)) ok = ok && (first >= plast);
+  }
+  __syncwarp();  // edge integrals complete; every lane is done reading tA
+#pragma unroll
+  for (int t = 0; t < C::GPL; t++) {
+    const int gg = ul + LPU * t;
+    double v = 0.0;
+    if (gg < G) v = __dmul_rn(__dsub_rn(sI[gg + 1], sI[gg]), s_ib[gg]);
+    tbl_put<P>(tA, gg, triv ? cf[t] : v, colbase, ul);
+  }
+  __syncwarp();
+  return ok;
+}
+
 // ---------------------------------------------------------------------------------------------
 // The kernel.  FAST: 32-bit quantised keys + certificate, failed units appended to `worklist`.
 // !FAST: exact 64-bit (value,index) keys; if `worklist` is given, only the listed units.
@@ -456,35 +471,43 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   typedef typename IdxT<C::IDXB>::type idx_t;
   constexpr int LPU = C::LPU, UPB = C::UPB, LOGP = C::LOGP, CW = C::CW;
   constexpr int IDXBITS = 2 * LOGP, FB = 32 - IDXBITS;
-  __shared__ double s_w[P];      // wbin, zero padded
-  __shared__ double s_E[P + 1];  // wbin_e
-  __shared__ double s_ib[P];     // 1/(wbin_e(g+1)-wbin_e(g))
+  __shared__ double s_w[P];       // wbin, zero padded
+  __shared__ double s_E[P + 1];   // wbin_e
+  __shared__ double s_En[P + 1];  // interior edges wbin_e(2..G), +inf beyond (single-edge walk)
+  __shared__ double s_ib[P];      // 1/(wbin_e(g+1)-wbin_e(g))
   extern __shared__ double s_dyn[];
-  double *s_wxy = s_dyn;  // [idx][copy]: wxy(j + i*P) = wbin(i)*wbin(j), types_create.f90:216-222
 
   const int G = FULL ? P : tb.G, nw = tb.nw, nz = ch.nz;
-  for (int i = threadIdx.x; i < P; i += blockDim.x) {
-    s_w[i] = i < G ? tb.wbin[i] : 0.0;
-    s_ib[i] = i < G ? tb.inv_dw[i] : 0.0;
-  }
-  for (int i = threadIdx.x; i < P + 1; i += blockDim.x) s_E[i] = tb.wbin_e[i < G ? i : G];
-  for (int i = threadIdx.x; i < C::N * C::WXC; i += blockDim.x) {
-    const int e = i / C::WXC, a = e >> LOGP, b = e & (P - 1);
-    s_wxy[i] = (a < G && b < G) ? __dmul_rn(tb.wbin[a], tb.wbin[b]) : 0.0;
-  }
-  __syncthreads();
-
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int ul = lane & (LPU - 1);   // lane within unit
   const int ub = threadIdx.x / LPU;  // unit within block
   const int mycol = (LPU == 32) ? (lane & 15) : lane;
   const int colbase = (LPU == 32) ? 0 : (lane - ul);
-  char *wbase = (char *)(s_dyn + C::N * C::WXC) + (size_t)warp * C::WARP_BYTES;
-  double *tA = (double *)wbase;  // running mixture a(i), [row][column]
-  double *tB = tA + C::TBL;      // new gas b(j)
-  double *sI = tB + C::TBL + (ub % C::UPW) * C::SPU;  // I(E_g), g = 0..G
-  idx_t *ip = (idx_t *)(tB + C::TBL + C::UPW * C::SPU) + lane;
+  // tables aligned to their own size (gather address = base | row offset)
+  const unsigned dyn_u = smem_u32(s_dyn);
+  const unsigned tb0 = (dyn_u + C::TBLB - 1u) & ~(C::TBLB - 1u);
+  char *dbase = (char *)s_dyn + (tb0 - dyn_u);
+  double *tA = (double *)(dbase + (size_t)warp * 2 * C::TBLB);  // running mixture a(i), [row][column]
+  double *tB = tA + C::TBL;                                      // new gas b(j)
+  double *s_wxy = (double *)(dbase + 8 * (size_t)C::TBLB);  // [idx][copy]: wxy(j + i*P), types_create.f90:216-222
+  double *sI = s_wxy + C::N * C::WXC + (size_t)warp * (C::UPW * C::SPU) + (ub % C::UPW) * C::SPU;  // I(E_g)
+  idx_t *ip = (idx_t *)(s_wxy + C::N * C::WXC + 4 * (C::UPW * C::SPU)) + (size_t)warp * (C::KPL * 32) + lane;
   const double *wx = s_wxy + (lane & (C::WXC - 1));
+  const unsigned aA = smem_u32(tA + mycol), aB = smem_u32(tB + mycol), aW = smem_u32(wx), aIP = smem_u32(ip);
+
+  for (int i = threadIdx.x; i < P; i += blockDim.x) {
+    s_w[i] = i < G ? tb.wbin[i] : 0.0;
+    s_ib[i] = i < G ? tb.inv_dw[i] : 0.0;
+  }
+  for (int i = threadIdx.x; i < P + 1; i += blockDim.x) {
+    s_E[i] = tb.wbin_e[i < G ? i : G];
+    s_En[i] = (i == 0) ? 0.0 : (i <= G - 1 ? tb.wbin_e[i] : __longlong_as_double(0x7ff0000000000000ll));
+  }
+  for (int i = threadIdx.x; i < C::N * C::WXC; i += blockDim.x) {
+    const int e = i / C::WXC, a = e >> LOGP, b = e & (P - 1);
+    s_wxy[i] = (a < G && b < G) ? __dmul_rn(tb.wbin[a], tb.wbin[b]) : 0.0;
+  }
+  __syncthreads();
 
   long long uid = (long long)blockIdx.x * UPB + ub;
   const int cap = ch.nslot_cap;
@@ -507,29 +530,28 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   if (__all_sync(0xffffffffu, !active)) return;
 
   const int k = ch.layer_of_slot[(size_t)c * nz + slot];  // ground-first layer index
-  const Continua q = rt_continua<LPU>(tb, ch, c, l, slot, k, ul);
   const unsigned umask = (LPU == 32 ? 0xffffffffu : ((1u << LPU) - 1u)) << (lane & ~(LPU - 1));
   bool unit_ok = true;
   const int kfirst = (FAST || tb.rows_sorted) ? LOGP + 1 : 1;
   const double *cA = tA + mycol, *cB = tB + mycol;
+  const bool general_walk = (tb.pad0 & 2) != 0;
 
-  // gas 0 -> table A; gas 1 -> registers (bn), put into table B at the top of its merge
+  // Gas pipeline: at the top of iteration jj `bn` holds k(g)*column of gas jj; the table loads of gas
+  // jj+1 are issued there and finished (interpolation + exp) at ONE place in the loop body.
+  // Iteration 0 only installs gas 0 as the running mixture.
   double bn[C::GPL];
   {
-    KgasRaw<P> r0, r1;
+    KgasRaw<P> r0;
     kgas_load<P>(tb, ch, c, l, slot, k, 0, ul, r0);
-    if (tb.nk > 1) kgas_load<P>(tb, ch, c, l, slot, k, 1, ul, r1);
-    double a0[C::GPL];
-    kgas_finish<P>(r0, G, ul, a0);
-#pragma unroll
-    for (int t = 0; t < C::GPL; t++) tbl_put<P>(tA, ul + LPU * t, a0[t], colbase, ul);
-    if (tb.nk > 1) kgas_finish<P>(r1, G, ul, bn);
+    kgas_finish<P>(r0, G, ul, bn);
   }
-  for (int jj = 1; jj < tb.nk; jj++) {
+  for (int jj = 0; jj < tb.nk; jj++) {
+    {
+      double *tdst = jj == 0 ? tA : tB;
 #pragma unroll
-    for (int t = 0; t < C::GPL; t++) tbl_put<P>(tB, ul + LPU * t, bn[t], colbase, ul);
+      for (int t = 0; t < C::GPL; t++) tbl_put<P>(tdst, ul + LPU * t, bn[t], colbase, ul);
+    }
     __syncwarp();
-    // loads of the next gas in flight during the non-interleaving test / key construction
     KgasRaw<P> rn;
     const bool more = jj + 1 < tb.nk;
     if (more) kgas_load<P>(tb, ch, c, l, slot, k, jj + 1, ul, rn);
@@ -539,11 +561,11 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     // cumulative-weight interval of new bin i, and the rebin (:843-849) returns
     // a_i * sum_j(w_j) + sum_j(w_j b_j) = a_i + <b>; symmetrically b_j + <a> when the columns do not
     // interleave.  (The reference's result differs from the closed form only by the rounding of
-    // its 256-term cumulative weights, O(1e-15) relative.)  Taken when every unit of the warp
-    // qualifies, so that the warp skips the sort as a whole.
+    // its 256-term cumulative weights, O(1e-15) relative.)  The warp skips the sort as a whole when
+    // every unit of the warp qualifies.
     bool triv = false, urow = false;
     double cf[C::GPL];
-    {
+    if (jj > 0) {
       const double a1 = cA[0], aG = cA[(G - 1) * CW], b1 = cB[0], bG = cB[(G - 1) * CW];
       bool rowmaj = true, colmaj = true;
       double ag[C::GPL], bg[C::GPL];
@@ -571,42 +593,46 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
         for (int t = 0; t < C::GPL; t++)
           cf[t] = (ul + LPU * t) < G ? __dadd_rn(urow ? ag[t] : bg[t], mean) : 0.0;
       }
-      if (__all_sync(0xffffffffu, triv)) {
-        if (more) kgas_finish<P>(rn, G, ul, bn);
-        __syncwarp();
+    }
+    if (more) kgas_finish<P>(rn, G, ul, bn);
+    if (jj == 0) continue;
+    if (__all_sync(0xffffffffu, triv)) {
+      __syncwarp();
 #pragma unroll
-        for (int t = 0; t < C::GPL; t++) tbl_put<P>(tA, ul + LPU * t, cf[t], colbase, ul);
-        __syncwarp();
-        continue;
-      }
+      for (int t = 0; t < C::GPL; t++) tbl_put<P>(tA, ul + LPU * t, cf[t], colbase, ul);
+      __syncwarp();
+      continue;
     }
 
-    // ---- keys: pos = ul*32 + r ;  i = pos >> LOGP (running mixture), j = pos & (P-1) (new gas)
+    // ---- keys: pos = ul*KPL + r ;  i = pos >> LOGP (running mixture), j = pos & (P-1) (new gas)
     double tot = 0.0;
     if (FAST) {
+      // f = ((bits >> S) - (bits_min >> S)) >> s2 : a 32-bit window of the IEEE-754 pattern, placed
+      // so that the largest sum (a_G + b_G) still fits in FB bits (S <= 32; s2 > 0 only when the
+      // sums span more than 2^56 patterns, i.e. more than 16 binades)
       const unsigned long long base = (unsigned long long)__double_as_longlong(cA[0] + cB[0]);
       const unsigned long long top =
           (unsigned long long)__double_as_longlong(cA[(G - 1) * CW] + cB[(G - 1) * CW]);
-      const unsigned long long range = top - base;
-      const int nb = 64 - __clzll((long long)range);  // bit length (0 for range == 0)
+      const int nb = 64 - __clzll((long long)(top - base));  // bit length (0 for range == 0)
       const int shift = nb > FB ? nb - FB : 0;
+      const int S = shift > 32 ? 32 : shift, s2 = shift - S;
+      const unsigned wb = __funnelshift_rc((unsigned)base, (unsigned)(base >> 32), S);
       unsigned x[C::KPL];
 #pragma unroll
       for (int r = 0; r < C::KPL; r++) {
         const int pos = ul * C::KPL + r;
         const int i = pos >> LOGP, j = pos & (P - 1);
         const double v = cA[i * CW] + cB[j * CW];  // :828 tau_xy
-        const unsigned f = (unsigned)(((unsigned long long)__double_as_longlong(v) - base) >> shift);
-        const unsigned key = (f << IDXBITS) | (unsigned)pos;
+        const unsigned wv = __funnelshift_rc((unsigned)__double2loint(v), (unsigned)__double2hiint(v), S);
+        const unsigned key = (((wv - wb) >> s2) << IDXBITS) | (unsigned)pos;
         x[r] = (FULL || ((i < G) && (j < G))) ? key : 0xffffffffu;
       }
-      if (more) kgas_finish<P>(rn, G, ul, bn);
       bitonic_network<P, unsigned>(x, ul, kfirst);
 #pragma unroll
       for (int r = 0; r < C::KPL; r++) {
         const unsigned idx = x[r] & C::IDXM;
         ip[r * 32] = (idx_t)idx;
-        tot = __dadd_rn(tot, wx[idx * C::WXC]);
+        tot = __dadd_rn(tot, lds_f64(aW + idx * (unsigned)(C::WXC * 8)));
       }
     } else {
       double x[C::KPL];
@@ -621,23 +647,27 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
         x[r] = __longlong_as_double(
             (long long)((bits & ~(unsigned long long)C::IDXM) | (unsigned long long)pos));
       }
-      if (more) kgas_finish<P>(rn, G, ul, bn);
       bitonic_network<P, double>(x, ul, kfirst);
 #pragma unroll
       for (int r = 0; r < C::KPL; r++) {
-        const unsigned idx = (unsigned)((unsigned long long)__double_as_longlong(x[r])) & C::IDXM;
+        const unsigned idx = (unsigned)__double2loint(x[r]) & C::IDXM;
         ip[r * 32] = (idx_t)idx;
-        tot = __dadd_rn(tot, wx[idx * C::WXC]);
+        tot = __dadd_rn(tot, lds_f64(aW + idx * (unsigned)(C::WXC * 8)));
       }
     }
     __syncwarp();
-    const bool ok = rt_rebin<P, FULL, FAST>(ip, tA, tB, sI, wx, s_E, s_ib, tot, G, ul, mycol, colbase);
-    if (__any_sync(0xffffffffu, triv)) {  // closed form for the qualifying units of a sorting warp
-      if (triv) {
+    bool ok;
+    if (!general_walk) {
+      ok = rt_rebin1<P, FULL, FAST>(aIP, tA, sI, aA, aB, aW, s_En, s_ib, tot, G, ul, colbase, triv, cf);
+    } else {
+      ok = rt_rebin<P, FULL, FAST>(ip, tA, tB, sI, wx, s_E, s_ib, tot, G, ul, mycol, colbase);
+      if (__any_sync(0xffffffffu, triv)) {  // closed form for the qualifying units of a sorting warp
+        if (triv) {
 #pragma unroll
-        for (int t = 0; t < C::GPL; t++) tbl_put<P>(tA, ul + LPU * t, cf[t], colbase, ul);
+          for (int t = 0; t < C::GPL; t++) tbl_put<P>(tA, ul + LPU * t, cf[t], colbase, ul);
+        }
+        __syncwarp();
       }
-      __syncwarp();
     }
     if (FAST) {
       const unsigned bal = __ballot_sync(0xffffffffu, ok || triv);
@@ -645,16 +675,18 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     }
   }
 
-  // ---- total tau, w0 clamp, band tau, asymmetry of the unit (:856-886) -> HBM (slot-indexed)
+  // ---- total tau, w0 clamp, band tau of the unit (:856-886) -> HBM (slot-indexed).  The
+  // g-independent terms come from continua_kernel (optics_rorr.cu).
   const size_t obase = (((size_t)c * tb.nw + l) * ch.nslot_cap + slot);
+  const size_t U = (size_t)ch.ncol * tb.nw * ch.nslot_cap;
+  const double q_s3 = ch.cont[obase], q_tauc = ch.cont[U + obase], q_sc = ch.cont[2 * U + obase];
 #pragma unroll
   for (int t = 0; t < C::GPL; t++) {
     const int gg = ul + LPU * t;
     if (gg < G) {
-      const double tau =
-          __dadd_rn(__dadd_rn(__dadd_rn(__dadd_rn(q.tausg, q.taua), q.taup), cA[gg * CW]), q.tauc);
+      const double tau = __dadd_rn(__dadd_rn(q_s3, cA[gg * CW]), q_tauc);
       double w0 = 0.0;
-      if (!(tau <= RT_TAU_MIN)) w0 = fmin(RT_MAX_W0, (q.tausg + q.tausp + q.tausc) / tau);
+      if (!(tau <= RT_TAU_MIN)) w0 = fmin(RT_MAX_W0, q_sc / tau);
       sI[gg] = tau;
       if (active) {
         ch.tau[obase * G + gg] = tau;
@@ -668,7 +700,6 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
 #pragma unroll 4
     for (int gg = 0; gg < G; gg++) tbnd = __dadd_rn(tbnd, __dmul_rn(sI[gg], s_w[gg]));
     ch.tband[obase] = tbnd;
-    ch.gt[obase] = q.gt;
   }
   if (FAST && !unit_ok && active && ul == 0) {
     const int p = atomicAdd(wcount, 1);

@@ -92,6 +92,7 @@ struct DevChunk {
   double *foreign_col; // [col][slot]
   // opacity (OpticalPropertiesResult, clima_radtran_types.f90:242-247), slot-indexed
   double *tau, *w0, *gt, *tband;
+  double *cont;  // [3][col][bin l][slot]: g-independent terms handed from continua_kernel to the RORR epilogue
   int *status;  // [col]
 };
 
