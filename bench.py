@@ -318,7 +318,12 @@ def run_ours(args):
                 "frac_of_issue_roof": achieved / (fp64_tf / 2.0),
                 "peak_source": "DFMA micro-kernel measured live in this run (FMA = 2 flops); "
                                "issue roof = peak/2 because the work is not FMA-shaped",
-                "algorithmic_ops_per_column": ops, "traffic": None,
+                "algorithmic_ops_per_column": ops,
+                # dram__bytes_read.sum + dram__bytes_write.sum of the fast RORR kernel from the
+                # ncu --set full capture at 256 columns (profiles/r1n_rorr_fast_raw.txt: 75.5 MB read,
+                # 626.1 MB written = the tau/w0 lines of every unit), scaled to this launch's columns
+                "traffic": roofline.RORR_FAST_DRAM_BYTES_PER_COLUMN * ncol,
+                "traffic_source": "ncu r1n capture at 256 columns, scaled per column",
                 "hbm": {"bound": "hbm", "achieved": k_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak,
                         "unit": "GB/s", "frac": k_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak,
                         "peak_source": hbm_src, "algorithmic_bytes_per_column": byt},

@@ -386,7 +386,7 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     const int exact = (h.rorr_exact_only || force_exact) ? 1 : 0;
     rt_launch_optics_rorr(h.tb, ch, h.d_worklist, h.d_wcount, h.wcap, exact, h.st);
     const bool two = !exact && h.tb.rows_sorted;
-    h.launches += two ? 2 : 1;
+    h.launches += two ? 3 : 2;  // continua + fast + exact, or continua + exact
     *h.h_wcount = 0;
     if (two)
       CK(cudaMemcpyAsync(h.h_wcount, h.d_wcount, sizeof(int), cudaMemcpyDeviceToHost, h.st));

@@ -309,3 +309,30 @@ def test_bit_reproducible_with_worklist_and_closed_form_merges():
         r2 = g.radiate_batch(cols, spectral=True)
         for k in r1:
             assert np.array_equal(r1[k], r2[k]), k
+
+
+def test_rorr_general_walk_matches_the_single_edge_walk(monkeypatch):
+    """Gauss-Legendre weight sets take the single-edge rebin walk (rt_rebin1); the general looping
+    walk (forced here) must give bit-identical opacities."""
+    tb, pr, cols = small_case(G=16, nw=12, nz=10, ncol=3)
+    g = Radtran(tb, pr)
+    r1 = g.radiate_batch(cols, spectral=True)
+    monkeypatch.setenv("CLIMA_RT_RORR_GENERAL_WALK", "1")
+    g2 = Radtran(tb, pr)
+    r2 = g2.radiate_batch(cols, spectral=True)
+    for k in r1:
+        assert np.array_equal(r1[k], r2[k]), k
+
+
+@pytest.mark.parametrize("G", [5, 16])
+def test_rorr_weights_with_several_edges_per_element(G):
+    """A weight set in which one sorted element (weight w_i*w_j) spans several new bins -- one
+    dominant g-point next to very narrow ones -- selects the general walk at table load
+    (capi.cu, DevTables::pad0 bit 1) and must still match the oracle."""
+    tb, pr, cols = small_case(G=G, nw=8, nz=8, ncol=2)
+    w = np.full(G, 0.02 / (G - 1))
+    w[G // 2] = 0.98
+    tb.weights[...] = w / w.sum()
+    assert (tb.weights.max() ** 2) > tb.weights.min()
+    g, o, rg, ro = run_both(tb, pr, cols)
+    compare(rg, ro)
