@@ -202,6 +202,8 @@ void build_tables(Handle &h, const clima_rt_tables *t) {
     }
     const char *gw = std::getenv("CLIMA_RT_RORR_GENERAL_WALK");
     if (!(wmax * wmax * 1.000001 < dmin) || (gw && gw[0] == '1')) d.pad0 |= 2;
+    const char *go = std::getenv("CLIMA_RT_RORR_GROUP");  // "layers": slot-fastest unit order
+    if (go && go[0] == 'l') d.pad0 |= 4;
   }
   h.d_photons = upload(h, t->photons_sol, h.nw_sol);
   h.d_albedo = upload<double>(h, nullptr, h.nw_sol);
@@ -290,7 +292,7 @@ void ensure_chunk(Handle &h, int ncol, int nz) {
   ch.cont = calloc_dev<double>(h, (size_t)3 * C * tb.nw * nz);
   ch.status = calloc_dev<int>(h, C);
   {
-    const long long units = (long long)C * tb.nw * nz;
+    const long long units = (long long)((C + 3) / 4 * 4) * tb.nw * nz;
     if (units >= (1ll << 31)) throw CudaError{"chunk too large: lower CLIMA_RT_CHUNK_COLS"};
     h.wcap = (int)std::min<long long>(units, std::max<long long>(65536, units / 8));
     h.d_worklist = calloc_dev<int>(h, h.wcap);

@@ -84,13 +84,15 @@ __global__ void tau_band_kernel(const DevTables tb, const DevChunk ch, int ind_s
 void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
                            int wcap, int exact_only, cudaStream_t st) {
   const long long units = (long long)ch.ncol * tb.nw * ch.nslot_cap;
+  // RORR unit ids run over columns rounded up to a multiple of 4 (column-grouped unit order)
+  const long long runits = (long long)((ch.ncol + 3) / 4 * 4) * tb.nw * ch.nslot_cap;
   continua_kernel<<<(unsigned)std::min<long long>((units + 255) / 256, 148 * 32), 256, 0, st>>>(tb, ch);
   if (exact_only || !tb.rows_sorted) {
-    rorr_launch_exact(tb, ch, nullptr, nullptr, 0, units, st);
+    rorr_launch_exact(tb, ch, nullptr, nullptr, 0, runits, st);
     return;
   }
   cudaMemsetAsync(wcount, 0, sizeof(int), st);
-  rorr_launch_fast(tb, ch, worklist, wcount, wcap, units, st);
+  rorr_launch_fast(tb, ch, worklist, wcount, wcap, runits, st);
   rorr_launch_exact(tb, ch, worklist, wcount, wcap, wcap, st);
 }
 

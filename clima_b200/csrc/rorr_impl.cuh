@@ -517,9 +517,22 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     if (n > wcap) n = wcap;
     if (uid < n) uid = worklist[uid]; else { active = false; uid = 0; }
   }
-  int slot = (int)(uid % cap);
-  const int l = (int)((uid / cap) % nw);
-  const long long cl = uid / ((long long)cap * nw);
+  // unit id -> (column, bin, slot).  Default: the units of a warp are the SAME (bin, slot) of
+  // adjacent columns (uid = ((c/4 * nw + l) * cap + slot) * 4 + c%4): neighbouring columns of a
+  // sweep take the closed-form / sort decision together far more often than neighbouring layers
+  // of one column, and they read the same k-table rows.  pad0 bit 2: slot-fastest order.
+  int slot, l;
+  long long cl;
+  if (tb.pad0 & 4) {
+    slot = (int)(uid % cap);
+    l = (int)((uid / cap) % nw);
+    cl = uid / ((long long)cap * nw);
+  } else {
+    const long long q = uid >> 2;
+    slot = (int)(q % cap);
+    l = (int)((q / cap) % nw);
+    cl = (q / ((long long)cap * nw)) * 4 + (uid & 3);
+  }
   if (cl >= ch.ncol) active = false;
   const int c = cl < ch.ncol ? (int)cl : ch.ncol - 1;
   const int nsl = ch.nslots[c];
