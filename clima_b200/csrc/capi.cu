@@ -557,6 +557,73 @@ void radiate_batch_impl(Handle &h, bool device, int ncol, int nz, int ng, int np
   }
 }
 
+
+// ---- N1: the temperature-perturbation loop of AdiabatClimate_jacobian_from_base --------------
+// AdiabatClimate_copy_atm_to_radiative_grid (src/adiabat/clima_adiabat.f90:729-773), temperature
+// only: model layer i -> RT layers 2i, 2i+1, two ghost copies of the top layer.
+__global__ void expand_T_kernel(const double *__restrict__ Tm, double *__restrict__ Tr, int nzm,
+                                int ncol) {
+  const int nzr = 2 * nzm + 2;
+  const size_t total = (size_t)ncol * nzr;
+  for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const int j = (int)(t % nzr);
+    const size_t c = t / nzr;
+    const int i = j < 2 * nzm ? j / 2 : nzm - 1;
+    Tr[t] = Tm[c * nzm + i];
+  }
+}
+// f_total(i) = rad%f_total(2*i-1), i = 1..nz+1 (src/adiabat/clima_adiabat_solve.f90:731-733)
+__global__ void extract_ftotal_kernel(const double *__restrict__ fr, double *__restrict__ fm,
+                                      int nzm, int ncol) {
+  const int Lr = 2 * nzm + 3, Lm = nzm + 1;
+  const size_t total = (size_t)ncol * Lm;
+  for (size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x; t < total;
+       t += (size_t)gridDim.x * blockDim.x) {
+    const int i = (int)(t % Lm);
+    const size_t c = t / Lm;
+    fm[t] = fr[c * Lr + 2 * i];
+  }
+}
+
+void jacobian_batch_impl(Handle &h, int ncol, int nzm, const double *T_surface, const double *T,
+                         double *f_total) {
+  CK(cudaSetDevice(h.device));
+  if (ncol < 1) throw CudaError{"\"ncol\" can not be less than 1."};
+  if (nzm < 1) throw CudaError{"\"nz\" can not be less than 1."};
+  const int nzr = 2 * nzm + 2;
+  if (h.retained_opacity_ncol != 1 || h.retained_nz != nzr || h.cap_nz != nzr)
+    throw CudaError{"clima_rt_jacobian_batch needs the opacity of ONE base column on the doubled grid "
+                    "(2*nz+2 layers) retained in the handle: call clima_rt_radiate_batch with ncol=1, "
+                    "compute_opacity=1 first"};
+  if (h.retained_solar_ncol != 1)
+    throw CudaError{"clima_rt_jacobian_batch needs the solar fluxes of the base column retained in the "
+                    "handle (compute_solar=1 in the base call)"};
+  grow_for_bcast(h, ncol, nzr);
+  const int C = h.cap_cols;
+  if ((size_t)C * (nzm + 1) * 8 > h.tmp_bytes) throw CudaError{"internal: staging buffer too small"};
+  for (int i = 0; i < 6; i++) h.stage_ms[i] = 0.0;
+  for (int c0 = 0; c0 < ncol; c0 += C) {
+    const int n = std::min(C, ncol - c0);
+    DevChunk &ch = h.ch;
+    CK(cudaMemcpyAsync(h.d_Tsurf, T_surface + c0, n * 8, cudaMemcpyHostToDevice, h.st));
+    // model-grid temperatures staged in the (unused in this mode) pressure buffer
+    CK(cudaMemcpyAsync(h.d_P, T + (size_t)c0 * nzm, (size_t)n * nzm * 8, cudaMemcpyHostToDevice, h.st));
+    expand_T_kernel<<<std::min(1184, (n * nzr + 255) / 256), 256, 0, h.st>>>(h.d_P, h.d_T, nzm, n);
+    h.launches++;
+    ch.T_surface = h.d_Tsurf; ch.T = h.d_T; ch.P = h.d_P; ch.dz = h.d_dz; ch.dens = h.d_dens;
+    ch.pdens = nullptr; ch.radii = nullptr;
+    run_chunk(h, n, nzr, false, false, true, true);
+    extract_ftotal_kernel<<<std::min(1184, (n * (nzm + 1) + 255) / 256), 256, 0, h.st>>>(
+        h.fx.f_total, h.d_tmp, nzm, n);
+    h.launches++;
+    CK(cudaMemcpyAsync(f_total + (size_t)c0 * (nzm + 1), h.d_tmp, (size_t)n * (nzm + 1) * 8,
+                       cudaMemcpyDeviceToHost, h.st));
+    CK(cudaStreamSynchronize(h.st));
+    accumulate_stage_ms(h);
+  }
+}
+
 }  // namespace
 
 // =============================================================================================
@@ -683,6 +750,20 @@ void clima_rt_radiate_batch_device(void *handle, const int32_t *ncol, const int3
                        *compute_solar != 0, *compute_opacity != 0, out);
   } catch (const CudaError &e) {
     set_err(err, e.msg);
+  }
+}
+
+void clima_rt_jacobian_batch(void *handle, const int32_t *ncol, const int32_t *nz,
+                             const double *T_surface, const double *T, double *f_total, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle) throw CudaError{"clima_rt: null handle"};
+    if (!ncol || !nz || !T_surface || !T || !f_total) throw CudaError{"clima_rt: null argument"};
+    jacobian_batch_impl(*static_cast<Handle *>(handle), *ncol, *nz, T_surface, T, f_total);
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  } catch (const std::exception &e) {
+    set_err(err, e.what());
   }
 }
 

@@ -26,7 +26,8 @@ _lib = None
 
 EXPORTS = ["clima_rt_create", "clima_rt_destroy", "clima_rt_set_params",
            "clima_rt_set_custom_optical_properties", "clima_rt_unset_custom_optical_properties",
-           "clima_rt_radiate_batch", "clima_rt_radiate_batch_device", "clima_rt_get_opacity",
+           "clima_rt_radiate_batch", "clima_rt_radiate_batch_device", "clima_rt_jacobian_batch",
+           "clima_rt_get_opacity",
            "clima_rt_get_launch_count", "clima_rt_get_stage_ms", "clima_rt_get_stream", "clima_rt_get_rorr_stats", "clima_rt_measure_fp64_peak",
            "clima_rt_version_get"]
 
@@ -174,6 +175,22 @@ class Radtran:
     def TOA_fluxes_batch(self, cols: Dict):
         r = self.radiate_batch(cols)
         return r["ISR"], r["OLR"]
+
+    def jacobian_batch(self, T_surface, T):
+        """Perturbed-temperature batch of AdiabatClimate_jacobian_from_base
+        (src/adiabat/clima_adiabat_solve.f90:798-820) in one call: T_surface(ncol), T(nz,ncol) on the
+        MODEL grid; the handle must hold the base column (radiate on the doubled grid, ncol=1).
+        Returns f_total(nz+1,ncol) = rad%f_total(2i-1) of every perturbed column."""
+        Ts = np.ascontiguousarray(T_surface, dtype=np.float64)
+        T = np.asfortranarray(T, dtype=np.float64)
+        nz, ncol = T.shape
+        if Ts.shape != (ncol,):
+            raise ClimaException("T_surface and T disagree on the number of columns")
+        out = np.zeros((nz + 1, ncol), order="F")
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self._lib.clima_rt_jacobian_batch(self._h, _i(ncol), _i(nz), dptr(Ts), dptr(T), dptr(out), err)
+        _check(err)
+        return out
 
     # ---- the reference's single-column API (clima_radtran.f90:221-342)
     def radiate(self, T_surface, T, P, densities, dz, pdensities=None, radii=None,

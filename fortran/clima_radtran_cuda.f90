@@ -107,6 +107,15 @@ module clima_radtran_cuda
       type(c_out), intent(in) :: res
       character(kind=c_char), intent(out) :: err(*)
     end subroutine
+    subroutine clima_rt_jacobian_batch(handle, ncol, nz, T_surface, T, f_total, err) &
+                                       bind(c, name='clima_rt_jacobian_batch')
+      import :: c_ptr, c_int32_t, c_double, c_char
+      type(c_ptr), value :: handle
+      integer(c_int32_t), intent(in) :: ncol, nz
+      real(c_double), intent(in) :: T_surface(*), T(*)
+      real(c_double), intent(out) :: f_total(*)
+      character(kind=c_char), intent(out) :: err(*)
+    end subroutine
   end interface
 
 contains
@@ -232,6 +241,33 @@ contains
 
     call clima_rt_radiate_batch(rc%handle, ncol, nz, ng, np, T_surface, T, P, densities, dz, &
                                 pd, rd, csol, cop, o, err_c)
+    call copy_err(err_c, err)
+  end subroutine
+
+  !> The perturbed-temperature radiative transfers of `AdiabatClimate_jacobian_from_base`
+  !> (src/adiabat/clima_adiabat_solve.f90:798-820) in one call.  `T_in(:,c)` is the model-grid vector
+  !> [T_surf, T(1:nz)] of perturbation `c` (the reference's `T_perturb`); `f_total(:,c)` receives
+  !> `rad%f_total(2*i-1)`, i = 1..nz+1 (:731-733), without `surface_heat_flow`.  The handle must hold
+  !> the base column (the objective evaluation that precedes the loop, :757).
+  subroutine radtran_jacobian_batch(rc, T_in, f_total, err)
+    type(RadtranCuda), intent(inout) :: rc
+    real(dp), intent(in) :: T_in(:,:)        !! (nz+1,ncol) K
+    real(dp), intent(out) :: f_total(:,:)    !! (nz+1,ncol) mW/m^2
+    character(:), allocatable, intent(out) :: err
+
+    integer(c_int32_t) :: ncol, nz
+    real(dp), allocatable :: T_surface(:), T(:,:)
+    character(kind=c_char) :: err_c(err_len+1)
+
+    ncol = int(size(T_in,2), c_int32_t); nz = int(size(T_in,1) - 1, c_int32_t)
+    if (any(shape(f_total) /= shape(T_in))) then
+      err = '"jacobian_batch": f_total must have the shape of T_in.'
+      return
+    endif
+    allocate(T_surface(ncol), T(nz,ncol))
+    T_surface(:) = T_in(1,:)
+    T(:,:) = T_in(2:,:)
+    call clima_rt_jacobian_batch(rc%handle, ncol, nz, T_surface, T, f_total, err_c)
     call copy_err(err_c, err)
   end subroutine
 

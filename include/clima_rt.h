@@ -208,6 +208,21 @@ void clima_rt_radiate_batch_device(void *handle, const int32_t *ncol, const int3
                                    const int32_t *compute_solar, const int32_t *compute_opacity,
                                    const clima_rt_out *out, char *err);
 
+/* N1: the temperature-perturbation loop of AdiabatClimate_jacobian_from_base
+   (src/adiabat/clima_adiabat_solve.f90:798-820) as ONE call.  The handle must hold the opacity and
+   the solar fluxes of the BASE column on the doubled radiative grid (a previous
+   clima_rt_radiate_batch with ncol=1, nz_r = 2*nz+2, compute_opacity=1, compute_solar=1, i.e. the
+   objective evaluation that precedes the Jacobian in the reference, :757-761).  Inputs are on the
+   MODEL grid: T_surface(ncol), T(nz,ncol), one perturbed temperature profile per column.  On the
+   device: AdiabatClimate_copy_atm_to_radiative_grid (src/adiabat/clima_adiabat.f90:729-773,
+   temperatures only: each layer twice + two ghost copies of the top layer), then `radiate` with
+   compute_opacity=.false., compute_solar=.false. for every column (opacity and stale solar fluxes
+   broadcast), then f_total(i) = rad%f_total(2*i-1) (:731-733).
+   Output: f_total(nz+1,ncol) [mW/m^2], WITHOUT surface_heat_flow (the caller adds it, :734).
+   All pointers are HOST pointers. */
+void clima_rt_jacobian_batch(void *handle, const int32_t *ncol, const int32_t *nz,
+                             const double *T_surface, const double *T, double *f_total, char *err);
+
 /* Copy the retained opacity of column `*icol` (0-based) of the last chunk to the host:
    tau(nz,ngauss,nw), w0(nz,ngauss,nw), g(nz,nw), tau_band(nz,nw), all TOP-first exactly like
    `type OpticalPropertiesResult` (clima_radtran_types.f90:242-247).  Test/debug hook. */

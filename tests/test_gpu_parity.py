@@ -336,3 +336,47 @@ def test_rorr_weights_with_several_edges_per_element(G):
     assert (tb.weights.max() ** 2) > tb.weights.min()
     g, o, rg, ro = run_both(tb, pr, cols)
     compare(rg, ro)
+
+
+def test_jacobian_batch_entry_matches_the_reference_loop():
+    """clima_rt_jacobian_batch == the loop of AdiabatClimate_jacobian_from_base
+    (clima_adiabat_solve.f90:798-820): for each perturbed model-grid temperature profile, copy to the
+    doubled radiative grid (clima_adiabat.f90:729-773), radiate with compute_opacity=.false.,
+    compute_solar=.false., take f_total(2i-1).  Checked against the oracle run column by column."""
+    nzm = 7
+    tb, pr, base = small_case(G=16, nw=10, nz=nzm, ncol=1, nzen=1, doubled=True)
+    g = Radtran(tb, pr)
+    o = OracleRadtran(tb, pr)
+    g.radiate_batch(base, spectral=False)   # objective at the base state (retains opacity + solar)
+    o.radiate(base, 0, spectral=False)
+    nzr = base["nz"]
+    assert nzr == 2 * nzm + 2
+    Tm = base["T"][0:2 * nzm:2, 0].copy()
+    Ts0 = float(base["T_surface"][0])
+    ncol = nzm + 1
+    T = np.repeat(Tm[:, None], ncol, axis=1).copy(order="F")
+    Ts = np.full(ncol, Ts0)
+    eps = 1.0e-2
+    Ts[0] += eps * Ts0
+    for i in range(nzm):
+        T[i, i + 1] += eps * Tm[i]
+    f = g.jacobian_batch(Ts, T)
+    assert f.shape == (nzm + 1, ncol)
+    for c in range(ncol):
+        Tr = np.empty(nzr)
+        Tr[0:2 * nzm:2] = T[:, c]; Tr[1:2 * nzm:2] = T[:, c]; Tr[2 * nzm:] = T[nzm - 1, c]
+        pert = dict(base, T_surface=np.array([Ts[c]]), T=np.asfortranarray(Tr[:, None]))
+        ro = o.radiate(pert, 0, compute_solar=False, compute_opacity=False, spectral=False)
+        ref = ro["f_total"][0:2 * nzm + 1:2, 0]
+        assert rel_err(f[:, c], ref) < TOL
+    # the base column itself is reproduced bit for bit by an unperturbed entry
+    f0 = g.jacobian_batch(np.array([Ts0]), Tm[:, None])
+    r0 = g.radiate_batch(base, compute_solar=False, compute_opacity=False)
+    assert np.array_equal(f0[:, 0], r0["f_total"][0:2 * nzm + 1:2, 0])
+
+
+def test_jacobian_batch_without_base_fails_loudly():
+    tb, pr, cols = small_case(G=16, nw=10, nz=6, ncol=2, nzen=1)
+    g = Radtran(tb, pr)
+    with pytest.raises(ClimaException, match="base column"):
+        g.jacobian_batch(np.array([300.0]), np.full((6, 1), 250.0))
