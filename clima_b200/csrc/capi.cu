@@ -193,6 +193,15 @@ void build_tables(Handle &h, const clima_rt_tables *t) {
   d.wbin = upload(h, wb.data(), G);
   d.wbin_e = upload(h, we.data(), G + 1);
   d.inv_dw = upload(h, iw.data(), G);
+  {  // RORR weight table wxy(j + i*P) = wbin(i)*wbin(j) (types_create.f90:216-222), in the kernel's
+     // shared-memory layout: P = ngauss padded to 8/16/32, 4 copies per entry, zero padding
+    const int P = G <= 8 ? 8 : (G <= 16 ? 16 : 32);
+    std::vector<double> wxy((size_t)P * P * 4, 0.0);
+    for (int a = 0; a < G; a++)
+      for (int b = 0; b < G; b++)
+        for (int cpy = 0; cpy < 4; cpy++) wxy[((size_t)a * P + b) * 4 + cpy] = wb[a] * wb[b];
+    d.wxy = upload(h, wxy.data(), wxy.size());
+  }
   {  // can one sorted element (weight w_i*w_j) contain two bin edges?  Never for Gauss-Legendre sets;
      // otherwise the RORR kernels take the general (looping) rebin walk: DevTables::pad0 bit 1.
     double wmax = 0.0, dmin = 1.0e300;

@@ -69,7 +69,7 @@ struct Cfg {
   static constexpr unsigned ROWMASK = (unsigned)(P - 1) << ROWSH;
   // dynamic shared memory: [alignment slack TBLB][4 warps x (tA, tB)][wxy N*WXC doubles]
   //                        [4 warps x edge integrals][4 warps x sorted-index bytes (general walk)]
-  static constexpr size_t SI_BYTES = (size_t)UPW * SPU * sizeof(double);
+  static constexpr size_t SI_BYTES = (size_t)UPW * 2 * SPU * sizeof(double);  // per unit: I(E_g), then its copy of the edges
   static constexpr size_t IP_BYTES = (size_t)KPL * 32 * IDXB;
   static constexpr size_t BLOCK_BYTES =
       (size_t)TBLB * 9 + (size_t)N * WXC * sizeof(double) + 4 * (SI_BYTES + IP_BYTES);
@@ -351,13 +351,14 @@ __device__ __forceinline__ bool rt_rebin(const typename IdxT<Cfg<P>::IDXB>::type
 //     branch: with 32 lanes walking, SOME lane has an edge in 85 % of the steps);
 //   * gathers by 32-bit shared address  base | row offset  (tables aligned to their size), issued
 //     one element ahead of the recurrence;
-//   * s_En = bin edges with +inf beyond the last interior edge (no g < G-1 test);
+//   * every unit has its own copy of the bin edges behind its I(E_g) slots, with +inf beyond the
+//     last interior edge (no g < G-1 test); the edge block walks ONE pointer through both;
 //   * a unit with `triv` set receives `cf` (its closed-form result) instead of the rebinned values.
 // Rolled (x4): the kernel is instruction-cache bound, every unrolled copy costs more than it saves.
 template <int P, bool FULL, bool CERT>
 __device__ __forceinline__ bool rt_rebin1(const unsigned aIP, double *tA, double *sI,
                                           const unsigned aA, const unsigned aB, const unsigned aW,
-                                          const double *s_En, const double *s_ib, const double tot,
+                                          const double *s_ib, const double tot,
                                           const int G, const int ul, const int colbase,
                                           const bool triv, const double (&cf)[Cfg<P>::GPL]) {
   using C = Cfg<P>;
@@ -371,12 +372,15 @@ __device__ __forceinline__ bool rt_rebin1(const unsigned aIP, double *tA, double
   const double off_next = off;  // bit-identically the start of the next lane (edge ownership)
   off = __shfl_up_sync(0xffffffffu, off_next, 1, LPU);
   if (ul == 0) off = 0.0;
+  const double *sEn = sI + C::SPU;  // the unit's copy of the edges (+inf beyond the last interior one)
   int g = 0;  // largest g with E[g] < off
 #pragma unroll
   for (int s = P / 2; s > 0; s >>= 1)
-    if (s_En[g + s] < off) g += s;
+    if (sEn[g + s] < off) g += s;
   const int g_first = g;
-  double n1 = s_En[g + 1];
+  // pg -> I(E_g) of the current bin; the edge block is  pg[1] = I(edge); n1 = next edge; pg++
+  double *pg = sI + g;
+  double n1 = pg[C::SPU + 1];
   double I = 0.0, o0 = off, prev = -1.0;
   bool ok = true;
   unsigned idx = lds_idx<C::IDXB>(aIP);
@@ -400,9 +404,9 @@ __device__ __forceinline__ bool rt_rebin1(const unsigned aIP, double *tA, double
     }
     const double o1 = __dadd_rn(o0, w);
     if (o1 > n1) {  // the element contains the right edge of new bin g
-      g++;
-      sI[g] = __fma_rn(__dsub_rn(n1, o0), tv, I);
-      n1 = s_En[g + 1];
+      pg[1] = __fma_rn(__dsub_rn(n1, o0), tv, I);
+      n1 = pg[C::SPU + 2];
+      pg++;
     }
     I = __fma_rn(w, tv, I);
     o0 = o1;
@@ -417,11 +421,12 @@ __device__ __forceinline__ bool rt_rebin1(const unsigned aIP, double *tA, double
     }
     const double o1 = ul < LPU - 1 ? off_next : __dadd_rn(o0, nw);
     if (o1 > n1) {
-      g++;
-      sI[g] = __fma_rn(__dsub_rn(n1, o0), tv, I);
+      pg[1] = __fma_rn(__dsub_rn(n1, o0), tv, I);
+      pg++;
     }
     I = __fma_rn(nw, tv, I);
   }
+  g = (int)(pg - sI);
   // lane offsets of the integral
   double Ioff = I;
 #pragma unroll
@@ -473,7 +478,6 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   constexpr int IDXBITS = 2 * LOGP, FB = 32 - IDXBITS;
   __shared__ double s_w[P];       // wbin, zero padded
   __shared__ double s_E[P + 1];   // wbin_e
-  __shared__ double s_En[P + 1];  // interior edges wbin_e(2..G), +inf beyond (single-edge walk)
   __shared__ double s_ib[P];      // 1/(wbin_e(g+1)-wbin_e(g))
   extern __shared__ double s_dyn[];
 
@@ -490,8 +494,8 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   double *tA = (double *)(dbase + (size_t)warp * 2 * C::TBLB);  // running mixture a(i), [row][column]
   double *tB = tA + C::TBL;                                      // new gas b(j)
   double *s_wxy = (double *)(dbase + 8 * (size_t)C::TBLB);  // [idx][copy]: wxy(j + i*P), types_create.f90:216-222
-  double *sI = s_wxy + C::N * C::WXC + (size_t)warp * (C::UPW * C::SPU) + (ub % C::UPW) * C::SPU;  // I(E_g)
-  idx_t *ip = (idx_t *)(s_wxy + C::N * C::WXC + 4 * (C::UPW * C::SPU)) + (size_t)warp * (C::KPL * 32) + lane;
+  double *sI = s_wxy + C::N * C::WXC + ((size_t)warp * C::UPW + (ub % C::UPW)) * (2 * C::SPU);  // I(E_g), then edges
+  idx_t *ip = (idx_t *)(s_wxy + C::N * C::WXC + 4 * (C::UPW * 2 * C::SPU)) + (size_t)warp * (C::KPL * 32) + lane;
   const double *wx = s_wxy + (lane & (C::WXC - 1));
   const unsigned aA = smem_u32(tA + mycol), aB = smem_u32(tB + mycol), aW = smem_u32(wx), aIP = smem_u32(ip);
 
@@ -499,14 +503,16 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     s_w[i] = i < G ? tb.wbin[i] : 0.0;
     s_ib[i] = i < G ? tb.inv_dw[i] : 0.0;
   }
-  for (int i = threadIdx.x; i < P + 1; i += blockDim.x) {
-    s_E[i] = tb.wbin_e[i < G ? i : G];
-    s_En[i] = (i == 0) ? 0.0 : (i <= G - 1 ? tb.wbin_e[i] : __longlong_as_double(0x7ff0000000000000ll));
+  for (int i = threadIdx.x; i < P + 1; i += blockDim.x) s_E[i] = tb.wbin_e[i < G ? i : G];
+  for (int i = threadIdx.x; i < UPB * (P + 1); i += blockDim.x) {  // per-unit edge copies
+    const int u = i / (P + 1), e = i % (P + 1);
+    s_wxy[C::N * C::WXC + (size_t)u * (2 * C::SPU) + C::SPU + e] =
+        (e == 0) ? 0.0 : (e <= G - 1 ? tb.wbin_e[e] : __longlong_as_double(0x7ff0000000000000ll));
   }
-  for (int i = threadIdx.x; i < C::N * C::WXC; i += blockDim.x) {
-    const int e = i / C::WXC, a = e >> LOGP, b = e & (P - 1);
-    s_wxy[i] = (a < G && b < G) ? __dmul_rn(tb.wbin[a], tb.wbin[b]) : 0.0;
-  }
+  // wxy(j + i*P) = wbin(i)*wbin(j) (types_create.f90:216-222), WXC copies per entry, precomputed
+  // on the host in exactly this layout (capi.cu)
+  for (int i = threadIdx.x; i < C::N * C::WXC / 2; i += blockDim.x)
+    reinterpret_cast<double2 *>(s_wxy)[i] = reinterpret_cast<const double2 *>(tb.wxy)[i];
   __syncthreads();
 
   long long uid = (long long)blockIdx.x * UPB + ub;
@@ -631,11 +637,19 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
       const int S = shift > 32 ? 32 : shift, s2 = shift - S;
       const unsigned wb = __funnelshift_rc((unsigned)base, (unsigned)(base >> 32), S);
       unsigned x[C::KPL];
+      double bj[P <= 16 ? P : 1], ai[P <= 16 ? C::KPL / P : 1];  // the lane's operands, loaded once
+      if (P <= 16) {
+#pragma unroll
+        for (int j = 0; j < P; j++) bj[j] = cB[j * CW];
+#pragma unroll
+        for (int t = 0; t < C::KPL / P; t++) ai[t] = cA[(ul * (C::KPL / P) + t) * CW];
+      }
 #pragma unroll
       for (int r = 0; r < C::KPL; r++) {
         const int pos = ul * C::KPL + r;
         const int i = pos >> LOGP, j = pos & (P - 1);
-        const double v = cA[i * CW] + cB[j * CW];  // :828 tau_xy
+        const double v = (P <= 16) ? __dadd_rn(ai[P <= 16 ? r / P : 0], bj[P <= 16 ? r % P : 0])
+                                   : __dadd_rn(cA[i * CW], cB[j * CW]);  // :828 tau_xy
         const unsigned wv = __funnelshift_rc((unsigned)__double2loint(v), (unsigned)__double2hiint(v), S);
         const unsigned key = (((wv - wb) >> s2) << IDXBITS) | (unsigned)pos;
         x[r] = (FULL || ((i < G) && (j < G))) ? key : 0xffffffffu;
@@ -649,11 +663,19 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
       }
     } else {
       double x[C::KPL];
+      double bj[P <= 16 ? P : 1], ai[P <= 16 ? C::KPL / P : 1];  // the lane's operands, loaded once
+      if (P <= 16) {
+#pragma unroll
+        for (int j = 0; j < P; j++) bj[j] = cB[j * CW];
+#pragma unroll
+        for (int t = 0; t < C::KPL / P; t++) ai[t] = cA[(ul * (C::KPL / P) + t) * CW];
+      }
 #pragma unroll
       for (int r = 0; r < C::KPL; r++) {
         const int pos = ul * C::KPL + r;
         const int i = pos >> LOGP, j = pos & (P - 1);
-        const double v = cA[i * CW] + cB[j * CW];  // :828 tau_xy
+        const double v = (P <= 16) ? __dadd_rn(ai[P <= 16 ? r / P : 0], bj[P <= 16 ? r % P : 0])
+                                   : __dadd_rn(cA[i * CW], cB[j * CW]);  // :828 tau_xy
         const unsigned long long bits = (FULL || ((i < G) && (j < G)))
                                             ? (unsigned long long)__double_as_longlong(v)
                                             : 0x7fe0000000000000ull;  // huge, finite
@@ -671,7 +693,7 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     __syncwarp();
     bool ok;
     if (!general_walk) {
-      ok = rt_rebin1<P, FULL, FAST>(aIP, tA, sI, aA, aB, aW, s_En, s_ib, tot, G, ul, colbase, triv, cf);
+      ok = rt_rebin1<P, FULL, FAST>(aIP, tA, sI, aA, aB, aW, s_ib, tot, G, ul, colbase, triv, cf);
     } else {
       ok = rt_rebin<P, FULL, FAST>(ip, tA, tB, sI, wx, s_E, s_ib, tot, G, ul, mycol, colbase);
       if (__any_sync(0xffffffffu, triv)) {  // closed form for the qualifying units of a sorting warp
