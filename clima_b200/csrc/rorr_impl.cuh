@@ -109,6 +109,9 @@ __device__ __forceinline__ unsigned lds_idx(unsigned addr) {
   else asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr));
   return v;
 }
+__device__ __forceinline__ void sts_f64(unsigned addr, double v) {
+  asm volatile("st.shared.f64 [%0], %1;" ::"r"(addr), "d"(v) : "memory");
+}
 __device__ __forceinline__ double lds_f64(unsigned addr) {
   double v;
   asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
@@ -170,7 +173,11 @@ __device__ __forceinline__ void bitonic_network(K (&x)[Cfg<P>::KPL], const int u
         if ((r & (1 << s)) == 0) ce(x[r], x[r | (1 << s)]);
     }
   }
+#ifdef RORR_UNROLL_CROSS
+#pragma unroll
+#else
 #pragma unroll 1
+#endif
   for (int k = (kfirst > LOGK + 1 ? kfirst : LOGK + 1); k <= K1; k++) {
     {  // flip step: pos <-> pos ^ (2^k - 1): partner lane ul ^ lm, partner register r ^ (KPL-1)
       const int lm = ((1 << k) - 1) >> LOGK;
@@ -183,7 +190,11 @@ __device__ __forceinline__ void bitonic_network(K (&x)[Cfg<P>::KPL], const int u
         x[r ^ (KPL - 1)] = pick(keepmin, x[r ^ (KPL - 1)], y2);
       }
     }
+#ifdef RORR_UNROLL_CROSS
+#pragma unroll
+#else
 #pragma unroll 1
+#endif
     for (int s = k - 2; s >= LOGK; s--) {  // cross-lane half-cleaners
       const int lm = 1 << (s - LOGK);
       const bool keepmin = (ul & lm) == 0;
@@ -400,9 +411,10 @@ __device__ __forceinline__ bool rt_rebin1(const unsigned aIP, double *tA, double
   for (int s = P / 2; s > 0; s >>= 1)
     if (sEn[g + s] < off) g += s;
   const int g_first = g;
-  // pg -> I(E_g) of the current bin; the edge block is  pg[1] = I(edge); n1 = next edge; pg++
-  double *pg = sI + g;
-  double n1 = pg[C::SPU + 1];
+  // pg -> I(E_g) of the current bin (32-bit shared address); the edge block is
+  //   pg[1] = I(edge); n1 = next edge; pg++
+  unsigned pg = smem_u32(sI + g);
+  double n1 = lds_f64(pg + (unsigned)(C::SPU + 1) * 8u);
   double I = 0.0, o0 = off, prev = -1.0;
   bool ok = true;
   unsigned idx = lds_idx<C::IDXB>(aIP);
@@ -426,9 +438,9 @@ __device__ __forceinline__ bool rt_rebin1(const unsigned aIP, double *tA, double
     }
     const double o1 = __dadd_rn(o0, w);
     if (o1 > n1) {  // the element contains the right edge of new bin g
-      pg[1] = __fma_rn(__dsub_rn(n1, o0), tv, I);
-      n1 = pg[C::SPU + 2];
-      pg++;
+      sts_f64(pg + 8u, __fma_rn(__dsub_rn(n1, o0), tv, I));
+      n1 = lds_f64(pg + (unsigned)(C::SPU + 2) * 8u);
+      pg += 8u;
     }
     I = __fma_rn(w, tv, I);
     o0 = o1;
@@ -443,12 +455,12 @@ __device__ __forceinline__ bool rt_rebin1(const unsigned aIP, double *tA, double
     }
     const double o1 = ul < LPU - 1 ? off_next : __dadd_rn(o0, nw);
     if (o1 > n1) {
-      pg[1] = __fma_rn(__dsub_rn(n1, o0), tv, I);
-      pg++;
+      sts_f64(pg + 8u, __fma_rn(__dsub_rn(n1, o0), tv, I));
+      pg += 8u;
     }
     I = __fma_rn(nw, tv, I);
   }
-  g = (int)(pg - sI);
+  g = (int)((pg - smem_u32(sI)) >> 3);
   // lane offsets of the integral
   double Ioff = I;
 #pragma unroll
