@@ -272,7 +272,10 @@ __device__ __forceinline__ void kgas_finish(const KgasRaw<P> &r, const int G, co
     const int g = ul + C::LPU * t;
     const double fx1 = p1 * r.f[4 * t + 0] + r.q1 * r.f[4 * t + 1];
     const double fx2 = p1 * r.f[4 * t + 2] + r.q1 * r.f[4 * t + 3];
-    v[t] = g < G ? rt_ten2power(p2 * fx1 + r.q2 * fx2) * r.col : 0.0;  // :660, :816-819 / :828
+    const double lk = p2 * fx1 + r.q2 * fx2;
+    // lean exp inside the physical range of k-tables, the library routine otherwise
+    const double kv = (lk > -280.0 && lk < 280.0) ? rt_ten2power_lean(lk) : rt_ten2power_cold(lk);
+    v[t] = g < G ? kv * r.col : 0.0;  // :660, :816-819 / :828
   }
 }
 
@@ -549,32 +552,32 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     reinterpret_cast<double2 *>(s_wxy)[i] = reinterpret_cast<const double2 *>(tb.wxy)[i];
   __syncthreads();
 
-  long long uid = (long long)blockIdx.x * UPB + ub;
-  const int cap = ch.nslot_cap;
+  // unit ids fit in 31 bits (the chunk is sized so, capi.cu): 32-bit divisions, no 64-bit subroutines
+  unsigned uid = blockIdx.x * (unsigned)UPB + (unsigned)ub;
+  const unsigned cap = (unsigned)ch.nslot_cap;
   bool active = true;
   if (!FAST && worklist) {
     int n = *wcount;
     if (n > wcap) n = wcap;
-    if (uid < n) uid = worklist[uid]; else { active = false; uid = 0; }
+    if (uid < (unsigned)n) uid = (unsigned)worklist[uid]; else { active = false; uid = 0; }
   }
   // unit id -> (column, bin, slot).  Default: the units of a warp are the SAME (bin, slot) of
   // adjacent columns (uid = ((c/4 * nw + l) * cap + slot) * 4 + c%4): neighbouring columns of a
   // sweep take the closed-form / sort decision together far more often than neighbouring layers
   // of one column, and they read the same k-table rows.  pad0 bit 2: slot-fastest order.
   int slot, l;
-  long long cl;
-  if (tb.pad0 & 4) {
-    slot = (int)(uid % cap);
-    l = (int)((uid / cap) % nw);
-    cl = uid / ((long long)cap * nw);
-  } else {
-    const long long q = uid >> 2;
-    slot = (int)(q % cap);
-    l = (int)((q / cap) % nw);
-    cl = (q / ((long long)cap * nw)) * 4 + (uid & 3);
+  unsigned cl;
+  {
+    const bool byslot = (tb.pad0 & 4) != 0;
+    const unsigned q = byslot ? uid : (uid >> 2);
+    const unsigned q1 = q / cap;
+    slot = (int)(q - q1 * cap);
+    const unsigned q2 = q1 / (unsigned)nw;
+    l = (int)(q1 - q2 * (unsigned)nw);
+    cl = byslot ? q2 : q2 * 4u + (uid & 3u);
   }
-  if (cl >= ch.ncol) active = false;
-  const int c = cl < ch.ncol ? (int)cl : ch.ncol - 1;
+  if (cl >= (unsigned)ch.ncol) active = false;
+  const int c = cl < (unsigned)ch.ncol ? (int)cl : ch.ncol - 1;
   const int nsl = ch.nslots[c];
   if (slot >= nsl) {
     active = false;

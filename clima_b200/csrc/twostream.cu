@@ -35,6 +35,10 @@ constexpr int TS_THREADS = 128;
 #ifndef TS_SOL_BLOCKS
 #define TS_SOL_BLOCKS 3
 #endif
+#ifndef TS_FWD_UNROLL
+#define TS_FWD_UNROLL 1
+#endif
+constexpr int TS_FWD_UNROLL_N = TS_FWD_UNROLL;  // forward-sweep unroll (register renaming instead of moves)
 constexpr int IR_ITEMS = 6;   // alpha, beta, Au, Bu, Ad, Bd
 constexpr int SOL_ITEMS = 7;  // alpha, beta, Au, Bu, Ad, Bd, K
 
@@ -131,6 +135,7 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
     int s1 = lslot(1), s2 = lslot(2);
     double t1 = tau_p[(size_t)s1 * G], w1 = w0_p[(size_t)s1 * G], g1 = gt_p[s1];
     double B1 = bp[nz >= 1 ? 1 : 0], B2 = bp[nz >= 2 ? 2 : nz];
+#pragma unroll TS_FWD_UNROLL_N
     for (int i = 0; i < nz; i++) {
       // issue the loads of layer i+2 / level i+3
       const int s3 = lslot(i + 3);
@@ -360,6 +365,7 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
     cprev = (-e2) / e1;
     double Ta = 0.0, Tb = 0.0;
 
+#pragma unroll TS_FWD_UNROLL_N
     for (int i = 0; i < nz; i++) {
       const int s3 = lslot(i + 3);
       const double t2 = tau_p[(size_t)s2 * G], w2 = w0_p[(size_t)s2 * G], g2 = gt_p[s2];
