@@ -320,10 +320,10 @@ def run_ours(args):
                                "issue roof = peak/2 because the work is not FMA-shaped",
                 "algorithmic_ops_per_column": ops,
                 # dram__bytes_read.sum + dram__bytes_write.sum of the fast RORR kernel from the
-                # ncu --set full capture at 256 columns (profiles/r1n_rorr_fast_raw.txt: 75.5 MB read,
-                # 626.1 MB written = the tau/w0 lines of every unit), scaled to this launch's columns
+                # ncu --set full capture at 256 columns (profiles/r1p_ncu_full_summary.txt: 73.9 MB read,
+                # 622.8 MB written = the tau/w0 lines of every unit), scaled to this launch's columns
                 "traffic": roofline.RORR_FAST_DRAM_BYTES_PER_COLUMN * ncol,
-                "traffic_source": "ncu r1n capture at 256 columns, scaled per column",
+                "traffic_source": "ncu r1p capture at 256 columns, scaled per column",
                 "hbm": {"bound": "hbm", "achieved": k_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak,
                         "unit": "GB/s", "frac": k_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak,
                         "peak_source": hbm_src, "algorithmic_bytes_per_column": byt},

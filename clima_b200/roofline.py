@@ -10,10 +10,10 @@ from dataclasses import dataclass
 
 
 # DRAM traffic of the dominant kernel (rorr_fast::optics_rorr_kernel<16,1,1>) per column, from
-# profiles/r1n_rorr_fast_raw.txt (ncu --set full, 256 columns of the cfg2 workload):
-# (75,458,560 + 626,117,120) bytes / 256 columns.  Almost all of it is the kernel's OUTPUT
+# profiles/r1p_ncu_full_summary.txt (ncu --set full, 256 columns of the cfg2 workload):
+# (73,949,000 + 622,805,000) bytes / 256 columns.  Almost all of it is the kernel's OUTPUT
 # (tau and w0 of every unit, 2 x 8 x G bytes x nw x unique layers = 2.59 MB per column).
-RORR_FAST_DRAM_BYTES_PER_COLUMN = (75458560 + 626117120) / 256.0
+RORR_FAST_DRAM_BYTES_PER_COLUMN = (73949000 + 622805000) / 256.0
 
 
 @dataclass
