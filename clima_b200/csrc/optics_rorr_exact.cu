@@ -1,6 +1,8 @@
 // optics_rorr_exact.cu -- instantiates the exact flavour of the optics + RORR kernel (rorr_impl.cuh).
 // keys per lane at P = 16 and a private namespace: the two flavours use different lane mappings
+#ifndef RORR_KPL16
 #define RORR_KPL16 32
+#endif
 #define RORR_NS rorr_exact
 #include "rorr_impl.cuh"
 

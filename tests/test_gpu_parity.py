@@ -420,3 +420,17 @@ def test_full_size_fast_keys_match_exact_kernel(monkeypatch):
     monkeypatch.setenv("CLIMA_RT_RORR", "exact")
     r2 = Radtran(tb, pr).radiate_batch(cols)
     compare(r1, r2, spectral=False, tol=1e-12)
+
+
+def test_absent_gases_give_exact_ties():
+    """A k-gas with zero density contributes b_j = 0 for every g-point: all sums of a row tie exactly
+    (the stable order of mrgrnk is the index order) and the merge must return the running mixture
+    unchanged; with the FIRST k-gas absent the mixture starts from zeros."""
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=3, nk=3)
+    for sp in (tb.k[1].sp_ind - 1, tb.k[0].sp_ind - 1):
+        c2 = dict(cols)
+        d = cols["densities"].copy(order="F")
+        d[:, sp, :] = 0.0
+        c2["densities"] = d
+        g, o, rg, ro = run_both(tb, pr, c2)
+        compare(rg, ro)
