@@ -655,7 +655,16 @@ void clima_rt_create(const clima_rt_tables *tables, const clima_rt_params *param
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, dev));
     h->num_sms = prop.multiProcessorCount;
-    CK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
+    {
+      // CLIMA_RT_STREAM_PRIORITY=high|low: priority of the handle's stream (experiments with
+      // concurrent handles, experiments/overlap_rorr_ts.py; default = the device default)
+      const char *sp = std::getenv("CLIMA_RT_STREAM_PRIORITY");
+      int lo = 0, hi = 0;
+      CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+      if (sp && sp[0] == 'h') CK(cudaStreamCreateWithPriority(&h->st, cudaStreamNonBlocking, hi));
+      else if (sp && sp[0] == 'l') CK(cudaStreamCreateWithPriority(&h->st, cudaStreamNonBlocking, lo));
+      else CK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
+    }
     for (auto &e : h->ev) CK(cudaEventCreate(&e));
     CK(cudaMallocHost(&h->h_wcount, sizeof(int)));
     *h->h_wcount = 0;

@@ -3,6 +3,7 @@
 #ifndef RORR_KPL16
 #define RORR_KPL16 32
 #endif
+#include <cstdlib>
 #define RORR_NS rorr_fast
 #include "rorr_impl.cuh"
 
@@ -14,7 +15,7 @@ void launch(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
   auto kern = rorr_fast::optics_rorr_kernel<P, FULL, true>;
   static bool attr_set = false;
   if (!attr_set) {
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::BLOCK_BYTES);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::BLOCK_BYTES + 65536);
     attr_set = true;
   }
   // One group of UPB units per block (NOT a persistent grid: the kernel is instruction-cache bound
@@ -22,7 +23,9 @@ void launch(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
   // a persistent grid of 592 blocks doubles the no-instruction stalls)
   const long long nb = (units + C::UPB - 1) / C::UPB;
   if (nb <= 0) return;
-  kern<<<(unsigned)nb, 128, C::BLOCK_BYTES, st>>>(tb, ch, worklist, wcount, wcap);
+  // experiment knob: extra dynamic shared memory lowers the blocks per SM (room for a concurrent kernel)
+  static const size_t pad = [] { const char *e = getenv("CLIMA_RT_RORR_SMEM_PAD"); return e ? (size_t)atoi(e) : (size_t)0; }();
+  kern<<<(unsigned)nb, 128, C::BLOCK_BYTES + pad, st>>>(tb, ch, worklist, wcount, wcap);
 }
 }  // namespace
 

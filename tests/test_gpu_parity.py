@@ -434,3 +434,4 @@ def test_absent_gases_give_exact_ties():
         c2["densities"] = d
         g, o, rg, ro = run_both(tb, pr, c2)
         compare(rg, ro)
+
