@@ -22,7 +22,7 @@ void launch(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
   // a persistent grid of 592 blocks doubles the no-instruction stalls)
   const long long nb = (units + C::UPB - 1) / C::UPB;
   if (nb <= 0) return;
-  kern<<<(unsigned)nb, 128, C::BLOCK_BYTES, st>>>(tb, ch, worklist, wcount, wcap);
+  kern<<<(unsigned)nb, 32 * RORR_WPB, C::BLOCK_BYTES, st>>>(tb, ch, worklist, wcount, wcap);
 }
 }  // namespace
 

@@ -25,7 +25,7 @@ void launch(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
   if (nb <= 0) return;
   // experiment knob: extra dynamic shared memory lowers the blocks per SM (room for a concurrent kernel)
   static const size_t pad = [] { const char *e = getenv("CLIMA_RT_RORR_SMEM_PAD"); return e ? (size_t)atoi(e) : (size_t)0; }();
-  kern<<<(unsigned)nb, 128, C::BLOCK_BYTES + pad, st>>>(tb, ch, worklist, wcount, wcap);
+  kern<<<(unsigned)nb, 32 * RORR_WPB, C::BLOCK_BYTES + pad, st>>>(tb, ch, worklist, wcount, wcap);
 }
 }  // namespace
 

@@ -39,6 +39,9 @@
 #define RORR_MIN_BLOCKS (RORR_KPL16 == 64 ? 3 : 4)
 #endif
 
+#ifndef RORR_WPB
+#define RORR_WPB 4  // warps per block; measured r1q per 1024 columns: 2 -> 39.1 ms, 4 -> 34.7 ms, 8 -> 36.1 ms
+#endif
 #ifndef RORR_NS
 #define RORR_NS rorr
 #endif
@@ -54,7 +57,7 @@ struct Cfg {
   static constexpr int LPU = N / KPL;   // lanes per unit: 2, 8, 32
   static constexpr int GPL = P / LPU;   // g-points per lane: 4, 2, 1
   static constexpr int UPW = 32 / LPU;  // units per warp: 16, 4, 1
-  static constexpr int UPB = 4 * UPW;   // units per 128-thread block
+  static constexpr int UPB = RORR_WPB * UPW;  // units per block
   static constexpr int NC = (LPU == 32 ? 16 : LPU);  // table columns of one unit
   static constexpr int CW = (LPU == 32 ? 16 : 32);   // table columns per warp
   static constexpr int TBL = P * CW;                 // doubles per table per warp
@@ -72,7 +75,7 @@ struct Cfg {
   static constexpr size_t SI_BYTES = (size_t)UPW * 2 * SPU * sizeof(double);  // per unit: I(E_g), then its copy of the edges
   static constexpr size_t IP_BYTES = (size_t)KPL * 32 * IDXB;
   static constexpr size_t BLOCK_BYTES =
-      (size_t)TBLB * 9 + (size_t)N * WXC * sizeof(double) + 4 * (SI_BYTES + IP_BYTES);
+      (size_t)TBLB * (2 * RORR_WPB + 1) + (size_t)N * WXC * sizeof(double) + RORR_WPB * (SI_BYTES + IP_BYTES);
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) {
@@ -506,7 +509,7 @@ __device__ __forceinline__ bool rt_rebin1(const unsigned aIP, double *tA, double
 // permutation as the reference's stable merge sort or hands the unit over.
 // ---------------------------------------------------------------------------------------------
 template <int P, bool FULL, bool FAST>
-__global__ void __launch_bounds__(128, RORR_MIN_BLOCKS)
+__global__ void __launch_bounds__(32 * RORR_WPB, RORR_MIN_BLOCKS * 4 / RORR_WPB)
 optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevChunk ch,
                    int *__restrict__ worklist, int *__restrict__ wcount, const int wcap) {
   using C = Cfg<P>;
@@ -530,9 +533,9 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
   char *dbase = (char *)s_dyn + (tb0 - dyn_u);
   double *tA = (double *)(dbase + (size_t)warp * 2 * C::TBLB);  // running mixture a(i), [row][column]
   double *tB = tA + C::TBL;                                      // new gas b(j)
-  double *s_wxy = (double *)(dbase + 8 * (size_t)C::TBLB);  // [idx][copy]: wxy(j + i*P), types_create.f90:216-222
+  double *s_wxy = (double *)(dbase + 2 * RORR_WPB * (size_t)C::TBLB);  // [idx][copy]: wxy(j + i*P), types_create.f90:216-222
   double *sI = s_wxy + C::N * C::WXC + ((size_t)warp * C::UPW + (ub % C::UPW)) * (2 * C::SPU);  // I(E_g), then edges
-  idx_t *ip = (idx_t *)(s_wxy + C::N * C::WXC + 4 * (C::UPW * 2 * C::SPU)) + (size_t)warp * (C::KPL * 32) + lane;
+  idx_t *ip = (idx_t *)(s_wxy + C::N * C::WXC + RORR_WPB * (C::UPW * 2 * C::SPU)) + (size_t)warp * (C::KPL * 32) + lane;
   const double *wx = s_wxy + (lane & (C::WXC - 1));
   const unsigned aA = smem_u32(tA + mycol), aB = smem_u32(tB + mycol), aW = smem_u32(wx), aIP = smem_u32(ip);
 
