@@ -42,6 +42,16 @@ constexpr int TS_FWD_UNROLL_N = TS_FWD_UNROLL;  // forward-sweep unroll (registe
 constexpr int IR_ITEMS = 6;   // alpha, beta, Au, Bu, Ad, Bd
 constexpr int SOL_ITEMS = 7;  // alpha, beta, Au, Bu, Ad, Bd, K
 
+#ifndef TS_L2_PREFETCH
+#define TS_L2_PREFETCH 8  // layers ahead of the back substitution (0 = off)
+#endif
+// The scratch of a persistent two-stream grid (~0.9 GB) is far larger than L2: by the time the back
+// substitution reads a layer it has left the cache.  The register prefetch reaches two layers
+// (~100 cycles of arithmetic); an L2 prefetch a few layers further ahead costs no registers.
+__device__ __forceinline__ void l2_prefetch(const double *p) {
+  asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+}
+
 template <int P>
 __device__ __forceinline__ double group_sum(double v) {
 #pragma unroll
@@ -237,6 +247,11 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
       const double *s = scr + (size_t)(i > 0 ? i : 0) * IR_ITEMS * nres;
 #pragma unroll
       for (int t = 0; t < IR_ITEMS; t++) b[t] = s[(size_t)t * nres];
+      if (TS_L2_PREFETCH > 0 && i >= TS_L2_PREFETCH) {
+        const double *pf = scr + (size_t)(i - TS_L2_PREFETCH) * IR_ITEMS * nres;
+#pragma unroll
+        for (int t = 0; t < IR_ITEMS; t++) l2_prefetch(pf + (size_t)t * nres);
+      }
     };
     auto bk = [&](const double (&b)[IR_ITEMS], int i) {
       const double fup = b[2] + b[3] * xnext;
@@ -470,6 +485,11 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       const double *s = scr + (size_t)(i > 0 ? i : 0) * SOL_ITEMS * nres;
 #pragma unroll
       for (int t = 0; t < SOL_ITEMS; t++) b[t] = s[(size_t)t * nres];
+      if (TS_L2_PREFETCH > 0 && i >= TS_L2_PREFETCH) {
+        const double *pf = scr + (size_t)(i - TS_L2_PREFETCH) * SOL_ITEMS * nres;
+#pragma unroll
+        for (int t = 0; t < SOL_ITEMS; t++) l2_prefetch(pf + (size_t)t * nres);
+      }
     };
     auto bk = [&](const double (&b)[SOL_ITEMS], int i) {
       const double fup = b[2] + b[3] * xnext;  // :146
