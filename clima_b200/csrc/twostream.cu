@@ -42,6 +42,14 @@ constexpr int TS_FWD_UNROLL_N = TS_FWD_UNROLL;  // forward-sweep unroll (registe
 constexpr int IR_ITEMS = 6;   // alpha, beta, Au, Bu, Ad, Bd
 constexpr int SOL_ITEMS = 7;  // alpha, beta, Au, Bu, Ad, Bd, K
 
+// forward sweep: tau/w0 lines this many layers ahead into L2 (0 = off).  Measured r1q per 1024 columns:
+// IR 5.16 (0) / 5.21 (6) ms; solar 6.94 (0) / 6.75 (6) / 6.93 (12) ms
+#ifndef TS_FWD_L2_PREFETCH_IR
+#define TS_FWD_L2_PREFETCH_IR 0
+#endif
+#ifndef TS_FWD_L2_PREFETCH_SOL
+#define TS_FWD_L2_PREFETCH_SOL 6
+#endif
 #ifndef TS_L2_PREFETCH
 #define TS_L2_PREFETCH 8  // layers ahead of the back substitution (0 = off)
 #endif
@@ -149,6 +157,13 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
     for (int i = 0; i < nz; i++) {
       // issue the loads of layer i+2 / level i+3
       const int s3 = lslot(i + 3);
+#if TS_FWD_L2_PREFETCH_IR > 0
+      {  // tau / w0 lines of a layer further down, into L2
+        const int sp = lslot(i + 3 + TS_FWD_L2_PREFETCH_IR);
+        l2_prefetch(tau_p + (size_t)sp * G);
+        l2_prefetch(w0_p + (size_t)sp * G);
+      }
+#endif
       const double t2 = tau_p[(size_t)s2 * G], w2 = w0_p[(size_t)s2 * G], g2 = gt_p[s2];
       const double B3 = bp[i + 3 <= nz ? i + 3 : nz];
       double c1, d1;              // row 2i+1 (0-based)
@@ -383,6 +398,13 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
 #pragma unroll TS_FWD_UNROLL_N
     for (int i = 0; i < nz; i++) {
       const int s3 = lslot(i + 3);
+#if TS_FWD_L2_PREFETCH_SOL > 0
+      {  // tau / w0 lines of a layer further down, into L2
+        const int sp = lslot(i + 3 + TS_FWD_L2_PREFETCH_SOL);
+        l2_prefetch(tau_p + (size_t)sp * G);
+        l2_prefetch(w0_p + (size_t)sp * G);
+      }
+#endif
       const double t2 = tau_p[(size_t)s2 * G], w2 = w0_p[(size_t)s2 * G], g2 = gt_p[s2];
       // layer i ("o"ld) values; layer_coeffs() overwrites e1..e4/cgam/wrk/fp/fm/ex with layer i+1
       const double e1o = e1, e2o = e2, e3o = e3, e4o = e4;
