@@ -198,8 +198,9 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
           const double D = e1n * e4n - e2n * e3n;
           const double E = e2n * (cp0n - cpb) - e4n * (cm0n - cmb);
           const double den = B - A * cprev;
-          c1 = D / den;
-          d1 = (E - A * dprev) / den;
+          const double rden = 1.0 / den;  // one reciprocal per row (the solar kernel does the same)
+          c1 = D * rden;
+          d1 = (E - A * dprev) * rden;
         }
         // odd Fortran row l=2i+1 (:257-262) -> 0-based row 2i+2
         {
@@ -208,8 +209,9 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
           const double D = e3 * e4n - e1 * e2n;
           const double E = e3 * (cp0n - cpb) + e1 * (cmb - cm0n);
           const double den = B - A * c1;
-          cn = D / den;
-          dn = (E - A * d1) / den;
+          const double rden = 1.0 / den;
+          cn = D * rden;
+          dn = (E - A * d1) * rden;
         }
       } else {
         // last row (:272-275); surface terms (:236-247)
