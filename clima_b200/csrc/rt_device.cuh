@@ -138,6 +138,20 @@ __device__ __forceinline__ double rt_exp_lean(const double x) {
   p = __fma_rn(p, r, 1.0);
   return __hiloint2double(__double2hiint(p) + (k << 20), __double2loint(p));
 }
+// 1/d for d well inside the normal range (Thomas pivots, e1 in [1,2], gamma sums): the hardware
+// seed (2^-23) and two Newton steps, ~1 ulp, no denormal/overflow slow path.  The two-stream kernels
+// are FP64-pipe / issue limited: the IEEE division costs ~20 instructions, this 5.
+__device__ __forceinline__ double rt_rcp_fast(const double d) {
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+  double e = __fma_rn(-d, r, 1.0);
+  r = __fma_rn(r, e, r);
+  e = __fma_rn(-d, r, 1.0);
+  return __fma_rn(r, e, r);
+}
+// exp(x) for x <= 0 (attenuation factors); below -700 the result is held at exp(-700) ~ 1e-304,
+// which no sum of the solver can tell from 0
+__device__ __forceinline__ double rt_exp_neg(const double x) { return rt_exp_lean(x < -700.0 ? -700.0 : x); }
 // ten2power for arguments known to be far from the overflow/underflow limits (k-table values:
 // log10 k in [-60, 10])
 __device__ __forceinline__ double rt_ten2power_lean(double y) { return rt_exp_lean(y * RT_LN10); }

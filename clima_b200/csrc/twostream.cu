@@ -128,22 +128,23 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
       const double tau = tau_p[(size_t)slot * G], w0 = w0_p[(size_t)slot * G], gt = gt_p[slot];
       const double gam1 = 2.0 - w0 * (1.0 + gt), gam2 = w0 * (1.0 - gt);  // :195-196
       const double lam = sqrt(gam1 * gam1 - gam2 * gam2);                 // :199
-      cgam = gam2 / (gam1 + lam);                                         // :200
-      wrk = exp(-lam * tau);                                              // :206
+      cgam = gam2 * rt_rcp_fast(gam1 + lam);                              // :200
+      wrk = rt_exp_neg(-lam * tau);                                       // :206
       e1 = 1.0 + cgam * wrk; e2 = 1.0 - cgam * wrk; e3 = cgam + wrk; e4 = cgam - wrk;
-      g12 = 1.0 / (gam1 + gam2);
+      g12 = rt_rcp_fast(gam1 + gam2);
       tau_i = tau;
       double b0, b1;  // :216-227
       const double Bt = bp[0], Bb = bp[1];
-      if (tau <= tmin) { b0 = 0.5 * (Bt + Bb); b1 = 0.0; } else { b0 = Bt; b1 = (Bb - b0) / tau; }
+      if (tau <= tmin) { b0 = 0.5 * (Bt + Bb); b1 = 0.0; } else { b0 = Bt; b1 = (Bb - b0) * rt_rcp_fast(tau); }
       const double cp0 = norm * (b0 + b1 * g12);
       cpb = norm * (b0 + b1 * (tau + g12));
       const double cm0 = norm * (b0 + b1 * (-g12));
       cmb = norm * (b0 + b1 * (tau - g12));
       cp0_top = cp0;
       // row 1 (:251-254) and its Thomas step (:302-303)
-      cprev = (-e2) / e1;
-      dprev = (0.0 - cm0) / e1;
+      const double re1 = rt_rcp_fast(e1);
+      cprev = (-e2) * re1;
+      dprev = (0.0 - cm0) * re1;
     }
     // Raw inputs are prefetched one layer ahead (slot index two layers ahead, so that the dependent
     // tau/w0/g loads can be issued a full iteration before they are needed): the sweep was
@@ -177,16 +178,16 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
           const double tau = t1, w0 = w1, gt = g1;
           const double gam1 = 2.0 - w0 * (1.0 + gt), gam2 = w0 * (1.0 - gt);
           const double lam = sqrt(gam1 * gam1 - gam2 * gam2);
-          cgamn = gam2 / (gam1 + lam);
-          wrkn = exp(-lam * tau);
+          cgamn = gam2 * rt_rcp_fast(gam1 + lam);
+          wrkn = rt_exp_neg(-lam * tau);
           e1n = 1.0 + cgamn * wrkn; e2n = 1.0 - cgamn * wrkn; e3n = cgamn + wrkn; e4n = cgamn - wrkn;
-          g12n = 1.0 / (gam1 + gam2);
+          g12n = rt_rcp_fast(gam1 + gam2);
           taun = tau;
           slot = slotn;
         }
         double b0, b1;
         const double Bt = B1, Bb = B2;
-        if (taun <= tmin) { b0 = 0.5 * (Bt + Bb); b1 = 0.0; } else { b0 = Bt; b1 = (Bb - b0) / taun; }
+        if (taun <= tmin) { b0 = 0.5 * (Bt + Bb); b1 = 0.0; } else { b0 = Bt; b1 = (Bb - b0) * rt_rcp_fast(taun); }
         const double cp0n = norm * (b0 + b1 * g12n);
         cpbn = norm * (b0 + b1 * (taun + g12n));
         const double cm0n = norm * (b0 + b1 * (-g12n));
@@ -198,7 +199,7 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
           const double D = e1n * e4n - e2n * e3n;
           const double E = e2n * (cp0n - cpb) - e4n * (cm0n - cmb);
           const double den = B - A * cprev;
-          const double rden = 1.0 / den;  // one reciprocal per row (the solar kernel does the same)
+          const double rden = rt_rcp_fast(den);  // one reciprocal per row
           c1 = D * rden;
           d1 = (E - A * dprev) * rden;
         }
@@ -209,7 +210,7 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
           const double D = e3 * e4n - e1 * e2n;
           const double E = e3 * (cp0n - cpb) + e1 * (cmb - cm0n);
           const double den = B - A * c1;
-          const double rden = 1.0 / den;
+          const double rden = rt_rcp_fast(den);
           cn = D * rden;
           dn = (E - A * d1) * rden;
         }
@@ -220,14 +221,14 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
           Ssfc = emis * RT_PI * bp[nz];
         } else {
           double b1_bot = 0.0;
-          if (!(tau_i <= tmin)) b1_bot = (bp[nz] - bp[nz - 1]) / tau_i;
+          if (!(tau_i <= tmin)) b1_bot = (bp[nz] - bp[nz - 1]) * rt_rcp_fast(tau_i);
           Ssfc = RT_PI * (bp[nz] + 0.5 * b1_bot);
         }
         const double A = e1 - Rsfc * e3;
         const double B = e2 - Rsfc * e4;
         const double E = Ssfc - cpb + Rsfc * cmb;
         c1 = 0.0;
-        d1 = (E - A * dprev) / (B - A * cprev);
+        d1 = (E - A * dprev) * rt_rcp_fast(B - A * cprev);
       }
       // What the back substitution needs from layer i, folded into 6 numbers.  With xn = x of row
       // 2i+2 (the solution entering the layer from below), Thomas (:311-313) gives
@@ -351,14 +352,14 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       // delta-Eddington scaling (:38-40)
       const double f = 1.0 - w0_in * gt_in * gt_in;
       const double tau = tau_in * f;
-      const double w0 = w0_in * (1.0 - gt_in * gt_in) / f;
-      const double gt = gt_in / (1.0 + gt_in);
+      const double w0 = w0_in * (1.0 - gt_in * gt_in) * rt_rcp_fast(f);
+      const double gt = gt_in * rt_rcp_fast(1.0 + gt_in);
       // quadrature coefficients (:43-46)
       const double gam1 = sq3 * (2.0 - w0 * (1.0 + gt)) / 2.0;
       const double gam2 = sq3 * w0 * (1.0 - gt) / 2.0;
       const double lam = sqrt(gam1 * gam1 - gam2 * gam2);  // :50
-      cgam = gam2 / (gam1 + lam);                          // :51
-      wrk = exp(-lam * tau);                               // :56
+      cgam = gam2 * rt_rcp_fast(gam1 + lam);               // :51
+      wrk = rt_exp_neg(-lam * tau);                        // :56
       e1 = 1.0 + cgam * wrk; e2 = 1.0 - cgam * wrk; e3 = cgam + wrk; e4 = cgam - wrk;
 #pragma unroll
       for (int z = 0; z < ZC; z++) {
@@ -366,10 +367,10 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
         const double gam4 = 1.0 - gam3;
         const double facp = w0 * ((gam1 - iu0[z]) * gam3 + gam4 * gam2);  // :76
         const double facm = w0 * ((gam1 + iu0[z]) * gam4 + gam2 * gam3);  // :77
-        const double rden = 1.0 / (lam * lam - iu02[z]);                  // :80
+        const double rden = rt_rcp_fast(lam * lam - iu02[z]);             // :80
         fp[z] = facp * rden;
         fm[z] = facm * rden;
-        ex[z] = exp(-tau * iu0[z]);
+        ex[z] = rt_exp_neg(-tau * iu0[z]);
       }
     };
 
@@ -381,6 +382,7 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
     int s1 = lslot(1), s2 = lslot(2);
     double t1 = tau_p[(size_t)s1 * G], w1 = w0_p[(size_t)s1 * G], g1 = gt_p[s1];
     double Dprev = 0.0;  // sum_z w_z d'_z of row 2i
+    const double re1_top = rt_rcp_fast(e1);
 #pragma unroll
     for (int z = 0; z < ZC; z++) {
       const double etb = ex[z];  // et0 = exp(-tauc(1)/u0) = 1
@@ -388,13 +390,13 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       cpb[z] = etb * fp[z];
       cmb[z] = etb * fm[z];
       et[z] = etb;
-      dprev[z] = (0.0 - cm0) / e1;  // rows :93-96, Thomas :302-303
+      dprev[z] = (0.0 - cm0) * re1_top;  // rows :93-96, Thomas :302-303
       Dprev += wz[z] * dprev[z];
       CP0_top += wz[z] * cp0;
       FDN_top += wz[z] * u0[z];  // direct(1) = u0*Fs_pi (:73)
       AM_top += wz[z];           // direct(1)/u0
     }
-    cprev = (-e2) / e1;
+    cprev = (-e2) * re1_top;
     double Ta = 0.0, Tb = 0.0;
 
 #pragma unroll TS_FWD_UNROLL_N
@@ -427,11 +429,11 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
         }
         // even Fortran row l=2i (:107-112) -> 0-based row 2i+1 ; (e1..e4 = layer i+1)
         const double A1 = e2 * e1o - e3o * e4, B1 = e2o * e2 - e4o * e4, Dd1 = e1 * e4 - e2 * e3;
-        const double r1 = 1.0 / (B1 - A1 * cprev);
+        const double r1 = rt_rcp_fast(B1 - A1 * cprev);
         c1 = Dd1 * r1;
         // odd Fortran row l=2i+1 (:99-104) -> 0-based row 2i+2
         const double A2 = e2o * e3o - e4o * e1o, B2 = e1o * e1 - e3o * e3, Dd2 = e3o * e4 - e1o * e2;
-        const double r2 = 1.0 / (B2 - A2 * c1);
+        const double r2 = rt_rcp_fast(B2 - A2 * c1);
         cn = Dd2 * r2;
 #pragma unroll
         for (int z = 0; z < ZC; z++) {
@@ -450,7 +452,7 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
         }
       } else {
         const double A = e1o - Rsfc * e3o, B = e2o - Rsfc * e4o;  // :114-117
-        const double r1 = 1.0 / (B - A * cprev);
+        const double r1 = rt_rcp_fast(B - A * cprev);
         c1 = 0.0;
 #pragma unroll
         for (int z = 0; z < ZC; z++) {
