@@ -435,3 +435,30 @@ def test_absent_gases_give_exact_ties():
         g, o, rg, ro = run_both(tb, pr, c2)
         compare(rg, ro)
 
+
+
+@pytest.mark.parametrize("scale", [1.0e6, 1.0e-10])
+def test_extreme_optical_depths(scale):
+    """Columns a million times denser (layer optical depths far beyond the point where exp(-lambda*tau)
+    underflows: the solver's lean exp holds its argument at -700) and ten orders thinner (every layer
+    under the thin-layer guard of two_stream_ir :216-227 and the tau clamps of radiate.f90).
+
+    In the thin limit the Toon matrix entries cancel (B = e2*e2n - e4*e4n ~ 2*lambda*tau), so ANY two
+    evaluation orders of the same recurrence differ by ~1e-16/(lambda*tau) of the flux scale; the
+    downward IR flux itself is ~1e-5 of the upward one there.  The contract is therefore checked
+    against the common flux scale of the channel (what f_total sees), not per array."""
+    tb, pr, cols = small_case(G=16, nw=12, nz=12, ncol=3, nk=3)
+    c2 = dict(cols)
+    c2["densities"] = (cols["densities"] * scale).copy(order="F")
+    g, o, rg, ro = run_both(tb, pr, c2)
+    for k in ("fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol"):
+        assert np.all(np.isfinite(rg[k])), k
+    if scale > 1.0:
+        compare(rg, ro)
+        return
+    for ch in ("ir", "sol"):
+        s_ch = max(np.max(np.abs(ro[f"fup_n_{ch}"])), np.max(np.abs(ro[f"fdn_n_{ch}"])))
+        for k in (f"fup_n_{ch}", f"fdn_n_{ch}"):
+            assert np.max(np.abs(rg[k] - ro[k])) <= TOL * s_ch, k
+    for k in ("OLR", "ISR"):
+        assert np.max(np.abs(rg[k] - ro[k]) / np.abs(ro[k])) <= TOL, k
