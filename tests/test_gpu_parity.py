@@ -462,3 +462,22 @@ def test_extreme_optical_depths(scale):
             assert np.max(np.abs(rg[k] - ro[k])) <= TOL * s_ch, k
     for k in ("OLR", "ISR"):
         assert np.max(np.abs(rg[k] - ro[k]) / np.abs(ro[k])) <= TOL, k
+
+
+def test_tables_from_the_load_time_packer(tmp_path):
+    """N2: Rayleigh cross sections and the solar photon flux produced by clima_b200.loader (the
+    restatement of create_RayleighXsection / read_stellar_flux) drive the device path."""
+    from clima_b200 import loader
+    tb, pr, cols = small_case(G=16, nw=12, nz=10, ncol=3, nk=3)
+    ray = {"N2": {"data": {"Delta": 0.0305, "A": 29.06e-5, "B": 7.70e-3}},
+           "CO2": {"data": {"Delta": 0.0805, "A": 43.9e-5, "B": 6.4e-3}}}
+    tb.ray_sp_ind, tb.ray_xs = loader.rayleigh_table(ray, tb.species_names, tb.wavl)
+    assert len(tb.ray_sp_ind) == 2
+    lam = np.geomspace(0.5 * tb.wavl[0], 2.0 * tb.wavl[-1], 300)
+    star = tmp_path / "star.txt"
+    star.write_text("nm mW/m2/nm\n" + "\n".join(f"{a:.8e} {1.0e3 * np.exp(-((np.log(a / 550.0)) ** 2)):.8e}" for a in lam))
+    i0, i1 = tb.sol_ind
+    tb.photons_sol = loader.read_stellar_flux(str(star), tb.wavl[i0 - 1:i1 + 1])
+    assert tb.photons_sol.shape == (i1 - i0 + 1,) and np.all(tb.photons_sol > 0.0)
+    g, o, rg, ro = run_both(tb, pr, cols)
+    compare(rg, ro)
