@@ -40,11 +40,12 @@ def load_library() -> C.CDLL:
     """Loads the CUDA C-ABI library.  Fails loudly when it has not been built."""
     global _lib
     if _lib is None:
-        if not os.path.exists(_LIB_PATH):
+        path = os.environ.get("CLIMA_RT_LIBRARY", _LIB_PATH)  # developer knob: A/B builds of the same ABI
+        if not os.path.exists(path):
             raise ClimaException(
-                f"{_LIB_PATH} is missing: build it with `python -m clima_b200.build` "
+                f"{path} is missing: build it with `python -m clima_b200.build` "
                 "(there is no CPU fallback)")
-        _lib = C.CDLL(_LIB_PATH)
+        _lib = C.CDLL(path)
         for name in EXPORTS:
             getattr(_lib, name).restype = None
     return _lib

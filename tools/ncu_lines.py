@@ -12,13 +12,15 @@ fi = next(i for i, r in enumerate(rows) if r and r[0] in ("Function Name", "Kern
 hi = next(i for i, r in enumerate(rows) if i > fi and r and r[0] == "Line No")
 hdr = rows[hi]
 ie, ismp = hdr.index("Instructions Executed"), hdr.index("# Samples")
-iw, iwi = hdr.index("L1 Wavefronts Shared"), hdr.index("L1 Wavefronts Shared Ideal")
+iw = hdr.index("L1 Wavefronts Shared") if "L1 Wavefronts Shared" in hdr else None  # absent when the kernel uses no shared memory
+iwi = hdr.index("L1 Wavefronts Shared Ideal") if iw is not None else None
 lines = []
 for r in rows[hi + 1:]:
     if len(r) <= ie: continue
-    if r[0] == "Line No": break
+    if r[0] in ("Function Name", "Kernel Name"): break  # next kernel
+    if r[0] == "Line No": continue  # next source file of the same kernel
     if r[0].isdigit():
-        lines.append((int(r[0]), r[1].strip(), int(r[ie]), int(r[ismp]), int(r[iw]), int(r[iwi])))
+        lines.append((int(r[0]), r[1].strip(), int(r[ie]), int(r[ismp]), int(r[iw]) if iw is not None else 0, int(r[iwi]) if iw is not None else 0))
 ti = sum(l[2] for l in lines); ts = sum(l[3] for l in lines); tw = sum(l[4] for l in lines)
 print(f"total inst {ti} samples {ts} shared wavefronts {tw} (ideal {sum(l[5] for l in lines)})")
 key = (lambda l: -l[2]) if (len(sys.argv) > 4 and sys.argv[4] == "inst") else (lambda l: -l[3])
