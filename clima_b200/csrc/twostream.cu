@@ -17,10 +17,11 @@
 //
 // Work skipped because it is provably invariant:
 //   * duplicated layers (same slot as the previous layer) reuse gamma/lambda/Gamma/exp;
-//   * solar: the matrix (A,B,D) does not depend on the zenith angle (A.5), so it is factored once
-//     and the zenith quadrature is folded into the right-hand side: back substitution and flux
-//     reconstruction are linear in the RHS, hence sum_z w_z flux_z is obtained from ONE back
-//     substitution of D' = sum_z w_z d'_z (and sum_z w_z C+-_z, sum_z w_z direct_z);
+//   * solar: the matrix (A,B,D) does not depend on the zenith angle (A.5) and elimination, back
+//     substitution and flux reconstruction are all linear in the right-hand side, so the zenith
+//     quadrature is taken on the RHS terms themselves (sum_z w_z C+-_z, sum_z w_z direct_z) and ONE
+//     Thomas solve runs on the summed system; per zenith angle only exp(-tau/u0), C+- and four
+//     multiply-adds per layer remain;
 //   * the direct beam exp(-tauc/u0) is carried as a running product (one exp per layer and zenith
 //     instead of two, :75-76).
 #include "rt_device.cuh"
@@ -44,8 +45,20 @@ constexpr int TS_THREADS = 128;
 #define TS_FWD_UNROLL_SOL 2
 #endif
 constexpr int TS_FWD_UNROLL_IR_N = TS_FWD_UNROLL_IR, TS_FWD_UNROLL_SOL_N = TS_FWD_UNROLL_SOL;
-constexpr int IR_ITEMS = 6;   // alpha, beta, Au, Bu, Ad, Bd
-constexpr int SOL_ITEMS = 7;  // alpha, beta, Au, Bu, Ad, Bd, K
+// Scratch per layer, [layer][item][resident thread] followed by [layer][resident group][slot]:
+//   IR    4 numbers per thread (alpha, beta, Bu, Bd) + per (column, bin) group the g-weighted sums of
+//         the terms that do not multiply the solution (sum w Au, sum w Ad): the kernel is HBM-bound,
+//         the two extra shuffle reductions of the forward sweep buy 31 % less traffic
+//         (r1r per 1024 columns: 4.01 -> 3.64 ms);
+//   solar 7 numbers per thread (alpha, beta, Au, Bu, Ad, Bd, K).  Group sums in this kernel's forward
+//         sweep cost more than the traffic they save (r1r per 1024 columns, zenith-folded sweep:
+//         4.88 ms as is, 5.30 with sum w K per group, 5.26 with Au/Ad/K per group, 5.15 at 4 blocks/SM).
+constexpr int IR_TITEMS = 4, IR_GITEMS = 2;
+#ifndef TS_SOL_PRESUM
+#define TS_SOL_PRESUM 0  // 0: all 7 per thread; 1: sum w K per group; 2: sum w Au, sum w Ad, sum w K per group
+#endif
+constexpr int SOL_TITEMS = TS_SOL_PRESUM == 2 ? 4 : (TS_SOL_PRESUM == 1 ? 6 : 7);
+constexpr int SOL_GITEMS = TS_SOL_PRESUM == 2 ? 4 : 1;  // group slots: (Au, Ad, K, -) or (K)
 
 // forward sweep: tau/w0 lines this many layers ahead into L2 (0 = off).  Measured r1q per 1024 columns:
 // IR 5.16 (0) / 5.21 (6) ms; solar 6.94 (0) / 6.75 (6) / 6.93 (12) ms
@@ -74,6 +87,18 @@ template <int P>
 __device__ __forceinline__ double group_sum(double v) {
 #pragma unroll
   for (int m = P / 2; m >= 1; m >>= 1) v += __shfl_xor_sync(0xffffffffu, v, m);
+  return v;
+}
+
+// Two sums over the P lanes of a group for the price of one and a third: the first exchange halves
+// the data (even lanes keep a and receive the partner's a, odd lanes keep b), the remaining steps
+// reduce one value.  Returns sum(a) in the even lanes of the group and sum(b) in the odd lanes.
+template <int P>
+__device__ __forceinline__ double group_sum2(const double a, const double b, const int gl) {
+  const bool odd = (gl & 1) != 0;
+  double v = (odd ? b : a) + __shfl_xor_sync(0xffffffffu, odd ? a : b, 1);
+#pragma unroll
+  for (int m = P / 2; m >= 2; m >>= 1) v += __shfl_xor_sync(0xffffffffu, v, m);
   return v;
 }
 
@@ -106,6 +131,9 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
   const size_t rtid = (size_t)blockIdx.x * TS_THREADS + threadIdx.x;
   double *scr = fx.scratch + rtid;
   const int gl = threadIdx.x % P;
+  const size_t ngres = nres / P;
+  // this lane's slot of its group's sums (even lanes: the upward term, odd lanes: the downward one)
+  double *gscr = fx.scratch + (size_t)IR_TITEMS * nz * nres + (rtid / P) * IR_GITEMS + (gl & 1);
   const int gq = gl < G ? gl : G - 1;
   const double wg = gl < G ? tb.wbin[gq] : 0.0;
   const double norm = 2.0 * RT_PI * 0.5;  // twostream.f90:185-186 (u1 = 0.5)
@@ -249,10 +277,12 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
         const double c0 = cprev, d0 = dprev;
         const double Qu = e2 - c0 * e1, Qd = e4 - c0 * e3;
         const double al = d0 - c0 * d1, be = c0 * c1;
-        double *s = scr + (size_t)i * IR_ITEMS * nres;
+        double *s = scr + (size_t)i * IR_TITEMS * nres;
         s[0] = al; s[nres] = be;
-        s[2 * nres] = (d0 * e1 + cpb) + Qu * d1; s[3 * nres] = -(Qu * c1);
-        s[4 * nres] = (d0 * e3 + cmb) + Qd * d1; s[5 * nres] = -(Qd * c1);
+        s[2 * nres] = -(Qu * c1); s[3 * nres] = -(Qd * c1);
+        // Au, Ad enter the fluxes only through their g-weighted sums (radiate.f90:122-126)
+        const double SA = group_sum2<P>(((d0 * e1 + cpb) + Qu * d1) * wg, ((d0 * e3 + cmb) + Qd * d1) * wg, gl);
+        if (gl < 2) gscr[(size_t)i * IR_GITEMS * ngres] = SA;
         if (i == 0) {  // top-of-atmosphere upward flux (:288): y1*e3 - y2*e4 + cp0 = Ta + Tb*xn
           Ta = (al * e3 - d1 * e4) + cp0_top;
           Tb = be * e3 + c1 * e4;
@@ -267,25 +297,30 @@ twostream_ir_kernel(const __grid_constant__ DevTables tb, const __grid_constant_
     double *fup_o = fx.fup_a_ir + ((size_t)c * nw_ir + ll) * (nz + 1);
     double *fdn_o = fx.fdn_a_ir + ((size_t)c * nw_ir + ll) * (nz + 1);
     const bool writer = gactive && gl == 0;
+    double *const out_o = (gl & 1) ? fdn_o : fup_o;  // lane 0 writes fup, lane 1 fdn
+    const bool writer2 = gactive && gl < 2;
     double xnext = 0.0, xtop = 0.0;
     // the scratch values of a layer do not depend on the recurrence: keep the loads two layers
     // ahead of the arithmetic (rotating register buffers, loop unrolled by 3)
-    double q[3][IR_ITEMS];
-    auto ld = [&](double (&b)[IR_ITEMS], int i) {
-      const double *s = scr + (size_t)(i > 0 ? i : 0) * IR_ITEMS * nres;
+    double q[3][IR_TITEMS + 1];
+    auto ld = [&](double (&b)[IR_TITEMS + 1], int i) {
+      const int ic = i > 0 ? i : 0;
+      const double *s = scr + (size_t)ic * IR_TITEMS * nres;
 #pragma unroll
-      for (int t = 0; t < IR_ITEMS; t++) b[t] = s[(size_t)t * nres];
+      for (int t = 0; t < IR_TITEMS; t++) b[t] = s[(size_t)t * nres];
+      b[IR_TITEMS] = gscr[(size_t)ic * IR_GITEMS * ngres];
       if (TS_L2_PREFETCH_IR > 0 && i >= TS_L2_PREFETCH_IR) {
-        const double *pf = scr + (size_t)(i - TS_L2_PREFETCH_IR) * IR_ITEMS * nres;
+        const double *pf = scr + (size_t)(i - TS_L2_PREFETCH_IR) * IR_TITEMS * nres;
 #pragma unroll
-        for (int t = 0; t < IR_ITEMS; t++) l2_prefetch(pf + (size_t)t * nres);
+        for (int t = 0; t < IR_TITEMS; t++) l2_prefetch(pf + (size_t)t * nres);
+        l2_prefetch(gscr + (size_t)(i - TS_L2_PREFETCH_IR) * IR_GITEMS * ngres);
       }
     };
-    auto bk = [&](const double (&b)[IR_ITEMS], int i) {
-      const double fup = b[2] + b[3] * xnext;
-      const double fdn = b[4] + b[5] * xnext;
-      const double su = group_sum<P>(fup * wg), sd = group_sum<P>(fdn * wg);
-      if (writer) { fup_o[nz - 1 - i] = su; fdn_o[nz - 1 - i] = sd; }
+    auto bk = [&](const double (&b)[IR_TITEMS + 1], int i) {
+      // fup = Au + Bu*xn, fdn = Ad + Bd*xn summed over g: even lanes get fup, odd lanes fdn
+      const double wx = wg * xnext;
+      const double R = group_sum2<P>(b[2] * wx, b[3] * wx, gl) + b[IR_TITEMS];
+      if (writer2) out_o[nz - 1 - i] = R;
       xtop = xnext;
       xnext = b[0] + b[1] * xnext;
     };
@@ -319,6 +354,8 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
   const size_t rtid = (size_t)blockIdx.x * TS_THREADS + threadIdx.x;
   double *scr = fx.scratch + rtid;
   const int gl = threadIdx.x % P;
+  const size_t ngres = nres / P;
+  double *gscr = fx.scratch + (size_t)SOL_TITEMS * nz * nres + (rtid / P) * SOL_GITEMS;  // the group's sum w K
   const int gq = gl < G ? gl : G - 1;
   const double wg = gl < G ? tb.wbin[gq] : 0.0;
   const double sq3 = sqrt(3.0);
@@ -352,8 +389,8 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
     double e1, e2, e3, e4, cgam, wrk;
     // per-zenith layer coefficients (reused by duplicated layers) and running state
     double fp[ZC], fm[ZC], ex[ZC];  // facp/denom, facm/denom, exp(-tau'/u0)
-    double et[ZC];                  // exp(-tauc/u0) at the top of layer i
-    double cpb[ZC], cmb[ZC], dprev[ZC];
+    double aw[ZC];                  // w_z * exp(-tauc/u0) at the bottom of layer i (= top of layer i+1)
+    double CPB, CMB;                // sum_z w_z C+-(bottom of layer i)
     double cprev;
     double CP0_top = 0.0, FDN_top = 0.0, AM_top = 0.0;
     int slot = -1;
@@ -391,20 +428,25 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
     auto lslot = [&](int i) { return sol[nz - 1 - (i < nz ? i : nz - 1)]; };
     int s1 = lslot(1), s2 = lslot(2);
     double t1 = tau_p[(size_t)s1 * G], w1 = w0_p[(size_t)s1 * G], g1 = gt_p[s1];
-    double Dprev = 0.0;  // sum_z w_z d'_z of row 2i
+    // The whole solve is linear in the right-hand side and the matrix does not depend on the zenith
+    // angle: the quadrature sum_z w_z is taken on the RHS terms (C+-, direct beam) BEFORE the
+    // elimination, so one Thomas recurrence runs on D' = sum_z w_z d'_z.
     const double re1_top = rt_rcp_fast(e1);
+    double Dprev;  // sum_z w_z d'_z of row 2i
+    {
+      double CM0 = 0.0;
+      CPB = 0.0; CMB = 0.0;
 #pragma unroll
-    for (int z = 0; z < ZC; z++) {
-      const double etb = ex[z];  // et0 = exp(-tauc(1)/u0) = 1
-      const double cp0 = fp[z], cm0 = fm[z];
-      cpb[z] = etb * fp[z];
-      cmb[z] = etb * fm[z];
-      et[z] = etb;
-      dprev[z] = (0.0 - cm0) * re1_top;  // rows :93-96, Thomas :302-303
-      Dprev += wz[z] * dprev[z];
-      CP0_top += wz[z] * cp0;
-      FDN_top += wz[z] * u0[z];  // direct(1) = u0*Fs_pi (:73)
-      AM_top += wz[z];           // direct(1)/u0
+      for (int z = 0; z < ZC; z++) {
+        CP0_top += wz[z] * fp[z];  // exp(-tauc(1)/u0) = 1 at the top
+        CM0 += wz[z] * fm[z];
+        aw[z] = wz[z] * ex[z];
+        CPB += aw[z] * fp[z];
+        CMB += aw[z] * fm[z];
+        FDN_top += wz[z] * u0[z];  // direct(1) = u0*Fs_pi (:73)
+        AM_top += wz[z];           // direct(1)/u0
+      }
+      Dprev = (0.0 - CM0) * re1_top;  // rows :93-96, Thomas :302-303
     }
     cprev = (-e2) * re1_top;
     double Ta = 0.0, Tb = 0.0;
@@ -422,14 +464,12 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       const double t2 = tau_p[(size_t)s2 * G], w2 = w0_p[(size_t)s2 * G], g2 = gt_p[s2];
       // layer i ("o"ld) values; layer_coeffs() overwrites e1..e4/cgam/wrk/fp/fm/ex with layer i+1
       const double e1o = e1, e2o = e2, e3o = e3, e4o = e4;
-      double c1, cn = 0.0, D1 = 0.0, Dn = 0.0;
-      double CPB = 0.0, CMB = 0.0, DIR = 0.0, DIRU = 0.0;
+      double c1, cn = 0.0, D1, Dn = 0.0;
+      double CPBn = 0.0, CMBn = 0.0, DIR = 0.0, DIRU = 0.0;
 #pragma unroll
       for (int z = 0; z < ZC; z++) {
-        CPB += wz[z] * cpb[z];
-        CMB += wz[z] * cmb[z];
-        DIR += wz[z] * (u0[z] * et[z]);  // direct(i+1) = u0*etb(i) (:84)
-        DIRU += wz[z] * et[z];           // direct(i+1)/u0
+        DIR += aw[z] * u0[z];  // direct(i+1) = u0*etb(i) (:84)
+        DIRU += aw[z];         // direct(i+1)/u0
       }
       if (i < nz - 1) {
         const int slotn = s1;
@@ -445,31 +485,26 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
         const double A2 = e2o * e3o - e4o * e1o, B2 = e1o * e1 - e3o * e3, Dd2 = e3o * e4 - e1o * e2;
         const double r2 = rt_rcp_fast(B2 - A2 * c1);
         cn = Dd2 * r2;
+        // zenith sums of C+-(top of layer i+1) and, after the layer's attenuation, C+-(its bottom)
+        double CP0n = 0.0, CM0n = 0.0;
 #pragma unroll
         for (int z = 0; z < ZC; z++) {
-          const double etb = et[z] * ex[z];
-          const double cp0n = et[z] * fp[z], cm0n = et[z] * fm[z];
-          const double E1 = e2 * (cp0n - cpb[z]) - e4 * (cm0n - cmb[z]);
-          const double d1 = (E1 - A1 * dprev[z]) * r1;
-          const double E2 = e3o * (cp0n - cpb[z]) + e1o * (cmb[z] - cm0n);
-          const double dn = (E2 - A2 * d1) * r2;
-          D1 += wz[z] * d1;
-          Dn += wz[z] * dn;
-          dprev[z] = dn;
-          cpb[z] = etb * fp[z];
-          cmb[z] = etb * fm[z];
-          et[z] = etb;
+          CP0n += aw[z] * fp[z];
+          CM0n += aw[z] * fm[z];
+          aw[z] *= ex[z];
+          CPBn += aw[z] * fp[z];
+          CMBn += aw[z] * fm[z];
         }
+        const double E1 = e2 * (CP0n - CPB) - e4 * (CM0n - CMB);
+        D1 = (E1 - A1 * Dprev) * r1;
+        const double E2 = e3o * (CP0n - CPB) + e1o * (CMB - CM0n);
+        Dn = (E2 - A2 * D1) * r2;
       } else {
         const double A = e1o - Rsfc * e3o, B = e2o - Rsfc * e4o;  // :114-117
         const double r1 = rt_rcp_fast(B - A * cprev);
         c1 = 0.0;
-#pragma unroll
-        for (int z = 0; z < ZC; z++) {
-          const double Ssfc = Rsfc * (u0[z] * et[z]);  // :90
-          const double E = Ssfc - cpb[z] + Rsfc * cmb[z];
-          D1 += wz[z] * ((E - A * dprev[z]) * r1);
-        }
+        const double E = Rsfc * DIR - CPB + Rsfc * CMB;  // Ssfc = Rsfc*u0*etb (:90), summed over z
+        D1 = (E - A * Dprev) * r1;
       }
       // folded back-substitution data of layer i (see the IR kernel): with xn entering from below,
       //   y1 = alpha + beta*xn, fup = Au + Bu*xn, fdn (incl. direct beam) = Ad + Bd*xn,
@@ -478,11 +513,26 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
         const double c0 = cprev, d0 = Dprev;
         const double Qu = e2o - c0 * e1o, Qd = e4o - c0 * e3o;
         const double al = d0 - c0 * D1, be = c0 * c1;
-        double *s = scr + (size_t)i * SOL_ITEMS * nres;
+        double *s = scr + (size_t)i * SOL_TITEMS * nres;
         s[0] = al; s[nres] = be;
-        s[2 * nres] = (d0 * e1o + CPB) + Qu * D1; s[3 * nres] = -(Qu * c1);
-        s[4 * nres] = ((d0 * e3o + CMB) + Qd * D1) + DIR; s[5 * nres] = -(Qd * c1);
-        s[6 * nres] = DIRU - u1i * DIR;
+        const double Au = (d0 * e1o + CPB) + Qu * D1, Ad = ((d0 * e3o + CMB) + Qd * D1) + DIR;
+        const double Kk = DIRU - u1i * DIR;
+        // Au, Ad and K enter the outputs only through their g-weighted sums (radiate.f90:122-126)
+#if TS_SOL_PRESUM == 2
+        s[2 * nres] = -(Qu * c1); s[3 * nres] = -(Qd * c1);
+        const double SA = group_sum2<P>(Au * wg, Ad * wg, gl);
+        const double SK = group_sum<P>(Kk * wg);
+        if (gl < 3) gscr[(size_t)i * SOL_GITEMS * ngres + gl] = gl == 2 ? SK : SA;
+#else
+        s[2 * nres] = Au; s[3 * nres] = -(Qu * c1);
+        s[4 * nres] = Ad; s[5 * nres] = -(Qd * c1);
+#if TS_SOL_PRESUM == 1
+        const double SK = group_sum<P>(Kk * wg);
+        if (gl == 0) gscr[(size_t)i * SOL_GITEMS * ngres] = SK;
+#else
+        s[6 * nres] = Kk;
+#endif
+#endif
         if (i == 0) {  // :143  y1*e3 - y2*e4 + cp0 = Ta + Tb*xn
           Ta = (al * e3o - D1 * e4o) + CP0_top;
           Tb = be * e3o + c1 * e4o;
@@ -490,13 +540,13 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       }
       cprev = cn;
       Dprev = Dn;
+      CPB = CPBn; CMB = CMBn;
       s1 = s2; s2 = s3; t1 = t2; w1 = w2; g1 = g2;
     }
 
     // ---- ONE back substitution for the zenith-weighted solution, fluxes (:135-148), g-weights
     const size_t obase = ((size_t)c * nw_sol + ll) * (nz + 1);
     double *fup_o = fx.fup_a_sol + obase, *fdn_o = fx.fdn_a_sol + obase, *am_o = fx.amean_sol + obase;
-    const bool writer = gactive && gl == 0;
     // scale factors applied after the g/zenith sums (radiate.f90:167-180)
     const double ps = pr.photons_sol[ll] * pr.photon_scale_factor;  // clima_radtran.f90:302
     const double avg_freq = 0.5 * (tb.freq[l] + tb.freq[l + 1]);
@@ -504,34 +554,53 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
     const double am1 = (avg_freq / avg_wavl);
     const double am2 = (avg_wavl / (RT_PLANK * RT_C_LIGHT * 1.0e16));
     const double dwl = (tb.wavl[l + 1] - tb.wavl[l]);
-    auto emit = [&](const int ig, double fup, double fdn, double am) {
-      const double su = group_sum<P>(fup * wg), sd = group_sum<P>(fdn * wg), sa = group_sum<P>(am * wg);
-      if (writer) {
-        double a = su * ps * pr.diurnal_fac, b = sd * ps * pr.diurnal_fac, m = sa * ps * pr.diurnal_fac;
-        m = m * am1;
-        m = m * am2 * dwl;
-        if (accumulate) { a += fup_o[ig]; b += fdn_o[ig]; m += am_o[ig]; }
-        fup_o[ig] = a; fdn_o[ig] = b; am_o[ig] = m;
+    // R: sum over g of the upward (even lanes) / downward (odd lanes) flux; sa: of the mean intensity
+    double *const out_o = (gl & 1) ? fdn_o : fup_o;  // lane 0 writes fup and amean, lane 1 fdn
+    auto emit = [&](const int ig, const double R, const double sa) {
+      if (gactive && gl < 2) {
+        double v = R * ps * pr.diurnal_fac;
+        if (accumulate) v += out_o[ig];
+        out_o[ig] = v;
+        if (gl == 0) {
+          double m = sa * ps * pr.diurnal_fac;
+          m = m * am1;
+          m = m * am2 * dwl;
+          if (accumulate) m += am_o[ig];
+          am_o[ig] = m;
+        }
       }
     };
     double xnext = 0.0, xtop = 0.0;
     // scratch loads two layers ahead of the arithmetic (rotating register buffers, unrolled by 3)
-    double q[3][SOL_ITEMS];
-    auto ld = [&](double (&b)[SOL_ITEMS], int i) {
-      const double *s = scr + (size_t)(i > 0 ? i : 0) * SOL_ITEMS * nres;
+    constexpr int NB = SOL_TITEMS + 2;  // + the group's sums (this lane's parity of Au/Ad; K)
+    double q[3][NB];
+    auto ld = [&](double (&b)[NB], int i) {
+      const int ic = i > 0 ? i : 0;
+      const double *s = scr + (size_t)ic * SOL_TITEMS * nres;
 #pragma unroll
-      for (int t = 0; t < SOL_ITEMS; t++) b[t] = s[(size_t)t * nres];
+      for (int t = 0; t < SOL_TITEMS; t++) b[t] = s[(size_t)t * nres];
+      const double *gs = gscr + (size_t)ic * SOL_GITEMS * ngres;
+      b[SOL_TITEMS] = TS_SOL_PRESUM == 2 ? gs[gl & 1] : 0.0;
+      b[SOL_TITEMS + 1] = TS_SOL_PRESUM == 2 ? gs[2] : (TS_SOL_PRESUM == 1 ? gs[0] : 0.0);
       if (TS_L2_PREFETCH_SOL > 0 && i >= TS_L2_PREFETCH_SOL) {
-        const double *pf = scr + (size_t)(i - TS_L2_PREFETCH_SOL) * SOL_ITEMS * nres;
+        const double *pf = scr + (size_t)(i - TS_L2_PREFETCH_SOL) * SOL_TITEMS * nres;
 #pragma unroll
-        for (int t = 0; t < SOL_ITEMS; t++) l2_prefetch(pf + (size_t)t * nres);
+        for (int t = 0; t < SOL_TITEMS; t++) l2_prefetch(pf + (size_t)t * nres);
+        if (TS_SOL_PRESUM) l2_prefetch(gscr + (size_t)(i - TS_L2_PREFETCH_SOL) * SOL_GITEMS * ngres);
       }
     };
-    auto bk = [&](const double (&b)[SOL_ITEMS], int i) {
-      const double fup = b[2] + b[3] * xnext;  // :146
-      const double fdn = b[4] + b[5] * xnext;  // :147
-      const double am = u1i * (fup + fdn) + b[6];  // :137-139
-      emit(nz - 1 - i, fup, fdn, am);
+    auto bk = [&](const double (&b)[NB], int i) {
+      // fup = Au + Bu*xn (:146), fdn = Ad + Bd*xn (:147), amean = (1/u1)(fup + fdn) + K (:137-139),
+      // all three summed over g
+#if TS_SOL_PRESUM == 2
+      const double wx = wg * xnext;
+      const double R = group_sum2<P>(b[2] * wx, b[3] * wx, gl) + b[SOL_TITEMS];
+#else
+      const double R = group_sum2<P>((b[2] + b[3] * xnext) * wg, (b[4] + b[5] * xnext) * wg, gl);
+#endif
+      const double Ro = __shfl_xor_sync(0xffffffffu, R, 1);
+      const double SK = TS_SOL_PRESUM ? b[SOL_TITEMS + 1] : group_sum<P>(b[SOL_TITEMS - 1] * wg);
+      emit(nz - 1 - i, R, u1i * (R + Ro) + SK);
       xtop = xnext;
       xnext = b[0] + b[1] * xnext;
     };
@@ -544,8 +613,8 @@ twostream_solar_kernel(const __grid_constant__ DevTables tb, const __grid_consta
       if (i - 2 >= 0) { ld(q[1], i - 4); bk(q[2], i - 2); }
     }
     {
-      const double up = Ta + Tb * xtop;            // :143
-      emit(nz, up, FDN_top, u1i * up + AM_top);  // :135, :144
+      const double up = Ta + Tb * xtop;  // :143
+      emit(nz, group_sum2<P>(up * wg, FDN_top * wg, gl), group_sum<P>((u1i * up + AM_top) * wg));  // :135, :144
     }
   }
 }
@@ -621,7 +690,8 @@ void rt_twostream_occupancy(int G, int nzen, int *ir_blocks_per_sm, int *sol_blo
 }
 
 int rt_twostream_block_threads() { return TS_THREADS; }
-int rt_twostream_items_per_layer() { return SOL_ITEMS > IR_ITEMS ? SOL_ITEMS : IR_ITEMS; }
+// doubles per layer and resident thread the scratch must hold (per-thread items + the group slots, P >= 8)
+int rt_twostream_items_per_layer() { return 8; }
 
 void rt_launch_planck(const DevTables &tb, const DevChunk &ch, const DevFlux &fx, cudaStream_t st) {
   planck_kernel<<<1184, 256, 0, st>>>(tb, ch, fx.bpl);
