@@ -141,7 +141,9 @@ def run_reference(args):
     lib = load("fast")
     cores = int(lib.oracle_max_threads())
     o = OracleRadtran(tb, pr, kind="fast")
-    n = 2 * cores  # bounded sample per step
+    n = 16 * cores  # bounded sample per step (~2.5 s of the 16-thread port: long enough that thread start-up
+    #                 and per-call allocation do not understate the CPU arm; r1r: 59 columns/s at 2 per thread,
+    #                 100 columns/s at 40 per thread)
     cs = synth.make_columns(n, nz=100, seed=synth.SEED)
     for _ in range(args.warmup):
         o.radiate_batch(cs, nthreads=cores)
