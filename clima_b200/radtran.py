@@ -225,6 +225,43 @@ class Radtran:
         r = self.radiate(T_surface, T, P, densities, dz, pdensities, radii)
         return float(r["ISR"][0]), float(r["OLR"][0])
 
+    # ---- host-side helpers of type Radtran that do not touch the device path
+    def bolometric_flux(self) -> float:
+        """Bolometric stellar flux at the planet in W/m^2 (Radtran_bolometric_flux,
+        clima_radtran.f90:353-364): sum of photons_sol * bin width in frequency, scaled."""
+        i0, i1 = self.tables.sol_ind
+        freq = self.tables.freq[i0 - 1:i1 + 1]
+        flux = 0.0
+        for i in range(self.tables.nw_sol):
+            flux = flux + float(self.tables.photons_sol[i]) * float(freq[i] - freq[i + 1])
+        return self._params.photon_scale_factor * flux / 1.0e3
+
+    def set_bolometric_flux(self, flux: float):
+        """Radtran_set_bolometric_flux (clima_radtran.f90:345-350): rescales photon_scale_factor."""
+        import dataclasses
+        p1 = dataclasses.replace(self._params, photon_scale_factor=1.0)
+        self._params = p1
+        self.params = dataclasses.replace(p1, photon_scale_factor=float(flux) / self.bolometric_flux())
+
+    def equilibrium_temperature(self, bond_albedo: float) -> float:
+        """clima_eqns.f90:248-254 through Radtran_equilibrium_temperature (clima_radtran.f90:376-382)"""
+        sigma_si = 5.670374419e-8  # clima_const.f90:16
+        return ((self.bolometric_flux() * (1.0 - bond_albedo)) / (4.0 * sigma_si)) ** 0.25
+
+    def skin_temperature(self, bond_albedo: float) -> float:
+        """clima_eqns.f90:256-261 through Radtran_skin_temperature (clima_radtran.f90:367-373)"""
+        return self.equilibrium_temperature(bond_albedo) * 0.5 ** 0.25
+
+    @staticmethod
+    def apply_radiation_enhancement(r: Dict, rad_enhancement: float) -> Dict:
+        """Radtran_apply_radiation_enhancement (clima_radtran.f90:402-411) on a result dict of
+        radiate / radiate_batch: scales the solar fluxes in place and rebuilds f_total."""
+        for k in ("fdn_n_sol", "fup_n_sol", "fdn_a_sol", "fup_a_sol"):
+            if k in r and r[k] is not None:
+                r[k] *= rad_enhancement
+        r["f_total"][...] = (r["fdn_n_sol"] - r["fup_n_sol"]) + (r["fdn_n_ir"] - r["fup_n_ir"])
+        return r
+
     # ---- introspection / test hooks
     def get_opacity(self, nz: int, icol: int = 0):
         G, nw = self.tables.ngauss, self.tables.nw

@@ -481,3 +481,33 @@ def test_tables_from_the_load_time_packer(tmp_path):
     assert tb.photons_sol.shape == (i1 - i0 + 1,) and np.all(tb.photons_sol > 0.0)
     g, o, rg, ro = run_both(tb, pr, cols)
     compare(rg, ro)
+
+
+def test_bolometric_flux_helpers_and_radiation_enhancement():
+    """Host helpers of type Radtran (clima_radtran.f90:345-411): set_bolometric_flux rescales
+    photon_scale_factor so that bolometric_flux() returns the request, the solar fluxes follow
+    linearly (and match the oracle run with the same scale factor), skin / equilibrium temperatures
+    follow clima_eqns.f90:248-261, apply_radiation_enhancement rebuilds f_total."""
+    import dataclasses
+    tb, pr, cols = small_case(G=16, nw=12, nz=10, ncol=2, nk=3)
+    g = Radtran(tb, pr)
+    f0 = g.bolometric_flux()
+    freq = tb.freq[tb.sol_ind[0] - 1:tb.sol_ind[1] + 1]
+    assert f0 == pytest.approx(pr.photon_scale_factor * np.sum(tb.photons_sol * (freq[:-1] - freq[1:])) / 1.0e3, rel=1e-14)
+    r0 = {k: v.copy() for k, v in g.radiate_batch(cols).items()}
+    g.set_bolometric_flux(1361.0)
+    assert g.bolometric_flux() == pytest.approx(1361.0, rel=1e-14)
+    scale = g.params.photon_scale_factor / pr.photon_scale_factor
+    r1 = g.radiate_batch(cols)
+    np.testing.assert_allclose(r1["ISR"], r0["ISR"] * scale, rtol=1e-13)
+    np.testing.assert_allclose(r1["fdn_n_sol"], r0["fdn_n_sol"] * scale, rtol=1e-13)
+    np.testing.assert_array_equal(r1["fup_n_ir"], r0["fup_n_ir"])
+    ro = OracleRadtran(tb, dataclasses.replace(pr, photon_scale_factor=g.params.photon_scale_factor)).radiate_batch(cols)
+    compare(r1, ro, spectral=False)
+    teq = g.equilibrium_temperature(0.3)
+    assert teq == pytest.approx((1361.0 * 0.7 / (4.0 * 5.670374419e-8)) ** 0.25, rel=1e-14)
+    assert g.skin_temperature(0.3) == pytest.approx(teq * 0.5 ** 0.25, rel=1e-15)
+    r2 = {k: v.copy() for k, v in r1.items()}
+    Radtran.apply_radiation_enhancement(r2, 1.25)
+    np.testing.assert_allclose(r2["fdn_n_sol"], 1.25 * r1["fdn_n_sol"], rtol=1e-15)
+    np.testing.assert_allclose(r2["f_total"], (r2["fdn_n_sol"] - r2["fup_n_sol"]) + (r1["fdn_n_ir"] - r1["fup_n_ir"]), rtol=1e-15, atol=0)
