@@ -72,6 +72,7 @@ struct Handle {
 
   // introspection
   int64_t launches = 0;
+  int last_unit_order = 0;  // RORR unit order of the last chunk: 0 column-grouped, 1 slot-fastest
   cudaEvent_t ev[6] = {};
   double stage_ms[6] = {0, 0, 0, 0, 0, 0};
 };
@@ -213,6 +214,7 @@ void build_tables(Handle &h, const clima_rt_tables *t) {
     if (!(wmax * wmax * 1.000001 < dmin) || (gw && gw[0] == '1')) d.pad0 |= 2;
     const char *go = std::getenv("CLIMA_RT_RORR_GROUP");  // "layers": slot-fastest unit order
     if (go && go[0] == 'l') d.pad0 |= 4;
+    if (go && go[0] == 'c') d.pad0 |= 8;  // "columns": column-grouped whatever the columns look like
   }
   h.d_photons = upload(h, t->photons_sol, h.nw_sol);
   h.d_albedo = upload<double>(h, nullptr, h.nw_sol);
@@ -300,6 +302,7 @@ void ensure_chunk(Handle &h, int ncol, int nz) {
   ch.tband = calloc_dev<double>(h, (size_t)C * tb.nw * nz);
   ch.cont = calloc_dev<double>(h, (size_t)3 * C * tb.nw * nz);
   ch.status = calloc_dev<int>(h, C);
+  ch.dissim = calloc_dev<int>(h, 1);
   {
     const long long units = (long long)((C + 3) / 4 * 4) * tb.nw * nz;
     if (units >= (1ll << 31)) throw CudaError{"chunk too large: lower CLIMA_RT_CHUNK_COLS"};
@@ -387,15 +390,23 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
   if (compute_opacity) {
     CK(cudaMemsetAsync(ch.status, 0, ncol * sizeof(int), h.st));
     rt_launch_prep(h.tb, ch, h.st);
-    h.launches++;
+    rt_launch_similarity(h.tb, ch, h.st);
+    h.launches += 2;  // prep + similarity
     // tight slot capacity: max number of unique layers over the chunk
     std::vector<int> ns(ncol);
+    int dissim = 0;
     CK(cudaMemcpyAsync(ns.data(), ch.nslots, ncol * sizeof(int), cudaMemcpyDeviceToHost, h.st));
+    CK(cudaMemcpyAsync(&dissim, ch.dissim, sizeof(int), cudaMemcpyDeviceToHost, h.st));
     CK(cudaStreamSynchronize(h.st));
     ch.nslot_cap = *std::max_element(ns.begin(), ns.end());
     record(h, 5);
     const int exact = (h.rorr_exact_only || force_exact) ? 1 : 0;
-    rt_launch_optics_rorr(h.tb, ch, h.d_worklist, h.d_wcount, h.wcap, exact, h.st);
+    // RORR unit order of this chunk (rorr_impl.cuh): 4 adjacent columns per warp when the columns of
+    // a group are alike, 4 adjacent slots of one column otherwise; CLIMA_RT_RORR_GROUP forces either
+    DevTables tbc = h.tb;
+    if (!(tbc.pad0 & (4 | 8)) && (long long)dissim * 64 > (long long)ncol) tbc.pad0 |= 4;
+    h.last_unit_order = (tbc.pad0 & 4) ? 1 : 0;
+    rt_launch_optics_rorr(tbc, ch, h.d_worklist, h.d_wcount, h.wcap, exact, h.st);
     const bool two = !exact && h.tb.rows_sorted;
     h.launches += two ? 3 : 2;  // continua + fast + exact, or continua + exact
     *h.h_wcount = 0;

@@ -564,10 +564,13 @@ optics_rorr_kernel(const __grid_constant__ DevTables tb, const __grid_constant__
     if (n > wcap) n = wcap;
     if (uid < (unsigned)n) uid = (unsigned)worklist[uid]; else { active = false; uid = 0; }
   }
-  // unit id -> (column, bin, slot).  Default: the units of a warp are the SAME (bin, slot) of
-  // adjacent columns (uid = ((c/4 * nw + l) * cap + slot) * 4 + c%4): neighbouring columns of a
-  // sweep take the closed-form / sort decision together far more often than neighbouring layers
-  // of one column, and they read the same k-table rows.  pad0 bit 2: slot-fastest order.
+  // unit id -> (column, bin, slot).  Two orders.  Column-grouped: the units of a warp are the SAME
+  // (bin, slot) of 4 adjacent columns (uid = ((c/4 * nw + l) * cap + slot) * 4 + c%4): neighbouring
+  // columns of a sweep take the closed-form / sort decision together and read the same k-table rows
+  // (cfg2: 34.6 vs 35.2 ms per 1024 columns).  Slot-fastest: 4 adjacent slots of ONE column, better
+  // when neighbouring columns are unrelated (cfg5, randomised composition: 37.9 vs 45.0 ms).
+  // similarity_kernel counts the 4-column groups with unlike k-gas amounts; the host picks
+  // column-grouped only if fewer than 1 in 16 are unlike and says so in pad0 bit 2 (slot-fastest).
   int slot, l;
   unsigned cl;
   {

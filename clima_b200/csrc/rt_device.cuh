@@ -95,6 +95,9 @@ struct DevChunk {
   double *tau, *w0, *gt, *tband;
   double *cont;  // [3][col][bin l][slot]: g-independent terms handed from continua_kernel to the RORR epilogue
   int *status;  // [col]
+  // [0]: groups of 4 adjacent columns whose k-gas amounts differ (counted by similarity_kernel);
+  // the RORR kernels choose their unit order from it
+  int *dissim;
 };
 
 // ---- small device helpers shared by kernels -------------------------------------------------

@@ -20,6 +20,8 @@ struct DevFlux {
 
 // prep.cu
 void rt_launch_prep(const DevTables &tb, const DevChunk &ch, cudaStream_t st);
+// counts the groups of 4 adjacent columns with unlike k-gas amounts into ch.dissim (RORR unit order)
+void rt_launch_similarity(const DevTables &tb, const DevChunk &ch, cudaStream_t st);
 // optics_rorr.cu
 void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
                            int wcap, int exact_only, cudaStream_t st);

@@ -511,3 +511,22 @@ def test_bolometric_flux_helpers_and_radiation_enhancement():
     Radtran.apply_radiation_enhancement(r2, 1.25)
     np.testing.assert_allclose(r2["fdn_n_sol"], 1.25 * r1["fdn_n_sol"], rtol=1e-15)
     np.testing.assert_allclose(r2["f_total"], (r2["fdn_n_sol"] - r2["fup_n_sol"]) + (r1["fdn_n_ir"] - r1["fup_n_ir"]), rtol=1e-15, atol=0)
+
+
+def test_rorr_unit_order_does_not_change_results(monkeypatch):
+    """The RORR kernels group 4 units per warp either as the same (bin, slot) of 4 adjacent columns
+    (chosen when neighbouring columns are alike) or as 4 adjacent slots of one column; the order is a
+    scheduling choice only.  Alike columns (a sweep) and unrelated ones (randomised), both orders
+    forced, against the automatic choice and the oracle."""
+    tb, pr, _ = small_case(G=16, nw=10, nz=12, ncol=9, nk=3)
+    for kw in (dict(), dict(randomize=True, seed=5)):
+        cols = synth.make_columns(9, nz=12, **kw)
+        monkeypatch.delenv("CLIMA_RT_RORR_GROUP", raising=False)
+        g, o, r_auto, ro = run_both(tb, pr, cols, spectral=False)
+        compare(r_auto, ro, spectral=False)
+        res = {}
+        for mode in ("layers", "columns"):
+            monkeypatch.setenv("CLIMA_RT_RORR_GROUP", mode)
+            res[mode] = Radtran(tb, pr).radiate_batch(cols)
+        compare(res["layers"], res["columns"], spectral=False, tol=1e-12)
+        compare(r_auto, res["columns"], spectral=False, tol=1e-12)
