@@ -69,6 +69,12 @@ struct Handle {
   // retained state
   int retained_opacity_ncol = 0, retained_nz = 0;
   int retained_solar_ncol = 0;
+  // compute_solar=.false. reuses the stale solar fluxes (clima_radtran.f90:286-289).  The all-zero
+  // state of a fresh handle is the reference's freshly allocated wrk_sol and may be reused; the
+  // state left by a multi-chunk solar call or by a reallocation of the chunk buffers may not.
+  bool solar_state_invalid = false;
+  bool had_solar_call = false;
+  int chunk_cols_env = 0;  // CLIMA_RT_CHUNK_COLS, read once at create (0 = default 4096)
 
   // introspection
   int64_t launches = 0;
@@ -228,7 +234,10 @@ void free_chunk(Handle &h) {
   h.cap_nz = 0;
   h.retained_opacity_ncol = 0;
   h.retained_solar_ncol = 0;
+  if (h.had_solar_call) h.solar_state_invalid = true;  // the retained solar fluxes are gone
 }
+
+int chunk_cols_max(const Handle &h) { return h.chunk_cols_env > 0 ? h.chunk_cols_env : 4096; }
 
 template <typename T>
 T *calloc_dev(Handle &h, size_t n) {
@@ -255,8 +264,7 @@ size_t per_col_bytes(const Handle &h, int nz) {
 void ensure_chunk(Handle &h, int ncol, int nz) {
   size_t free_b = 0, total_b = 0;
   {
-    const char *cc0 = std::getenv("CLIMA_RT_CHUNK_COLS");
-    const int want = std::min(ncol, cc0 ? std::max(1, atoi(cc0)) : 4096);
+    const int want = std::min(ncol, chunk_cols_max(h));
     if (h.cap_nz == nz && h.cap_cols > 0 && (h.cap_cols >= want || h.cap_mem_limited)) return;
   }
   free_chunk(h);
@@ -274,8 +282,7 @@ void ensure_chunk(Handle &h, int ncol, int nz) {
   const double budget = 0.7 * (double)free_b - (double)scratch_b;
   if (budget < (double)pcb) throw CudaError{"not enough device memory for one column"};
   long long cols = (long long)(budget / (double)pcb);
-  const char *cc = std::getenv("CLIMA_RT_CHUNK_COLS");
-  long long maxc = cc ? std::max(1, atoi(cc)) : 4096;
+  long long maxc = chunk_cols_max(h);
   h.cap_mem_limited = cols < std::min<long long>(maxc, ncol);
   cols = std::min<long long>(cols, maxc);
   cols = std::min<long long>(cols, ncol);
@@ -339,8 +346,7 @@ void ensure_chunk(Handle &h, int ncol, int nz) {
 // Frozen-opacity broadcast with more columns than the buffers hold: keep column 0's opacity,
 // slot map and stale solar fluxes across the reallocation.
 void grow_for_bcast(Handle &h, int ncol, int nz) {
-  const char *cc0 = std::getenv("CLIMA_RT_CHUNK_COLS");
-  const int want = std::min(ncol, cc0 ? std::max(1, atoi(cc0)) : 4096);
+  const int want = std::min(ncol, chunk_cols_max(h));
   if (want <= h.cap_cols || h.cap_mem_limited) return;
   const DevTables &tb = h.tb;
   const int cap = h.ch.nslot_cap;
@@ -348,6 +354,7 @@ void grow_for_bcast(Handle &h, int ncol, int nz) {
   const int rs = h.retained_solar_ncol;
   double *sv = nullptr;
   int *svi = nullptr;
+  const bool inv0 = h.solar_state_invalid;
   CK(cudaMalloc(&sv, (2 * n1 + 2 * n2 + 2 * L) * 8));
   CK(cudaMalloc(&svi, (size_t)nz * sizeof(int)));
   CK(cudaMemcpy(sv, h.ch.tau, n1 * 8, cudaMemcpyDeviceToDevice));
@@ -371,6 +378,7 @@ void grow_for_bcast(Handle &h, int ncol, int nz) {
   h.retained_opacity_ncol = 1;
   h.retained_nz = nz;
   h.retained_solar_ncol = rs == 1 ? 1 : 0;
+  h.solar_state_invalid = (rs == 1) ? false : inv0 || h.had_solar_call;
 }
 
 struct HostIn {
@@ -484,15 +492,21 @@ void radiate_batch_impl(Handle &h, bool device, int ncol, int nz, int ng, int np
   }
   const int C = h.cap_cols;
   if (!compute_solar) {
+    if (h.solar_state_invalid)
+      throw CudaError{"compute_solar=.false. but the solar fluxes retained in the handle are not valid (the last "
+                      "solar call spanned several chunks or the chunk buffers were reallocated)"};
     if (h.retained_solar_ncol == 1) solar_bcast = true;
     else if (h.retained_solar_ncol != 0 && (h.retained_solar_ncol != ncol || ncol > C))
       throw CudaError{"compute_solar=.false. needs the retained solar fluxes of 1 column (broadcast) or of the same single-chunk batch"};
+    else if (h.retained_solar_ncol == 0 && ncol > C)
+      throw CudaError{"compute_solar=.false. with more columns than one chunk holds"};
   }
   const DevTables &tb = h.tb;
   const size_t L = nz + 1;
   const cudaMemcpyKind kin = device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
   const cudaMemcpyKind kout = device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
   for (int i = 0; i < 6; i++) h.stage_ms[i] = 0.0;
+  bool radius_clamped = false;
   for (int c0 = 0; c0 < ncol; c0 += C) {
     const int n = std::min(C, ncol - c0);
     DevChunk &ch = h.ch;
@@ -564,17 +578,21 @@ void radiate_batch_impl(Handle &h, bool device, int ncol, int nz, int ng, int np
       h.retained_opacity_ncol = (ncol <= C) ? ncol : 0;
       h.retained_nz = nz;
     }
-    if (compute_solar) h.retained_solar_ncol = (ncol <= C) ? ncol : 0;
+    if (compute_solar) {
+      h.retained_solar_ncol = (ncol <= C) ? ncol : 0;
+      h.had_solar_call = true;
+      h.solar_state_invalid = ncol > C;  // several chunks: only the last one's fluxes remain
+    }
+    // particle radius outside the table: the reference fails the whole call
+    // (clima_radtran_types.f90:773-776).  Checked per chunk: ch.status holds this chunk only.
+    if (compute_opacity && tb.npart > 0) {
+      std::vector<int> stv(n);
+      CK(cudaMemcpy(stv.data(), h.ch.status, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost));
+      for (int s : stv)
+        if (s & CLIMA_RT_STATUS_RADIUS_CLAMPED) radius_clamped = true;
+    }
   }
-  // particle radius outside the table: the reference fails the whole call
-  // (clima_radtran_types.f90:773-776)
-  if (compute_opacity && tb.npart > 0) {
-    std::vector<int> stv(std::min(ncol, C));
-    CK(cudaMemcpy(stv.data(), h.ch.status, stv.size() * sizeof(int), cudaMemcpyDeviceToHost));
-    for (int s : stv)
-      if (s & CLIMA_RT_STATUS_RADIUS_CLAMPED)
-        throw CudaError{"Opacity computation failed in one or more wavelength bins."};
-  }
+  if (radius_clamped) throw CudaError{"Opacity computation failed in one or more wavelength bins."};
 }
 
 
@@ -683,6 +701,10 @@ void clima_rt_create(const clima_rt_tables *tables, const clima_rt_params *param
       const char *m = std::getenv("CLIMA_RT_RORR");
       h->rorr_exact_only = (m && std::string(m) == "exact") ? 1 : 0;
     }
+    {
+      const char *cc = std::getenv("CLIMA_RT_CHUNK_COLS");
+      h->chunk_cols_env = cc ? std::max(1, atoi(cc)) : 0;
+    }
     build_tables(*h, tables);
     {
       const char *m = std::getenv("CLIMA_RT_RORR_NOSKIP");  // debug: always sort (no closed-form merges)
@@ -712,6 +734,7 @@ void clima_rt_destroy(void *handle) {
 void clima_rt_set_params(void *handle, const clima_rt_params *params, char *err) {
   set_err(err, "");
   try {
+    if (!handle || !params) throw CudaError{"clima_rt: NULL handle or params"};
     Handle &h = *static_cast<Handle *>(handle);
     CK(cudaSetDevice(h.device));
     upload_params(h, params);
@@ -725,6 +748,7 @@ void clima_rt_set_custom_optical_properties(void *handle, const int32_t *nP, con
                                             const double *g0, char *err) {
   set_err(err, "");
   try {
+    if (!handle || !nP || !log10P || !dtau_dz || !w0 || !g0) throw CudaError{"clima_rt: NULL argument"};
     Handle &h = *static_cast<Handle *>(handle);
     CK(cudaSetDevice(h.device));
     if (*nP < 2) throw CudaError{"custom optical properties need at least 2 pressure points"};
@@ -744,6 +768,7 @@ void clima_rt_set_custom_optical_properties(void *handle, const int32_t *nP, con
 }
 
 void clima_rt_unset_custom_optical_properties(void *handle) {
+  if (!handle) return;
   Handle &h = *static_cast<Handle *>(handle);
   h.tb.has_custom = 0;
 }
@@ -800,6 +825,7 @@ void clima_rt_get_opacity(void *handle, const int32_t *icol, double *tau, double
                           double *tau_band, char *err) {
   set_err(err, "");
   try {
+    if (!handle || !icol) throw CudaError{"clima_rt: NULL handle"};
     Handle &h = *static_cast<Handle *>(handle);
     CK(cudaSetDevice(h.device));
     if (h.retained_opacity_ncol < 1 || *icol < 0 || *icol >= h.retained_opacity_ncol)
@@ -821,10 +847,12 @@ void clima_rt_get_opacity(void *handle, const int32_t *icol, double *tau, double
 }
 
 void clima_rt_get_launch_count(void *handle, int64_t *count) {
+  if (!handle) { if (count) *count = 0; return; }
   *count = static_cast<Handle *>(handle)->launches;
 }
 
 void clima_rt_get_rorr_stats(void *handle, int64_t *stats3) {
+  if (!handle) { stats3[0] = stats3[1] = stats3[2] = 0; return; }
   Handle &h = *static_cast<Handle *>(handle);
   stats3[0] = h.rorr_units;
   stats3[1] = h.rorr_exact_units;
@@ -832,10 +860,12 @@ void clima_rt_get_rorr_stats(void *handle, int64_t *stats3) {
 }
 
 void clima_rt_get_stream(void *handle, void **stream) {
+  if (!handle) { *stream = nullptr; return; }
   *stream = (void *)static_cast<Handle *>(handle)->st;
 }
 
 void clima_rt_get_stage_ms(void *handle, double *ms6) {
+  if (!handle) { for (int i = 0; i < 6; i++) ms6[i] = 0.0; return; }
   Handle &h = *static_cast<Handle *>(handle);
   for (int i = 0; i < 6; i++) ms6[i] = h.stage_ms[i];
 }

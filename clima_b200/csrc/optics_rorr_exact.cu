@@ -12,10 +12,15 @@ void launch(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
             long long units, cudaStream_t st) {
   using C = rorr_exact::Cfg<P>;
   auto kern = rorr_exact::optics_rorr_kernel<P, FULL, false>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::BLOCK_BYTES);
-    attr_set = true;
+  // the opt-in above 48 KB of dynamic shared memory is per device: one flag per device ordinal
+  static bool attr_set[64] = {};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    // on failure the launch below fails too and run_chunk reports it (cudaGetLastError)
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)C::BLOCK_BYTES) == cudaSuccess &&
+        dev >= 0 && dev < 64)
+      attr_set[dev] = true;
   }
   // One group of UPB units per block (NOT a persistent grid: the kernel is instruction-cache bound
   // and the warps of a block that start together share their instruction stream; measured r1n:

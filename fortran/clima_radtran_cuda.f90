@@ -17,7 +17,7 @@ module clima_radtran_cuda
 
   public :: RadtranCuda, RadtranBatchResult
   public :: radtran_cuda_create, radtran_cuda_destroy, radtran_cuda_sync_params
-  public :: radtran_radiate_batch
+  public :: radtran_radiate_batch, radtran_jacobian_batch, pack_params
   public :: c_tables, c_params, c_out
 
   integer, parameter :: dp = c_double

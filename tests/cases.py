@@ -26,8 +26,10 @@ def rel_err(a, b):
     return float(np.max(np.abs(a - b)) / s)
 
 
-def elem_rel_err(a, b, floor=1e-6):
-    """max elementwise relative error over elements with |b| > floor*max|b|."""
+def elem_rel_err(a, b, floor=1e-12):
+    """max elementwise relative error over elements with |b| > floor*max|b| (the floor only keeps
+    0/0 out: fluxes 12 decades below the column maximum -- deep fdn_n_sol under an opaque
+    atmosphere -- are below one ulp of every sum they enter)."""
     a = np.asarray(a, dtype=np.float64)
     b = np.asarray(b, dtype=np.float64)
     s = np.max(np.abs(b))

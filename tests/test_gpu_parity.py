@@ -102,6 +102,57 @@ def test_particle_radius_out_of_range_fails_like_reference():
         g.radiate_batch(cols)
 
 
+def test_particle_radius_out_of_range_in_an_early_chunk(monkeypatch):
+    """The radius check looks at every chunk, not only at the last one (ncol=7 in chunks of 3, the
+    bad radius in column 0)."""
+    monkeypatch.setenv("CLIMA_RT_CHUNK_COLS", "3")
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=7, npart=1)
+    cols["radii"][:, :, 0] = 1.0
+    g = Radtran(tb, pr)
+    with pytest.raises(ClimaException, match="Opacity computation failed"):
+        g.radiate_batch(cols)
+    # the same batch without the bad column is fine
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=7, npart=1)
+    Radtran(tb, pr).radiate_batch(cols)
+
+
+def test_stale_solar_state_is_refused_when_it_is_not_the_callers(monkeypatch):
+    """compute_solar=.false. (clima_radtran.f90:286-289) reuses the previous call's solar fluxes.
+    A fresh handle has the reference's all-zero wrk_sol; after a multi-chunk solar call only the
+    last chunk's fluxes remain and the call must fail instead of mixing columns."""
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=7)
+    o = OracleRadtran(tb, pr)
+    g = Radtran(tb, pr)
+    r0 = g.radiate_batch(cols, compute_solar=False)  # fresh handle: zeros, like the reference
+    assert np.all(r0["fup_n_sol"] == 0.0) and np.all(r0["fdn_n_sol"] == 0.0)
+    ro = o.radiate(cols, 2, compute_solar=False, spectral=False)
+    assert rel_err(r0["f_total"][:, 2], ro["f_total"][:, 0]) < TOL
+    r1 = g.radiate_batch(cols)
+    r2 = g.radiate_batch(cols, compute_solar=False)  # same single-chunk batch: allowed
+    assert np.array_equal(r1["f_total"], r2["f_total"])
+    monkeypatch.setenv("CLIMA_RT_CHUNK_COLS", "3")
+    g3 = Radtran(tb, pr)
+    g3.radiate_batch(cols)  # three chunks
+    with pytest.raises(ClimaException, match="solar"):
+        g3.radiate_batch(cols, compute_solar=False)
+
+
+def test_null_handle_is_an_error_string_not_a_crash():
+    import ctypes as C
+    from clima_b200.radtran import load_library
+    from clima_b200._abi import ERR_LEN
+    lib = load_library()
+    err = C.create_string_buffer(ERR_LEN + 1)
+    lib.clima_rt_set_params(None, None, err)
+    assert b"NULL" in err.value
+    n = C.c_int64(-1)
+    lib.clima_rt_get_launch_count(None, C.byref(n))
+    assert n.value == 0
+    lib.clima_rt_unset_custom_optical_properties(None)
+    ms = (C.c_double * 6)()
+    lib.clima_rt_get_stage_ms(None, ms)
+
+
 def test_frozen_opacity_jacobian_mode():
     """compute_opacity=.false., compute_solar=.false. (clima_adiabat_solve.f90:798-820): perturbed
     temperatures re-use ONE column's opacity and the stale solar fluxes."""

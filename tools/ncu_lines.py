@@ -20,7 +20,8 @@ for r in rows[hi + 1:]:
     if r[0] in ("Function Name", "Kernel Name"): break  # next kernel
     if r[0] == "Line No": continue  # next source file of the same kernel
     if r[0].isdigit():
-        lines.append((int(r[0]), r[1].strip(), int(r[ie]), int(r[ismp]), int(r[iw]) if iw is not None else 0, int(r[iwi]) if iw is not None else 0))
+        I = lambda s: int(s) if s.lstrip("-").isdigit() else 0
+        lines.append((int(r[0]), r[1].strip(), I(r[ie]), I(r[ismp]), I(r[iw]) if iw is not None else 0, I(r[iwi]) if iw is not None else 0))
 ti = sum(l[2] for l in lines); ts = sum(l[3] for l in lines); tw = sum(l[4] for l in lines)
 print(f"total inst {ti} samples {ts} shared wavefronts {tw} (ideal {sum(l[5] for l in lines)})")
 key = (lambda l: -l[2]) if (len(sys.argv) > 4 and sys.argv[4] == "inst") else (lambda l: -l[3])
