@@ -43,15 +43,43 @@ import numpy as np  # noqa: E402
 METRIC = "column RT solves/sec (IR+solar, RORR)"
 UNIT = "columns/s"
 NCOL_PER_GPU = 4096
-WORKLOAD = ("cfg2: AdiabatClimate OLR-vs-T_surf sweep 200-400 K, 4096 columns per GPU, nz=100 doubled "
-            "(nz_r=202), Z=4, S-canon synthetic tables nw=100 G=16 K=5 (IR 64 bins, solar 64 bins)")
+TABLES = "nz=100 doubled (nz_r=202), Z=4, S-canon synthetic tables nw=100 G=16 K=5 (IR 64 bins, solar 64 bins)"
+# BASELINE.json configs[1], [2], [4]; the column generators are synth.make_columns
+CONFIGS = {
+    "cfg2": dict(name="cfg2: AdiabatClimate OLR-vs-T_surf sweep 200-400 K", ncol=4096, kw={}, albedo=0.25, photon_scale=1.0),
+    "cfg3": dict(name="cfg3: Early Mars CO2-H2O-N2 with CIA, pCO2 x T_surf grid, Mars gravity", ncol=4096,
+                 kw=dict(pco2_range=(1.0e-2, 10 ** 0.5), T_surf_range=(200.0, 320.0), gravity=371.0), albedo=0.2,
+                 photon_scale=0.4286),
+    "cfg5": dict(name="cfg5: cfg2 generator with randomised (log-uniform) composition", ncol=8192,
+                 kw=dict(randomize=True), albedo=0.25, photon_scale=1.0),
+}
 
 
-def make_workload(ncol, rank=0):
+def workload_name(cfg, ncol):
+    return f"{CONFIGS[cfg]['name']}, {ncol} columns per GPU, {TABLES}"
+
+
+def host_cores():
+    """Host threads the CPU arm may use: the affinity mask, NOT omp_get_max_threads() -- torchrun
+    exports OMP_NUM_THREADS=1, which must not shrink the reference arm."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def make_workload(ncol, rank=0, cfg="cfg2"):
     from clima_b200 import synth
+    c = CONFIGS[cfg]
     tb = synth.make_tables()
-    pr = synth.default_params(tb, nzenith=4, albedo=0.25)
-    cols = synth.make_columns(ncol, nz=100, seed=synth.SEED + rank, doubled=True)
+    pr = synth.default_params(tb, nzenith=4, albedo=c["albedo"])
+    pr.photon_scale_factor = c["photon_scale"]
+    kw = dict(c["kw"])
+    if cfg == "cfg3":  # one slice of the 128 x 128 (pCO2, T_surf) grid per rank
+        kw["seed"] = synth.SEED + rank
+    else:
+        kw["seed"] = synth.SEED + rank
+    cols = synth.make_columns(ncol, nz=100, doubled=True, **kw)
     return tb, pr, cols
 
 
@@ -114,8 +142,8 @@ def cpu_port_rate(tb, pr, target_s=12.0, rank_seed=0):
     the same workload.  Returns (columns/s, cores, sample description)."""
     from clima_b200 import synth
     from oracle_lib import OracleRadtran, load
-    lib = load("fast")
-    cores = int(lib.oracle_max_threads())
+    load("fast")
+    cores = host_cores()
     o = OracleRadtran(tb, pr, kind="fast")
     c1 = synth.make_columns(cores, nz=100, seed=synth.SEED + rank_seed)
     t = time.perf_counter()
@@ -137,14 +165,16 @@ def run_reference(args):
         return 0
     from clima_b200 import synth
     from oracle_lib import OracleRadtran, load
-    tb, pr, _ = make_workload(1)
-    lib = load("fast")
-    cores = int(lib.oracle_max_threads())
+    tb, pr, _ = make_workload(1, 0, args.config)
+    load("fast")
+    cores = host_cores()
+    if (os.cpu_count() or 1) > 1 and cores < 2:
+        print("bench.py: reference arm confined to one host core by the affinity mask", file=sys.stderr)
     o = OracleRadtran(tb, pr, kind="fast")
     n = 16 * cores  # bounded sample per step (~2.5 s of the 16-thread port: long enough that thread start-up
     #                 and per-call allocation do not understate the CPU arm; r1r: 59 columns/s at 2 per thread,
     #                 100 columns/s at 40 per thread)
-    cs = synth.make_columns(n, nz=100, seed=synth.SEED)
+    _, _, cs = make_workload(n, 0, args.config)
     for _ in range(args.warmup):
         o.radiate_batch(cs, nthreads=cores)
     t = time.perf_counter()
@@ -157,9 +187,10 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample_columns_per_step": n},
+        "config": {"workload": workload_name(args.config, args.ncol if args.ncol > 0 else CONFIGS[args.config]["ncol"]),
+                   "sample_columns_per_step": n},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{n} columns of the cfg2 sweep per step, OpenMP over columns; C++ "
+                         "sample": f"{n} columns of the {args.config} workload per step, OpenMP over columns ({cores} threads); C++ "
                                    "restatement of the reference algorithm (the Fortran binary cannot be "
                                    "built on this box)"},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -170,6 +201,65 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------
+class DeviceLeg:
+    """Inputs resident in HBM, results into one device block; the step adds the all-gather when world > 1."""
+
+    def __init__(self, rt, cols, tb, dev, world):
+        import torch
+        self.rt, self.cols, self.world = rt, cols, world
+        self.ncol = cols["T"].shape[-1]
+        self.nz, self.ng = cols["nz"], cols["ng"]
+        L = self.nz + 1
+        self.names = ["T_surface", "T", "P", "densities", "dz"]
+        self.host_in = {k: np.ascontiguousarray(cols[k].ravel(order="F")) for k in self.names}
+        self.d_in = {k: torch.from_numpy(self.host_in[k]).to(dev) for k in self.names}
+        self.nres = (5 * L + 2) * self.ncol
+        self.d_res = torch.zeros(self.nres, dtype=torch.float64, device=dev)
+        self.offs, o = {}, 0
+        for k in ["fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol", "f_total"]:
+            self.offs[k] = o; o += L * self.ncol
+        for k in ["ISR", "OLR"]:
+            self.offs[k] = o; o += self.ncol
+        self.outp = {k: self.d_res.data_ptr() + 8 * v for k, v in self.offs.items()}
+        self.inp = {k: self.d_in[k].data_ptr() for k in self.names}
+        self.d_all = torch.zeros(self.nres * world, dtype=torch.float64, device=dev) if world > 1 else None
+        self.ext = torch.cuda.ExternalStream(rt.stream(), device=dev)
+
+    def step(self):
+        import torch
+        import torch.distributed as dist
+        self.rt.radiate_batch_device(self.ncol, self.nz, self.ng, 0, self.inp, self.outp)
+        if self.world > 1:  # return every rank's flux profiles to every rank (NVLink all-gather)
+            with torch.cuda.stream(self.ext):
+                dist.all_gather_into_tensor(self.d_all, self.d_res)
+
+    def timed(self, steps, warmup, barrier, dev, sampler=None):
+        """(ms per step: CUDA events on the launching stream, max over ranks; stage ms; launches; wall s)"""
+        import torch
+        import torch.distributed as dist
+        for _ in range(warmup):
+            self.step()
+        barrier()
+        if sampler:
+            sampler.start()
+        n0 = self.rt.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        stage = np.zeros(6)
+        t_wall = time.perf_counter()
+        e0.record(self.ext)
+        for _ in range(steps):
+            self.step()
+            stage += np.array(self.rt.stage_ms())
+        e1.record(self.ext)
+        barrier()
+        t_wall = time.perf_counter() - t_wall
+        clocks = sampler.stop() if sampler else None
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if self.world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()) / steps, stage / steps, self.rt.launch_count() - n0, t_wall, clocks
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -186,65 +276,23 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
 
-    ncol = args.ncol
-    tb, pr, cols = make_workload(ncol, rank)
-    nz, ng = cols["nz"], cols["ng"]
-    L = nz + 1
-    rt = Radtran(tb, pr, device=local)
-    ext = torch.cuda.ExternalStream(rt.stream(), device=dev)
-
-    # ---- device-resident inputs / outputs (value leg)
-    names = ["T_surface", "T", "P", "densities", "dz"]
-    host_in = {k: np.ascontiguousarray(cols[k].ravel(order="F")) for k in names}
-    d_in = {k: torch.from_numpy(host_in[k]).to(dev) for k in names}
-    nres = (5 * L + 2) * ncol
-    d_res = torch.zeros(nres, dtype=torch.float64, device=dev)
-    offs, o = {}, 0
-    for k in ["fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol", "f_total"]:
-        offs[k] = o; o += L * ncol
-    for k in ["ISR", "OLR"]:
-        offs[k] = o; o += ncol
-    outp = {k: d_res.data_ptr() + 8 * v for k, v in offs.items()}
-    inp = {k: d_in[k].data_ptr() for k in names}
-    d_all = torch.zeros(nres * world, dtype=torch.float64, device=dev) if world > 1 else None
-
-    def step_device():
-        rt.radiate_batch_device(ncol, nz, ng, 0, inp, outp)
-        if world > 1:  # return every rank's flux profiles to every rank (NVLink all-gather)
-            with torch.cuda.stream(ext):
-                dist.all_gather_into_tensor(d_all, d_res)
-
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        step_device()
-    barrier()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    n0 = rt.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    stage = np.zeros(6)
-    t_wall = time.perf_counter()
-    e0.record(ext)
-    for _ in range(args.steps):
-        step_device()
-        stage += np.array(rt.stage_ms())
-    e1.record(ext)
-    barrier()
-    t_wall = time.perf_counter() - t_wall
-    clocks = sampler.stop() if rank == 0 else None
-    launches = rt.launch_count() - n0
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_total = float(ms.item())
-    ms_per_step = ms_total / args.steps
+    cfg = args.config
+    ncol = args.ncol if args.ncol > 0 else CONFIGS[cfg]["ncol"]
+    tb, pr, cols = make_workload(ncol, rank, cfg)
+    nz = cols["nz"]
+    L = nz + 1
+    rt = Radtran(tb, pr, device=local)
+    leg = DeviceLeg(rt, cols, tb, dev, world)
+    names, host_in, offs, nres, d_res = leg.names, leg.host_in, leg.offs, leg.nres, leg.d_res
+    ms_per_step, stage, launches, t_wall, clocks = leg.timed(
+        args.steps, args.warmup, barrier, dev, ClockSampler(local) if rank == 0 else None)
     value = world * ncol / (ms_per_step * 1e-3)
-    stage /= args.steps
+    rorr_stats = rt.rorr_stats()
 
     # ---- e2e leg: host pointers through the C ABI, pinned buffers, H2D + D2H inside the timing
     from clima_b200._abi import alloc_out
@@ -262,7 +310,7 @@ def run_ours(args):
     for k, v in offs.items():
         n = (L * ncol) if k not in ("ISR", "OLR") else ncol
         setattr(o_struct, k, pout[v:v + n].ctypes.data_as(type(o_struct.ISR)))
-    e2e_steps = max(1, min(args.steps, 3))
+    e2e_steps = max(1, args.steps)
     rt.radiate_batch(pcols, out=(o_struct, o_arrs))
     barrier()
     t = time.perf_counter()
@@ -277,6 +325,34 @@ def run_ours(args):
     d2h = int(nres * 8 + 4 * ncol)
     # sanity: host-path result equals the device-path result
     same = bool(np.array_equal(pout, d_res.cpu().numpy()))
+
+    # ---- N > 1: the config north_star names for 8 GPUs (cfg5, 8192 randomised columns per GPU) and a
+    # strong-scaling line (the N=1 batch split over the ranks), same timing rules, fewer steps
+    extra = {}
+    if world > 1 and not args.no_extra:
+        xs, xw = max(2, min(args.steps, 3)), 2
+        del leg
+        tb5, pr5, cols5 = make_workload(CONFIGS["cfg5"]["ncol"], rank, "cfg5")
+        rt5 = Radtran(tb5, pr5, device=local)
+        leg5 = DeviceLeg(rt5, cols5, tb5, dev, world)
+        ms5, st5, _, _, _ = leg5.timed(xs, xw, barrier, dev)
+        extra["cfg5_weak"] = {"workload": workload_name("cfg5", CONFIGS["cfg5"]["ncol"]), "scaling": "weak",
+                              "value": world * CONFIGS["cfg5"]["ncol"] / (ms5 * 1e-3), "unit": UNIT,
+                              "ms_per_step": ms5, "steps": xs, "warmup": xw,
+                              "stage_ms_per_step": {"optics_rorr": st5[0], "kernels_total": st5[4]}}
+        del leg5, rt5, cols5
+        tot = CONFIGS[cfg]["ncol"]
+        per = (tot + world - 1) // world
+        lo, hi = min(rank * per, tot), min((rank + 1) * per, tot)
+        _, _, call = make_workload(tot, 0, cfg)  # the SAME batch on every rank; this rank takes its block
+        sl = {k: (np.asfortranarray(v[..., lo:hi]) if isinstance(v, np.ndarray) and v.shape[-1] == tot else v)
+              for k, v in call.items()}
+        if world * per == tot:
+            legs = DeviceLeg(rt, sl, tb, dev, world)
+            mss, sts, _, _, _ = legs.timed(xs, xw, barrier, dev)
+            extra["strong"] = {"workload": workload_name(cfg, tot) + f" in total, {per} per GPU", "scaling": "strong",
+                               "value": tot / (mss * 1e-3), "unit": UNIT, "ms_per_step": mss, "steps": xs, "warmup": xw,
+                               "stage_ms_per_step": {"optics_rorr": sts[0], "kernels_total": sts[4], "prep": sts[5]}}
 
     if rank == 0:
         d = roofline.dims_of(tb, pr, cols)
@@ -301,7 +377,7 @@ def run_ours(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "columns_per_gpu": ncol, "nz_r": nz, "unique_layers": d.U,
+            "config": {"workload": workload_name(cfg, ncol), "columns_per_gpu": ncol, "nz_r": nz, "unique_layers": d.U,
                        "nw": d.nw, "ngauss": d.G, "n_kgases": d.K, "n_zenith": d.Z,
                        "l2": "per-step working set (tau/w0 of all columns, ~10 GB) is far larger than the 126 MB L2",
                        "sharding": f"columns block-partitioned over {world} rank(s), tables replicated"
@@ -313,7 +389,7 @@ def run_ours(args):
             "stage_ms_per_step": {"optics_rorr": stage[0], "planck_ir": stage[1], "solar": stage[2],
                                   "integrate": stage[3], "kernels_total": stage[4], "prep": stage[5]},
             "wall_ms_per_step": 1e3 * t_wall / args.steps,
-            "rorr": dict(zip(("units", "exact_kernel_units", "worklist_overflows"), rt.rorr_stats())),
+            "rorr": dict(zip(("units", "exact_kernel_units", "worklist_overflows"), rorr_stats)),
             "roofline": {
                 "kernel": "optics_rorr_kernel<16>", "bound": "fp64", "achieved": achieved,
                 "peak": fp64_tf, "unit": "TFLOP/s", "frac": achieved / fp64_tf,
@@ -332,6 +408,8 @@ def run_ours(args):
                 "whole_step_tflops": whole_tf, "whole_step_frac": whole_tf / fp64_tf,
             },
         }
+        if extra:
+            line["extra"] = extra
         if world == 1 and not args.no_cpu:
             v, cores, sample = cpu_port_rate(tb, pr)
             line["cpu_baseline"] = {
@@ -364,7 +442,9 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--ncol", type=int, default=NCOL_PER_GPU, help="columns per GPU")
+    ap.add_argument("--ncol", type=int, default=0, help="columns per GPU (default: the config's)")
+    ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS), help="workload (BASELINE.json configs)")
+    ap.add_argument("--no-extra", action="store_true", help="N>1: skip the cfg5 / strong-scaling legs")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":

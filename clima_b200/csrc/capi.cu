@@ -64,6 +64,11 @@ struct Handle {
   int wcap = 0;
   int *h_wcount = nullptr;  // pinned
   int rorr_exact_only = 0;  // CLIMA_RT_RORR=exact
+  int rorr_sort = 0;        // CLIMA_RT_RORR=sort: the sorting kernels instead of the staircase kernel
+  int rorr_chain_env = -1;  // CLIMA_RT_RORR_CHAIN=slot|col forces the chain direction (0 / 1)
+  int rorr_chain_len = 128; // CLIMA_RT_RORR_CHAIN_LEN: columns per chain (column chains)
+  int rorr_cut_mincols = 1;
+  int last_rorr_kernel = 0; // 0 staircase (slot chains), 1 staircase (column chains), 2 sort, 3 exact
   int64_t rorr_units = 0, rorr_exact_units = 0, rorr_overflows = 0;
 
   // retained state
@@ -200,6 +205,7 @@ void build_tables(Handle &h, const clima_rt_tables *t) {
   d.wbin = upload(h, wb.data(), G);
   d.wbin_e = upload(h, we.data(), G + 1);
   d.inv_dw = upload(h, iw.data(), G);
+  for (int i = 0; i < 32; i++) d.wq[i] = i < G ? wb[i] : 0.0;
   {  // RORR weight table wxy(j + i*P) = wbin(i)*wbin(j) (types_create.f90:216-222), in the kernel's
      // shared-memory layout: P = ngauss padded to 8/16/32, 4 copies per entry, zero padding
     const int P = G <= 8 ? 8 : (G <= 16 ? 16 : 32);
@@ -414,7 +420,13 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     DevTables tbc = h.tb;
     if (!(tbc.pad0 & (4 | 8)) && (long long)dissim * 64 > (long long)ncol) tbc.pad0 |= 4;
     h.last_unit_order = (tbc.pad0 & 4) ? 1 : 0;
-    rt_launch_optics_rorr(tbc, ch, h.d_worklist, h.d_wcount, h.wcap, exact, h.st);
+    // staircase kernel: chains along columns when neighbouring columns are alike, else along the
+    // layer slots of each column; tiny batches keep the sorting kernel (too few chains)
+    int cut_chain = -1;
+    if (!exact && !h.rorr_sort && h.tb.rows_sorted && ncol >= h.rorr_cut_mincols)
+      cut_chain = h.rorr_chain_env >= 0 ? h.rorr_chain_env : ((tbc.pad0 & 4) ? 0 : 1);
+    h.last_rorr_kernel = exact || !h.tb.rows_sorted ? 3 : (cut_chain >= 0 ? cut_chain : 2);
+    rt_launch_optics_rorr(tbc, ch, h.d_worklist, h.d_wcount, h.wcap, exact, cut_chain, h.rorr_chain_len, h.st);
     const bool two = !exact && h.tb.rows_sorted;
     h.launches += two ? 3 : 2;  // continua + fast + exact, or continua + exact
     *h.h_wcount = 0;
@@ -700,6 +712,14 @@ void clima_rt_create(const clima_rt_tables *tables, const clima_rt_params *param
     {
       const char *m = std::getenv("CLIMA_RT_RORR");
       h->rorr_exact_only = (m && std::string(m) == "exact") ? 1 : 0;
+      h->rorr_sort = (m && std::string(m) == "sort") ? 1 : 0;
+      const char *cd = std::getenv("CLIMA_RT_RORR_CHAIN");
+      if (cd && cd[0] == 's') h->rorr_chain_env = 0;
+      if (cd && cd[0] == 'c') h->rorr_chain_env = 1;
+      const char *cl = std::getenv("CLIMA_RT_RORR_CHAIN_LEN");
+      if (cl) h->rorr_chain_len = std::max(1, atoi(cl));
+      const char *mc = std::getenv("CLIMA_RT_RORR_CUT_MINCOLS");
+      if (mc) h->rorr_cut_mincols = std::max(1, atoi(mc));
     }
     {
       const char *cc = std::getenv("CLIMA_RT_CHUNK_COLS");

@@ -11,6 +11,8 @@ void rorr_launch_fast(const DevTables &tb, const DevChunk &ch, int *worklist, in
                       long long units, cudaStream_t st);
 void rorr_launch_exact(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount, int wcap,
                        long long units, cudaStream_t st);
+void rorr_launch_cut(const DevTables &tb, const DevChunk &ch, int mode, int Lc, int *worklist, int *wcount,
+                     int wcap, cudaStream_t st);
 
 namespace {
 
@@ -81,8 +83,10 @@ __global__ void tau_band_kernel(const DevTables tb, const DevChunk ch, int ind_s
 // exact_only != 0: every unit through the 64-bit exact kernel.  Otherwise fast kernel, then the
 // exact kernel over the units the fast kernel could not certify (worklist of capacity wcap; the
 // caller checks *wcount <= wcap afterwards and re-runs with exact_only on overflow).
+// cut_chain >= 0: the sort-free staircase kernel (optics_rorr_cut.cu) instead of the fast sorting
+// kernel; 0 = chains over the layer slots of a column, 1 = chains over cut_len consecutive columns.
 void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
-                           int wcap, int exact_only, cudaStream_t st) {
+                           int wcap, int exact_only, int cut_chain, int cut_len, cudaStream_t st) {
   const long long units = (long long)ch.ncol * tb.nw * ch.nslot_cap;
   // RORR unit ids run over columns rounded up to a multiple of 4 (column-grouped unit order)
   const long long runits = (long long)((ch.ncol + 3) / 4 * 4) * tb.nw * ch.nslot_cap;
@@ -92,7 +96,8 @@ void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, int *worklis
     return;
   }
   cudaMemsetAsync(wcount, 0, sizeof(int), st);
-  rorr_launch_fast(tb, ch, worklist, wcount, wcap, runits, st);
+  if (cut_chain >= 0) rorr_launch_cut(tb, ch, cut_chain, cut_len, worklist, wcount, wcap, st);
+  else rorr_launch_fast(tb, ch, worklist, wcount, wcap, runits, st);
   rorr_launch_exact(tb, ch, worklist, wcount, wcap, wcap, st);
 }
 

@@ -65,6 +65,7 @@ struct DevTables {
   const double *wbin, *wbin_e, *inv_dw;  // (G),(G+1),(G): Ksettings + 1/(wbin_e(g+1)-wbin_e(g))
   const double *c_log10P, *c_dtau, *c_w0, *c_g0;  // custom optical properties (nP),(nP,nw)
   const double *wxy;  // (P*P*4): wbin(i)*wbin(j) at [(i*P+j)*4 + copy], P = padded ngauss, 0 for padding
+  double wq[32];      // wbin by value (zero padded): constant-bank operands of the staircase kernel
 };
 
 // number of bracket records per (col,slot): [k gases: 2 each][cia][pxs][cont][part][custom]

@@ -24,7 +24,7 @@ void rt_launch_prep(const DevTables &tb, const DevChunk &ch, cudaStream_t st);
 void rt_launch_similarity(const DevTables &tb, const DevChunk &ch, cudaStream_t st);
 // optics_rorr.cu
 void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
-                           int wcap, int exact_only, cudaStream_t st);
+                           int wcap, int exact_only, int cut_chain, int cut_len, cudaStream_t st);
 // twostream.cu.  `ocol_bcast`: every column reads the opacity of column 0 (frozen-opacity mode).
 void rt_launch_planck(const DevTables &tb, const DevChunk &ch, const DevFlux &fx, cudaStream_t st);
 void rt_launch_twostream_ir(const DevTables &tb, const DevParams &pr, const DevChunk &ch,
