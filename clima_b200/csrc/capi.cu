@@ -66,8 +66,8 @@ struct Handle {
   int rorr_exact_only = 0;  // CLIMA_RT_RORR=exact
   int rorr_sort = 0;        // CLIMA_RT_RORR=sort: the sorting kernels instead of the staircase kernel
   int rorr_chain_env = -1;  // CLIMA_RT_RORR_CHAIN=slot|col forces the chain direction (0 / 1)
-  int rorr_chain_len = 128; // CLIMA_RT_RORR_CHAIN_LEN: columns per chain (column chains)
-  int rorr_cut_mincols = 1;
+  int rorr_chain_len = 256; // CLIMA_RT_RORR_CHAIN_LEN: columns per chain (column chains)
+  int rorr_cut_mincols = 16;
   int last_rorr_kernel = 0; // 0 staircase (slot chains), 1 staircase (column chains), 2 sort, 3 exact
   int64_t rorr_units = 0, rorr_exact_units = 0, rorr_overflows = 0;
 
@@ -316,6 +316,7 @@ void ensure_chunk(Handle &h, int ncol, int nz) {
   ch.cont = calloc_dev<double>(h, (size_t)3 * C * tb.nw * nz);
   ch.status = calloc_dev<int>(h, C);
   ch.dissim = calloc_dev<int>(h, 1);
+  ch.cut_stats = calloc_dev<unsigned long long>(h, 8);
   {
     const long long units = (long long)((C + 3) / 4 * 4) * tb.nw * nz;
     if (units >= (1ll << 31)) throw CudaError{"chunk too large: lower CLIMA_RT_CHUNK_COLS"};
@@ -420,11 +421,18 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     DevTables tbc = h.tb;
     if (!(tbc.pad0 & (4 | 8)) && (long long)dissim * 64 > (long long)ncol) tbc.pad0 |= 4;
     h.last_unit_order = (tbc.pad0 & 4) ? 1 : 0;
-    // staircase kernel: chains along columns when neighbouring columns are alike, else along the
-    // layer slots of each column; tiny batches keep the sorting kernel (too few chains)
+    // Which RORR kernel.  The sort-free staircase kernel (optics_rorr_cut.cu) carries its staircases
+    // along chains of consecutive COLUMNS and needs ~1.15 passes per merge when neighbouring columns
+    // are alike (a sweep); it breaks even with the sorting kernels at ~1.45 passes (measured r2b: cfg2
+    // at 2048 / 1024 / 512 / 256 columns over 200 K: 22.5 / 23.9 / 28.2 / 37.1 us per column against
+    // 34 us sorted).  Unlike neighbours (randomised composition, cfg3's shuffled pCO2) keep the sorting
+    // kernels: chains over the layer slots of a column need 2.3-2.5 passes per merge (cfg5: 48 vs 36 us).
+    // similarity_kernel's verdict (pad0 bit 2 = unlike) decides; CLIMA_RT_RORR_CHAIN forces a direction.
     int cut_chain = -1;
-    if (!exact && !h.rorr_sort && h.tb.rows_sorted && ncol >= h.rorr_cut_mincols)
-      cut_chain = h.rorr_chain_env >= 0 ? h.rorr_chain_env : ((tbc.pad0 & 4) ? 0 : 1);
+    if (!exact && !h.rorr_sort && h.tb.rows_sorted) {
+      if (h.rorr_chain_env >= 0) cut_chain = h.rorr_chain_env;
+      else if (!(tbc.pad0 & 4) && ncol >= h.rorr_cut_mincols) cut_chain = 1;
+    }
     h.last_rorr_kernel = exact || !h.tb.rows_sorted ? 3 : (cut_chain >= 0 ? cut_chain : 2);
     rt_launch_optics_rorr(tbc, ch, h.d_worklist, h.d_wcount, h.wcap, exact, cut_chain, h.rorr_chain_len, h.st);
     const bool two = !exact && h.tb.rows_sorted;
@@ -877,6 +885,18 @@ void clima_rt_get_rorr_stats(void *handle, int64_t *stats3) {
   stats3[0] = h.rorr_units;
   stats3[1] = h.rorr_exact_units;
   stats3[2] = h.rorr_overflows;
+}
+
+void clima_rt_get_rorr_cut_stats(void *handle, int64_t *stats8) {
+  for (int i = 0; i < 8; i++) stats8[i] = 0;
+  if (!handle) return;
+  Handle &h = *static_cast<Handle *>(handle);
+  if (!h.ch.cut_stats) return;
+  unsigned long long v[8];
+  if (cudaSetDevice(h.device) != cudaSuccess) return;
+  if (cudaMemcpy(v, h.ch.cut_stats, sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return;
+  for (int i = 0; i < 8; i++) stats8[i] = (int64_t)v[i];
+  stats8[5] = h.last_rorr_kernel;
 }
 
 void clima_rt_get_stream(void *handle, void **stream) {

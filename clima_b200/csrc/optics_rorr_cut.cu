@@ -32,6 +32,7 @@
 //
 // What it costs: 4 shared-memory gathers + ~20 instructions per (edge, row) and pass, 15 x 16 pairs
 // per merge, against ~94 instructions per ELEMENT (256 per merge) of the sorting kernel.
+#include <cstdio>
 #include <cstdlib>
 
 #include "rt_device.cuh"
@@ -56,15 +57,26 @@ struct Cfg {
   static constexpr int UPB = CUT_WPB * UPW;  // chains per block
   static constexpr int CWN = P / 4;          // count words (4 rows each) per lane and merge
   static constexpr int ROWU = CUT_ROW_UNROLL;
+  // The pass gathers four numbers by the row's count c in 0..P.  The lanes of a unit (one per edge)
+  // hold non-decreasing counts for a given row, typically a run of 0 (row outside), a few values in
+  // between, and a run of P (row inside): with 8-byte entries c = 0 and c = P fall into the same
+  // banks and nearly every gather took two wavefronts (ncu r2a: x1.8).  Counts are therefore kept as
+  // POSITIONS pos(c) = c for c < P, P + P/2 for c = P: the full row shares its banks with c = P/2.
+  static constexpr int NPOS = P + P / 2 + 1;
   // per-unit tables, in doubles
-  static constexpr int BX = 0;               // [0] = -inf, [1..G] = b, [G+1..2P+1] = +inf
-  static constexpr int SB = 2 * P + 2;       // Sb[0..G]
-  static constexpr int WB = SB + P + 1;      // Wb[0..G]  (static copy per unit: one gather address)
-  static constexpr int AT = WB + P + 1;      // a[0..P-1]
+  static constexpr int BX = 0;               // search table: [0] = -inf, [1..G] = b, [G+1..2P+1] = +inf
+  static constexpr int BM = 2 * P + 2;       // by position: b[c-1]  (-inf for c = 0)
+  static constexpr int BP = BM + NPOS;       //              b[c]    (+inf for c = G)
+  static constexpr int SB = BP + NPOS;       //              Sb[c] = sum_{j<c} w_j b_j
+  static constexpr int WB = SB + NPOS;       //              Wb[c] = sum_{j<c} w_j   (static)
+  static constexpr int AT = WB + NPOS;       // a[0..P-1]
   static constexpr int TT = AT + P;          // scratch: total tau of the unit (band sum)
   static constexpr int UNIT = TT + P;        // doubles per unit
-  static constexpr int NBIS = 13;            // bisection steps of a cold start
+  static constexpr int NBIS = 44;            // cap on the bisection steps of a cold start (a plateau of nearly equal rows needs ~25 to get inside it)
   static constexpr int MAXPASS = 48;         // passes before a restart from bisection / giving up
+  static constexpr int SINGLES = 8;          // single-element moves of a lane before it jumps by tie groups
+  __host__ __device__ static constexpr unsigned pos_of(unsigned c) { return c + ((c >> LOGP) << (LOGP - 1)); }
+  __host__ __device__ static constexpr unsigned cnt_of(unsigned pb) { return pb < (unsigned)P ? pb : (unsigned)P; }
 };
 
 __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -87,86 +99,145 @@ __device__ __forceinline__ void sts_u32(unsigned addr, unsigned v) {
 
 struct PassOut {
   double L, R, W, S;
-  int iL, tagR;  // tagR = row | (count of that row << 8)
+  int iL, iR;  // rows of the largest element inside / the smallest element outside
 };
 
-// One pass over the rows for the lane's staircase (count words at cnt, stride 128 bytes).
+// One pass over the rows for the lane's staircase (position bytes at cnt, 4 rows per word, word
+// stride 128 bytes).  Four rows per trip; inside a trip the extrema and the sums are formed as
+// trees / from zero, so that only one compare-select and one add per trip sit on the loop-carried
+// dependency chains (the pass is latency bound: r2a 56 % issue slots, stall_wait 2.7 per issue).
 template <int P, bool FULL>
 __device__ __forceinline__ PassOut cut_pass(const unsigned ua, const unsigned cnt, const double (&w)[32], const int G) {
   using C = Cfg<P>;
+  const double NINF = __longlong_as_double(0xfff0000000000000ll), PINF = __longlong_as_double(0x7ff0000000000000ll);
   PassOut o;
-  o.L = __longlong_as_double(0xfff0000000000000ll);
-  o.R = __longlong_as_double(0x7ff0000000000000ll);
+  o.L = NINF;
+  o.R = PINF;
   o.W = 0.0;
   o.S = 0.0;
   o.iL = 0;
-  o.tagR = 0;
+  o.iR = 0;
 #pragma unroll(C::ROWU)
   for (int q = 0; q < C::CWN; q++) {
     const unsigned cw = lds_u32(cnt + q * 128u);
+    double lo[4], hi[4], t1[4], wb[4];
 #pragma unroll
     for (int r = 0; r < 4; r++) {
       const int i = 4 * q + r;
-      if (FULL || i < G) {
-        const unsigned c = (cw >> (8 * r)) & 0xffu;
-        const unsigned ad = ua + c * 8u;
-        const double bm = lds_f64(ad + C::BX * 8u), bp = lds_f64(ad + C::BX * 8u + 8u);
-        const double sb = lds_f64(ad + C::SB * 8u), wb = lds_f64(ad + C::WB * 8u);
-        const double ai = lds_f64(ua + (unsigned)(C::AT + i) * 8u);
-        const double lo = __dadd_rn(ai, bm), hi = __dadd_rn(ai, bp);  // :828 tau_xy of the two boundary elements
-        if (lo > o.L) { o.L = lo; o.iL = i; }
-        if (hi < o.R) { o.R = hi; o.tagR = i | (int)(c << 8); }
-        const double t1 = __fma_rn(ai, wb, sb);
-        o.S = __fma_rn(w[i], t1, o.S);  // w[i]: constant-bank operand (DevTables::wq)
-        o.W = __fma_rn(w[i], wb, o.W);
-      }
+      const unsigned pb = (cw >> (8 * r)) & 0xffu;
+      const unsigned ad = ua + pb * 8u;
+      const double bm = lds_f64(ad + C::BM * 8u), bp = lds_f64(ad + C::BP * 8u);
+      const double sb = lds_f64(ad + C::SB * 8u);
+      wb[r] = lds_f64(ad + C::WB * 8u);
+      const double ai = lds_f64(ua + (unsigned)(C::AT + i) * 8u);
+      lo[r] = __dadd_rn(ai, bm);  // :828 tau_xy of the last element inside ...
+      hi[r] = __dadd_rn(ai, bp);  // ... and of the first one outside
+      t1[r] = __fma_rn(ai, wb[r], sb);
+      if (!FULL && i >= G) { lo[r] = NINF; hi[r] = PINF; t1[r] = 0.0; wb[r] = 0.0; }
     }
+    {  // largest inside / smallest outside of the trip (ties: any), then against the running ones
+      const bool p01 = lo[1] > lo[0], p23 = lo[3] > lo[2];
+      const double l01 = p01 ? lo[1] : lo[0], l23 = p23 ? lo[3] : lo[2];
+      const int i01 = p01 ? 1 : 0, i23 = p23 ? 3 : 2;
+      const bool pq = l23 > l01;
+      const double lq = pq ? l23 : l01;
+      const int iq = pq ? i23 : i01;
+      if (lq > o.L) { o.L = lq; o.iL = 4 * q + iq; }
+    }
+    {
+      const bool p01 = hi[1] < hi[0], p23 = hi[3] < hi[2];
+      const double h01 = p01 ? hi[1] : hi[0], h23 = p23 ? hi[3] : hi[2];
+      const int i01 = p01 ? 1 : 0, i23 = p23 ? 3 : 2;
+      const bool pq = h23 < h01;
+      const double hq = pq ? h23 : h01;
+      const int iq = pq ? i23 : i01;
+      if (hq < o.R) { o.R = hq; o.iR = 4 * q + iq; }
+    }
+    // w[i]: constant-bank operands (DevTables::wq)
+    double sq = __dmul_rn(w[4 * q], t1[0]), wq = __dmul_rn(w[4 * q], wb[0]);
+#pragma unroll
+    for (int r = 1; r < 4; r++) {
+      sq = __fma_rn(w[4 * q + r], t1[r], sq);
+      wq = __fma_rn(w[4 * q + r], wb[r], wq);
+    }
+    o.S = __dadd_rn(o.S, sq);
+    o.W = __dadd_rn(o.W, wq);
   }
   return o;
 }
 
-// number of j with b_j < x (bx[k] = b_(k-1), +inf beyond G)
-template <int P>
-__device__ __forceinline__ unsigned count_lt(const unsigned ua, const double x) {
-  unsigned c = 0;
-#pragma unroll
-  for (int s = P; s >= 1; s >>= 1)
-    if (lds_f64(ua + (Cfg<P>::BX + c + s) * 8u) < x) c += s;
-  return c;
+// position byte of row i of the staircase at cnt
+__device__ __forceinline__ unsigned row_pos(const unsigned cnt, const int i) {
+  return (lds_u32(cnt + (unsigned)(i >> 2) * 128u) >> (8 * (i & 3))) & 0xffu;
+}
+__device__ __forceinline__ void row_set(const unsigned cnt, const int i, const unsigned pb) {
+  const unsigned a = cnt + (unsigned)(i >> 2) * 128u;
+  const int sh = 8 * (i & 3);
+  sts_u32(a, (lds_u32(a) & ~(0xffu << sh)) | (pb << sh));
 }
 
-// Cold start: bisection (on the IEEE-754 pattern) for the value of the element that contains edge
-// E, then the staircase of everything below it.  Only an initial guess: cut_pass decides.
-// Out of line and rolled: it runs once per chain (and merge), the pass loop must stay small.
+// Staircase of all elements with a_i + b_j < X (LE: <= X), compared on the rounded sums the pass
+// uses; returns its weight W and the packed positions.  Out of line: repair path only.
 template <int P>
-__device__ __noinline__ void cut_bisect(const unsigned ua, const unsigned cnt, const unsigned swa,
-                                        const int G, const double E) {
+struct Stair {
+  unsigned cw[Cfg<P>::CWN];
+  double W;
+  int n;  // elements inside
+};
+template <int P, bool LE>
+__device__ __noinline__ Stair<P> stair_of(const unsigned ua, const unsigned swa, const int G, const double X) {
   using C = Cfg<P>;
-  long long lo = __double_as_longlong(__dadd_rn(lds_f64(ua + C::AT * 8u), lds_f64(ua + (C::BX + 1) * 8u)));
-  long long hi = __double_as_longlong(__dadd_rn(lds_f64(ua + (unsigned)(C::AT + G - 1) * 8u), lds_f64(ua + (unsigned)(C::BX + G) * 8u)));
-#pragma unroll 1
-  for (int it = 0; it < C::NBIS; it++) {
-    const double t = __longlong_as_double((lo + hi) >> 1);
-    double W = 0.0;
-#pragma unroll 4
-    for (int i = 0; i < G; i++) {
-      const unsigned c = count_lt<P>(ua, __dsub_rn(t, lds_f64(ua + (unsigned)(C::AT + i) * 8u)));
-      W = __fma_rn(lds_f64(swa + (unsigned)i * 8u), lds_f64(ua + (C::WB + c) * 8u), W);
-    }
-    if (W > E) hi = __double_as_longlong(t); else lo = __double_as_longlong(t);
-  }
-  const double t = __longlong_as_double(lo);
+  Stair<P> st;
+  st.W = 0.0;
+  st.n = 0;
 #pragma unroll 1
   for (int q = 0; q < C::CWN; q++) {
     unsigned cw = 0;
 #pragma unroll
     for (int r = 0; r < 4; r++) {
       const int i = 4 * q + r;
-      if (i < G)
-        cw |= count_lt<P>(ua, __dsub_rn(t, lds_f64(ua + (unsigned)(C::AT + i) * 8u))) << (8 * r);
+      if (i < G) {
+        const double ai = lds_f64(ua + (unsigned)(C::AT + i) * 8u);
+        unsigned c = 0;
+#pragma unroll
+        for (int s = P; s >= 1; s >>= 1) {
+          const double v = __dadd_rn(ai, lds_f64(ua + (C::BX + c + s) * 8u));
+          if (LE ? (v <= X) : (v < X)) c += s;
+        }
+        const unsigned pb = C::pos_of(c);
+        cw |= pb << (8 * r);
+        st.n += (int)c;
+        st.W = __fma_rn(lds_f64(swa + (unsigned)i * 8u), lds_f64(ua + (C::WB + pb) * 8u), st.W);
+      }
     }
-    sts_u32(cnt + q * 128u, cw);
+    st.cw[q] = cw;
   }
+  return st;
+}
+template <int P>
+__device__ __forceinline__ void stair_store(const unsigned cnt, const Stair<P> &st) {
+#pragma unroll
+  for (int q = 0; q < Cfg<P>::CWN; q++) sts_u32(cnt + q * 128u, st.cw[q]);
+}
+
+// Cold start: bisection (on the IEEE-754 pattern) for the value of the element that contains edge
+// E, until at most 3 elements lie between the brackets (or NBIS steps), then the staircase of everything below
+// the lower bracket.  Only an initial guess: cut_pass decides.  Out of line and rolled: it runs once
+// per chain (and merge), the pass loop must stay small.
+template <int P>
+__device__ __noinline__ void cut_bisect(const unsigned ua, const unsigned cnt, const unsigned swa,
+                                        const int G, const double E, const double tol) {
+  using C = Cfg<P>;
+  long long lo = __double_as_longlong(__dadd_rn(lds_f64(ua + C::AT * 8u), lds_f64(ua + (C::BX + 1) * 8u)));
+  long long hi = __double_as_longlong(__dadd_rn(lds_f64(ua + (unsigned)(C::AT + G - 1) * 8u), lds_f64(ua + (unsigned)(C::BX + G) * 8u)));
+  int nlo = 0, nhi = G * G;
+#pragma unroll 1
+  for (int it = 0; it < C::NBIS && hi - lo > 1 && nhi - nlo > 3; it++) {
+    const double t = __longlong_as_double(lo + ((hi - lo) >> 1));
+    const Stair<P> st = stair_of<P, false>(ua, swa, G, t);
+    if (st.W > E + tol) { hi = __double_as_longlong(t); nhi = st.n; } else { lo = __double_as_longlong(t); nlo = st.n; }
+  }
+  stair_store<P>(cnt, stair_of<P, false>(ua, swa, G, __longlong_as_double(lo)));
 }
 
 // k(g) * column amount of k-gas jj for one unit: bilinear log10k(P,T) interpolation, lane per
@@ -175,25 +246,37 @@ __device__ __noinline__ void cut_bisect(const unsigned ua, const unsigned cnt, c
 struct KRaw {
   double f0, f1, f2, f3, q1, q2, col;
 };
-__device__ __forceinline__ KRaw kgas_load(const DevTables &tb, const DevChunk &ch, const int c, const int l,
-                                          const int slot, const int k, const int jj, const int g) {
-  const int G = tb.G, nz = ch.nz;
-  const int nbr = rt_nbr(tb);
-  const int *ib = ch.ibr + ((size_t)c * nz + slot) * nbr;
-  const double *qb = ch.qbr + ((size_t)c * nz + slot) * nbr;
+struct UnitIn {  // per-unit bases of the k-gas inputs (64-bit address arithmetic once per unit, not per gas)
+  const int *ib;
+  const double *qb, *dens;
+  double dz;
+};
+__device__ __forceinline__ UnitIn unit_in(const DevTables &tb, const DevChunk &ch, const int c, const int slot, const int k) {
+  const int nz = ch.nz;
+  const size_t rec = ((size_t)c * nz + slot) * rt_nbr(tb);
+  UnitIn u;
+  u.ib = ch.ibr + rec;
+  u.qb = ch.qbr + rec;
+  u.dens = ch.dens + (size_t)c * nz * tb.ng + k;
+  u.dz = ch.dz[(size_t)c * nz + k];
+  return u;
+}
+__device__ __forceinline__ KRaw kgas_load(const DevTables &tb, const UnitIn &u, const int nz, const int l,
+                                          const int jj, const int g) {
+  const int G = tb.G;
   const DevK &kt = tb.k[jj];
-  const int ix = ib[2 * jj], iy = ib[2 * jj + 1];
+  const int ix = u.ib[2 * jj], iy = u.ib[2 * jj + 1];
   KRaw r;
-  r.q1 = qb[2 * jj];
-  r.q2 = qb[2 * jj + 1];
-  r.col = ch.dens[(size_t)c * nz * tb.ng + k + (size_t)(kt.sp - 1) * nz] * ch.dz[(size_t)c * nz + k];  // cols(j,sp) :607
-  const double *f = kt.log10k + (size_t)G * (ix + (size_t)kt.np * (iy + (size_t)kt.nt * l));
-  const size_t sy = (size_t)G * kt.np;
+  r.q1 = u.qb[2 * jj];
+  r.q2 = u.qb[2 * jj + 1];
+  r.col = u.dens[(unsigned)((kt.sp - 1) * nz)] * u.dz;  // cols(j,sp) :607
   const int gc = g < G ? g : G - 1;
-  r.f0 = f[gc];
-  r.f1 = f[gc + G];
-  r.f2 = f[gc + sy];
-  r.f3 = f[gc + sy + G];
+  const int sy = G * kt.np;
+  const double *f = kt.log10k + (unsigned)(G * (ix + kt.np * (iy + kt.nt * l)) + gc);
+  r.f0 = f[0];
+  r.f1 = f[G];
+  r.f2 = f[sy];
+  r.f3 = f[sy + G];
   return r;
 }
 __device__ __forceinline__ double kgas_finish(const KRaw &r, const bool live) {
@@ -231,14 +314,18 @@ rorr_cut_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ De
 
   // ---- static parts of the unit tables and of the staircases
   if (threadIdx.x < 32) s_w[threadIdx.x] = threadIdx.x < G ? tb.wbin[threadIdx.x] : 0.0;
-  for (int i = ul; i < C::UNIT; i += P) {
-    double v = 0.0;
-    if (i < C::SB) v = (i == 0) ? __longlong_as_double(0xfff0000000000000ll) : __longlong_as_double(0x7ff0000000000000ll);
-    else if (i >= C::WB && i < C::AT) v = tb.wbin_e[(i - C::WB) < G ? (i - C::WB) : G];
-    ut[i] = v;
-  }
   {
-    const unsigned full = (unsigned)G * 0x01010101u;
+    const double NINF = __longlong_as_double(0xfff0000000000000ll), PINF = __longlong_as_double(0x7ff0000000000000ll);
+    for (int i = ul; i < C::UNIT; i += P) {
+      double v = 0.0;
+      if (i < C::BM) v = (i == 0) ? NINF : PINF;                  // search table sentinels
+      else if (i < C::BP) v = NINF;                               // b[c-1]: position 0 stays -inf
+      else if (i < C::SB) v = PINF;                               // b[c]: position of c = G stays +inf
+      ut[i] = v;
+    }
+    __syncwarp();
+    for (int c = ul; c <= G; c += P) ut[C::WB + C::pos_of((unsigned)c)] = tb.wbin_e[c];
+    const unsigned full = C::pos_of((unsigned)G) * 0x01010101u;
     for (int m = 0; m < nk - 1; m++)
       for (int q = 0; q < C::CWN; q++) {
         unsigned wq = 0;
@@ -281,6 +368,8 @@ rorr_cut_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ De
   }
   if (__all_sync(0xffffffffu, !chain_ok)) return;
 
+  unsigned need_cold = 0xffffffffu;  // merges whose staircases have not been initialised yet (bit jj)
+  unsigned st_merges = 0, st_passes = 0, st_restarts = 0, st_fail = 0, st_cold = 0, st_closed = 0;
   for (int n = 0; n < len; n++) {
     bool active = chain_ok;
     int us = slot;  // the unit's slot
@@ -295,13 +384,13 @@ rorr_cut_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ De
     const size_t obase = (((size_t)c * nw + l) * cap + us);
     const size_t U = (size_t)ch.ncol * nw * cap;
     const double q_s3 = ch.cont[obase], q_tauc = ch.cont[U + obase], q_sc = ch.cont[2 * U + obase];
-    const bool cold = (n == 0);
     bool unit_ok = true;
 
-    KRaw raw = kgas_load(tb, ch, c, l, us, k, 0, ul);
+    const UnitIn uin = unit_in(tb, ch, c, us, k);
+    KRaw raw = kgas_load(tb, uin, nz, l, 0, ul);
     for (int jj = 0; jj < nk; jj++) {
       const double v = kgas_finish(raw, live);
-      if (jj + 1 < nk) raw = kgas_load(tb, ch, c, l, us, k, jj + 1, ul);
+      if (jj + 1 < nk) raw = kgas_load(tb, uin, nz, l, jj + 1, ul);
       if (jj == 0) {
         if (live) sts_f64(ua + (unsigned)(C::AT + ul) * 8u, v);  // tau_k(:,g) = k_1 * col_1  :816-819
         __syncwarp();
@@ -315,41 +404,102 @@ rorr_cut_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ De
         if (ul >= d) s = __dadd_rn(s, t);
       }
       if (live) {
+        const unsigned p1 = C::pos_of((unsigned)ul + 1u);
         sts_f64(ua + (unsigned)(C::BX + 1 + ul) * 8u, v);
-        sts_f64(ua + (unsigned)(C::SB + 1 + ul) * 8u, s);
+        sts_f64(ua + (unsigned)(C::BP + ul) * 8u, v);  // pos_of(ul) = ul
+        sts_f64(ua + (C::BM + p1) * 8u, v);
+        sts_f64(ua + (C::SB + p1) * 8u, s);
       }
       __syncwarp();
+      // ---- merges that need no staircase.  If the rows do not interleave (a_i + b_G <= a_i+1 + b_1
+      // for every i) the sorted order is the row-major index order, row i covers exactly the
+      // cumulative-weight interval of new bin i, and the rebin (:843-849) returns
+      // a_i + sum_j w_j b_j = a_i + <b>; symmetrically b_j + <a> when the columns do not interleave.
+      // The decision is per unit (a qualifying unit takes the closed form also when its warp evaluates
+      // staircases for its other unit); the unit's staircases are left as they are for its successor.
+      bool triv;
+      double cf = 0.0;
+      {
+        const unsigned gn = (ul + 1 < G) ? ul + 1 : ul;
+        const double a1 = lds_f64(ua + C::AT * 8u), aG = lds_f64(ua + (unsigned)(C::AT + G - 1) * 8u);
+        const double am = lds_f64(ua + (unsigned)(C::AT + ul) * 8u), an = lds_f64(ua + (C::AT + gn) * 8u);
+        const double b1 = lds_f64(ua + (C::BX + 1) * 8u), bG = lds_f64(ua + (unsigned)(C::BX + G) * 8u);
+        const double bn = lds_f64(ua + (C::BX + 1 + gn) * 8u);
+        const bool rowsep = !(ul < G - 1) || (__dadd_rn(am, bG) <= __dadd_rn(an, b1));
+        const bool colsep = !(ul < G - 1) || (__dadd_rn(v, aG) <= __dadd_rn(bn, a1));
+        const unsigned br = __ballot_sync(0xffffffffu, rowsep), bc = __ballot_sync(0xffffffffu, colsep);
+        const bool urow = (br & umask) == umask, ucol = (bc & umask) == umask;
+        triv = !(tb.pad0 & 1) && (urow || ucol);
+        if (__any_sync(0xffffffffu, triv)) {
+          const double bmean = lds_f64(ua + (C::SB + C::pos_of((unsigned)G)) * 8u);  // <b> = Sb[G]
+          double amean = __dmul_rn(wl, am);  // <a>, summed like Sb
+#pragma unroll
+          for (int d = 1; d < P; d <<= 1) {
+            const double t = __shfl_up_sync(0xffffffffu, amean, d, P);
+            if (ul >= d) amean = __dadd_rn(amean, t);
+          }
+          amean = __shfl_sync(0xffffffffu, amean, G - 1, P);
+          cf = urow ? __dadd_rn(am, bmean) : __dadd_rn(v, amean);
+        }
+      }
+      if (__all_sync(0xffffffffu, triv)) {
+        __syncwarp();
+        if (live) sts_f64(ua + (unsigned)(C::AT + ul) * 8u, cf);
+        __syncwarp();
+        st_closed++;
+        continue;
+      }
       const unsigned cntm = cnt0 + (unsigned)((jj - 1) * C::CWN) * 128u;
-      if (cold && isEdge) cut_bisect<P>(ua, cntm, swa, G, E);
+      const bool cold = (need_cold >> jj) & 1u;
+      if (cold) {
+        if (isEdge) cut_bisect<P>(ua, cntm, swa, G, E, TOL);
+        need_cold &= ~(1u << jj);
+        st_cold++;
+      }
+      st_merges++;
       // ---- evaluate / repair the staircases
       PassOut o;
-      bool ok;
-      int passes = 0;
+      bool ok, tie_ok = false;
+      int passes = 0, moves = 0;
       bool restarted = false;
       while (true) {
         o = cut_pass<P, FULL>(ua, cntm, tb.wq, G);
-        const int iR = o.tagR & 0xff, cR = o.tagR >> 8;
-        const double we = __dmul_rn(s_w[iR], s_w[cR < G ? cR : G - 1]);  // weight of the element that would come next
+        st_passes++;
+        const unsigned pbR = row_pos(cntm, o.iR);
+        const double we = __dmul_rn(s_w[o.iR], s_w[pbR < (unsigned)G ? pbR : G - 1]);  // weight of the element that would come next
         const bool inv = o.L > o.R;
         const bool over = o.W > E + TOL;
-        const bool under = E >= __dadd_rn(o.W, we) + TOL;
-        ok = !isEdge || !(inv || over || under);
+        const bool under = E >= __dadd_rn(o.W, we) - TOL;  // an edge AT an element boundary belongs to the staircase that ends there
+        ok = !isEdge || tie_ok || triv || !(inv || over || under);
         if (__all_sync(0xffffffffu, ok)) break;
         if (++passes >= C::MAXPASS) {
           if (restarted) break;
           restarted = true;
+          st_restarts++;
           passes = 0;
-          if (!ok) cut_bisect<P>(ua, cntm, swa, G, E);
+          if (!ok) cut_bisect<P>(ua, cntm, swa, G, E, TOL);
           continue;
         }
         if (!ok) {
-          if (inv || over) {  // drop the largest element inside
-            const unsigned a = cntm + (unsigned)(o.iL >> 2) * 128u;
-            sts_u32(a, lds_u32(a) - (1u << (8 * (o.iL & 3))));
+          // single-element moves first (the staircase of the chain predecessor is a few elements
+          // off); a lane that keeps moving is inside a group of tied sums and jumps by groups
+          const bool single = moves++ < C::SINGLES;
+          if (inv || (single && over)) {  // drop the largest element inside
+            const unsigned pbL = row_pos(cntm, o.iL);
+            row_set(cntm, o.iL, C::pos_of(C::cnt_of(pbL) - 1u));
           }
-          if (inv || (!over && under)) {  // take the smallest element outside
-            const unsigned a = cntm + (unsigned)(iR >> 2) * 128u;
-            sts_u32(a, lds_u32(a) + (1u << (8 * (iR & 3))));
+          if (inv || (single && !over && under)) {  // take the smallest element outside
+            row_set(cntm, o.iR, C::pos_of(C::cnt_of(row_pos(cntm, o.iR)) + 1u));
+          }
+          if (!inv && !single) {
+            if (over) {  // drop the largest element inside and everything tied with it
+              stair_store<P>(cntm, stair_of<P, false>(ua, swa, G, o.L));
+            } else {  // take the next element and everything tied with it ...
+              const Stair<P> st = stair_of<P, true>(ua, swa, G, o.R);
+              // ... unless the edge falls INSIDE that tie group: every element between the staircase
+              // and the edge then has the value R, and I(E) = S + R (E - W) holds as it stands
+              if (E < st.W - TOL) tie_ok = true; else stair_store<P>(cntm, st);
+            }
           }
         }
       }
@@ -357,11 +507,18 @@ rorr_cut_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ De
         const unsigned bal = __ballot_sync(0xffffffffu, ok);
         unit_ok = unit_ok && ((bal & umask) == umask);
       }
+#ifdef CUT_DEBUG
+      if (!ok && atomicAdd(ch.cut_stats + 7, 1ull) < 4ull) {
+        printf("FAIL c=%d l=%d slot=%d jj=%d edge=%d E=%.17g L=%.17g iL=%d R=%.17g iR=%d W=%.17g S=%.17g\n", c, l, us, jj, ul, E, o.L, o.iL, o.R, o.iR, o.W, o.S);
+        for (int i = 0; i < G; i++)
+          printf("  e%d row %2d a=%.17g b=%.17g pos=%u\n", ul, i, lds_f64(ua + (unsigned)(C::AT + i) * 8u), lds_f64(ua + (unsigned)(C::BX + 1 + i) * 8u), row_pos(cntm, i));
+      }
+#endif
       // I(E) at the lane's edge, then the rebinned bin (:847): (I(E_g+1) - I(E_g)) / (E_g+1 - E_g)
       const double I = isTot ? o.S : __fma_rn(o.R, __dsub_rn(E, o.W), o.S);
       double Iprev = __shfl_up_sync(0xffffffffu, I, 1, P);
       if (ul == 0) Iprev = 0.0;
-      const double na = __dmul_rn(__dsub_rn(I, Iprev), idw);
+      const double na = triv ? cf : __dmul_rn(__dsub_rn(I, Iprev), idw);
       __syncwarp();  // every lane is done reading a
       if (live) sts_f64(ua + (unsigned)(C::AT + ul) * 8u, na);
       __syncwarp();
@@ -392,8 +549,20 @@ rorr_cut_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ De
                                          : ((((unsigned)c >> 2) * (unsigned)nw + (unsigned)l) * (unsigned)cap + (unsigned)us) * 4u + ((unsigned)c & 3u);
       const int p = atomicAdd(wcount, 1);
       if (p < wcap) worklist[p] = (int)uid;
+      st_fail++;
     }
     __syncwarp();
+  }
+  if (ch.cut_stats) {
+    st_fail = __reduce_add_sync(0xffffffffu, st_fail);
+    if (lane == 0) {
+      atomicAdd(ch.cut_stats + 0, (unsigned long long)st_merges);
+      atomicAdd(ch.cut_stats + 1, (unsigned long long)st_passes);
+      if (st_restarts) atomicAdd(ch.cut_stats + 2, (unsigned long long)st_restarts);
+      if (st_fail) atomicAdd(ch.cut_stats + 3, (unsigned long long)st_fail);
+      atomicAdd(ch.cut_stats + 4, (unsigned long long)st_cold);
+      if (st_closed) atomicAdd(ch.cut_stats + 6, (unsigned long long)st_closed);
+    }
   }
 }
 

@@ -99,6 +99,9 @@ struct DevChunk {
   // [0]: groups of 4 adjacent columns whose k-gas amounts differ (counted by similarity_kernel);
   // the RORR kernels choose their unit order from it
   int *dissim;
+  // staircase RORR kernel bookkeeping (accumulates over calls): [0] warp-merges, [1] warp-passes,
+  // [2] restarts from bisection, [3] units handed to the exact kernel, [4] cold starts (warp-merges)
+  unsigned long long *cut_stats;
 };
 
 // ---- small device helpers shared by kernels -------------------------------------------------

@@ -31,6 +31,69 @@ class LoaderError(Exception):
     """The reference returns `err` strings from these routines; the packer raises them."""
 
 
+# ----------------------------------------------------------------------------- atmosphere files
+K_BOLTZ = 1.380649e-16  # erg/K, src/clima_const.f90:10
+
+
+def read_atmosphere_file(path: str) -> Tuple[Sequence[str], np.ndarray]:
+    """`AtmosphereFile` (src/clima_types_create.f90: create_AtmosphereFile): a header line of column
+    labels, then one row per level.  Returns (labels, columns[nlabels, nz])."""
+    with open(path) as f:
+        lines = [ln for ln in f.read().splitlines() if ln.strip()]
+    labels = lines[0].split()
+    rows = [[float(x) for x in ln.split()] for ln in lines[1:]]
+    if any(len(r) != len(labels) for r in rows):
+        raise LoaderError(f'Number of columns is not consistent in "{path}"')
+    return labels, np.asarray(rows, dtype=np.float64).T.copy()
+
+
+def vertical_grid(bottom: float, top: float, nz: int) -> Tuple[np.ndarray, np.ndarray]:
+    """src/clima_eqns.f90:172-184: uniform layers, z at the layer centres (cm)."""
+    dz = np.full(nz, (top - bottom) / nz)
+    z = np.empty(nz)
+    z[0] = dz[0] / 2.0
+    for i in range(1, nz):
+        z[i] = z[i - 1] + dz[i]
+    return z, dz
+
+
+def unpack_atmospherefile(labels: Sequence[str], columns: np.ndarray, species_names: Sequence[str],
+                          z: np.ndarray, filename: str = "atmosphere.txt"):
+    """src/clima_types_create.f90:424-514: log10(mixing ratio), temperature and log10(pressure) of the
+    file interpolated linearly in altitude (file `alt` is in km) onto the layer centres z (cm).
+    futils `interp` is restated as linear interpolation that holds the end values outside the file's
+    range (immaterial for the ModernEarth template: its 200 levels ARE vertical_grid(0, 1e7, 200))."""
+    labels = list(labels)
+    if "alt" not in labels:
+        raise LoaderError(f'"alt" was not found in input file "{filename}"')
+    alt = columns[labels.index("alt")] * 1.0e5
+    mix = np.empty((len(z), len(species_names)), order="F")
+    for i, sp in enumerate(species_names):
+        if sp not in labels:
+            raise LoaderError(f'Species "{sp}" was not found in "{filename}"')
+        mix[:, i] = 10.0 ** np.interp(z, alt, np.log10(columns[labels.index(sp)]))
+    if not np.all(np.isclose(mix.sum(1), 1.0, rtol=1.0e-2, atol=0.0)):
+        raise LoaderError(f'mixing ratios do not sum to close to 1 in "{filename}"')
+    for need in ("temp", "press"):
+        if need not in labels:
+            raise LoaderError(f'"{need}" was not found in input file "{filename}"')
+    T = np.interp(z, alt, columns[labels.index("temp")])
+    P = 10.0 ** np.interp(z, alt, np.log10(columns[labels.index("press")]))
+    return mix, T, P
+
+
+def column_from_atmosphere(labels, columns, species_names, nz: int, top: float = 1.0e7) -> Dict:
+    """The single column of tests/test_radtran.f90:44-58: vertical_grid(0, top, nz), the file unpacked
+    onto it, number densities P*1e6/(k T) times the mixing ratios.  Returns the `cols` dict of
+    Radtran.radiate_batch with ncol = 1 (ground-first)."""
+    z, dz = vertical_grid(0.0, top, nz)
+    mix, T, P = unpack_atmospherefile(labels, columns, species_names, z)
+    density = (P * 1.0e6) / (K_BOLTZ * T)
+    dens = np.asfortranarray((mix * density[:, None])[:, :, None])
+    return dict(nz=nz, ng=len(species_names), np=0, ncol=1, T_surface=np.array([T[0]]), T=np.asfortranarray(T[:, None]),
+                P=np.asfortranarray(P[:, None]), densities=dens, dz=np.asfortranarray(dz[:, None]))
+
+
 # ----------------------------------------------------------------------------- futils: addpnt, inter2
 def addpnt(x: np.ndarray, y: np.ndarray, n: int, xnew: float, ynew: float) -> int:
     """Insert (xnew, ynew) into the ascending grid x[:n] (arrays have spare capacity); returns n+1.

@@ -28,7 +28,7 @@ EXPORTS = ["clima_rt_create", "clima_rt_destroy", "clima_rt_set_params",
            "clima_rt_set_custom_optical_properties", "clima_rt_unset_custom_optical_properties",
            "clima_rt_radiate_batch", "clima_rt_radiate_batch_device", "clima_rt_jacobian_batch",
            "clima_rt_get_opacity",
-           "clima_rt_get_launch_count", "clima_rt_get_stage_ms", "clima_rt_get_stream", "clima_rt_get_rorr_stats", "clima_rt_measure_fp64_peak",
+           "clima_rt_get_launch_count", "clima_rt_get_stage_ms", "clima_rt_get_stream", "clima_rt_get_rorr_stats", "clima_rt_get_rorr_cut_stats", "clima_rt_measure_fp64_peak",
            "clima_rt_version_get"]
 
 
@@ -290,6 +290,14 @@ class Radtran:
         a = (C.c_int64 * 3)()
         self._lib.clima_rt_get_rorr_stats(self._h, a)
         return tuple(a)
+
+    def rorr_cut_stats(self):
+        """dict of the staircase-kernel counters (clima_rt_get_rorr_cut_stats)."""
+        a = (C.c_int64 * 8)()
+        self._lib.clima_rt_get_rorr_cut_stats(self._h, a)
+        k = ("warp_merges", "warp_passes", "restarts", "units_to_exact", "cold_warp_merges", "last_kernel",
+             "closed_form_warp_merges")
+        return dict(zip(k, list(a)[:7]))
 
     def stage_ms(self):
         a = (C.c_double * 6)()

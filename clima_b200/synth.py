@@ -54,7 +54,7 @@ def make_tables(nw=100, G=16, nk=5, ncia=10, nray=5, npxs=3, cont=True, npart=0,
     weights = gauss_weights(G)
     gq = np.cumsum(weights) - 0.5 * weights  # g at bin centres
 
-    k_species = ["H2O", "CO2", "CH4", "CO", "O2"][:nk]
+    k_species = [n for n in ["H2O", "CO2", "CH4", "CO", "O2", "O3"] if n in species][:nk]
     ktabs = []
     for i, name in enumerate(k_species):
         # per-gas grids differ a little so the per-table clamps are exercised
@@ -64,7 +64,7 @@ def make_tables(nw=100, G=16, nk=5, ncia=10, nray=5, npxs=3, cont=True, npart=0,
         nb = 6
         centres = rng.uniform(x.min(), x.max(), nb)
         widths = rng.uniform(0.08, 0.35, nb)
-        amp_max = {"H2O": 7.0, "CO2": 7.5, "CH4": 8.0, "CO": 8.0, "O2": 3.5}[name]
+        amp_max = {"H2O": 7.0, "CO2": 7.5, "CH4": 8.0, "CO": 8.0, "O2": 3.5, "O3": 7.0}[name]
         amps = rng.uniform(2.0, amp_max, nb)
         band = np.full(nw, -28.5 + rng.uniform(-0.5, 0.5))
         for c, wd, a in zip(centres, widths, amps):

@@ -242,6 +242,15 @@ void clima_rt_get_stage_ms(void *handle, double *ms6);
    fast kernel could not certify), [2] worklist overflows (whole chunk redone exactly). */
 void clima_rt_get_rorr_stats(void *handle, int64_t *stats3);
 
+/* Bookkeeping of the sort-free (staircase) RORR kernel since the chunk buffers were allocated:
+   [0] warp-merges (one merge of the 32/P units of a warp), [1] warp-passes over the rows (1 per merge
+   when the predecessor's staircases are still the right ones), [2] restarts from bisection,
+   [3] units handed to the exact sorting kernel, [4] cold starts (warp-merges at the head of a chain),
+   [5] RORR kernel of the last chunk: 0 staircase/slot chains, 1 staircase/column chains, 2 sorting
+   kernels, 3 exact sorting kernel only.  [6] warp-merges that took the closed form (rows or columns
+   of a_i + b_j do not interleave).  [7] reserved. */
+void clima_rt_get_rorr_cut_stats(void *handle, int64_t *stats8);
+
 /* The CUDA stream (a cudaStream_t, returned as an opaque pointer) every kernel of the handle is
    launched on, so that a caller can bracket calls with its own CUDA events on the launching
    stream or order its own work (e.g. an NCCL all-gather of the flux profiles) after them. */

@@ -61,3 +61,29 @@ def compare(r_gpu, r_ref, spectral=True, tol=TOL, verbose=False, elem_tol=None):
     bad = {k: v for k, v in worst.items() if not (v <= (etol if k.endswith('_elem') else tol))}
     assert not bad, f"parity failure (tol {tol}): {bad}"
     return worst
+
+
+def cfg1_template_case():
+    """BASELINE.json configs[0]: the ModernEarth template column of the reference's own test
+    (/root/reference/tests/test_radtran.f90:33-65): atmosphere.txt on vertical_grid(0, 1e7, 200),
+    optical-properties species of templates/ModernEarth/settings.yaml, 8 zenith angles, surface albedo
+    0.15, the Sun_now.txt spectrum.  The k-tables / CIA / continuum are S-canon SYNTHETIC tables (the
+    photochem_clima_data files are not on this box); the template data come from the fixture written by
+    tests/golden/make_cfg1_template.py."""
+    import os
+    from clima_b200 import loader
+    fx = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "cfg1_modern_earth.npz"))
+    species = ["H2O", "CO2", "O2", "N2", "O3", "CH4"]  # settings.yaml optical-properties: species: gases
+    tb = synth.make_tables(species=species)
+    assert np.array_equal(tb.wavl, fx["wavl"])
+    tb.photons_sol = np.ascontiguousarray(fx["stellar_flux_on_scanon_grid"][tb.sol_ind[0] - 1:tb.sol_ind[1]])
+    pr = synth.default_params(tb, nzenith=8, albedo=0.15)
+    cols = loader.column_from_atmosphere([str(x) for x in fx["labels"]], fx["columns"], species, nz=200)
+    return tb, pr, cols
+
+
+def rayleigh_dominated_case(nz=12, ncol=1, seed=3):
+    """Solar-resonance probe (clima_radtran_twostream.f90:80, `denom = lambda**2 - 1/u0**2`, no guard):
+    small tables in which UV bins are Rayleigh dominated (w0 up to max_w0, g = 0), one zenith angle."""
+    tb, pr, cols = small_case(G=16, nw=10, nz=nz, ncol=ncol, nk=3, nzen=1, seed=seed, doubled=False)
+    return tb, pr, cols

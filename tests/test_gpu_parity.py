@@ -10,6 +10,46 @@ from oracle_lib import OracleRadtran
 
 pytestmark = pytest.mark.gpu
 
+# Tests of the SORTING RORR kernels (rorr_impl.cuh: quantised keys, certificate, worklist, closed-form
+# merges, unit order).  The default RORR path is the sort-free staircase kernel (optics_rorr_cut.cu);
+# these select the sorting kernels with CLIMA_RT_RORR=sort.
+SORT_KERNEL_TESTS = {
+    "test_rorr_fast_path_is_bit_identical_to_exact_path", "test_rorr_near_ties_go_through_the_exact_kernel",
+    "test_rorr_worklist_overflow_falls_back_to_exact", "test_rorr_closed_form_merges_match_the_sorted_path",
+    "test_bit_reproducible_with_worklist_and_closed_form_merges", "test_rorr_general_walk_matches_the_single_edge_walk",
+    "test_full_size_fast_keys_match_exact_kernel", "test_rorr_unit_order_does_not_change_results",
+}
+
+
+@pytest.fixture(autouse=True)
+def _rorr_flavour(request, monkeypatch):
+    if request.node.name.split("[")[0] in SORT_KERNEL_TESTS:
+        monkeypatch.setenv("CLIMA_RT_RORR", "sort")
+    yield
+
+
+def _same(a, b, bitwise, tol=1e-12):
+    """Results of one column computed in different batches: bit-identical with the sorting kernels; the
+    staircase kernel starts a unit from the staircases of its chain predecessor, and where sums tie
+    exactly ANY staircase through the tie group is a valid sorted prefix (same integral, different
+    summation order), so a column's result depends on its neighbours at the rounding level."""
+    if bitwise:
+        return np.array_equal(a, b)
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    s = np.max(np.abs(b)) if b.size else 0.0
+    return bool(np.all(np.abs(a - b) <= tol * max(s, 1e-300)))
+
+
+FLAVOURS = pytest.mark.parametrize("flavour", ["cut", "sort"])
+
+
+def _set_flavour(monkeypatch, flavour):
+    if flavour == "sort":
+        monkeypatch.setenv("CLIMA_RT_RORR", "sort")
+    else:  # the staircase kernel also for batches smaller than its automatic threshold
+        monkeypatch.delenv("CLIMA_RT_RORR", raising=False)
+        monkeypatch.setenv("CLIMA_RT_RORR_CHAIN", "col")
+
 
 def run_both(tb, pr, cols, spectral=True, **kw):
     g = Radtran(tb, pr)
@@ -190,14 +230,17 @@ def test_same_batch_frozen_opacity():
         assert np.array_equal(r1[k], r2[k])
 
 
-def test_single_column_api_matches_batch():
+@FLAVOURS
+def test_single_column_api_matches_batch(flavour, monkeypatch):
+    _set_flavour(monkeypatch, flavour)
     tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=2)
     g = Radtran(tb, pr)
     rb = g.radiate_batch(cols)
     isr, olr = g.TOA_fluxes(cols["T_surface"][1], cols["T"][:, 1], cols["P"][:, 1],
                             cols["densities"][:, :, 1], cols["dz"][:, 1])
-    assert isr == rb["ISR"][1] and olr == rb["OLR"][1]
-    assert np.array_equal(g.f_total, rb["f_total"][:, 1])
+    bw = flavour == "sort"
+    assert _same(isr, rb["ISR"][1], bw) and _same(olr, rb["OLR"][1], bw)
+    assert _same(g.f_total, rb["f_total"][:, 1], bw)
     assert g.wrk_ir.fup_a.shape == (cols["nz"] + 1, tb.nw_ir)
 
 
@@ -212,13 +255,15 @@ def test_error_convention():
         Radtran(tb, pr).radiate_batch(cols, compute_opacity=False)
 
 
-def test_chunking_is_transparent(monkeypatch):
+@FLAVOURS
+def test_chunking_is_transparent(flavour, monkeypatch):
+    _set_flavour(monkeypatch, flavour)
     tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=7)
     r1 = Radtran(tb, pr).radiate_batch(cols, spectral=True)
     monkeypatch.setenv("CLIMA_RT_CHUNK_COLS", "3")
     r2 = Radtran(tb, pr).radiate_batch(cols, spectral=True)
     for k in r1:
-        assert np.array_equal(r1[k], r2[k]), k
+        assert _same(r1[k], r2[k], flavour == "sort"), k
 
 
 def test_bit_reproducible():
@@ -326,20 +371,23 @@ def test_rorr_closed_form_merges_match_the_sorted_path(monkeypatch):
     compare(r1, OracleRadtran(tb, pr).radiate_batch(cols, spectral=True))
 
 
-def test_sharded_matches_single():
+@FLAVOURS
+def test_sharded_matches_single(flavour, monkeypatch):
     """clima_b200/shard.py with the production compute callable: the blocks of a 2-way partition,
     computed one after the other on this GPU and re-assembled, equal the single-batch result bit for
     bit (columns are independent units; the multi-process gather itself is covered on CPU by
     tests/test_shard_gloo.py)."""
     from clima_b200 import shard
+    _set_flavour(monkeypatch, flavour)
+    bw = flavour == "sort"
     tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=5)
     g = Radtran(tb, pr)
     whole = g.radiate_batch(cols)
     parts = [g.radiate_batch(shard.slice_columns(cols, b, e)) for b, e in shard.partition(5, 2)]
     for k in shard.RESULT_PROFILES:
-        assert np.array_equal(np.concatenate([p[k] for p in parts], axis=1), whole[k]), k
+        assert _same(np.concatenate([p[k] for p in parts], axis=1), whole[k], bw), k
     for k in shard.RESULT_SCALARS:
-        assert np.array_equal(np.concatenate([p[k] for p in parts]), whole[k]), k
+        assert _same(np.concatenate([p[k] for p in parts]), whole[k], bw), k
     one = shard.radiate_sharded(g.radiate_batch, cols, dist=None)
     for k in shard.RESULT_PROFILES + shard.RESULT_SCALARS:
         assert np.array_equal(one[k], whole[k]), k
@@ -581,3 +629,137 @@ def test_rorr_unit_order_does_not_change_results(monkeypatch):
             res[mode] = Radtran(tb, pr).radiate_batch(cols)
         compare(res["layers"], res["columns"], spectral=False, tol=1e-12)
         compare(r_auto, res["columns"], spectral=False, tol=1e-12)
+
+
+# ------------------------------------------------------------------ sort-free (staircase) RORR kernel
+def _opacity_err(g1, g2, nz, icols):
+    e = 0.0
+    for i in icols:
+        for a, b in zip(g1.get_opacity(nz, icol=i), g2.get_opacity(nz, icol=i)):
+            m = np.abs(b) > 0
+            if m.any():
+                e = max(e, float(np.max(np.abs(a[m] - b[m]) / np.abs(b[m]))))
+    return e
+
+
+@pytest.mark.parametrize("G", [16, 8, 11, 32])
+def test_staircase_kernel_matches_the_sorting_kernels(G, monkeypatch):
+    """optics_rorr_cut.cu (no sort: the rebin from staircase cuts, chains over columns or over layer
+    slots) against the sorting kernels (mrgrnk order + rebin walk) on the same columns: tau, w0, tau_band
+    to 1e-12 elementwise, fluxes to 1e-11; and against the oracle."""
+    tb, pr, cols = small_case(G=G, nw=10, nz=14, ncol=7, nk=3)
+    monkeypatch.setenv("CLIMA_RT_RORR", "sort")
+    gs = Radtran(tb, pr)
+    rs = gs.radiate_batch(cols, spectral=True)
+    monkeypatch.delenv("CLIMA_RT_RORR")
+    ro = OracleRadtran(tb, pr).radiate_batch(cols, spectral=True)
+    for chain in ("slot", "col"):
+        monkeypatch.setenv("CLIMA_RT_RORR_CHAIN", chain)
+        gc = Radtran(tb, pr)
+        rc = gc.radiate_batch(cols, spectral=True)
+        units, exact, ovf = gc.rorr_stats()
+        assert units > 0 and exact == 0 and ovf == 0, (units, exact, ovf)
+        assert _opacity_err(gc, gs, cols["nz"], range(7)) < 1e-12
+        compare(rc, rs, tol=1e-11)
+        compare(rc, ro)
+
+
+@pytest.mark.parametrize("chain", ["col", "slot"])
+@pytest.mark.parametrize("kw", [dict(), dict(randomize=True, seed=11),
+                                dict(pco2_range=(1.0e-2, 10 ** 0.5), T_surf_range=(200.0, 320.0), gravity=371.0)])
+def test_staircase_kernel_full_size_columns(kw, chain, monkeypatch):
+    """cfg2 / cfg5 / cfg3 columns at S-canon size (nz_r=202, nw=100, G=16, K=5), 16 columns each: the
+    staircase kernel (both chain directions) against the oracle, and tau against the sorting kernels."""
+    tb = synth.make_tables()
+    pr = synth.default_params(tb)
+    cols = synth.make_columns(16, nz=100, **kw)
+    monkeypatch.setenv("CLIMA_RT_RORR_CHAIN", chain)
+    g = Radtran(tb, pr)
+    rg = g.radiate_batch(cols, spectral=True)
+    units, exact, ovf = g.rorr_stats()
+    assert exact <= 1e-4 * units and ovf == 0, (units, exact, ovf)
+    ro = OracleRadtran(tb, pr, kind="parity").radiate_batch(cols, spectral=True, nthreads=8)
+    compare(rg, ro)
+    assert g.rorr_cut_stats()["last_kernel"] == (1 if chain == "col" else 0)
+    monkeypatch.delenv("CLIMA_RT_RORR_CHAIN")
+    monkeypatch.setenv("CLIMA_RT_RORR", "sort")
+    gs = Radtran(tb, pr)
+    gs.radiate_batch(cols)
+    assert gs.rorr_cut_stats()["last_kernel"] == 2
+    assert _opacity_err(g, gs, cols["nz"], (0, 7, 15)) < 1e-11
+
+
+@pytest.mark.parametrize("chain", ["col", "slot"])
+def test_staircase_kernel_ties_plateaus_and_absent_gases(chain, monkeypatch):
+    """Exact ties (two clusters of identical k values, an absent gas: b = 0) and near ties (steps of
+    1e-13 in log10 k): any staircase through a tie group is a valid sorted prefix, the rebin does not
+    depend on the order inside it."""
+    tb, pr, cols = small_case(G=16, nw=8, nz=8, ncol=5, nk=3)
+    gidx = np.arange(16)
+    tb.k[0].log10k[...] = tb.k[0].log10k[0:1] + (np.where(gidx < 8, 0.0, 6.0) + 1e-13 * gidx)[:, None, None, None]
+    tb.k[1].log10k[...] = tb.k[1].log10k[0:1] + np.where(gidx < 5, 0.0, 3.0)[:, None, None, None]
+    d = cols["densities"].copy(order="F")
+    d[:, tb.k[2].sp_ind - 1, 1::2] = 0.0
+    c2 = dict(cols, densities=d)
+    monkeypatch.setenv("CLIMA_RT_RORR_CHAIN", chain)
+    g, o, rg, ro = run_both(tb, pr, c2)
+    compare(rg, ro)
+    assert g.rorr_stats()[1] == 0
+
+
+def test_cfg1_modern_earth_template_column():
+    """BASELINE.json configs[0] from the reference's own template files (tests/test_radtran.f90:33-65):
+    atmosphere.txt (200 levels) + Sun_now.txt, 8 zenith angles, albedo 0.15; synthetic k-tables."""
+    from cases import cfg1_template_case
+    tb, pr, cols = cfg1_template_case()
+    assert cols["nz"] == 200 and abs(cols["T_surface"][0] - 288.15) < 0.01
+    g, o, rg, ro = run_both(tb, pr, cols)
+    w = compare(rg, ro, verbose=True)
+    assert w["OLR"] < TOL and w["ISR"] < TOL
+    assert 2.0e5 < rg["OLR"][0] < 4.5e5  # mW/m2: an Earth-like OLR
+
+
+@pytest.mark.parametrize("eps", [1e-3, 1e-6, 1e-9, 1e-12])
+def test_solar_resonance_lambda_u0(eps):
+    """two_stream_solar divides by denom = lambda**2 - 1/u0**2 without a guard
+    (clima_radtran_twostream.f90:80; SURVEY Appendix C.10 "preserve").  The zenith cosine is put a
+    relative distance eps from 1/lambda of one (layer, bin, g-point) of a Rayleigh-dominated column
+    (g = 0: lambda**2 = 3 (1 - w0)).  Near the pole C+ and C- grow like 1/eps while the boundary
+    conditions subtract them again, so ANY two evaluation orders differ by ~1e-16/eps in that term;
+    the GPU (reciprocal-multiply) must stay within that of the oracle (IEEE division) and both must
+    stay finite."""
+    from cases import rayleigh_dominated_case
+    tb, pr, cols = rayleigh_dominated_case()
+    g0 = Radtran(tb, pr)
+    g0.radiate_batch(cols)
+    tau, w0, gt, _ = g0.get_opacity(cols["nz"], icol=0)
+    lam = np.sqrt(3.0 * (1.0 - w0)) if np.all(gt == 0) else None
+    assert lam is not None
+    sol = slice(tb.sol_ind[0] - 1, tb.sol_ind[1])
+    cand = np.argwhere((1.0 / lam[:, :, sol] > 0.6) & (1.0 / lam[:, :, sol] < 0.95) & (tau[:, :, sol] > 1e-3))
+    assert len(cand) > 0
+    n, gg, ll = cand[len(cand) // 2]
+    u0 = (1.0 / lam[n, gg, sol][ll]) * (1.0 + eps)
+    pr.zenith_u = np.array([u0])
+    pr.zenith_weights = np.array([1.0])
+    g, o, rg, ro = run_both(tb, pr, cols)
+    for k in ("fup_n_sol", "fdn_n_sol", "fup_a_sol", "fdn_a_sol", "amean_sol"):
+        assert np.all(np.isfinite(rg[k])) == np.all(np.isfinite(ro[k])), k
+    tol = max(TOL, 1.0e-14 / eps)
+    for k in ("fup_n_sol", "fdn_n_sol", "fup_a_sol", "fdn_a_sol"):
+        assert rel_err(rg[k], ro[k]) <= tol, (k, rel_err(rg[k], ro[k]), tol)
+
+
+def test_rorr_kernel_choice_follows_the_columns():
+    """A sweep of alike columns takes the staircase kernel with column chains; columns with randomised
+    composition keep the sorting kernels; a tiny batch keeps them too (too few chains)."""
+    tb = synth.make_tables(nw=20, n_sol=12, ir_start=8)
+    pr = synth.default_params(tb, nzenith=1)
+    g = Radtran(tb, pr)
+    g.radiate_batch(synth.make_columns(64, nz=20, T_surf_range=(280.0, 290.0)))
+    st = g.rorr_cut_stats()
+    assert st["last_kernel"] == 1 and st["warp_merges"] > 0 and st["warp_passes"] < 1.5 * st["warp_merges"], st
+    g.radiate_batch(synth.make_columns(64, nz=20, randomize=True, seed=3))
+    assert g.rorr_cut_stats()["last_kernel"] == 2
+    g.radiate_batch(synth.make_columns(4, nz=20, T_surf_range=(280.0, 281.0)))
+    assert g.rorr_cut_stats()["last_kernel"] == 2

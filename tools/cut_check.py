@@ -30,8 +30,8 @@ def run(cols, env):
     s1 = g.stage_ms()
     units, exact, ovf = g.rorr_stats()
     op = [g.get_opacity(cols["nz"], icol=i) for i in (0, ncol // 3, ncol - 1)]
-    return dict(r=r, op=op, rorr_ms=s1[0] - s0[0], total_ms=s1[4] - s0[4], wall_ms=dt * 1e3,
-                exact_share=exact / max(units, 1), ovf=int(ovf))
+    return dict(r=r, op=op, rorr_ms=s1[0], total_ms=s1[4], wall_ms=dt * 1e3,
+                exact_share=exact / max(units, 1), ovf=int(ovf), cut=g.rorr_cut_stats())
 
 
 out = {}
@@ -51,7 +51,7 @@ for name in cfgs:
                 if m.any():
                     e = max(e, float(np.max(np.abs(a[j][m] - b[j][m]) / np.abs(b[j][m]))))
             d[nm] = e
-        res[tag] = dict(rorr_ms=x["rorr_ms"], total_ms=x["total_ms"], exact_share=x["exact_share"], ovf=x["ovf"],
+        res[tag] = dict(rorr_ms=x["rorr_ms"], total_ms=x["total_ms"], exact_share=x["exact_share"], ovf=x["ovf"], cut=x["cut"],
                         max_rel_vs_sort=max(d.values()), worst=max(d, key=d.get), tau=d["tau"],
                         finite=bool(all(np.all(np.isfinite(x["r"][k])) for k in FL)))
     out[name] = res
