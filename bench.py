@@ -293,6 +293,7 @@ def run_ours(args):
         args.steps, args.warmup, barrier, dev, ClockSampler(local) if rank == 0 else None)
     value = world * ncol / (ms_per_step * 1e-3)
     rorr_stats = rt.rorr_stats()
+    cut_stats = rt.rorr_cut_stats()
 
     # ---- e2e leg: host pointers through the C ABI, pinned buffers, H2D + D2H inside the timing
     from clima_b200._abi import alloc_out
@@ -373,6 +374,10 @@ def run_ours(args):
         # HBM view of the dominant kernel: reads the column inputs, writes tau/w0/g/tau_band of the
         # unique layers (those writes are an implementation intermediate, not algorithmic output)
         k_bytes = byt["in"] * ncol
+        staircase = cut_stats["last_kernel"] in (0, 1)
+        kernel_name = ("rorr_cut::rorr_cut_kernel<16> (sort-free staircase RORR, column chains)" if staircase
+                       else "rorr_fast::optics_rorr_kernel<16> (sorting RORR)")
+        dram_per_col = roofline.RORR_CUT_DRAM_BYTES_PER_COLUMN if staircase else roofline.RORR_FAST_DRAM_BYTES_PER_COLUMN
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
@@ -389,9 +394,12 @@ def run_ours(args):
             "stage_ms_per_step": {"optics_rorr": stage[0], "planck_ir": stage[1], "solar": stage[2],
                                   "integrate": stage[3], "kernels_total": stage[4], "prep": stage[5]},
             "wall_ms_per_step": 1e3 * t_wall / args.steps,
-            "rorr": dict(zip(("units", "exact_kernel_units", "worklist_overflows"), rorr_stats)),
+            "rorr": dict(zip(("units", "exact_kernel_units", "worklist_overflows"), rorr_stats),
+                         passes_per_merge=cut_stats["warp_passes"] / max(cut_stats["warp_merges"], 1),
+                         closed_form_share=cut_stats["closed_form_warp_merges"] / max(cut_stats["warp_merges"] + cut_stats["closed_form_warp_merges"], 1),
+                         kernel=("staircase/slot chains", "staircase/column chains", "sorting", "exact sorting")[cut_stats["last_kernel"]]),
             "roofline": {
-                "kernel": "optics_rorr_kernel<16>", "bound": "fp64", "achieved": achieved,
+                "kernel": kernel_name, "bound": "fp64", "achieved": achieved,
                 "peak": fp64_tf, "unit": "TFLOP/s", "frac": achieved / fp64_tf,
                 "frac_of_issue_roof": achieved / (fp64_tf / 2.0),
                 "peak_source": "DFMA micro-kernel measured live in this run (FMA = 2 flops); "
@@ -400,8 +408,9 @@ def run_ours(args):
                 # dram__bytes_read.sum + dram__bytes_write.sum of the fast RORR kernel from the
                 # ncu --set full capture at 256 columns (profiles/r1p_ncu_full_summary.txt: 73.9 MB read,
                 # 622.8 MB written = the tau/w0 lines of every unit), scaled to this launch's columns
-                "traffic": roofline.RORR_FAST_DRAM_BYTES_PER_COLUMN * ncol,
-                "traffic_source": "ncu r1p capture at 256 columns, scaled per column",
+                "traffic": dram_per_col * ncol,
+                "traffic_over_algorithmic_bytes": dram_per_col / byt["in"],
+                "traffic_source": roofline.RORR_DRAM_SOURCE["cut" if staircase else "fast"],
                 "hbm": {"bound": "hbm", "achieved": k_bytes / (k_ms * 1e-3) / 1e9, "peak": hbm_peak,
                         "unit": "GB/s", "frac": k_bytes / (k_ms * 1e-3) / 1e9 / hbm_peak,
                         "peak_source": hbm_src, "algorithmic_bytes_per_column": byt},
