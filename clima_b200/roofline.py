@@ -15,12 +15,13 @@ from dataclasses import dataclass
 # (tau and w0 of every unit, 2 x 8 x G bytes x nw x unique layers = 2.59 MB per column).
 RORR_FAST_DRAM_BYTES_PER_COLUMN = (73949000 + 622805000) / 256.0
 # The same for rorr_cut::rorr_cut_kernel<16,true> (the default kernel on sweeps), ncu --set full at
-# 512 columns of the cfg2 workload, column chains (gpurun_out/cut2.ncu-rep, r2a build):
-# dram__bytes_read.sum 183.7 MB + dram__bytes_write.sum 1343.2 MB.
-RORR_CUT_DRAM_BYTES_PER_COLUMN = (183.7312e6 + 1343.186e6) / 512.0
+# 1024 columns of the cfg2 workload, column chains (profiles/r2b_ncu_rorr_cut_summary.txt):
+# dram__bytes_read.sum 443.0 MB + dram__bytes_write.sum 2742.2 MB; the writes are the kernel's
+# output (tau, w0 of every unit: 2.59 MB per column), which the two-stream kernels read back.
+RORR_CUT_DRAM_BYTES_PER_COLUMN = (443.00032e6 + 2742.222e6) / 1024.0
 RORR_DRAM_SOURCE = {
     "fast": "ncu r1p capture at 256 columns (profiles/r1p_ncu_full_summary.txt), scaled per column",
-    "cut": "ncu r2a capture at 512 columns (profiles/r2a_ncu_rorr_cut_summary.txt), scaled per column",
+    "cut": "ncu r2b capture at 1024 columns (profiles/r2b_ncu_rorr_cut_summary.txt), scaled per column",
 }
 
 
