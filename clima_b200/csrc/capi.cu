@@ -17,6 +17,8 @@
 
 #include "../../include/clima_rt.h"
 #include "rt_kernels.h"
+#include <dlfcn.h>
+#include <nccl.h>  // types only: the library is bound at run time (dlopen), see Nccl below
 
 namespace {
 
@@ -80,6 +82,12 @@ struct Handle {
   bool solar_state_invalid = false;
   bool had_solar_call = false;
   int chunk_cols_env = 0;  // CLIMA_RT_CHUNK_COLS, read once at create (0 = default 4096)
+
+  // multi-GPU: one NCCL communicator per handle, collectives on the handle's stream
+  ncclComm_t comm = nullptr;
+  int comm_nranks = 0, comm_rank = -1;
+  double *d_send = nullptr, *d_recv = nullptr;  // result block of this rank / of all ranks
+  size_t comm_block = 0;                        // doubles per rank the buffers hold
 
   // introspection
   int64_t launches = 0;
@@ -490,7 +498,8 @@ std::string check_inputs(const Handle &h, int ncol, int nz, int ng, int np, cons
 
 // device==true: all pointers are device pointers.
 void radiate_batch_impl(Handle &h, bool device, int ncol, int nz, int ng, int np, const HostIn &in,
-                        bool compute_solar, bool compute_opacity, const clima_rt_out *out) {
+                        bool compute_solar, bool compute_opacity, const clima_rt_out *out,
+                        int out_device = -1) {
   CK(cudaSetDevice(h.device));
   const std::string e = check_inputs(h, ncol, nz, ng, np, in.pd, in.rd);
   if (!e.empty()) throw CudaError{e};
@@ -524,7 +533,8 @@ void radiate_batch_impl(Handle &h, bool device, int ncol, int nz, int ng, int np
   const DevTables &tb = h.tb;
   const size_t L = nz + 1;
   const cudaMemcpyKind kin = device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
-  const cudaMemcpyKind kout = device ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
+  const bool odev = out_device < 0 ? device : out_device != 0;  // sharded entry: host inputs, device results
+  const cudaMemcpyKind kout = odev ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost;
   for (int i = 0; i < 6; i++) h.stage_ms[i] = 0.0;
   bool radius_clamped = false;
   for (int c0 = 0; c0 < ncol; c0 += C) {
@@ -682,6 +692,50 @@ void jacobian_batch_impl(Handle &h, int ncol, int nzm, const double *T_surface, 
   }
 }
 
+// ---- NCCL, bound at run time.  The library must not carry a link-time dependency on one particular
+// libnccl: a host process (torch in bench.py, an MPI launcher) may already have its own copy loaded,
+// and a single-GPU user needs none.  dlopen picks the copy that is already in the process, else the
+// system one.
+struct Nccl {
+  void *lib = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+Nccl &nccl() {
+  static Nccl n;
+  if (n.lib) return n;
+  const char *names[] = {"libnccl.so.2", "libnccl.so"};
+  void *lib = nullptr;
+  for (const char *nm : names) if (!lib) lib = dlopen(nm, RTLD_NOW | RTLD_NOLOAD | RTLD_GLOBAL);
+  for (const char *nm : names) if (!lib) lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+  if (!lib) throw CudaError{"clima_rt: libnccl.so.2 not found (multi-GPU entry points need NCCL)"};
+  n.GetUniqueId = (decltype(n.GetUniqueId))dlsym(lib, "ncclGetUniqueId");
+  n.CommInitRank = (decltype(n.CommInitRank))dlsym(lib, "ncclCommInitRank");
+  n.CommDestroy = (decltype(n.CommDestroy))dlsym(lib, "ncclCommDestroy");
+  n.AllGather = (decltype(n.AllGather))dlsym(lib, "ncclAllGather");
+  n.GetErrorString = (decltype(n.GetErrorString))dlsym(lib, "ncclGetErrorString");
+  if (!n.GetUniqueId || !n.CommInitRank || !n.CommDestroy || !n.AllGather || !n.GetErrorString)
+    throw CudaError{"clima_rt: libnccl lacks a required symbol"};
+  n.lib = lib;
+  return n;
+}
+void nccl_check(ncclResult_t r, const char *what) {
+  if (r != ncclSuccess) throw CudaError{std::string("NCCL error in ") + what + ": " + nccl().GetErrorString(r)};
+}
+void comm_buffers(Handle &h, size_t block) {
+  if (block <= h.comm_block) return;
+  if (h.d_send) cudaFree(h.d_send);
+  if (h.d_recv) cudaFree(h.d_recv);
+  h.d_send = h.d_recv = nullptr;
+  h.comm_block = 0;
+  CK(cudaMalloc(&h.d_send, block * sizeof(double)));
+  CK(cudaMalloc(&h.d_recv, block * sizeof(double) * (size_t)h.comm_nranks));
+  h.comm_block = block;
+}
+
 }  // namespace
 
 // =============================================================================================
@@ -750,6 +804,7 @@ void clima_rt_destroy(void *handle) {
   if (!handle) return;
   Handle *h = static_cast<Handle *>(handle);
   cudaSetDevice(h->device);
+  clima_rt_comm_destroy(handle);
   free_chunk(*h);
   for (void *p : h->table_allocs) cudaFree(p);
   for (auto &p : h->d_custom) if (p) cudaFree(p);
@@ -830,6 +885,125 @@ void clima_rt_radiate_batch_device(void *handle, const int32_t *ncol, const int3
     HostIn in{T_surface, T, P, densities, dz, pdensities, radii};
     radiate_batch_impl(*static_cast<Handle *>(handle), true, *ncol, *nz, *ng, *np, in,
                        *compute_solar != 0, *compute_opacity != 0, out);
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+
+/* ---- multi-GPU: columns are block-partitioned over the ranks, tables replicated, no
+   exchange during compute, ONE all-gather of the flux profiles.  One process (or thread) per GPU,
+   each with its own handle; the NCCL communicator belongs to the handle and every collective runs
+   on the handle's stream, ordered after the kernels without a host synchronisation. */
+void clima_rt_comm_unique_id(char *id /* [CLIMA_RT_COMM_ID_BYTES] */, char *err) {
+  set_err(err, "");
+  try {
+    static_assert(sizeof(ncclUniqueId) == CLIMA_RT_COMM_ID_BYTES, "ncclUniqueId size");
+    ncclUniqueId u;
+    nccl_check(nccl().GetUniqueId(&u), "ncclGetUniqueId");
+    std::memcpy(id, &u, sizeof(u));
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_comm_init(void *handle, const int32_t *nranks, const int32_t *rank, const char *id, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle || !nranks || !rank || !id) throw CudaError{"clima_rt: NULL argument"};
+    Handle &h = *static_cast<Handle *>(handle);
+    if (*nranks < 1 || *rank < 0 || *rank >= *nranks) throw CudaError{"clima_rt_comm_init: rank outside [0, nranks)"};
+    if (h.comm) throw CudaError{"clima_rt_comm_init: the handle already has a communicator"};
+    CK(cudaSetDevice(h.device));
+    ncclUniqueId u;
+    std::memcpy(&u, id, sizeof(u));
+    nccl_check(nccl().CommInitRank(&h.comm, *nranks, u, *rank), "ncclCommInitRank");
+    h.comm_nranks = *nranks;
+    h.comm_rank = *rank;
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_comm_destroy(void *handle) {
+  if (!handle) return;
+  Handle &h = *static_cast<Handle *>(handle);
+  cudaSetDevice(h.device);
+  if (h.comm) {
+    cudaStreamSynchronize(h.st);
+    try { nccl().CommDestroy(h.comm); } catch (const CudaError &) {}
+  }
+  h.comm = nullptr;
+  h.comm_nranks = 0;
+  h.comm_rank = -1;
+  if (h.d_send) cudaFree(h.d_send);
+  if (h.d_recv) cudaFree(h.d_recv);
+  h.d_send = h.d_recv = nullptr;
+  h.comm_block = 0;
+}
+
+void clima_rt_allgather_device(void *handle, const double *send, double *recv, const int64_t *count, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle || !send || !recv || !count) throw CudaError{"clima_rt: NULL argument"};
+    Handle &h = *static_cast<Handle *>(handle);
+    if (!h.comm) throw CudaError{"clima_rt_allgather_device: no communicator (call clima_rt_comm_init)"};
+    CK(cudaSetDevice(h.device));
+    nccl_check(nccl().AllGather(send, recv, (size_t)*count, ncclDouble, h.comm, h.st), "ncclAllGather");
+    h.launches++;
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_radiate_batch_sharded(void *handle, const int32_t *ncol, const int32_t *ncol_max,
+                                    const int32_t *nz, const int32_t *ng, const int32_t *np,
+                                    const double *T_surface, const double *T, const double *P,
+                                    const double *densities, const double *dz, const double *pdensities,
+                                    const double *radii, const int32_t *compute_solar,
+                                    const int32_t *compute_opacity, const clima_rt_out *out_all, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle || !ncol || !ncol_max || !nz || !out_all) throw CudaError{"clima_rt: NULL argument"};
+    Handle &h = *static_cast<Handle *>(handle);
+    if (!h.comm) throw CudaError{"clima_rt_radiate_batch_sharded: no communicator (call clima_rt_comm_init)"};
+    if (*ncol < 0 || *ncol > *ncol_max) throw CudaError{"clima_rt_radiate_batch_sharded: ncol must be in [0, ncol_max]"};
+    if (!out_all->fup_n_ir || !out_all->fdn_n_ir || !out_all->fup_n_sol || !out_all->fdn_n_sol ||
+        !out_all->f_total || !out_all->ISR || !out_all->OLR)
+      throw CudaError{"mandatory output pointers are NULL"};
+    CK(cudaSetDevice(h.device));
+    const size_t L = (size_t)*nz + 1, M = (size_t)*ncol_max, block = (5 * L + 2) * M;
+    comm_buffers(h, block);
+    CK(cudaMemsetAsync(h.d_send, 0, block * sizeof(double), h.st));
+    // this rank's block, on the device: five profiles (nz+1, ncol_max), then ISR, OLR (ncol_max)
+    clima_rt_out loc{};
+    double *p = h.d_send;
+    loc.fup_n_ir = p; p += L * M;
+    loc.fdn_n_ir = p; p += L * M;
+    loc.fup_n_sol = p; p += L * M;
+    loc.fdn_n_sol = p; p += L * M;
+    loc.f_total = p; p += L * M;
+    loc.ISR = p; p += M;
+    loc.OLR = p;
+    if (*ncol > 0) {  // a rank may hold an empty block
+      HostIn in{T_surface, T, P, densities, dz, pdensities, radii};
+      radiate_batch_impl(h, false, *ncol, *nz, *ng, *np, in, *compute_solar != 0, *compute_opacity != 0, &loc, 1);
+    }
+    nccl_check(nccl().AllGather(h.d_send, h.d_recv, block, ncclDouble, h.comm, h.st), "ncclAllGather");
+    h.launches++;
+    // (nz+1, ncol_max, nranks): rank r's columns at [.., r*ncol_max .. r*ncol_max + ncol_r)
+    for (int r = 0; r < h.comm_nranks; r++) {
+      const double *b = h.d_recv + (size_t)r * block;
+      double *dst[7] = {out_all->fup_n_ir, out_all->fdn_n_ir, out_all->fup_n_sol, out_all->fdn_n_sol,
+                        out_all->f_total, out_all->ISR, out_all->OLR};
+      size_t off = 0;
+      for (int k = 0; k < 7; k++) {
+        const size_t n = (k < 5 ? L : 1) * M;
+        CK(cudaMemcpyAsync(dst[k] + (size_t)r * n, b + off, n * sizeof(double), cudaMemcpyDeviceToHost, h.st));
+        off += n;
+      }
+    }
+    CK(cudaStreamSynchronize(h.st));
   } catch (const CudaError &e) {
     set_err(err, e.msg);
   }

@@ -29,7 +29,10 @@ EXPORTS = ["clima_rt_create", "clima_rt_destroy", "clima_rt_set_params",
            "clima_rt_radiate_batch", "clima_rt_radiate_batch_device", "clima_rt_jacobian_batch",
            "clima_rt_get_opacity",
            "clima_rt_get_launch_count", "clima_rt_get_stage_ms", "clima_rt_get_stream", "clima_rt_get_rorr_stats", "clima_rt_get_rorr_cut_stats", "clima_rt_measure_fp64_peak",
-           "clima_rt_version_get"]
+           "clima_rt_version_get",
+           "clima_rt_comm_unique_id", "clima_rt_comm_init", "clima_rt_comm_destroy", "clima_rt_allgather_device",
+           "clima_rt_radiate_batch_sharded"]
+COMM_ID_BYTES = 128
 
 
 class ClimaException(Exception):
@@ -176,6 +179,61 @@ class Radtran:
     def TOA_fluxes_batch(self, cols: Dict):
         r = self.radiate_batch(cols)
         return r["ISR"], r["OLR"]
+
+    # ---- multi-GPU: the NCCL entry points of the C ABI (include/clima_rt.h)
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        """ncclGetUniqueId through the C ABI: rank 0 calls it and hands the bytes to the other ranks."""
+        buf = C.create_string_buffer(COMM_ID_BYTES)
+        err = C.create_string_buffer(ERR_LEN + 1)
+        load_library().clima_rt_comm_unique_id(buf, err)
+        _check(err)
+        return buf.raw
+
+    def comm_init(self, nranks: int, rank: int, uid: bytes):
+        if len(uid) != COMM_ID_BYTES:
+            raise ClimaException("comm_init: the unique id must be %d bytes" % COMM_ID_BYTES)
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self._lib.clima_rt_comm_init(self._h, _i(nranks), _i(rank), C.create_string_buffer(uid, COMM_ID_BYTES), err)
+        _check(err)
+        self._nranks = nranks
+
+    def comm_destroy(self):
+        self._lib.clima_rt_comm_destroy(self._h)
+
+    def allgather_device(self, send_ptr: int, recv_ptr: int, count: int):
+        """ncclAllGather of `count` doubles per rank between device buffers, on the handle's stream."""
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self._lib.clima_rt_allgather_device(self._h, C.cast(C.c_void_p(send_ptr), c_double_p),
+                                            C.cast(C.c_void_p(recv_ptr), c_double_p),
+                                            C.byref(C.c_int64(int(count))), err)
+        _check(err)
+
+    def radiate_batch_sharded(self, cols: Dict, ncol_max: int, compute_solar=True, compute_opacity=True):
+        """This rank's columns (`cols`, possibly empty) through `radiate_batch`, then the all-gather:
+        returns the dict of integrated results of ALL ranks, arrays (nz+1, ncol_max, nranks) /
+        (ncol_max, nranks), padding columns zero."""
+        nz, ng, npp, ncol = cols["nz"], cols["ng"], cols["np"], cols["ncol"]
+        nr = self._nranks
+        L = nz + 1
+        o = COut()
+        arrs = {}
+        for k in ("fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol", "f_total"):
+            arrs[k] = np.zeros((L, ncol_max, nr), order="F")
+        for k in ("ISR", "OLR"):
+            arrs[k] = np.zeros((ncol_max, nr), order="F")
+        for k, a in arrs.items():
+            setattr(o, k, dptr(a))
+        err = C.create_string_buffer(ERR_LEN + 1)
+        nul = c_double_p()
+        g = lambda k: dptr(cols[k]) if ncol > 0 else nul  # noqa: E731
+        pd = dptr(cols["pdensities"]) if "pdensities" in cols and ncol > 0 else nul
+        rd = dptr(cols["radii"]) if "radii" in cols and ncol > 0 else nul
+        self._lib.clima_rt_radiate_batch_sharded(self._h, _i(ncol), _i(ncol_max), _i(nz), _i(ng), _i(npp),
+                                                 g("T_surface"), g("T"), g("P"), g("densities"), g("dz"), pd, rd,
+                                                 _i(compute_solar), _i(compute_opacity), C.byref(o), err)
+        _check(err)
+        return arrs
 
     def jacobian_batch(self, T_surface, T):
         """Perturbed-temperature batch of AdiabatClimate_jacobian_from_base

@@ -7,6 +7,11 @@ every rank -- `(nz+1)*5 + 2` doubles per column.  The collective goes through `t
 (NCCL over NVLink on the GPU box, gloo on CPU in the tests); torch is plumbing only, the compute
 callable is injected (`Radtran.radiate_batch` in production).
 
+Two gathers: `radiate_sharded_nccl` is the product path -- `clima_rt_radiate_batch_sharded` of the C
+ABI (ncclAllGather of the device-resident result block on the handle's stream); `radiate_sharded` is
+the same partition logic over any `torch.distributed`-like object with a host-staged gather, kept for
+the world_size-2 gloo tests on CPU (tests/test_shard_gloo.py), where no GPU and no NCCL exist.
+
 Host logic only: nothing here touches the oracle or offers a CPU compute path.
 """
 from __future__ import annotations
@@ -117,3 +122,21 @@ def radiate_sharded(compute: Callable[[Dict], Dict], cols: Dict, dist=None, devi
     b, e = blocks[rank]
     local = compute(slice_columns(cols, b, e)) if e > b else {}
     return gather_results(local, cols["nz"], blocks, dist if world > 1 else None, device)
+
+
+def radiate_sharded_nccl(rt, cols: Dict, rank: int, world: int, **kw) -> Dict:
+    """Product path: this rank's block through `Radtran.radiate_batch_sharded` (C ABI: compute, then
+    ncclAllGather on the handle's stream; the handle must have a communicator, `Radtran.comm_init`).
+    Returns the results of ALL columns in their original order."""
+    ncol = cols["ncol"]
+    parts = partition(ncol, world)
+    b, e = parts[rank]
+    ncol_max = max(pe - pb for pb, pe in parts)
+    mine = slice_columns(cols, b, e)
+    out = rt.radiate_batch_sharded(mine, max(ncol_max, 1), **kw)
+    res = {}
+    for k in RESULT_PROFILES:
+        res[k] = np.concatenate([out[k][:, :pe - pb, r] for r, (pb, pe) in enumerate(parts)], axis=1)
+    for k in RESULT_SCALARS:
+        res[k] = np.concatenate([out[k][:pe - pb, r] for r, (pb, pe) in enumerate(parts)])
+    return res

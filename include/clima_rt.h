@@ -208,6 +208,40 @@ void clima_rt_radiate_batch_device(void *handle, const int32_t *ncol, const int3
                                    const int32_t *compute_solar, const int32_t *compute_opacity,
                                    const clima_rt_out *out, char *err);
 
+/* ---- multi-GPU.  Columns are independent: every rank (one process or thread per GPU,
+   each with its own handle and a replica of the tables) computes a contiguous block of columns and
+   ONE all-gather returns every rank's flux profiles to every rank.  The communicator is NCCL's
+   (bound at run time with dlopen: no link-time dependency, a single-GPU caller needs no NCCL).
+     clima_rt_comm_unique_id   rank 0 obtains the id (ncclGetUniqueId) and hands the 128 bytes to the other
+                               ranks by its own means (MPI_Bcast, a file, torch.distributed ...)
+     clima_rt_comm_init        collective: ncclCommInitRank on the handle's device
+     clima_rt_comm_destroy     also called by clima_rt_destroy
+   The reference has no multi-device path; the caller these replace is the loop over columns of a
+   sweep (examples/EarlyMars.ipynb cell 7) split over processes. */
+#define CLIMA_RT_COMM_ID_BYTES 128
+void clima_rt_comm_unique_id(char *id /* [CLIMA_RT_COMM_ID_BYTES] */, char *err);
+void clima_rt_comm_init(void *handle, const int32_t *nranks, const int32_t *rank,
+                        const char *id /* [CLIMA_RT_COMM_ID_BYTES] */, char *err);
+void clima_rt_comm_destroy(void *handle);
+
+/* ncclAllGather of `*count` doubles per rank between DEVICE buffers (recv holds nranks * count), on
+   the handle's stream: ordered after the kernels of a preceding clima_rt_radiate_batch_device, no
+   host synchronisation.  The building block of clima_rt_radiate_batch_sharded; bench.py times it. */
+void clima_rt_allgather_device(void *handle, const double *send, double *recv, const int64_t *count,
+                               char *err);
+
+/* clima_rt_radiate_batch for this rank's `*ncol` columns (HOST inputs, 0 <= ncol <= ncol_max; ncol_max
+   is the same on every rank) followed by the all-gather: every rank receives
+     fup_n_ir, fdn_n_ir, fup_n_sol, fdn_n_sol, f_total (nz+1, ncol_max, nranks), ISR, OLR (ncol_max, nranks)
+   in HOST memory; rank r's columns are [.., 0 .. ncol_r) of slab r, the padding columns are zero.
+   Spectral pointers of out_all are ignored (727 KB per column stay on the rank that computed them). */
+void clima_rt_radiate_batch_sharded(void *handle, const int32_t *ncol, const int32_t *ncol_max,
+                                    const int32_t *nz, const int32_t *ng, const int32_t *np,
+                                    const double *T_surface, const double *T, const double *P,
+                                    const double *densities, const double *dz, const double *pdensities,
+                                    const double *radii, const int32_t *compute_solar,
+                                    const int32_t *compute_opacity, const clima_rt_out *out_all, char *err);
+
 /* N1: the temperature-perturbation loop of AdiabatClimate_jacobian_from_base
    (src/adiabat/clima_adiabat_solve.f90:798-820) as ONE call.  The handle must hold the opacity and
    the solar fluxes of the BASE column on the doubled radiative grid (a previous

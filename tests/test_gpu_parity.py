@@ -763,3 +763,33 @@ def test_rorr_kernel_choice_follows_the_columns():
     assert g.rorr_cut_stats()["last_kernel"] == 2
     g.radiate_batch(synth.make_columns(4, nz=20, T_surf_range=(280.0, 281.0)))
     assert g.rorr_cut_stats()["last_kernel"] == 2
+
+
+def test_nccl_entry_points_single_rank():
+    """The multi-GPU entry points of the C ABI with a communicator of ONE rank (the only size a single
+    GPU can host): clima_rt_comm_unique_id / _init, clima_rt_radiate_batch_sharded == radiate_batch
+    padded to ncol_max, clima_rt_allgather_device, and the error strings without a communicator."""
+    tb, pr, cols = small_case(G=16, nw=10, nz=8, ncol=5)
+    g = Radtran(tb, pr)
+    ref = g.radiate_batch(cols)
+    with pytest.raises(ClimaException, match="no communicator"):
+        g._nranks = 1
+        g.radiate_batch_sharded(cols, 7)
+    uid = Radtran.comm_unique_id()
+    assert len(uid) == 128
+    g.comm_init(1, 0, uid)
+    with pytest.raises(ClimaException, match="already has a communicator"):
+        g.comm_init(1, 0, uid)
+    out = g.radiate_batch_sharded(cols, 7)
+    for k in ("fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol", "f_total"):
+        assert out[k].shape == (cols["nz"] + 1, 7, 1)
+        assert np.array_equal(out[k][:, :5, 0], ref[k]), k
+        assert np.all(out[k][:, 5:, 0] == 0.0)
+    for k in ("ISR", "OLR"):
+        assert np.array_equal(out[k][:5, 0], ref[k]), k
+    with pytest.raises(ClimaException, match="ncol must be in"):
+        g.radiate_batch_sharded(cols, 3)
+    g.comm_destroy()
+    g.comm_init(1, 0, Radtran.comm_unique_id())  # a handle can be given a new communicator
+    out2 = g.radiate_batch_sharded(cols, 5)
+    assert np.array_equal(out2["OLR"][:, 0], ref["OLR"])
