@@ -94,3 +94,17 @@ def test_zenith_quadrature_matches_reference_definition():
         u, w = _abi.zenith_angles_and_weights(n)
         assert abs(w.sum() - 1.0) < 1e-14 and np.all((u > 0) & (u < 1))
         assert abs((u * w).sum() - 0.5) < 1e-14  # integral of mu over [0,1]
+
+
+def test_c_driver_compiles_against_the_header(tmp_path):
+    """tests/c_driver.c (a C99 caller of the ABI, run on the GPU by tests/test_gpu_parity.py) compiles
+    against include/clima_rt.h with gcc: the header is valid C, not only C++."""
+    import shutil
+    import subprocess
+    gcc = shutil.which("gcc")
+    assert gcc, "gcc is part of the image"
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([gcc, "-std=c99", "-Wall", "-Wextra", "-Werror", "-I", os.path.join(root, "include"), "-c",
+                        os.path.join(root, "tests", "c_driver.c"), "-o", str(tmp_path / "c_driver.o")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr

@@ -793,3 +793,49 @@ def test_nccl_entry_points_single_rank():
     g.comm_init(1, 0, Radtran.comm_unique_id())  # a handle can be given a new communicator
     out2 = g.radiate_batch_sharded(cols, 5)
     assert np.array_equal(out2["OLR"][:, 0], ref["OLR"])
+
+
+def test_c_driver_runs_the_abi_without_python(tmp_path):
+    """tests/c_driver.c: plain C against include/clima_rt.h, linked with libclima_rt.so -- the closest
+    thing to the Fortran bind(c) caller this box can compile.  It reads a case file (tables, params,
+    columns, the ORACLE's fluxes, a frozen-opacity Jacobian case from the oracle loop), calls
+    clima_rt_create / radiate_batch / jacobian_batch / destroy and checks 1e-9 itself."""
+    import os
+    import shutil
+    import subprocess
+    from clima_b200 import blob
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    nzm = 6
+    tb, pr, cols = small_case(G=16, nw=10, nz=nzm, ncol=3, nzen=2, doubled=True)
+    o = OracleRadtran(tb, pr)
+    gold = o.radiate_batch(cols, spectral=False)
+    # Jacobian case on column 0 (the loop of clima_adiabat_solve.f90:798-820 run by the oracle)
+    base = {k: (np.asfortranarray(v[..., :1]) if isinstance(v, np.ndarray) and v.shape[-1] == 3 else v) for k, v in cols.items()}
+    base["ncol"] = 1
+    o.radiate(base, 0, spectral=False)
+    nzr = cols["nz"]
+    Tm = base["T"][0:2 * nzm:2, 0].copy()
+    Ts0 = float(base["T_surface"][0])
+    ncj = nzm + 1
+    T = np.repeat(Tm[:, None], ncj, axis=1).copy(order="F")
+    Ts = np.full(ncj, Ts0)
+    Ts[0] += 1.0e-2 * Ts0
+    for i in range(nzm):
+        T[i, i + 1] += 1.0e-2 * Tm[i]
+    f = np.zeros((nzm + 1, ncj), order="F")
+    for c in range(ncj):
+        Tr = np.empty(nzr)
+        Tr[0:2 * nzm:2] = T[:, c]; Tr[1:2 * nzm:2] = T[:, c]; Tr[2 * nzm:] = T[nzm - 1, c]
+        pert = dict(base, T_surface=np.array([Ts[c]]), T=np.asfortranarray(Tr[:, None]))
+        ro = o.radiate(pert, 0, compute_solar=False, compute_opacity=False, spectral=False)
+        f[:, c] = ro["f_total"][0:2 * nzm + 1:2, 0] if ro["f_total"].ndim == 2 else ro["f_total"][0:2 * nzm + 1:2]
+    case = str(tmp_path / "case.crtb")
+    blob.write_case(case, tb, pr, cols, gold, jac=dict(T_surface=Ts, T=T, f=f))
+    exe = str(tmp_path / "c_driver")
+    libdir = os.path.join(root, "clima_b200")
+    r = subprocess.run([shutil.which("gcc"), "-std=c99", "-O1", "-I", os.path.join(root, "include"),
+                        os.path.join(root, "tests", "c_driver.c"), "-o", exe, "-L", libdir, "-lclima_rt", "-lm",
+                        "-Wl,-rpath," + libdir, "-Wl,--allow-shlib-undefined"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe, case], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "PASS" in r.stdout, r.stdout + r.stderr
