@@ -285,3 +285,265 @@ def check_same_grid(tables: Dict[str, Tuple[KTable, np.ndarray, np.ndarray]]) ->
         if len(wl) != len(wl0) or not np.allclose(wl, wl0, rtol=1e-10, atol=0.0):
             raise LoaderError(f'k-distribution "{nm}" has different wavelength bins than "{names[0]}"')
     return w0, wl0
+
+
+# =====================================================================================================
+# N2 continued: the remaining readers of clima_radtran_types_create.f90 and the selection logic of
+# create_OpticalProperties.  Every HDF5 reader takes a mapping with the h5py dataset interface.
+# =====================================================================================================
+LOG10TINY = float(np.log10(np.sqrt(np.finfo(np.float64).tiny)))  # src/clima_const.f90:21
+
+
+def read_wavl(h: Mapping, channel: str, filename: str = "bins.h5") -> np.ndarray:
+    """`read_wavl` (types_create.f90:647-687): channel bin edges "sol_wavl" / "ir_wavl" in micron -> nm."""
+    name = {"solar": "sol_wavl", "sol": "sol_wavl", "ir": "ir_wavl"}.get(channel)
+    if name is None:
+        raise LoaderError("read_wavl received an invalid channel_type")
+    return _dataset(h, name, 1, f"{filename}/{name}") * 1.0e3
+
+
+def _rebin_rows(wav_um: np.ndarray, rows: np.ndarray, wavl: np.ndarray, filename: str) -> np.ndarray:
+    """The block repeated in read_h5_Xsection (:1181-1236) and create_WaterContinuum (:945-1040): for
+    every row (one temperature) of log10 values on the file's wavelength grid, pad with `log10tiny`
+    just outside the range and at 0 / huge (four `addpnt`), then bin-average onto the opacity grid
+    with `inter2`.  rows: (n, nwf) -> (n, nw)."""
+    wav = np.asarray(wav_um, dtype=np.float64) * 1.0e3  # micron -> nm
+    n, nwf = rows.shape
+    out = np.empty((n, len(wavl) - 1))
+    rdelta = 1.0e-4
+    for i in range(n):
+        x = np.zeros(nwf + 4)
+        y = np.zeros(nwf + 4)
+        x[:nwf], y[:nwf] = wav, rows[i]
+        try:
+            k = nwf
+            k = addpnt(x, y, k, x[0] * (1.0 - rdelta), LOG10TINY)
+            k = addpnt(x, y, k, 0.0, LOG10TINY)
+            k = addpnt(x, y, k, x[k - 1] * (1.0 + rdelta), LOG10TINY)
+            k = addpnt(x, y, k, np.finfo(np.float64).max, LOG10TINY)
+            out[i] = inter2(wavl, x, y)
+        except LoaderError:
+            raise LoaderError(f'Problem interpolating data in "{filename}"')
+    return out
+
+
+def xsection_from_hdf5(h: Mapping, sp_ind: Sequence[int], wavl: np.ndarray, filename: str = "<memory>"):
+    """`read_h5_Xsection` (types_create.f90:1106-1263; used by create_CIAXsection :1090-1104 and the
+    absorption cross sections): datasets "wavelengths" [micron], "log10xs" (nwf) or (ntemp, nwf),
+    "T" (ntemp).  dim 0 -> xs_0d(nw) = 10**rebinned; dim 1 -> log10 xs (ntemp, nw), interpolated
+    linearly in T at run time."""
+    from ._abi import XS1D
+    if "log10xs" not in h:
+        raise LoaderError(f'{filename}: dataset "log10xs" does not exist')
+    data = np.asarray(h["log10xs"][...], dtype=np.float64)
+    dim = data.ndim - 1
+    if dim not in (0, 1):
+        raise LoaderError(f"Issue reading {filename}")
+    wav = _dataset(h, "wavelengths", 1, filename)
+    if dim == 0:
+        if data.shape[0] != wav.shape[0]:
+            raise LoaderError(f'"log10xs" has a bad dimension in "{filename}"')
+        xs0 = 10.0 ** _rebin_rows(wav, data[None, :], wavl, filename)[0]
+        return XS1D(list(sp_ind), 0, None, xs0)
+    temp = _dataset(h, "T", 1, filename)
+    if data.shape[0] != temp.shape[0]:
+        raise LoaderError(f'"log10xs" has a bad dimension in "{filename}"')
+    return XS1D(list(sp_ind), 1, temp, np.asfortranarray(_rebin_rows(wav, data, wavl, filename)))
+
+
+def water_continuum_from_hdf5(h: Mapping, species_names: Sequence[str], wavl: np.ndarray, model: str = "MT_CKD",
+                              filename: str = "<memory>") -> Dict:
+    """`create_WaterContinuum` (types_create.f90:868-1046): "wavelengths" [micron], "T", "log10xs_H2O" and
+    "log10xs_foreign" (ntemp, nwf).  Returns the keyword arguments of OpacityTables."""
+    species_names = list(species_names)
+    if "H2O" not in species_names:
+        raise LoaderError('"H2O" must be a species to include the "continuum" opacity')
+    if not len(species_names) > 1:
+        raise LoaderError('There must be more than 1 species in order to use the "continuum" opacity')
+    wav = _dataset(h, "wavelengths", 1, filename)
+    temp = _dataset(h, "T", 1, filename)
+    out = dict(cont_LH2O=species_names.index("H2O") + 1, cont_temp=temp)
+    for ds, key in (("log10xs_H2O", "cont_log10_H2O"), ("log10xs_foreign", "cont_log10_foreign")):
+        d = _dataset(h, ds, 2, filename)
+        if d.shape[0] != temp.shape[0]:
+            raise LoaderError(f'"{ds}" has a bad dimension in "{filename}"')
+        out[key] = np.asfortranarray(_rebin_rows(wav, d, wavl, filename))
+    return out
+
+
+def interp_discrete_to_bins(wavl: np.ndarray, wv: np.ndarray, f: np.ndarray, mode: str, fill: float = 0.0) -> np.ndarray:
+    """futils `interp_discrete_to_bins` (v0.1.14, not under /root/reference; restated from its name, its
+    arguments and its two call sites, types_create.f90:830-838 and :1461): discrete samples (wv, f) ->
+    one value per bin of `wavl` = the mean over the bin of the piecewise-linear function through the
+    samples; outside the sampled range the function is held at its end value ('Constant') or set to
+    `fill` ('FillValue').  PARITY UNPINNED like every futils routine."""
+    wavl = np.asarray(wavl, dtype=np.float64)
+    wv = np.asarray(wv, dtype=np.float64)
+    f = np.asarray(f, dtype=np.float64)
+    if np.any(np.diff(wv) <= 0.0):
+        raise LoaderError("interp_discrete_to_bins: wavelengths must be strictly ascending")
+    lo, hi = (f[0], f[-1]) if mode == "Constant" else (fill, fill)
+    if mode not in ("Constant", "FillValue"):
+        raise LoaderError(f'interp_discrete_to_bins: unknown extrapolation "{mode}"')
+    big = np.finfo(np.float64).max
+    x = np.concatenate(([-big, np.nextafter(wv[0], -np.inf)], wv, [np.nextafter(wv[-1], np.inf), big]))
+    y = np.concatenate(([lo, lo], f, [hi, hi]))
+    out = np.empty(len(wavl) - 1)
+    for i in range(len(wavl) - 1):
+        a, b = wavl[i], wavl[i + 1]
+        inner = x[(x > a) & (x < b)]
+        xs = np.concatenate(([a], inner, [b]))
+        ys = np.interp(xs, x, y)
+        out[i] = np.sum(0.5 * (ys[1:] + ys[:-1]) * np.diff(xs)) / (b - a)
+    return out
+
+
+def particle_from_hdf5(h: Mapping, p_ind: int, wavl: np.ndarray, filename: str = "<memory>"):
+    """`create_ParticleXsection` (types_create.f90:734-866): "wavelengths" (on the opacity grid's unit,
+    nm), "radii" [micron -> cm], "w0", "qext", "g0" (nrad, nwf), each row put on the bins with
+    interp_discrete_to_bins(..., 'Constant')."""
+    from ._abi import Particle
+    wv = _dataset(h, "wavelengths", 1, filename)
+    radii = _dataset(h, "radii", 1, filename) / 1.0e4
+    arrs = {}
+    for ds in ("w0", "qext", "g0"):
+        d = _dataset(h, ds, 2, filename)
+        if d.shape != (radii.shape[0], wv.shape[0]):
+            raise LoaderError(f'"{ds}" has the wrong shape in "{filename}"')
+        arrs[ds] = np.asfortranarray(np.stack([interp_discrete_to_bins(wavl, wv, d[i], "Constant")
+                                                for i in range(radii.shape[0])]))
+    return Particle(p_ind, radii, arrs["w0"], arrs["qext"], arrs["g0"])
+
+
+def photolysis_from_hdf5(h: Mapping, sp_ind: int, wavl: np.ndarray, filename: str = "<memory>"):
+    """`create_PhotolysisXsection` (types_create.f90:1407-1468): "wavelengths", "photoabsorption";
+    log10(max(xs, tiny)) on the bins with interp_discrete_to_bins(..., 'FillValue', log10tiny), then 10**."""
+    from ._abi import XS1D
+    wv = _dataset(h, "wavelengths", 1, filename)
+    xs = _dataset(h, "photoabsorption", 1, filename)
+    lx = np.log10(np.maximum(xs, np.finfo(np.float64).tiny))
+    return XS1D([sp_ind], 0, None, 10.0 ** interp_discrete_to_bins(wavl, wv, lx, "FillValue", LOG10TINY))
+
+
+def parse_optical_properties(settings: Mapping) -> Dict:
+    """The `optical-properties` block of settings.yaml as `unpack_settingsopacity` reads it
+    (src/clima_types_create.f90:760-960): species lists, k-method, and per opacity either `true`/`false`
+    (everything the data directory offers) or an explicit list."""
+    op = settings.get("optical-properties")
+    if op is None:
+        raise LoaderError('"optical-properties" is required in the settings file')
+    sp = op.get("species", {})
+    out = dict(gases=list(sp.get("gases", [])), particles=list(sp.get("particles", []) or []),
+               k_method=op.get("k-method", "RandomOverlapResortRebin"), number_of_bins=op.get("number-of-bins"),
+               wavelength_bins_file=op.get("wavelength-bins-file"))
+    if out["k_method"] not in ("RandomOverlapResortRebin", "AdaptiveEquivalentExtinction"):
+        raise LoaderError(f'k-method "{out["k_method"]}" is not an option.')
+    oc = op.get("opacities", {})
+    for key, name in (("k-distributions", "k"), ("CIA", "cia"), ("rayleigh", "rayleigh"), ("photolysis-xs", "pxs")):
+        v = oc.get(key)
+        if isinstance(v, bool):
+            out[name] = v
+        elif v is None:
+            out[name] = False
+        else:
+            v = list(v)
+            if len(set(v)) != len(v):
+                raise LoaderError(f'duplicate in optical-properties/opacities/{key}')
+            out[name] = v
+    wc = oc.get("water-continuum")
+    out["water_continuum"] = wc if isinstance(wc, str) else None
+    out["particle_xs"] = [dict(name=p["name"], dat=p.get("data", p["name"])) for p in (oc.get("particle-xs") or [])]
+    return out
+
+
+def build_tables(settings: Mapping, data: Mapping, star_file: str):
+    """`create_OpticalProperties` (types_create.f90:272-645) + the two `create_RTChannel` + `read_stellar_flux`
+    of `create_Radtran_2` (clima_radtran.f90:128-219): settings dict (parsed YAML) + data directory ->
+    OpacityTables.  `data` maps a path relative to the data directory ("kdistributions/H2O.h5",
+    "CIA/CO2-CO2.h5", "rayleigh/rayleigh.yaml", "kdistributions/bins.h5", ...) to an opened HDF5-like
+    mapping (or, for the YAML file, its parsed dict); a missing key is a missing file."""
+    from ._abi import OpacityTables
+    so = parse_optical_properties(settings)
+    species, particles = so["gases"], so["particles"]
+
+    def listing(kind, folder, names):
+        if kind is True:
+            return [n for n in names if f"{folder}/{n}.h5" in data]
+        return list(kind) if kind else []
+
+    # k-distributions (:300-380)
+    knames = listing(so["k"], "kdistributions", species)
+    if so["k"] is True and not knames:
+        raise LoaderError("No k-distribution data was found, but at least one k-distribution is needed.")
+    if not knames:
+        raise LoaderError("You must specify at least one k-distribution in the settings file.")
+    tabs = {}
+    for n in knames:
+        if n not in species:
+            raise LoaderError(f'Species "{n}" in optical property "k-distributions" is not in the list of species.')
+        tabs[n] = ktable_from_hdf5(data[f"kdistributions/{n}.h5"], species.index(n) + 1, f"kdistributions/{n}.h5")
+    weights, wavl = check_same_grid(tabs)
+    # CIA (:384-460): with `true` every pair the directory offers, minus the H2O pairs when the water
+    # continuum is on (:431-432)
+    if so["cia"] is True:
+        pairs = [f"{a}-{b}" for a in species for b in species if f"CIA/{a}-{b}.h5" in data
+                 and not (so["water_continuum"] and "H2O" in (a, b))]
+    else:
+        pairs = list(so["cia"]) if so["cia"] else []
+    cia = []
+    for pr in pairs:
+        a, _, b = pr.partition("-")
+        if a not in species or b not in species:
+            raise LoaderError(f'CIA pair "{pr}" contains a species that is not in the list of species.')
+        if so["water_continuum"] and "H2O" in (a, b):
+            raise LoaderError(f'Optical property "water-continuum" is set, but CIA "{pr}" is also set.')
+        cia.append(xsection_from_hdf5(data[f"CIA/{pr}.h5"], [species.index(a) + 1, species.index(b) + 1], wavl, f"CIA/{pr}.h5"))
+    # Rayleigh (:470-530)
+    ray_ind, ray_xs = [], None
+    if so["rayleigh"]:
+        ry = data.get("rayleigh/rayleigh.yaml")
+        if ry is None:
+            raise LoaderError('There is an issue with formatting in "rayleigh/rayleigh.yaml"')
+        if so["rayleigh"] is not True:
+            for n in so["rayleigh"]:
+                if n not in species:
+                    raise LoaderError(f'Species "{n}" in optical property "rayleigh" is not in the list of species.')
+                if n not in ry:
+                    raise LoaderError(f'There is an issue with formatting in "rayleigh/rayleigh.yaml"')
+            ry = {n: ry[n] for n in so["rayleigh"]}
+        ray_ind, ray_xs = rayleigh_table(ry, species, wavl, "rayleigh/rayleigh.yaml")
+    # photolysis cross sections (:540-580)
+    pnames = listing(so["pxs"], "xsections", species)
+    pxs = []
+    for n in pnames:
+        if n not in species:
+            raise LoaderError(f'Species "{n}" in optical property "photolysis-xs" is not in the list of species.')
+        if f"xsections/{n}.h5" not in data:
+            raise LoaderError(f'Species "{n}" does not have photolysis xsection data')
+        pxs.append(photolysis_from_hdf5(data[f"xsections/{n}.h5"], species.index(n) + 1, wavl, f"xsections/{n}.h5"))
+    # particles (:586-600)
+    part = []
+    for p in so["particle_xs"]:
+        if p["name"] not in particles:
+            raise LoaderError(f'Species "{p["name"]}" in optical property "particle-xs" is not in the list of particles.')
+        fn = f'aerosol_xsections/{p["dat"]}/mie_{p["dat"]}.h5'
+        if fn not in data:
+            raise LoaderError(f"Was unable to open mie data file {fn}")
+        part.append(particle_from_hdf5(data[fn], particles.index(p["name"]) + 1, wavl, fn))
+    kw = {}
+    if so["water_continuum"]:
+        fn = f'water_continuum/{so["water_continuum"]}.h5'
+        if fn not in data:
+            raise LoaderError(f'Continuum "{so["water_continuum"]}" is not avaliable.')
+        kw.update(water_continuum_from_hdf5(data[fn], species, wavl, so["water_continuum"], fn))
+    # channels (:226-270) and the stellar flux on the solar channel's bins (clima_radtran.f90:172-180)
+    bins = so["wavelength_bins_file"] or "kdistributions/bins.h5"
+    if bins not in data:
+        raise LoaderError(f'Failed to read "{bins}".')
+    ir_ind = channel_indices(read_wavl(data[bins], "ir", bins), wavl, bins)
+    sol_wavl = read_wavl(data[bins], "solar", bins)
+    sol_ind = channel_indices(sol_wavl, wavl, bins)
+    photons = read_stellar_flux(star_file, sol_wavl)
+    return OpacityTables(wavl=wavl, species_names=list(species), particle_names=list(particles), weights=weights,
+                         k=[tabs[n][0] for n in knames], cia=cia, ray_sp_ind=ray_ind, ray_xs=ray_xs, pxs=pxs, part=part,
+                         ir_ind=ir_ind, sol_ind=sol_ind, photons_sol=photons, **kw)

@@ -138,3 +138,161 @@ def test_ktable_schema_roundtrip_and_errors():
         loader.check_same_grid(bad)
     with pytest.raises(LoaderError, match="h5py"):
         loader.open_hdf5("/nonexistent.h5")
+
+
+# ------------------------------------------------------------------ N2: the remaining readers
+class _DS:
+    """stand-in for an h5py dataset: `f[name][...]`"""
+    def __init__(self, a): self.a = np.asarray(a)
+    def __getitem__(self, k): return self.a
+
+
+def _h5(**kw):
+    return {k: _DS(v) for k, v in kw.items()}
+
+
+def _fake_datadir(tb, extra_cia=("H2O-H2O",)):
+    """An in-memory data directory in the reference's schema, generated FROM synthetic tables so that
+    build_tables can be checked against them: k-tables as h5py would show them (C-ordered transpose),
+    CIA / continuum / photolysis / Mie on finer file grids, rayleigh.yaml, bins.h5."""
+    G, nw = tb.ngauss, tb.nw
+    data = {}
+    wl_um = tb.wavl / 1.0e3
+    for k in tb.k:
+        name = tb.species_names[k.sp_ind - 1]
+        data[f"kdistributions/{name}.h5"] = _h5(weights=tb.weights, log10P=k.log10P, T=k.temp, wavelengths=wl_um,
+                                               log10k=np.ascontiguousarray(np.asarray(k.log10k).transpose(3, 2, 1, 0)))
+    fine = np.geomspace(wl_um[0] * 1.001, wl_um[-1] * 0.999, 900)
+    rng = np.random.default_rng(4)
+    for a, b in (("CO2", "CO2"), ("N2", "N2"), ("H2O", "H2O")):
+        T = np.linspace(150.0, 800.0, 7)
+        data[f"CIA/{a}-{b}.h5"] = _h5(wavelengths=fine, T=T, log10xs=-46.0 + np.sin(3.0 * np.log10(fine))[None, :] + 1e-3 * T[:, None])
+    data["CIA/N2-H2.h5"] = _h5(wavelengths=fine, log10xs=-47.0 + 0.5 * np.cos(2.0 * np.log10(fine)))
+    Tc = np.linspace(200.0, 700.0, 9)
+    data["water_continuum/MT_CKD.h5"] = _h5(wavelengths=fine, T=Tc, log10xs_H2O=-42.0 - 1e-3 * Tc[:, None] + 0.0 * fine[None, :],
+                                            log10xs_foreign=-44.0 + 0.3 * np.sin(np.log10(fine))[None, :] + 0.0 * Tc[:, None])
+    wv_nm = np.geomspace(150.0, 400.0, 60)
+    data["xsections/O2.h5"] = _h5(wavelengths=wv_nm, photoabsorption=1e-19 * np.exp(-(wv_nm - 150.0) / 40.0))
+    r_um = np.geomspace(0.01, 10.0, 8)
+    wv_mie = np.geomspace(tb.wavl[0] * 1.01, tb.wavl[-1] * 0.99, 120)
+    data["aerosol_xsections/khare1984/mie_khare1984.h5"] = _h5(
+        wavelengths=wv_mie, radii=r_um, w0=rng.uniform(0.1, 0.9, (8, 120)), qext=rng.uniform(0.5, 3.0, (8, 120)),
+        g0=rng.uniform(0.0, 0.8, (8, 120)))
+    data["rayleigh/rayleigh.yaml"] = {"N2": {"data": {"Delta": 0.0305, "A": 29.06e-5, "B": 7.7e-3}},
+                                      "CO2": {"data": {"Delta": 0.0805, "A": 43.9e-5, "B": 6.4e-3}},
+                                      "Ar": {"data": {"Delta": 0.0006, "A": 27.92e-5, "B": 5.6e-3}}}
+    data["kdistributions/bins.h5"] = _h5(sol_wavl=wl_um[tb.sol_ind[0] - 1:tb.sol_ind[1] + 1],
+                                         ir_wavl=wl_um[tb.ir_ind[0] - 1:tb.ir_ind[1] + 1])
+    return data
+
+
+def test_xsection_reader_rebins_log10_values_and_pads_with_log10tiny():
+    wavl = np.geomspace(200.0, 20000.0, 25)
+    wf = np.geomspace(0.5, 10.0, 300)  # micron: covers 500 nm .. 10 um only
+    xs = loader.xsection_from_hdf5(_h5(wavelengths=wf, log10xs=np.full(300, -45.0)), [1, 2], wavl)
+    assert xs.dim == 0 and xs.data.shape == (24,)
+    inside = (wavl[:-1] >= 500.0) & (wavl[1:] <= 10000.0)
+    np.testing.assert_allclose(xs.data[inside], 1.0e-45, rtol=1e-12)
+    outside = (wavl[1:] < 499.0) | (wavl[:-1] > 10002.0)
+    np.testing.assert_allclose(np.log10(xs.data[outside]), loader.LOG10TINY, rtol=1e-12)  # the padding value
+    T = np.array([100.0, 300.0, 900.0])
+    x1 = loader.xsection_from_hdf5(_h5(wavelengths=wf, T=T, log10xs=-44.0 - 1e-3 * T[:, None] + 0.0 * wf[None, :]), [3, 3], wavl)
+    assert x1.dim == 1 and x1.data.shape == (3, 24) and np.isfortran(x1.data)
+    np.testing.assert_allclose(x1.data[:, inside], (-44.0 - 1e-3 * T)[:, None] * np.ones((1, inside.sum())), rtol=1e-12)
+    with pytest.raises(LoaderError, match="log10xs"):
+        loader.xsection_from_hdf5(_h5(wavelengths=wf), [1, 1], wavl)
+    with pytest.raises(LoaderError, match="bad dimension"):
+        loader.xsection_from_hdf5(_h5(wavelengths=wf, T=T, log10xs=np.zeros((2, 300))), [1, 1], wavl)
+
+
+def test_interp_discrete_to_bins_modes():
+    wavl = np.array([0.0, 1.0, 2.0, 4.0, 8.0])
+    wv = np.array([1.5, 2.5, 3.5])
+    f = np.array([10.0, 20.0, 30.0])
+    c = loader.interp_discrete_to_bins(wavl, wv, f, "Constant")
+    assert c[0] == pytest.approx(10.0) and c[3] == pytest.approx(30.0)       # held at the end values
+    assert c[2] == pytest.approx((0.5 * (15.0 + 20.0) * 0.5 + 0.5 * (20.0 + 30.0) * 1.0 + 30.0 * 0.5) / 2.0)
+    z = loader.interp_discrete_to_bins(wavl, wv, f, "FillValue", -5.0)
+    assert z[0] == pytest.approx(-5.0, abs=1e-9) and z[3] == pytest.approx(-5.0, abs=1e-9)
+    with pytest.raises(LoaderError):
+        loader.interp_discrete_to_bins(wavl, wv[::-1], f, "Constant")
+
+
+def test_parse_optical_properties_of_the_reference_templates():
+    """The `optical-properties` blocks of the reference's own templates (inline copies, and the files
+    themselves where /root/reference exists)."""
+    import os
+    import yaml
+    modern_earth = yaml.safe_load("""
+optical-properties:
+  species:
+    gases: [H2O, CO2, O2, N2, O3, CH4]
+    particles: [HCaer1]
+  k-method: RandomOverlapResortRebin
+  opacities: {k-distributions: true, CIA: true, rayleigh: true, photolysis-xs: true,
+    water-continuum: MT_CKD}
+""")
+    so = loader.parse_optical_properties(modern_earth)
+    assert so["gases"] == ["H2O", "CO2", "O2", "N2", "O3", "CH4"] and so["particles"] == ["HCaer1"]
+    assert so["k"] is True and so["cia"] is True and so["rayleigh"] is True and so["pxs"] is True
+    assert so["water_continuum"] == "MT_CKD" and so["particle_xs"] == []
+    for rel in ("templates/ModernEarth/settings.yaml", "templates/AdiabatClimate/Earth/settings.yaml",
+                "tests/settings_RCE_test.yaml"):
+        path = os.path.join("/root/reference", rel)
+        if os.path.exists(path):
+            s2 = loader.parse_optical_properties(yaml.safe_load(open(path)))
+            assert s2["k_method"] == "RandomOverlapResortRebin" and len(s2["gases"]) >= 3
+    with pytest.raises(LoaderError, match="k-method"):
+        loader.parse_optical_properties({"optical-properties": {"k-method": "Nope", "species": {"gases": ["H2O"]}}})
+    with pytest.raises(LoaderError, match="required"):
+        loader.parse_optical_properties({})
+
+
+def test_build_tables_from_a_data_directory(tmp_path):
+    """create_OpticalProperties + create_RTChannel + read_stellar_flux on an in-memory data directory:
+    `true` selects what the directory offers, the H2O CIA pair is dropped because the water continuum is
+    on (types_create.f90:431-432), explicit lists are honoured, the k-tables come back bit for bit, and
+    the result drives the CPU oracle."""
+    import sys, os
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from oracle_lib import OracleRadtran
+    tb0 = synth.make_tables(nw=14, G=8, nk=3, npress=6, ntemp=5, n_sol=9, ir_start=5)
+    data = _fake_datadir(tb0)
+    star = tmp_path / "star.txt"
+    lam = np.geomspace(100.0, 6.0e5, 500)
+    star.write_text("Wavelength (nm)  flux\n" + "\n".join(f"{a:.8e} {1.0e3 * np.exp(-a / 2000.0) + 1e-3:.8e}" for a in lam) + "\n")
+    settings = {"optical-properties": {"species": {"gases": list(tb0.species_names), "particles": ["haze"]},
+                                       "k-method": "RandomOverlapResortRebin",
+                                       "opacities": {"k-distributions": True, "CIA": True, "rayleigh": True, "photolysis-xs": True,
+                                                     "water-continuum": "MT_CKD",
+                                                     "particle-xs": [{"name": "haze", "data": "khare1984"}]}}}
+    tb = loader.build_tables(settings, data, str(star))
+    assert [tb.species_names[k.sp_ind - 1] for k in tb.k] == [tb0.species_names[k.sp_ind - 1] for k in tb0.k]
+    for k, k0 in zip(tb.k, tb0.k):
+        assert np.array_equal(k.log10k, k0.log10k) and np.array_equal(k.log10P, k0.log10P)
+    np.testing.assert_allclose(tb.wavl, tb0.wavl, rtol=1e-14)
+    pairs = [(tb.species_names[c.sp_ind[0] - 1], tb.species_names[c.sp_ind[1] - 1]) for c in tb.cia]
+    assert ("CO2", "CO2") in pairs and ("N2", "N2") in pairs and ("N2", "H2") in pairs
+    assert not any("H2O" in p for p in pairs)
+    assert [tb.species_names[i - 1] for i in tb.ray_sp_ind] == ["CO2", "N2"]  # species order; Ar is not a species
+    assert len(tb.pxs) == 1 and tb.species_names[tb.pxs[0].sp_ind[0] - 1] == "O2"
+    assert tb.cont_LH2O == tb.species_names.index("H2O") + 1 and tb.cont_log10_H2O.shape == (9, 14)
+    assert len(tb.part) == 1 and tb.part[0].w0.shape == (8, 14) and tb.part[0].radii[0] == pytest.approx(1.0e-6)
+    assert tb.ir_ind == tb0.ir_ind and tb.sol_ind == tb0.sol_ind and tb.photons_sol.shape == (tb0.nw_sol,)
+    # explicit lists
+    s2 = {"optical-properties": {"species": {"gases": list(tb0.species_names)},
+                                 "opacities": {"k-distributions": ["CO2"], "CIA": ["CO2-CO2"], "rayleigh": ["N2"]}}}
+    t2 = loader.build_tables(s2, data, str(star))
+    assert len(t2.k) == 1 and len(t2.cia) == 1 and t2.ray_sp_ind == [tb0.species_names.index("N2") + 1] and t2.cont_LH2O == 0
+    with pytest.raises(LoaderError, match="water-continuum"):
+        loader.build_tables({"optical-properties": {"species": {"gases": list(tb0.species_names)},
+                                                    "opacities": {"k-distributions": True, "CIA": ["H2O-H2O"],
+                                                                  "water-continuum": "MT_CKD"}}}, data, str(star))
+    with pytest.raises(LoaderError, match="at least one k-distribution"):
+        loader.build_tables({"optical-properties": {"species": {"gases": ["Xe"]}, "opacities": {"k-distributions": True}}},
+                            data, str(star))
+    # the packed tables drive the checker end to end (1 particle species in the model)
+    pr = synth.default_params(tb, nzenith=2)
+    cols = synth.make_columns(2, nz=6, seed=3, doubled=False, npart=1)
+    r = OracleRadtran(tb, pr).radiate_batch(cols)
+    assert np.all(np.isfinite(r["fup_n_ir"])) and np.all(r["OLR"] > 0)
