@@ -241,7 +241,9 @@ optical-properties:
         path = os.path.join("/root/reference", rel)
         if os.path.exists(path):
             s2 = loader.parse_optical_properties(yaml.safe_load(open(path)))
-            assert s2["k_method"] == "RandomOverlapResortRebin" and len(s2["gases"]) >= 3
+            assert s2["k_method"] == "RandomOverlapResortRebin" and s2["k"] is True and s2["water_continuum"] == "MT_CKD"
+            # AdiabatClimate settings take their species from species.yaml, not from this block
+            assert rel.startswith("templates/ModernEarth") == (len(s2["gases"]) > 0)
     with pytest.raises(LoaderError, match="k-method"):
         loader.parse_optical_properties({"optical-properties": {"k-method": "Nope", "species": {"gases": ["H2O"]}}})
     with pytest.raises(LoaderError, match="required"):
