@@ -839,3 +839,39 @@ def test_c_driver_runs_the_abi_without_python(tmp_path):
     assert r.returncode == 0, r.stderr
     r = subprocess.run([exe, case], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "PASS" in r.stdout, r.stdout + r.stderr
+
+
+def test_cfg4_jacobian_batch_at_nz50():
+    """BASELINE.json configs[3] at its real size: nz = 50 model layers (nz_r = 102), Z = 1, albedo 0.3,
+    51 perturbed columns (dT = 1e-2 T, `epsj`, clima_adiabat.f90:139), S-canon tables.  The batched entry
+    against the reference loop run by the oracle, column by column."""
+    nzm = 50
+    tb = synth.make_tables()
+    pr = synth.default_params(tb, nzenith=1, albedo=0.3)
+    base = synth.make_columns(1, nz=nzm, doubled=True, T_surf_range=(288.0, 288.0))
+    g = Radtran(tb, pr)
+    o = OracleRadtran(tb, pr)
+    g.radiate_batch(base)
+    o.radiate(base, 0, spectral=False)
+    nzr = base["nz"]
+    assert nzr == 2 * nzm + 2
+    Tm = base["T"][0:2 * nzm:2, 0].copy()
+    Ts0 = float(base["T_surface"][0])
+    ncol = nzm + 1
+    T = np.repeat(Tm[:, None], ncol, axis=1).copy(order="F")
+    Ts = np.full(ncol, Ts0)
+    Ts[0] += 1.0e-2 * Ts0
+    for i in range(nzm):
+        T[i, i + 1] += 1.0e-2 * Tm[i]
+    f = g.jacobian_batch(Ts, T)
+    assert f.shape == (nzm + 1, ncol)
+    scale = 0.0
+    ref = np.zeros_like(f)
+    for c in range(ncol):
+        Tr = np.empty(nzr)
+        Tr[0:2 * nzm:2] = T[:, c]; Tr[1:2 * nzm:2] = T[:, c]; Tr[2 * nzm:] = T[nzm - 1, c]
+        pert = dict(base, T_surface=np.array([Ts[c]]), T=np.asfortranarray(Tr[:, None]))
+        ro = o.radiate(pert, 0, compute_solar=False, compute_opacity=False, spectral=False)
+        ref[:, c] = ro["f_total"][0:2 * nzm + 1:2, 0]
+        scale = max(scale, float(np.max(np.abs(ro["fup_n_ir"]))))
+    assert np.max(np.abs(f - ref)) <= TOL * scale

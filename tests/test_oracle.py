@@ -96,6 +96,43 @@ def test_rebin_conserves_the_integral_and_is_identity_on_equal_bins(lib):
     assert np.allclose(same, old_v, rtol=1e-14, atol=0)
 
 
+def test_rebin_against_brute_force_integration(lib):
+    """The oracle's `rebin` (a reconstruction: futils is not on the box) against numerical integration of
+    the piecewise-constant function it stands for -- a midpoint sum on a grid 200x finer than the finest
+    bin -- on random, unaligned, tie-laden bins: zero-width old bins (repeated edges), new edges that
+    coincide with old ones, and new bins narrower than an old bin."""
+    rng = np.random.default_rng(7)
+    for trial in range(12):
+        n_old = int(rng.integers(3, 40))
+        n_new = int(rng.integers(1, 12))
+        w = rng.uniform(0.0, 1.0, n_old)
+        w[rng.uniform(size=n_old) < 0.2] = 0.0          # zero-width old bins
+        if w.sum() == 0.0:
+            w[0] = 1.0
+        old_e = np.concatenate(([0.0], np.cumsum(w / w.sum()))); old_e[-1] = 1.0
+        old_v = 10.0 ** rng.uniform(-3, 3, n_old)
+        inner = np.sort(rng.uniform(0.0, 1.0, n_new - 1))
+        take = rng.uniform(size=n_new - 1) < 0.3          # some new edges sit exactly on old edges
+        inner[take] = rng.choice(old_e[1:-1], size=int(take.sum())) if n_old > 2 else inner[take]
+        new_e = np.concatenate(([0.0], np.sort(inner), [1.0]))
+        if np.any(np.diff(new_e) <= 0.0):
+            continue
+        new_v = np.zeros(n_new)
+        lib.oracle_rebin(_d(old_e), _d(old_v), _i(n_old), _d(new_e), _d(new_v), _i(n_new))
+        # brute force: f(x) = old_v[j] on [old_e[j], old_e[j+1]); exact integral per new bin by splitting
+        # at every old edge, cross-checked by a fine midpoint sum
+        for i in range(n_new):
+            a, b = new_e[i], new_e[i + 1]
+            cuts = np.unique(np.concatenate(([a, b], old_e[(old_e > a) & (old_e < b)])))
+            mids = 0.5 * (cuts[1:] + cuts[:-1])
+            j = np.clip(np.searchsorted(old_e, mids, side="right") - 1, 0, n_old - 1)
+            exact = np.sum(old_v[j] * np.diff(cuts)) / (b - a)
+            assert new_v[i] == pytest.approx(exact, rel=1e-12), (trial, i)
+            xs = a + (np.arange(4000) + 0.5) * (b - a) / 4000.0
+            jj = np.clip(np.searchsorted(old_e, xs, side="right") - 1, 0, n_old - 1)
+            assert new_v[i] == pytest.approx(np.mean(old_v[jj]), rel=2e-2 if n_old > 1 else 1e-12)
+
+
 def test_weights_to_bins(lib):
     w = np.array([0.1, 0.2, 0.3, 0.4]); b = np.zeros(5)
     lib.oracle_weights_to_bins(_d(w), _i(4), _d(b))
