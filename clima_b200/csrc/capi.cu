@@ -69,7 +69,7 @@ struct Handle {
   int rorr_exact_only = 0;  // CLIMA_RT_RORR=exact
   int rorr_sort = 0;        // CLIMA_RT_RORR=sort: the sorting kernels instead of the staircase kernel
   int rorr_chain_env = -1;  // CLIMA_RT_RORR_CHAIN=slot|col forces the chain direction (0 / 1)
-  int rorr_chain_len = 256; // CLIMA_RT_RORR_CHAIN_LEN: columns per chain (column chains)
+  int rorr_chain_len = 512; // CLIMA_RT_RORR_CHAIN_LEN: columns per chain (column chains)
   int rorr_cut_mincols = 16;
   int last_rorr_kernel = 0; // 0 staircase (slot chains), 1 staircase (column chains), 2 sort, 3 exact
   int64_t rorr_units = 0, rorr_exact_units = 0, rorr_overflows = 0;

@@ -231,6 +231,8 @@ __device__ __noinline__ void cut_bisect(const unsigned ua, const unsigned cnt, c
   long long lo = __double_as_longlong(__dadd_rn(lds_f64(ua + C::AT * 8u), lds_f64(ua + (C::BX + 1) * 8u)));
   long long hi = __double_as_longlong(__dadd_rn(lds_f64(ua + (unsigned)(C::AT + G - 1) * 8u), lds_f64(ua + (unsigned)(C::BX + G) * 8u)));
   int nlo = 0, nhi = G * G;
+  // plain bisection: regula falsi on (pattern, cumulative weight) was tried and is slower (26 against
+  // 17 steps on average: the weight below t is a staircase with long flats in the pattern)
 #pragma unroll 1
   for (int it = 0; it < C::NBIS && hi - lo > 1 && nhi - nlo > 3; it++) {
     const double t = __longlong_as_double(lo + ((hi - lo) >> 1));
@@ -432,13 +434,16 @@ rorr_cut_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ De
         triv = !(tb.pad0 & 1) && (urow || ucol);
         if (__any_sync(0xffffffffu, triv)) {
           const double bmean = lds_f64(ua + (C::SB + C::pos_of((unsigned)G)) * 8u);  // <b> = Sb[G]
-          double amean = __dmul_rn(wl, am);  // <a>, summed like Sb
+          double amean = 0.0;
+          if (__any_sync(0xffffffffu, triv && !urow)) {  // <a>, summed like Sb; rarely needed
+            amean = __dmul_rn(wl, am);
 #pragma unroll
-          for (int d = 1; d < P; d <<= 1) {
-            const double t = __shfl_up_sync(0xffffffffu, amean, d, P);
-            if (ul >= d) amean = __dadd_rn(amean, t);
+            for (int d = 1; d < P; d <<= 1) {
+              const double t = __shfl_up_sync(0xffffffffu, amean, d, P);
+              if (ul >= d) amean = __dadd_rn(amean, t);
+            }
+            amean = __shfl_sync(0xffffffffu, amean, G - 1, P);
           }
-          amean = __shfl_sync(0xffffffffu, amean, G - 1, P);
           cf = urow ? __dadd_rn(am, bmean) : __dadd_rn(v, amean);
         }
       }
