@@ -44,6 +44,9 @@
 #ifndef CUT_MIN_BLOCKS
 #define CUT_MIN_BLOCKS 6  // 80 registers, 24 warps per SM
 #endif
+#ifndef CUT_UNIT_PAD
+#define CUT_UNIT_PAD 0
+#endif
 #ifndef CUT_ROW_UNROLL
 #define CUT_ROW_UNROLL 1  // count words (4 rows) per trip of the pass loop: fully unrolled it needs 168 registers
 #endif
@@ -71,7 +74,7 @@ struct Cfg {
   static constexpr int WB = SB + NPOS;       //              Wb[c] = sum_{j<c} w_j   (static)
   static constexpr int AT = WB + NPOS;       // a[0..P-1]
   static constexpr int TT = AT + P;          // scratch: total tau of the unit (band sum)
-  static constexpr int UNIT = TT + P;        // doubles per unit
+  static constexpr int UNIT = TT + P + CUT_UNIT_PAD;  // doubles per unit (the pad sets the bank offset between the units of a warp)
   static constexpr int NBIS = 44;            // cap on the bisection steps of a cold start (a plateau of nearly equal rows needs ~25 to get inside it)
   static constexpr int MAXPASS = 48;         // passes before a restart from bisection / giving up
   static constexpr int SINGLES = 8;          // single-element moves of a lane before it jumps by tie groups
