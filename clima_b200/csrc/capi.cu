@@ -90,6 +90,19 @@ struct Handle {
   double *d_send = nullptr, *d_recv = nullptr;  // result block of this rank / of all ranks
   size_t comm_block = 0;                        // doubles per rank the buffers hold
 
+  // N1 fast path (jacobian_delta.cu): the base column's radiative-grid temperatures and f_total, the
+  // shared factorisation, per-call work buffers
+  double *d_baseT = nullptr, *d_basef = nullptr, *d_factor = nullptr;
+  int base_nz = 0;
+  bool base_valid = false, factor_valid = false;
+  size_t factor_doubles = 0;
+  double *d_jTm = nullptr, *d_jTs = nullptr, *d_jpartial = nullptr, *d_jout = nullptr;
+  int *d_jwin = nullptr, *d_jflag = nullptr;
+  size_t jac_cap_cols = 0, jac_cap_partial = 0;
+  int jac_cap_nzm = 0;
+  int jac_delta = 1;  // CLIMA_RT_JAC=full: every column through the full IR solve (the round-1 path)
+  int64_t jac_delta_calls = 0, jac_full_calls = 0;
+
   // introspection
   int64_t launches = 0;
   int last_unit_order = 0;  // RORR unit order of the last chunk: 0 column-grouped, 1 slot-fastest
@@ -620,6 +633,25 @@ void radiate_batch_impl(Handle &h, bool device, int ncol, int nz, int ng, int np
     if (compute_opacity) {
       h.retained_opacity_ncol = (ncol <= C) ? ncol : 0;
       h.retained_nz = nz;
+      // a single column with fresh opacity is a candidate base of a finite-difference Jacobian: keep
+      // its temperatures and f_total for the delta path of clima_rt_jacobian_batch
+      h.base_valid = false;
+      h.factor_valid = false;
+      if (ncol == 1 && h.jac_delta) {
+        if (h.base_nz != nz) {
+          if (h.d_baseT) cudaFree(h.d_baseT);
+          if (h.d_basef) cudaFree(h.d_basef);
+          h.d_baseT = h.d_basef = nullptr;
+          CK(cudaMalloc(&h.d_baseT, (size_t)(nz + 1) * 8));
+          CK(cudaMalloc(&h.d_basef, (size_t)(nz + 1) * 8));
+          h.base_nz = nz;
+        }
+        CK(cudaMemcpyAsync(h.d_baseT, h.ch.T, (size_t)nz * 8, cudaMemcpyDeviceToDevice, h.st));
+        CK(cudaMemcpyAsync(h.d_baseT + nz, h.ch.T_surface, 8, cudaMemcpyDeviceToDevice, h.st));
+        CK(cudaMemcpyAsync(h.d_basef, h.fx.f_total, (size_t)(nz + 1) * 8, cudaMemcpyDeviceToDevice, h.st));
+        CK(cudaStreamSynchronize(h.st));
+        h.base_valid = true;
+      }
     }
     if (compute_solar) {
       h.retained_solar_ncol = (ncol <= C) ? ncol : 0;
@@ -667,6 +699,66 @@ __global__ void extract_ftotal_kernel(const double *__restrict__ fr, double *__r
   }
 }
 
+// N1 fast path: all columns share the base column's frozen opacity, hence ONE factorisation of the
+// two-stream matrix per (bin, g); each column is a delta solve against the base (jacobian_delta.cu).
+// Returns false when a column differs from the base in more levels than the window holds (the caller
+// then takes the full solve for the whole call).  Leaves the handle's retained state untouched.
+bool jacobian_delta(Handle &h, int ncol, int nzm, const double *T_surface, const double *T, double *f_total) {
+  const int nzr = 2 * nzm + 2;
+  DevChunk &ch = h.ch;  // holds the base column's opacity in column 0
+  if (!h.factor_valid) {
+    const size_t need = rt_jac_factor_doubles(h.tb, nzr);
+    if (need > h.factor_doubles) {
+      if (h.d_factor) cudaFree(h.d_factor);
+      h.d_factor = nullptr;
+      CK(cudaMalloc(&h.d_factor, need * 8));
+      h.factor_doubles = need;
+    }
+    DevChunk bc = ch;
+    bc.ncol = 1;
+    bc.nz = nzr;
+    rt_launch_jac_factor(h.tb, h.pr, bc, h.d_factor, h.st);
+    h.launches++;
+    h.factor_valid = true;
+  }
+  const int nsplit = rt_jac_splits(h.tb, ncol, h.num_sms);
+  if ((size_t)ncol > h.jac_cap_cols || nzm != h.jac_cap_nzm) {
+    for (double **p : {&h.d_jTm, &h.d_jTs, &h.d_jout}) { if (*p) cudaFree(*p); *p = nullptr; }
+    if (h.d_jwin) cudaFree(h.d_jwin);
+    h.d_jwin = nullptr;
+    CK(cudaMalloc(&h.d_jTm, (size_t)ncol * nzm * 8));
+    CK(cudaMalloc(&h.d_jTs, (size_t)ncol * 8));
+    CK(cudaMalloc(&h.d_jout, (size_t)ncol * (nzm + 1) * 8));
+    CK(cudaMalloc(&h.d_jwin, (size_t)ncol * 2 * sizeof(int)));
+    if (!h.d_jflag) CK(cudaMalloc(&h.d_jflag, sizeof(int)));
+    h.jac_cap_cols = ncol;
+    h.jac_cap_nzm = nzm;
+  }
+  const size_t np = (size_t)nsplit * ncol * (nzm + 1);
+  if (np > h.jac_cap_partial) {
+    if (h.d_jpartial) cudaFree(h.d_jpartial);
+    h.d_jpartial = nullptr;
+    CK(cudaMalloc(&h.d_jpartial, np * 8));
+    h.jac_cap_partial = np;
+  }
+  record(h, 0); record(h, 5); record(h, 1);
+  CK(cudaMemcpyAsync(h.d_jTs, T_surface, (size_t)ncol * 8, cudaMemcpyHostToDevice, h.st));
+  CK(cudaMemcpyAsync(h.d_jTm, T, (size_t)ncol * nzm * 8, cudaMemcpyHostToDevice, h.st));
+  rt_launch_jac_delta(h.tb, h.pr, nzm, ncol, h.d_jTm, h.d_jTs, h.d_baseT, h.d_factor, h.d_jwin, h.d_jflag,
+                      h.d_jpartial, nsplit, h.st);
+  rt_launch_jac_reduce(h.d_jpartial, h.d_basef, h.d_jout, nzm, ncol, nsplit, h.st);
+  h.launches += 3;
+  record(h, 2); record(h, 3); record(h, 4);
+  int flag = 0;
+  CK(cudaMemcpyAsync(&flag, h.d_jflag, sizeof(int), cudaMemcpyDeviceToHost, h.st));
+  CK(cudaMemcpyAsync(f_total, h.d_jout, (size_t)ncol * (nzm + 1) * 8, cudaMemcpyDeviceToHost, h.st));
+  CK(cudaStreamSynchronize(h.st));
+  CK(cudaGetLastError());
+  if (flag) return false;
+  accumulate_stage_ms(h);
+  return true;
+}
+
 void jacobian_batch_impl(Handle &h, int ncol, int nzm, const double *T_surface, const double *T,
                          double *f_total) {
   CK(cudaSetDevice(h.device));
@@ -680,10 +772,15 @@ void jacobian_batch_impl(Handle &h, int ncol, int nzm, const double *T_surface, 
   if (h.retained_solar_ncol != 1)
     throw CudaError{"clima_rt_jacobian_batch needs the solar fluxes of the base column retained in the "
                     "handle (compute_solar=1 in the base call)"};
+  for (int i = 0; i < 6; i++) h.stage_ms[i] = 0.0;
+  if (h.jac_delta && h.base_valid && h.base_nz == nzr && jacobian_delta(h, ncol, nzm, T_surface, T, f_total)) {
+    h.jac_delta_calls++;
+    return;
+  }
+  h.jac_full_calls++;
   grow_for_bcast(h, ncol, nzr);
   const int C = h.cap_cols;
   if ((size_t)C * (nzm + 1) * 8 > h.tmp_bytes) throw CudaError{"internal: staging buffer too small"};
-  for (int i = 0; i < 6; i++) h.stage_ms[i] = 0.0;
   for (int c0 = 0; c0 < ncol; c0 += C) {
     const int n = std::min(C, ncol - c0);
     DevChunk &ch = h.ch;
@@ -788,6 +885,8 @@ void clima_rt_create(const clima_rt_tables *tables, const clima_rt_params *param
       const char *m = std::getenv("CLIMA_RT_RORR");
       h->rorr_exact_only = (m && std::string(m) == "exact") ? 1 : 0;
       h->rorr_sort = (m && std::string(m) == "sort") ? 1 : 0;
+      const char *jm = std::getenv("CLIMA_RT_JAC");
+      h->jac_delta = (jm && std::string(jm) == "full") ? 0 : 1;
       const char *cd = std::getenv("CLIMA_RT_RORR_CHAIN");
       if (cd && cd[0] == 's') h->rorr_chain_env = 0;
       if (cd && cd[0] == 'c') h->rorr_chain_env = 1;
@@ -818,6 +917,9 @@ void clima_rt_destroy(void *handle) {
   Handle *h = static_cast<Handle *>(handle);
   cudaSetDevice(h->device);
   clima_rt_comm_destroy(handle);
+  for (double *p : {h->d_baseT, h->d_basef, h->d_factor, h->d_jTm, h->d_jTs, h->d_jpartial, h->d_jout}) if (p) cudaFree(p);
+  if (h->d_jwin) cudaFree(h->d_jwin);
+  if (h->d_jflag) cudaFree(h->d_jflag);
   free_chunk(*h);
   for (void *p : h->table_allocs) cudaFree(p);
   for (auto &p : h->d_custom) if (p) cudaFree(p);
@@ -834,6 +936,7 @@ void clima_rt_set_params(void *handle, const clima_rt_params *params, char *err)
     Handle &h = *static_cast<Handle *>(handle);
     CK(cudaSetDevice(h.device));
     upload_params(h, params);
+    h.factor_valid = false;  // emissivity / surface flags enter the shared factorisation of the Jacobian path
   } catch (const CudaError &e) {
     set_err(err, e.msg);
   }
@@ -1084,6 +1187,7 @@ void clima_rt_get_rorr_cut_stats(void *handle, int64_t *stats8) {
   if (cudaMemcpy(v, h.ch.cut_stats, sizeof(v), cudaMemcpyDeviceToHost) != cudaSuccess) return;
   for (int i = 0; i < 8; i++) stats8[i] = (int64_t)v[i];
   stats8[5] = h.last_rorr_kernel;
+  stats8[7] = h.jac_delta_calls;
 }
 
 void clima_rt_get_stream(void *handle, void **stream) {

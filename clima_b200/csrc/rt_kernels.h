@@ -40,5 +40,15 @@ void rt_launch_expand_opacity(const DevTables &tb, const DevChunk &ch, int icol,
 void rt_twostream_occupancy(int G, int nzen, int *ir_blocks_per_sm, int *sol_blocks_per_sm);
 int rt_twostream_block_threads();
 int rt_twostream_items_per_layer();
+// jacobian_delta.cu (N1: shared factorisation + delta solves)
+size_t rt_jac_factor_doubles(const DevTables &tb, int nz);
+void rt_launch_jac_factor(const DevTables &tb, const DevParams &pr, const DevChunk &ch, double *factor,
+                          cudaStream_t st);
+int rt_jac_splits(const DevTables &tb, int ncol, int num_sms);
+void rt_launch_jac_delta(const DevTables &tb, const DevParams &pr, int nzm, int ncol, const double *Tm,
+                         const double *Ts, const double *baseT, const double *factor, int *win, int *flag,
+                         double *partial, int nsplit, cudaStream_t st);
+void rt_launch_jac_reduce(const double *partial, const double *basef, double *out, int nzm, int ncol, int nsplit,
+                          cudaStream_t st);
 // fp64_peak.cu
 double rt_measure_fp64_tflops(int device, cudaStream_t st);

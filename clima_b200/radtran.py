@@ -354,8 +354,8 @@ class Radtran:
         a = (C.c_int64 * 8)()
         self._lib.clima_rt_get_rorr_cut_stats(self._h, a)
         k = ("warp_merges", "warp_passes", "restarts", "units_to_exact", "cold_warp_merges", "last_kernel",
-             "closed_form_warp_merges")
-        return dict(zip(k, list(a)[:7]))
+             "closed_form_warp_merges", "jacobian_delta_calls")
+        return dict(zip(k, list(a)[:8]))
 
     def stage_ms(self):
         a = (C.c_double * 6)()

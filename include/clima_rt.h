@@ -282,7 +282,8 @@ void clima_rt_get_rorr_stats(void *handle, int64_t *stats3);
    [3] units handed to the exact sorting kernel, [4] cold starts (warp-merges at the head of a chain),
    [5] RORR kernel of the last chunk: 0 staircase/slot chains, 1 staircase/column chains, 2 sorting
    kernels, 3 exact sorting kernel only.  [6] warp-merges that took the closed form (rows or columns
-   of a_i + b_j do not interleave).  [7] reserved. */
+   of a_i + b_j do not interleave).  [7] clima_rt_jacobian_batch calls served by the delta path
+   (shared factorisation, jacobian_delta.cu). */
 void clima_rt_get_rorr_cut_stats(void *handle, int64_t *stats8);
 
 /* The CUDA stream (a cudaStream_t, returned as an opaque pointer) every kernel of the handle is

@@ -875,3 +875,57 @@ def test_cfg4_jacobian_batch_at_nz50():
         ref[:, c] = ro["f_total"][0:2 * nzm + 1:2, 0]
         scale = max(scale, float(np.max(np.abs(ro["fup_n_ir"]))))
     assert np.max(np.abs(f - ref)) <= TOL * scale
+
+
+@pytest.mark.parametrize("hard", [True, False])
+def test_jacobian_delta_path_matches_the_full_solves(hard, monkeypatch):
+    """clima_rt_jacobian_batch, delta path (jacobian_delta.cu: one factorisation of the two-stream matrix
+    shared by all columns, per column a window solve + two chains) against the round-1 path that re-solves
+    every column (CLIMA_RT_JAC=full), and against the oracle loop: surface, every layer, the top layer
+    (4 radiative levels incl. the ghosts), an unchanged column, and a column that differs everywhere (too
+    wide for the window: the call falls back to the full solves)."""
+    nzm = 9
+    tb, pr, base = small_case(G=16, nw=10, nz=nzm, ncol=1, nzen=1, doubled=True, has_hard_surface=hard)
+    Tm = base["T"][0:2 * nzm:2, 0].copy()
+    Ts0 = float(base["T_surface"][0])
+    ncol = nzm + 2
+    T = np.repeat(Tm[:, None], ncol, axis=1).copy(order="F")
+    Ts = np.full(ncol, Ts0)
+    Ts[0] += 1.0e-2 * Ts0
+    for i in range(nzm):
+        T[i, i + 1] += 1.0e-2 * Tm[i]
+    # column ncol-1 stays equal to the base
+    res = {}
+    for mode in ("delta", "full"):
+        if mode == "full":
+            monkeypatch.setenv("CLIMA_RT_JAC", "full")
+        g = Radtran(tb, pr)
+        g.radiate_batch(base)
+        res[mode] = g.jacobian_batch(Ts, T)
+        st = g.rorr_cut_stats()
+        assert (st["jacobian_delta_calls"] == 1) == (mode == "delta"), st
+        if mode == "delta":
+            fb = g.radiate_batch(base)["f_total"][0:2 * nzm + 1:2, 0]
+            assert np.array_equal(res[mode][:, ncol - 1], fb)  # unchanged column: exactly the base
+            # a column that differs in every level: falls back, same answer as the full path below
+            Tall = np.asfortranarray((Tm * 1.01)[:, None]); Tsall = np.array([Ts0 * 1.01])
+            f_all = g.jacobian_batch(Tsall, Tall)
+            assert g.rorr_cut_stats()["jacobian_delta_calls"] == 1
+            g.radiate_batch(base)
+            res["wide"] = f_all
+    scale = np.max(np.abs(res["full"]))
+    assert np.max(np.abs(res["delta"] - res["full"])) <= 1e-12 * scale
+    o = OracleRadtran(tb, pr)
+    o.radiate(base, 0, spectral=False)
+    nzr = base["nz"]
+    for c in (0, 1, nzm, ncol - 1):
+        Tr = np.empty(nzr)
+        Tr[0:2 * nzm:2] = T[:, c]; Tr[1:2 * nzm:2] = T[:, c]; Tr[2 * nzm:] = T[nzm - 1, c]
+        pert = dict(base, T_surface=np.array([Ts[c]]), T=np.asfortranarray(Tr[:, None]))
+        ro = o.radiate(pert, 0, compute_solar=False, compute_opacity=False, spectral=False)
+        assert np.max(np.abs(res["delta"][:, c] - ro["f_total"][0:2 * nzm + 1:2, 0])) <= TOL * scale
+    Tr = np.empty(nzr)
+    Tr[0:2 * nzm:2] = Tm * 1.01; Tr[1:2 * nzm:2] = Tm * 1.01; Tr[2 * nzm:] = Tm[-1] * 1.01
+    ro = o.radiate(dict(base, T_surface=np.array([Ts0 * 1.01]), T=np.asfortranarray(Tr[:, None])), 0,
+                   compute_solar=False, compute_opacity=False, spectral=False)
+    assert np.max(np.abs(res["wide"][:, 0] - ro["f_total"][0:2 * nzm + 1:2, 0])) <= TOL * scale
