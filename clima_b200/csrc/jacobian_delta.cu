@@ -37,7 +37,7 @@ namespace {
 constexpr int JR = 8;      // per-row arrays
 constexpr int JL = 9;      // per-layer arrays
 constexpr int MAXLEV = 5;  // changed levels a column may span (2 for a model layer, 4 for the top one, 1 for the surface)
-constexpr int MAXW = 16;   // rows of the window
+constexpr int MAXW = 14;   // rows of the window: 2 (lev1 - lev0) + 6 <= 14 for MAXLEV levels
 enum { R_PSI = 0, R_CK, R_PHI, R_KAP, R_A, R_RDEN, R_D, R_RDEN2 };
 enum { L_E1 = 0, L_E2, L_E3, L_E4, L_G12, L_TAU, L_RTAU, L_U, L_V };
 
@@ -174,7 +174,10 @@ __global__ void jac_window_kernel(const double *__restrict__ Tm, const double *_
 
 // lane = column; the warp walks units u = u0, u0 + ustep, ... (u = ll*G + g).  partial:
 // [split][col][nzm+1] sums of dnu * w_g * (dfdn - dfup) at model level i (ground-first).
-__global__ void __launch_bounds__(128)
+#ifndef JAC_MIN_BLOCKS
+#define JAC_MIN_BLOCKS 3  // measured r2d, 1024 stacked Jacobians: 2 -> 26.2 ms, 3 -> 20.4, 4 -> 22.1, 6 -> 25.7
+#endif
+__global__ void __launch_bounds__(128, JAC_MIN_BLOCKS)
 jac_delta_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ DevParams pr, const int nzm,
                  const int ncol, const double *__restrict__ Tm, const double *__restrict__ Ts,
                  const double *__restrict__ baseT, const int *__restrict__ win,
@@ -317,6 +320,7 @@ jac_delta_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ D
       }
       const int mtop = changed ? (r >> 2) : -1;  // first whole group (r = 4m+3), -1: none
       const int mmax = __reduce_max_sync(0xffffffffu, mtop);
+#pragma unroll 4
       for (int m = mmax; m >= 0; m--) {
         const double gu = fg[G_GU * ngrp + m], pu = fg[G_PU * ngrp + m];
         if (m <= mtop) {
@@ -334,6 +338,7 @@ jac_delta_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ D
       }
       const int mbot = changed ? (r >> 2) : ngrp;  // first whole group (r = 4m), ngrp: none
       const int mmin = __reduce_min_sync(0xffffffffu, mbot);
+#pragma unroll 4
       for (int m = mmin; m < ngrp; m++) {
         const double gd = fg[G_GD * ngrp + m], pd = fg[G_PD * ngrp + m];
         if (m >= mbot) {
