@@ -463,7 +463,10 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
       else if (!(tbc.pad0 & 4) && ncol >= h.rorr_cut_mincols) cut_chain = 1;
     }
     h.last_rorr_kernel = exact || !h.tb.rows_sorted ? 3 : (cut_chain >= 0 ? cut_chain : 2);
-    rt_launch_optics_rorr(tbc, ch, h.d_worklist, h.d_wcount, h.wcap, exact, cut_chain, h.rorr_chain_len, h.st);
+    // chain length: long chains amortise the cold start of their first unit (~20 row passes), but a small
+    // chunk still needs >= 4 chains per (bin, slot pair) to fill the GPU evenly
+    const int chain_len = std::min(h.rorr_chain_len, std::max(64, ncol / 4));
+    rt_launch_optics_rorr(tbc, ch, h.d_worklist, h.d_wcount, h.wcap, exact, cut_chain, chain_len, h.st);
     const bool two = !exact && h.tb.rows_sorted;
     h.launches += two ? 3 : 2;  // continua + fast + exact, or continua + exact
     *h.h_wcount = 0;
@@ -936,7 +939,11 @@ void clima_rt_set_params(void *handle, const clima_rt_params *params, char *err)
     Handle &h = *static_cast<Handle *>(handle);
     CK(cudaSetDevice(h.device));
     upload_params(h, params);
-    h.factor_valid = false;  // emissivity / surface flags enter the shared factorisation of the Jacobian path
+    // emissivity / surface flags enter both the shared factorisation of the Jacobian delta path and the
+    // base f_total it adds its deltas to: the next clima_rt_jacobian_batch takes the full solves until a
+    // new base column has been radiated with the new parameters
+    h.factor_valid = false;
+    h.base_valid = false;
   } catch (const CudaError &e) {
     set_err(err, e.msg);
   }
