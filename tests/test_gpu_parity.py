@@ -929,3 +929,38 @@ def test_jacobian_delta_path_matches_the_full_solves(hard, monkeypatch):
     ro = o.radiate(dict(base, T_surface=np.array([Ts0 * 1.01]), T=np.asfortranarray(Tr[:, None])), 0,
                    compute_solar=False, compute_opacity=False, spectral=False)
     assert np.max(np.abs(res["wide"][:, 0] - ro["f_total"][0:2 * nzm + 1:2, 0])) <= TOL * scale
+
+
+def test_jacobian_after_set_params_takes_the_new_parameters():
+    """Changing the emissivity after the base call invalidates the Jacobian delta path's base state (its
+    f_total was computed with the old emissivity): the next clima_rt_jacobian_batch re-solves every column
+    with the new parameters, like the reference would (frozen opacity, stale solar, new `surface_emissivity`)."""
+    import copy
+    nzm = 6
+    tb, pr, base = small_case(G=16, nw=10, nz=nzm, ncol=1, nzen=1, doubled=True)
+    g = Radtran(tb, pr)
+    g.radiate_batch(base)
+    pr2 = copy.deepcopy(pr)
+    pr2.surface_emissivity = np.full(tb.nw_ir, 0.8)
+    g.params = pr2
+    Tm = base["T"][0:2 * nzm:2, 0].copy()
+    Ts = np.array([float(base["T_surface"][0]) * 1.01, float(base["T_surface"][0])])
+    T = np.repeat(Tm[:, None], 2, axis=1).copy(order="F")
+    T[2, 1] *= 1.01
+    f = g.jacobian_batch(Ts, T)
+    assert g.rorr_cut_stats()["jacobian_delta_calls"] == 0
+    o = OracleRadtran(tb, pr2)
+    o.radiate(base, 0, spectral=False)
+    nzr = base["nz"]
+    for c in range(2):
+        Tr = np.empty(nzr)
+        Tr[0:2 * nzm:2] = T[:, c]; Tr[1:2 * nzm:2] = T[:, c]; Tr[2 * nzm:] = T[nzm - 1, c]
+        ro = o.radiate(dict(base, T_surface=np.array([Ts[c]]), T=np.asfortranarray(Tr[:, None])), 0,
+                       compute_solar=False, compute_opacity=False, spectral=False)
+        ref = ro["f_total"][0:2 * nzm + 1:2, 0]
+        assert np.max(np.abs(f[:, c] - ref)) <= TOL * np.max(np.abs(ro["fup_n_ir"]))
+    # a new base call with the new parameters re-arms the delta path
+    g.radiate_batch(base)
+    f2 = g.jacobian_batch(Ts, T)
+    assert g.rorr_cut_stats()["jacobian_delta_calls"] == 1
+    assert np.max(np.abs(f2 - f)) <= 1e-12 * np.max(np.abs(f))
