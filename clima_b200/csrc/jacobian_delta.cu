@@ -182,7 +182,7 @@ jac_delta_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ D
                  const int ncol, const double *__restrict__ Tm, const double *__restrict__ Ts,
                  const double *__restrict__ baseT, const int *__restrict__ win,
                  const double *__restrict__ factor, double *__restrict__ partial, const int nsplit) {
-  extern __shared__ double acc[];  // [warp][nzm+1][32]
+  extern __shared__ double acc[];  // [warp][nzm+1][32] sums, then [warp][2][4*(nzm+1)] staged group factors
   const int nz = 2 * nzm + 2, n = 2 * nz, G = tb.G;
   const int nw_ir = tb.ir_end - tb.ir_start + 1, nunits = nw_ir * G;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
@@ -191,6 +191,11 @@ jac_delta_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ D
   const bool live = c < ncol;
   const int cc = live ? c : ncol - 1;
   double *my = acc + (size_t)warp * (nzm + 1) * 32 + lane;
+  // the group factors of a unit (GU, PU, GD, PD: 4 (nzm+1) doubles) are staged through shared memory by one
+  // coalesced warp load, two units ahead in two buffers: the chains were bound on the latency of ~200
+  // dependent-issue uniform global loads per unit (ncu r2d: long scoreboard 6.3 warps per issue, 25 % issue)
+  const int ng4 = 4 * (nzm + 1);
+  double *sgw = acc + (size_t)wpb * (nzm + 1) * 32 + (size_t)warp * 2 * ng4;
   for (int i = 0; i <= nzm; i++) my[i * 32] = 0.0;
   const int lev0 = win[2 * cc], lev1 = win[2 * cc + 1];
   const bool changed = lev1 >= lev0 && (lev1 - lev0 + 1) <= MAXLEV;
@@ -224,12 +229,20 @@ jac_delta_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ D
   double dB[MAXLEV + 2];  // dB[k] = delta B(level lev0 - 1 + k): zero pads on both sides
 #pragma unroll
   for (int k = 0; k < MAXLEV + 2; k++) dB[k] = 0.0;
+  auto stage = [&](int u, int buf) {  // group factors of unit u -> buffer buf (coalesced)
+    const double *src = factor + (size_t)u * jac_stride(nz) + (size_t)JR * n + (size_t)JL * nz;
+    double *dst = sgw + buf * ng4;
+    for (int k = lane; k < ng4; k += 32) dst[k] = src[k];
+  };
+  if (ubeg < uend) stage(ubeg, 0);
+  __syncwarp();
   for (int u = ubeg; u < uend; u++) {
     const int ll = u / G, g = u - ll * G;
     const int l = tb.ir_start + ll;
     const double *fr = factor + (size_t)u * jac_stride(nz);
     const double *fl = fr + (size_t)JR * n;
-    const double *fg = fl + (size_t)JL * nz;
+    const double *fg = sgw + ((u - ubeg) & 1) * ng4;
+    if (u + 1 < uend) stage(u + 1, (u + 1 - ubeg) & 1);  // in flight while this unit's window is solved
     const double wgt = (tb.freq[l] - tb.freq[l + 1]) * tb.wbin[g];  // integrate_kernel x radiate.f90:122-126
     if (ll != ll_cur) {
       ll_cur = ll;
@@ -347,6 +360,7 @@ jac_delta_kernel(const __grid_constant__ DevTables tb, const __grid_constant__ D
         }
       }
     }
+    __syncwarp();  // every lane is done with this unit's buffer; the next unit's is complete
   }
   __syncwarp();
   // cross-warp sum in warp order, then out
@@ -400,7 +414,7 @@ void rt_launch_jac_delta(const DevTables &tb, const DevParams &pr, int nzm, int 
                          double *partial, int nsplit, cudaStream_t st) {
   cudaMemsetAsync(flag, 0, sizeof(int), st);
   jac_window_kernel<<<(ncol + 127) / 128, 128, 0, st>>>(Tm, Ts, baseT, nzm, ncol, win, flag);
-  const size_t smem = (size_t)4 * (nzm + 1) * 32 * sizeof(double);
+  const size_t smem = (size_t)4 * ((nzm + 1) * 32 + 2 * 4 * (nzm + 1)) * sizeof(double);
   static bool attr_set[64] = {};
   int dev = 0;
   cudaGetDevice(&dev);
