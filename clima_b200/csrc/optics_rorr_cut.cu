@@ -22,16 +22,21 @@
 // One lane per bin edge (lane G-1: the whole integral), P lanes per unit, 32/P units per warp.  One
 // PASS over the G rows evaluates L, R, W, S for the lane's staircase; a staircase that fails the
 // test is repaired by single-element moves (drop the largest inside element / take the smallest
-// outside one) and re-evaluated.  The staircases of a unit are the initial guess of the NEXT unit
-// of a CHAIN: the same (bin, layer slot) of the next column when neighbouring columns are alike
-// (a sweep: 99 % of the warp passes are the only pass), else the next layer slot of the same
-// (column, bin) (2.3 passes per merge on randomised columns; experiments/rorr_cut_proto.py).
-// The first unit of a chain starts from a 13-step bisection on the value of the edge element.
-// A unit that does not settle within the pass budget is appended to the worklist of the exact
-// sorting kernel (optics_rorr_exact.cu).
+// outside one), after 8 of them by jumps over whole groups of tied sums, and re-evaluated.  The
+// staircases of a unit are the initial guess of the NEXT unit of a CHAIN: the same (bin, layer slot)
+// of the next column when neighbouring columns are alike (a sweep: 1.06-1.19 passes per merge; the
+// default use), or the next layer slot of the same (column, bin) (2.3-2.5 passes per merge: slower than
+// the sorting kernels, kept behind CLIMA_RT_RORR_CHAIN=slot; experiments/rorr_cut_proto.py).
+// The first unit of a chain starts from a bisection on the IEEE-754 pattern of the edge element's
+// value (until <= 3 elements lie between the brackets).  Merges whose rows or columns do not
+// interleave take the closed form a_i + <b> / b_j + <a>.  A unit that does not settle within the
+// pass budget (none in any measured workload) is appended to the worklist of the exact sorting
+// kernel (optics_rorr_exact.cu).
 //
-// What it costs: 4 shared-memory gathers + ~20 instructions per (edge, row) and pass, 15 x 16 pairs
-// per merge, against ~94 instructions per ELEMENT (256 per merge) of the sorting kernel.
+// What it costs (ncu, profiles/r2b_ncu_rorr_cut_summary.txt): 4 shared-memory gathers + ~24
+// instructions per (edge, row) and pass, 15 x 16 pairs per merge; 16.7 M warp-instructions per column
+// against 24.2 M for the sorting kernel; shared-memory wavefronts 69 % of peak, issue slots 66 %.
+// DESIGN.md section 3.1 has the derivation, the measurements and the dead ends.
 #include <cstdio>
 #include <cstdlib>
 
