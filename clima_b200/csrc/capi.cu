@@ -66,6 +66,12 @@ struct Handle {
   int *d_worklist = nullptr, *d_wcount = nullptr;
   int wcap = 0;
   int *h_wcount = nullptr;  // pinned
+  // staircase kernel self-check: counters of the last staircase chunk (pinned copies of cut_stats[0..1]),
+  // their previous totals, and how many further chunks take the sorting kernels after a poor showing
+  unsigned long long *h_cutstat = nullptr, cut_prev[2] = {0, 0};
+  bool cut_pending = false;
+  int cut_backoff = 0;
+  double last_passes_per_merge = 0.0;
   int rorr_exact_only = 0;  // CLIMA_RT_RORR=exact
   int rorr_sort = 0;        // CLIMA_RT_RORR=sort: the sorting kernels instead of the staircase kernel
   int rorr_chain_env = -1;  // CLIMA_RT_RORR_CHAIN=slot|col forces the chain direction (0 / 1)
@@ -339,6 +345,8 @@ void ensure_chunk(Handle &h, int ncol, int nz) {
   ch.status = calloc_dev<int>(h, C);
   ch.dissim = calloc_dev<int>(h, 1);
   ch.cut_stats = calloc_dev<unsigned long long>(h, 8);
+  h.cut_prev[0] = h.cut_prev[1] = 0;  // the counters restart with the buffers
+  h.cut_pending = false;
   {
     const long long units = (long long)((C + 3) / 4 * 4) * tb.nw * nz;
     if (units >= (1ll << 31)) throw CudaError{"chunk too large: lower CLIMA_RT_CHUNK_COLS"};
@@ -457,10 +465,25 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     // 34 us sorted).  Unlike neighbours (randomised composition, cfg3's shuffled pCO2) keep the sorting
     // kernels: chains over the layer slots of a column need 2.3-2.5 passes per merge (cfg5: 48 vs 36 us).
     // similarity_kernel's verdict (pad0 bit 2 = unlike) decides; CLIMA_RT_RORR_CHAIN forces a direction.
+    // The verdict is checked against what the kernel then reports: if the previous staircase chunk
+    // needed more than 1.5 passes per merge (alike by column amounts, yet staircases that do not carry
+    // over), the next 8 chunks take the sorting kernels before the staircase kernel is tried again.
+    if (h.cut_pending) {  // the stream was synchronised above: the copies of the last chunk have landed
+      const unsigned long long dm = h.h_cutstat[0] - h.cut_prev[0], dp = h.h_cutstat[1] - h.cut_prev[1];
+      h.cut_prev[0] = h.h_cutstat[0]; h.cut_prev[1] = h.h_cutstat[1];
+      h.cut_pending = false;
+      if (dm > 0) {
+        h.last_passes_per_merge = (double)dp / (double)dm;
+        if (h.last_passes_per_merge > 1.5 && h.rorr_chain_env < 0) h.cut_backoff = 8;
+      }
+    }
     int cut_chain = -1;
     if (!exact && !h.rorr_sort && h.tb.rows_sorted) {
       if (h.rorr_chain_env >= 0) cut_chain = h.rorr_chain_env;
-      else if (!(tbc.pad0 & 4) && ncol >= h.rorr_cut_mincols) cut_chain = 1;
+      else if (!(tbc.pad0 & 4) && ncol >= h.rorr_cut_mincols) {
+        if (h.cut_backoff > 0) h.cut_backoff--;
+        else cut_chain = 1;
+      }
     }
     h.last_rorr_kernel = exact || !h.tb.rows_sorted ? 3 : (cut_chain >= 0 ? cut_chain : 2);
     // chain length: long chains amortise the cold start of their first unit (~20 row passes), but a small
@@ -472,6 +495,10 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     *h.h_wcount = 0;
     if (two)
       CK(cudaMemcpyAsync(h.h_wcount, h.d_wcount, sizeof(int), cudaMemcpyDeviceToHost, h.st));
+    if (cut_chain >= 0) {
+      CK(cudaMemcpyAsync(h.h_cutstat, ch.cut_stats, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, h.st));
+      h.cut_pending = true;
+    }
     h.rorr_units += (long long)ncol * h.tb.nw * ch.nslot_cap;
     if (!two) h.rorr_exact_units += (long long)ncol * h.tb.nw * ch.nslot_cap;
   }
@@ -884,6 +911,8 @@ void clima_rt_create(const clima_rt_tables *tables, const clima_rt_params *param
     for (auto &e : h->ev) CK(cudaEventCreate(&e));
     CK(cudaMallocHost(&h->h_wcount, sizeof(int)));
     *h->h_wcount = 0;
+    CK(cudaMallocHost(&h->h_cutstat, 2 * sizeof(unsigned long long)));
+    h->h_cutstat[0] = h->h_cutstat[1] = 0;
     {
       const char *m = std::getenv("CLIMA_RT_RORR");
       h->rorr_exact_only = (m && std::string(m) == "exact") ? 1 : 0;
@@ -929,6 +958,7 @@ void clima_rt_destroy(void *handle) {
   for (auto &e : h->ev) if (e) cudaEventDestroy(e);
   if (h->st) cudaStreamDestroy(h->st);
   if (h->h_wcount) cudaFreeHost(h->h_wcount);
+  if (h->h_cutstat) cudaFreeHost(h->h_cutstat);
   delete h;
 }
 

@@ -964,3 +964,24 @@ def test_jacobian_after_set_params_takes_the_new_parameters():
     f2 = g.jacobian_batch(Ts, T)
     assert g.rorr_cut_stats()["jacobian_delta_calls"] == 1
     assert np.max(np.abs(f2 - f)) <= 1e-12 * np.max(np.abs(f))
+
+
+def test_staircase_kernel_backs_off_when_its_chains_do_not_carry():
+    """Columns that are alike by their gas amounts (what similarity_kernel looks at) but have unrelated
+    temperatures: the staircase kernel is chosen, reports > 1.5 passes per merge, and the following chunks
+    take the sorting kernels; results match the oracle either way."""
+    tb = synth.make_tables(nw=16, n_sol=10, ir_start=6)
+    pr = synth.default_params(tb, nzenith=1)
+    cols = synth.make_columns(48, nz=16, T_surf_range=(260.0, 260.0), doubled=False)
+    rng = np.random.default_rng(9)
+    T = np.asfortranarray(cols["T"] * rng.uniform(0.7, 2.5, (1, cols["T"].shape[1])))  # one factor per column
+    cols = dict(cols, T=T)
+    g = Radtran(tb, pr)
+    r1 = g.radiate_batch(cols)
+    st = g.rorr_cut_stats()
+    assert st["last_kernel"] == 1 and st["warp_passes"] > 1.5 * st["warp_merges"], st
+    r2 = g.radiate_batch(cols)
+    assert g.rorr_cut_stats()["last_kernel"] == 2
+    ro = OracleRadtran(tb, pr).radiate_batch(cols, nthreads=8)
+    compare(r1, ro, spectral=False)
+    compare(r2, ro, spectral=False)
