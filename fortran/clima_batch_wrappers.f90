@@ -46,9 +46,50 @@ subroutine radtran_radiate_batch_wrapper(ptr, ncol, nz, ng, T_surface, T, P, den
   f_total = res%f_total; ISR = res%ISR; OLR = res%OLR
 end subroutine
 
+!> To be added to src/adiabat/clima_adiabat.f90 as a type-bound procedure of AdiabatClimate
+!> (`procedure :: TOA_fluxes_batch => AdiabatClimate_TOA_fluxes_batch`), next to
+!> AdiabatClimate_TOA_fluxes (:776-799), whose steps it repeats per column up to the RT call:
+!> `copy_atm_to_radiative_grid` is a private binding (:219), so this cannot live outside the module.
+subroutine AdiabatClimate_TOA_fluxes_batch(self, T_surf, P_i_surf, ISR, OLR, err)
+  use clima_radtran_cuda, only: RadtranBatchResult
+  class(AdiabatClimate), intent(inout) :: self
+  real(dp), intent(in) :: T_surf(:)      !! (ncol) K
+  real(dp), intent(in) :: P_i_surf(:,:)  !! (ng,ncol) dynes/cm^2
+  real(dp), intent(out) :: ISR(:), OLR(:)  !! (ncol) mW/m^2
+  character(:), allocatable, intent(out) :: err
+
+  type(RadtranBatchResult) :: res
+  real(dp), allocatable :: T(:,:), P(:,:), dens(:,:,:), dz(:,:), pdens(:,:,:), radii(:,:,:)
+  integer :: i, ncol
+
+  ncol = size(T_surf)
+  if (size(P_i_surf,2) /= ncol .or. size(ISR) /= ncol .or. size(OLR) /= ncol) then
+    err = 'TOA_fluxes_batch: inconsistent number of columns'
+    return
+  endif
+  if (associated(self%albedo_fcn)) then
+    ! one set of run-time knobs per batched call: a surface albedo that depends on T_surf (:789-791)
+    ! needs one call per albedo value
+    err = 'TOA_fluxes_batch: "albedo_fcn" is set; call TOA_fluxes per column or batch columns of equal albedo'
+    return
+  endif
+  allocate(T(self%nz_r,ncol), P(self%nz_r,ncol), dens(self%nz_r,self%sp%ng,ncol), dz(self%nz_r,ncol))
+  allocate(pdens(self%nz_r,self%sp%np,ncol), radii(self%nz_r,self%sp%np,ncol))
+  do i = 1,ncol
+    ! column construction stays the reference's (row N4): pseudo-adiabat, then the doubled grid
+    call self%make_profile(T_surf(i), P_i_surf(:,i), err)
+    if (allocated(err)) return
+    call self%copy_atm_to_radiative_grid()
+    T(:,i) = self%T_r; P(:,i) = self%P_r/1.0e6_dp; dens(:,:,i) = self%densities_r; dz(:,i) = self%dz_r
+    pdens(:,:,i) = self%pdensities_r; radii(:,:,i) = self%pradii_r
+  enddo
+  call self%rad%radiate_batch(T_surf, T, P, dens, dz, pdens, radii, res=res, err=err)
+  if (allocated(err)) return
+  ISR = res%ISR; OLR = res%OLR
+end subroutine
+
 subroutine adiabatclimate_toa_fluxes_batch_wrapper(ptr, ncol, T_surf, ng, P_i_surf, ISR, OLR, err) bind(c)
   use clima, only: AdiabatClimate
-  use clima_radtran_cuda, only: RadtranBatchResult
   type(c_ptr), value, intent(in) :: ptr
   integer(c_int), intent(in) :: ncol
   real(c_double), intent(in) :: T_surf(ncol)
@@ -59,28 +100,11 @@ subroutine adiabatclimate_toa_fluxes_batch_wrapper(ptr, ncol, T_surf, ng, P_i_su
 
   character(:), allocatable :: err_f
   type(AdiabatClimate), pointer :: c
-  type(RadtranBatchResult) :: res
-  real(c_double), allocatable :: T(:,:), P(:,:), dens(:,:,:), dz(:,:)
-  integer :: i, nzr
 
   call c_f_pointer(ptr, c)
+  call c%TOA_fluxes_batch(T_surf, P_i_surf, ISR, OLR, err_f)
   err(1) = c_null_char
-  nzr = c%rad%nz                      ! the radiative grid of copy_atm_to_radiative_grid: 2*nz + 2
-  allocate(T(nzr,ncol), P(nzr,ncol), dens(nzr,c%sp%ng,ncol), dz(nzr,ncol))
-  do i = 1,ncol
-    ! column construction stays the reference's (row N4): pseudo-adiabat, then the doubled grid
-    call c%make_profile(T_surf(i), P_i_surf(:,i), err_f)
-    if (allocated(err_f)) then
-      call copy_string_ftoc(err_f, err)
-      return
-    endif
-    call c%copy_atm_to_radiative_grid()
-    T(:,i) = c%T_r; P(:,i) = c%P_r/1.0e6_dp; dens(:,:,i) = c%densities_r; dz(:,i) = c%dz_r
-  enddo
-  call c%rad%radiate_batch(T_surf, T, P, dens, dz, res=res, err=err_f)
   if (allocated(err_f)) then
     call copy_string_ftoc(err_f, err)
-    return
   endif
-  ISR = res%ISR; OLR = res%OLR
 end subroutine
