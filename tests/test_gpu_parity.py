@@ -985,3 +985,60 @@ def test_staircase_kernel_backs_off_when_its_chains_do_not_carry():
     ro = OracleRadtran(tb, pr).radiate_batch(cols, nthreads=8)
     compare(r1, ro, spectral=False)
     compare(r2, ro, spectral=False)
+
+
+def test_full_size_sweep_properties():
+    """BASELINE config 2 at its full size (4096 columns, nz_r = 202, S-canon tables), where the oracle is too
+    slow to be the checker: size-independent properties.  (a) every column finite, status 0, the staircase
+    kernel with no unit handed to the exact kernel; (b) the same batch in REVERSED column order (every chain
+    runs the other way, every staircase has another predecessor) gives the same per-column fluxes to 1e-11;
+    (c) 48 columns picked across the sweep, radiated as their own batch, agree to 1e-11; (d) a second call is
+    bit-identical; (e) 16 of the columns against the oracle."""
+    tb = synth.make_tables()
+    pr = synth.default_params(tb)
+    n = 4096
+    cols = synth.make_columns(n, nz=100)
+    g = Radtran(tb, pr)
+    r = {k: v.copy() for k, v in g.radiate_batch(cols).items()}
+    st = g.rorr_cut_stats()
+    assert st["last_kernel"] == 1 and st["units_to_exact"] == 0 and g.rorr_stats()[2] == 0, st
+    assert st["warp_passes"] < 1.2 * st["warp_merges"], st
+    assert np.all(r["status"] == 0)
+    for k in ("fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol", "f_total", "ISR", "OLR"):
+        assert np.all(np.isfinite(r[k])), k
+    r2 = g.radiate_batch(cols)
+    for k in r:
+        assert np.array_equal(r[k], r2[k]), k  # (d)
+    rev = {k: (np.asfortranarray(v[..., ::-1]) if isinstance(v, np.ndarray) and v.shape[-1] == n else v) for k, v in cols.items()}
+    rr = g.radiate_batch(rev)
+    scale = max(np.max(np.abs(r[k])) for k in ("fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol"))
+    for k in ("fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol", "f_total"):
+        assert np.max(np.abs(rr[k][:, ::-1] - r[k])) <= 1e-11 * scale, k  # (b)
+    assert np.max(np.abs(rr["OLR"][::-1] / r["OLR"] - 1.0)) <= 1e-11
+    pick = np.linspace(0, n - 1, 48).astype(int)
+    sub = {k: (np.asfortranarray(v[..., pick]) if isinstance(v, np.ndarray) and v.shape[-1] == n else v) for k, v in cols.items()}
+    sub["ncol"] = 48
+    rs = g.radiate_batch(sub)
+    for k in ("fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol", "f_total"):
+        assert np.max(np.abs(rs[k] - r[k][:, pick])) <= 1e-11 * scale, k  # (c)
+    ro = OracleRadtran(tb, pr, kind="parity").radiate_batch(
+        {k: (np.asfortranarray(v[..., :16]) if isinstance(v, np.ndarray) and v.shape[-1] == 48 else v) for k, v in sub.items()} | {"ncol": 16},
+        nthreads=8)
+    compare({k: (v[..., :16] if v.ndim > 1 else v[:16]) for k, v in rs.items()}, ro, spectral=False)  # (e)
+
+
+def test_full_size_randomised_columns_chunking(monkeypatch):
+    """BASELINE config 5 at the per-GPU size of the 8-GPU run (8192 randomised columns = two chunks of 4096;
+    sorting kernels): every column finite, and the same batch cut into chunks of 2048 is bit-identical
+    (columns are independent units: a result must not depend on which columns share a chunk)."""
+    tb = synth.make_tables()
+    pr = synth.default_params(tb)
+    cols = synth.make_columns(8192, nz=100, randomize=True, seed=11)
+    g = Radtran(tb, pr)
+    r1 = {k: v.copy() for k, v in g.radiate_batch(cols).items()}
+    assert g.rorr_cut_stats()["last_kernel"] == 2
+    assert np.all(r1["status"] == 0) and all(np.all(np.isfinite(r1[k])) for k in ("fup_n_ir", "fdn_n_ir", "f_total", "OLR"))
+    monkeypatch.setenv("CLIMA_RT_CHUNK_COLS", "2048")
+    r2 = Radtran(tb, pr).radiate_batch(cols)
+    for k in ("fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol", "f_total", "ISR", "OLR"):
+        assert np.array_equal(r1[k], r2[k]), k
