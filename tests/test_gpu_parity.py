@@ -423,11 +423,14 @@ def test_rorr_general_walk_matches_the_single_edge_walk(monkeypatch):
         assert np.array_equal(r1[k], r2[k]), k
 
 
+@pytest.mark.parametrize("flavour", ["default", "staircase"])
 @pytest.mark.parametrize("G", [5, 16])
-def test_rorr_weights_with_several_edges_per_element(G):
+def test_rorr_weights_with_several_edges_per_element(G, flavour, monkeypatch):
     """A weight set in which one sorted element (weight w_i*w_j) spans several new bins -- one
     dominant g-point next to very narrow ones -- selects the general walk at table load
     (capi.cu, DevTables::pad0 bit 1) and must still match the oracle."""
+    if flavour == "staircase":  # the staircase kernel has no single-edge assumption to fall back from
+        monkeypatch.setenv("CLIMA_RT_RORR_CHAIN", "col")
     tb, pr, cols = small_case(G=G, nw=8, nz=8, ncol=2)
     w = np.full(G, 0.02 / (G - 1))
     w[G // 2] = 0.98
