@@ -1045,3 +1045,45 @@ def test_full_size_randomised_columns_chunking(monkeypatch):
     r2 = Radtran(tb, pr).radiate_batch(cols)
     for k in ("fup_n_ir", "fdn_n_ir", "fup_n_sol", "fdn_n_sol", "f_total", "ISR", "OLR"):
         assert np.array_equal(r1[k], r2[k]), k
+
+
+def test_adiabat_climate_batch_entry_matches_the_per_column_loop():
+    """N3 at the Python level: AdiabatClimateBatch.TOA_fluxes_batch (make_profile per column on the host, ONE
+    doubled-grid batch on the GPU) against the loop the reference's users write (TOA_fluxes once per column,
+    examples/EarlyMars.ipynb cell 7), here with the oracle doing each column; the column builder is an
+    analytic stand-in for `make_profile` (row N4 is not built)."""
+    from clima_b200.adiabat import AdiabatClimateBatch, copy_atm_to_radiative_grid
+    tb, pr, _ = small_case(G=16, nw=10, nz=6, ncol=1, nzen=2)
+    nzm, ng = 6, tb.ng
+    kB = 1.380649e-16
+
+    def make_profile(T_surf, P_i_surf):  # dry adiabat down to 200 K on log-spaced pressure layers
+        Ps = float(np.sum(P_i_surf))
+        edges = Ps * np.logspace(0.0, -4.0, nzm + 1)
+        P = np.sqrt(edges[:-1] * edges[1:])
+        T = np.maximum(200.0, T_surf * (P / Ps) ** 0.2)
+        n = P / (kB * T)
+        dens = n[:, None] * (P_i_surf / Ps)[None, :]
+        dz = 8.0e5 * np.log(edges[:-1] / edges[1:]) * T / 250.0
+        return dict(T=T, P=P, densities=dens, dz=dz)
+
+    # the doubled grid: layers twice, dz halved, two ghost copies of the last radiative layer (:729-773)
+    d = copy_atm_to_radiative_grid(np.arange(1.0, 4.0), np.arange(1.0, 4.0), np.ones((3, 2)), np.full(3, 2.0))
+    assert list(d["T"]) == [1, 1, 2, 2, 3, 3, 3, 3] and list(d["dz"]) == [1, 1, 1, 1, 1, 1, 1, 1]
+    rng = np.random.default_rng(2)
+    ncol = 5
+    T_surf = np.linspace(260.0, 320.0, ncol)
+    P_i = np.asfortranarray(1.0e6 * np.abs(rng.uniform(1e-4, 0.6, (ng, ncol))))
+    g = Radtran(tb, pr)
+    acb = AdiabatClimateBatch(g, make_profile)
+    isr, olr = acb.TOA_fluxes_batch(T_surf, P_i)
+    o = OracleRadtran(tb, pr)
+    cols = acb.columns(T_surf, P_i)
+    assert cols["nz"] == 2 * nzm + 2
+    for c in range(ncol):
+        ro = o.radiate(cols, c, spectral=False)
+        assert abs(isr[c] / ro["ISR"][0] - 1.0) < TOL and abs(olr[c] / ro["OLR"][0] - 1.0) < TOL
+    i1, o1 = acb.TOA_fluxes(float(T_surf[2]), P_i[:, 2])
+    assert abs(i1 / isr[2] - 1.0) < 1e-12 and abs(o1 / olr[2] - 1.0) < 1e-12
+    with pytest.raises(ClimaException, match="inconsistent"):
+        acb.TOA_fluxes_batch(T_surf[:3], P_i)
