@@ -77,3 +77,228 @@ class AdiabatClimateBatch:
     def TOA_fluxes(self, T_surf: float, P_i_surf: np.ndarray) -> Tuple[float, float]:
         isr, olr = self.TOA_fluxes_batch([T_surf], np.asarray(P_i_surf, dtype=np.float64)[:, None])
         return float(isr[0]), float(olr[0])
+
+
+# ------------------------------------------------------------------------------------------------------
+# N4: make_profile itself on the GPU (include/clima_rt.h `clima_rt_adiabat_set`, `clima_rt_make_profile_batch`,
+# `clima_rt_adiabat_toa_fluxes_batch`; kernel clima_b200/csrc/adiabat_profile.cu)
+# ------------------------------------------------------------------------------------------------------
+import ctypes as C  # noqa: E402
+from dataclasses import dataclass, field  # noqa: E402
+from typing import List, Optional  # noqa: E402
+
+from ._abi import ERR_LEN, alloc_out, c_double_p, c_int32_p  # noqa: E402
+from .radtran import _check, _i  # noqa: E402
+
+MAX_GASES, MAX_TEMPS = 16, 4
+SAT_KEYS = ("mu", "T_ref", "P_ref", "T_triple", "T_critical", "a_v", "b_v", "a_s", "b_s", "a_c", "b_c")
+PROFILE_STATUS = {1: "T_surf below T_trop", 2: "negative surface pressure", 3: "P_top above the surface pressure",
+                  4: "dop853 failed", 5: "brent failed", 6: "heat capacity out of range", 7: "negative altitudes",
+                  8: "altitude integration failed", 9: "pressure grid not decreasing", 10: "negative T_trop"}
+
+
+def species_from_yaml(path_or_dict, names: Optional[Sequence[str]] = None) -> Dict:
+    """The `species:` list of a species.yaml (templates/AdiabatClimate/species.yaml) as the dict this module
+    and the oracle use: names, mass [g/mol] (from the `atoms:` masses and each composition, as
+    src/clima_types_create.f90 does), thermo (model, temps, data) and sat (None or the LinearLatentHeat
+    parameters of src/clima_saturationdata.f90:186-283).  `names` selects and orders the gases."""
+    if isinstance(path_or_dict, dict):
+        y = path_or_dict
+    else:
+        import yaml
+        with open(path_or_dict) as f:
+            y = yaml.safe_load(f)
+    atoms = {a["name"]: float(a["mass"]) for a in y["atoms"]}
+    by_name = {s["name"]: s for s in y["species"]}
+    order = list(names) if names is not None else [s["name"] for s in y["species"]]
+    sp = dict(names=[], mass=[], thermo=[], sat=[])
+    for n in order:
+        if n not in by_name:
+            raise ClimaException('species "%s" is not in the species file' % n)
+        s = by_name[n]
+        sp["names"].append(n)
+        sp["mass"].append(sum(atoms[k] * float(v) for k, v in s["composition"].items()))
+        t = s["thermo"]
+        if t["model"] not in ("Shomate", "Nasa9"):
+            raise ClimaException('thermo "model" must be Shomate or Nasa9 for species "%s"' % n)
+        sp["thermo"].append(dict(model=t["model"], temps=[float(v) for v in t["temperature-ranges"]],
+                                 data=[[float(v) for v in r] for r in t["data"]]))
+        q = s.get("saturation")
+        if q is None:
+            sp["sat"].append(None)
+            continue
+        if q["model"] != "LinearLatentHeat":
+            raise ClimaException('Saturation "model" must be "LinearLatentHeat" for species "%s"' % n)
+        p = q["parameters"]
+        vals = (p["mu"], p["T-ref"], p["P-ref"], p["T-triple"], p["T-critical"], q["vaporization"]["a"],
+                q["vaporization"]["b"], q["sublimation"]["a"], q["sublimation"]["b"], q["super-critical"]["a"],
+                q["super-critical"]["b"])
+        sp["sat"].append({k: float(v) for k, v in zip(SAT_KEYS, vals)})
+    return sp
+
+
+class CAdiabat(C.Structure):
+    _fields_ = [("ng", C.c_int32), ("nz", C.c_int32), ("double_radiative_grid", C.c_int32),
+                ("mass", c_double_p), ("thermo_model", c_int32_p), ("thermo_ntemps", c_int32_p),
+                ("thermo_temps", c_double_p), ("thermo_data", c_double_p), ("has_sat", c_int32_p),
+                ("sat", c_double_p), ("RH", c_double_p),
+                ("planet_mass", C.c_double), ("planet_radius", C.c_double), ("P_top", C.c_double),
+                ("T_trop", C.c_double), ("rtol", C.c_double), ("atol", C.c_double)]
+
+
+PROFILE_FIELDS = ("P", "T", "z", "dz", "f_i", "f_i_surf", "N_surface", "P_surf", "P_trop")
+
+
+class CProfileOut(C.Structure):
+    _fields_ = [(k, c_double_p) for k in PROFILE_FIELDS] + [("status", c_int32_p), ("nfcn", c_int32_p)]
+
+
+class AdiabatClimate:
+    """The part of `AdiabatClimate` (src/adiabat/clima_adiabat.f90) on the path make_profile -> TOA_fluxes,
+    with the column loop of a sweep inside the call.  Public members keep the reference's names: P_top,
+    T_trop, RH, rtol, atol, double_radiative_grid; after `make_profile` P, T, f_i, z, dz, densities, P_surf,
+    P_trop, N_surface, N_atmos, convecting_with_below, lapse_rate describe the (last) column."""
+
+    def __init__(self, rad: Radtran, species: Dict, nz: int, planet_mass: float, planet_radius: float,
+                 double_radiative_grid: bool = True):
+        self.rad, self.sp, self.nz = rad, species, int(nz)
+        self.planet_mass, self.planet_radius = float(planet_mass), float(planet_radius)
+        self.double_radiative_grid = bool(double_radiative_grid)
+        self.ng = len(species["mass"])
+        self.P_top, self.T_trop = 1.0, 180.0
+        self.RH = np.ones(self.ng)
+        self.rtol, self.atol = 1.0e-9, 1.0e-12
+        self._sent = None
+
+    # -- the adiabat description goes to the device whenever a public member has changed
+    def _sync(self):
+        key = (self.P_top, self.T_trop, tuple(np.asarray(self.RH, float)), self.rtol, self.atol,
+               self.double_radiative_grid, self.nz)
+        if key == self._sent:
+            return
+        sp, ng = self.sp, self.ng
+        if ng > MAX_GASES:
+            raise ClimaException("more than %d gases" % MAX_GASES)
+        if len(self.RH) != ng:
+            raise ClimaException('make_profile: Input "RH" has the wrong dimension.')
+        mass = np.ascontiguousarray(sp["mass"], dtype=np.float64)
+        model = np.zeros(ng, np.int32)
+        ntemps = np.zeros(ng, np.int32)
+        temps = np.zeros((ng, MAX_TEMPS + 1))
+        data = np.zeros((ng, MAX_TEMPS, 9))
+        has_sat = np.zeros(ng, np.int32)
+        sat = np.zeros((ng, 11))
+        for i in range(ng):
+            t = sp["thermo"][i]
+            model[i] = 1 if t["model"] == "Shomate" else 2
+            nt = len(t["temps"]) - 1
+            if nt < 1 or nt > MAX_TEMPS:
+                raise ClimaException("1 to %d temperature ranges per gas" % MAX_TEMPS)
+            ntemps[i] = nt
+            temps[i, :nt + 1] = t["temps"]
+            for k in range(nt):
+                data[i, k, :len(t["data"][k])] = t["data"][k]
+            if sp["sat"][i] is not None:
+                has_sat[i] = 1
+                sat[i] = [sp["sat"][i][k] for k in SAT_KEYS]
+        RH = np.ascontiguousarray(self.RH, dtype=np.float64)
+        a = CAdiabat(ng, self.nz, int(self.double_radiative_grid), mass.ctypes.data_as(c_double_p),
+                     model.ctypes.data_as(c_int32_p), ntemps.ctypes.data_as(c_int32_p),
+                     temps.ctypes.data_as(c_double_p), data.ctypes.data_as(c_double_p),
+                     has_sat.ctypes.data_as(c_int32_p), sat.ctypes.data_as(c_double_p), RH.ctypes.data_as(c_double_p),
+                     self.planet_mass, self.planet_radius, float(self.P_top), float(self.T_trop), float(self.rtol),
+                     float(self.atol))
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self.rad._lib.clima_rt_adiabat_set(self.rad._h, C.byref(a), err)
+        _check(err)
+        self._sent = key
+
+    def _inputs(self, T_surf, P_i_surf):
+        T_surf = np.ascontiguousarray(T_surf, dtype=np.float64).reshape(-1)
+        P_i = np.asfortranarray(P_i_surf, dtype=np.float64)
+        if P_i.ndim == 1:
+            P_i = np.asfortranarray(P_i[:, None])
+        if P_i.shape[0] != self.ng:
+            raise ClimaException("P_i_surf has the wrong dimension")
+        if P_i.shape[1] != T_surf.shape[0]:
+            raise ClimaException('"T_surf" and "P_i_surf" have inconsistent dimensions')
+        return T_surf, P_i
+
+    def _profile_out(self, ncol):
+        nz, ng = self.nz, self.ng
+        shapes = dict(P=(nz, ncol), T=(nz, ncol), z=(nz, ncol), dz=(nz, ncol), f_i=(nz, ng, ncol),
+                      f_i_surf=(ng, ncol), N_surface=(ng, ncol), P_surf=(ncol,), P_trop=(ncol,))
+        arrs = {k: np.zeros(s, order="F") for k, s in shapes.items()}
+        arrs["status"] = np.zeros(ncol, np.int32)
+        arrs["nfcn"] = np.zeros(ncol, np.int32)
+        o = CProfileOut()
+        for k in PROFILE_FIELDS:
+            setattr(o, k, arrs[k].ctypes.data_as(c_double_p))
+        o.status = arrs["status"].ctypes.data_as(c_int32_p)
+        o.nfcn = arrs["nfcn"].ctypes.data_as(c_int32_p)
+        return o, arrs
+
+    def _derived(self, p: Dict) -> Dict:
+        """densities, N_atmos, convecting_with_below, lapse_rate (clima_adiabat.f90:446-470) on the host."""
+        k_boltz, N_avo = 1.380649e-16, 6.02214076e23
+        density = p["P"] / (k_boltz * p["T"])
+        p["densities"] = p["f_i"] * density[:, None, :]
+        p["N_atmos"] = np.einsum("zc,zgc,zc->gc", density, p["f_i"], p["dz"]) / N_avo
+        p["convecting_with_below"] = p["P"] > p["P_trop"][None, :]
+        lnT = np.log(np.vstack([self._T_surf[None, :], p["T"]]))
+        lnP = np.log(np.vstack([p["P_surf"][None, :], p["P"]]))
+        p["lapse_rate"] = np.diff(lnT, axis=0) / np.diff(lnP, axis=0)
+        return p
+
+    def make_profile_batch(self, T_surf, P_i_surf, check: bool = True) -> Dict:
+        """`make_profile` for every (T_surf[c], P_i_surf[:, c]) -> dict of (nz, ncol) / (nz, ng, ncol) arrays
+        (+ status, nfcn per column).  check=False returns the per-column status instead of raising."""
+        self._sync()
+        T_surf, P_i = self._inputs(T_surf, P_i_surf)
+        ncol = T_surf.shape[0]
+        o, arrs = self._profile_out(ncol)
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self.rad._lib.clima_rt_make_profile_batch(self.rad._h, _i(ncol), T_surf.ctypes.data_as(c_double_p),
+                                                  P_i.ctypes.data_as(c_double_p), C.byref(o), err)
+        if check or not arrs["status"].any():
+            _check(err)
+        self._T_surf = T_surf
+        with np.errstate(all="ignore"):
+            return self._derived(arrs)
+
+    def make_profile(self, T_surf: float, P_i_surf):
+        """One column; leaves the reference's member names on the object."""
+        p = self.make_profile_batch([T_surf], np.asarray(P_i_surf, dtype=np.float64)[:, None])
+        self.T_surf = float(T_surf)
+        for k in ("P", "T", "z", "dz", "lapse_rate", "convecting_with_below"):
+            setattr(self, k, p[k][:, 0].copy())
+        for k in ("f_i", "densities"):
+            setattr(self, k, p[k][:, :, 0].copy())
+        for k in ("f_i_surf", "N_surface", "N_atmos"):
+            setattr(self, k, p[k][:, 0].copy())
+        self.P_surf, self.P_trop = float(p["P_surf"][0]), float(p["P_trop"][0])
+
+    def TOA_fluxes_batch(self, T_surf, P_i_surf, full: bool = False):
+        """(ISR, OLR) of every column: make_profile, the radiative grid and the RT in ONE device call
+        (`AdiabatClimate%TOA_fluxes` per column in the reference).  full=True returns the whole result dict
+        of `Radtran.radiate_batch` plus the profile arrays."""
+        self._sync()
+        T_surf, P_i = self._inputs(T_surf, P_i_surf)
+        ncol = T_surf.shape[0]
+        nzr = 2 * self.nz + 2 if self.double_radiative_grid else self.nz
+        o, arrs = alloc_out(nzr, ncol, self.rad.tables.nw_ir, self.rad.tables.nw_sol, False)
+        po, parrs = self._profile_out(ncol) if full else (None, None)
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self.rad._lib.clima_rt_adiabat_toa_fluxes_batch(self.rad._h, _i(ncol), T_surf.ctypes.data_as(c_double_p),
+                                                        P_i.ctypes.data_as(c_double_p),
+                                                        C.byref(po) if full else None, C.byref(o), err)
+        _check(err)
+        if full:
+            self._T_surf = T_surf
+            arrs["profile"] = self._derived(parrs)
+            return arrs
+        return arrs["ISR"], arrs["OLR"]
+
+    def TOA_fluxes(self, T_surf: float, P_i_surf):
+        isr, olr = self.TOA_fluxes_batch([T_surf], np.asarray(P_i_surf, dtype=np.float64)[:, None])
+        return float(isr[0]), float(olr[0])

@@ -1,0 +1,681 @@
+// adiabat_profile.cu -- row N4 of SURVEY.md section 8(f): `AdiabatClimate%make_profile` for a batch of columns.
+//
+// One thread per column.  Each thread integrates the multispecies pseudo-adiabat (T, z)(P) from the surface
+// to P_top with DOP853 (dense output, events for "a dry gas reaches saturation" and "T reaches T_trop" located
+// with Brent's zeroin), samples it on the log-spaced pressure grid, joins the isothermal stratosphere, then
+// integrates the hydrostatic altitude again on the model grid (`compute_altitude`) and writes the column on the
+// radiative grid (`copy_atm_to_radiative_grid`) straight into the arrays the RT kernels read.
+//
+// Reference: src/adiabat/clima_adiabat_general.f90:89-669 (make_profile, integrate, solout_dop, find_root,
+// root_fcn, update_f_i_dry, mixing_ratios, right_hand_side, altitude_vs_P), src/adiabat/clima_adiabat.f90:401-472
+// and :729-773, src/adiabat/clima_adiabat_altitude.f90:16-243, src/clima_useful.f90:97-236,
+// src/clima_saturationdata.f90:56-166, src/clima_eqns.f90:82-133,201-211.  The integrator (jacobwilliams/dop853
+// 1.2.0) and the root finder (futils 0.1.14 brent_class) are dependencies that are not in the reference tree:
+// both are restated from the published algorithms (Hairer, Norsett, Wanner II.5 / dop853.f; Brent 1973).
+// The step sequence of a column depends only on that column, so a thread's result does not depend on the batch.
+#include <cfloat>
+#include <cmath>
+
+#include "dop853_tables.h"
+#include "rt_kernels.h"
+
+namespace adiabat {
+
+constexpr int MAXG = ADIABAT_MAXG;
+constexpr double RGAS = 8.31446261815324e7;  // clima_const.f90:9
+constexpr double K_BOLTZ = 1.380649e-16;     // clima_const.f90:10
+constexpr double G_GRAV = 6.67430e-11;       // clima_const.f90:12
+constexpr double N_AVO = 6.02214076e23;      // clima_const.f90:15
+
+__device__ __forceinline__ double gravity(double radius, double mass, double z) {  // clima_eqns.f90:201-211
+  const double r = (radius + z) / 1.0e2;
+  return G_GRAV * (mass / 1.0e3) / (r * r) * 1.0e2;
+}
+
+__device__ __forceinline__ double integral_fcn(double A, double B, double T) { return -A / T + B * log(T); }
+
+// SaturationData%sat_pressure (clima_saturationdata.f90:97-155); s = mu, T_ref, P_ref, T_triple, T_critical,
+// a_v, b_v, a_s, b_s, a_c, b_c
+__device__ double sat_pressure(const double *s, double T) {
+  double tmp;
+  if (T >= s[4])
+    tmp = (integral_fcn(s[5], s[6], s[4]) - integral_fcn(s[5], s[6], s[1])) +
+          (integral_fcn(s[9], s[10], T) - integral_fcn(s[9], s[10], s[4]));
+  else if (T > s[3])
+    tmp = integral_fcn(s[5], s[6], T) - integral_fcn(s[5], s[6], s[1]);
+  else
+    tmp = (integral_fcn(s[5], s[6], s[3]) - integral_fcn(s[5], s[6], s[1])) +
+          (integral_fcn(s[7], s[8], T) - integral_fcn(s[7], s[8], s[3]));
+  return s[2] * exp((s[0] / RGAS) * tmp);
+}
+
+__device__ __forceinline__ double latent_heat(const double *s, double T) {  // :56-91 [erg/g]
+  if (T >= s[4]) return s[9] + s[10] * T;
+  if (T > s[3]) return s[5] + s[6] * T;
+  return s[7] + s[8] * T;
+}
+
+// heat_capacity_eval (clima_eqns.f90:105-133) [J/(mol K)]; false when T is outside every range
+__device__ bool heat_capacity(const AdiabatData &a, int i, double T, double &cp) {
+  for (int k = 0; k < a.ntemps[i]; k++) {
+    if (T >= a.temps[i][k] && T < a.temps[i][k + 1]) {
+      const double *c = a.coef[i][k];
+      if (a.model[i] == 1) {
+        const double TT = T / 1000.0;
+        cp = c[0] + c[1] * TT + c[2] * (TT * TT) + c[3] * (TT * TT * TT) + c[4] / (TT * TT);
+      } else {
+        const double T2 = T * T;
+        cp = 8.31446261815324 *
+             (c[0] / T2 + c[1] / T + c[2] + c[3] * T + c[4] * T2 + c[5] * (T2 * T) + c[6] * (T2 * T2));
+      }
+      return true;
+    }
+  }
+  return false;
+}
+
+// AdiabatProfileData (:18-71): what the procedures below share
+struct Col {
+  const AdiabatData *a;
+  int ng;
+  signed char cond[MAXG];  // 1 = CondensingSpeciesType, 0 = DrySpeciesType
+  double f_i_dry[MAXG];
+  int err;
+  int nfcn;
+};
+
+__device__ void update_f_i_dry(Col &d, double P, const double *f_layer) {  // :529-546
+  double P_dry = 0.0;
+  for (int i = 0; i < d.ng; i++)
+    if (!d.cond[i]) P_dry += f_layer[i] * P;
+  for (int i = 0; i < d.ng; i++) d.f_i_dry[i] = (f_layer[i] * P) / P_dry;
+}
+
+__device__ void mixing_ratios(const Col &d, double P, double T, double *f, double &f_dry) {  // :548-574
+  const AdiabatData &a = *d.a;
+  double f_moist = 0.0;
+  for (int i = 0; i < d.ng; i++)
+    if (d.cond[i]) {
+      f[i] = fmin(a.RH[i] * sat_pressure(a.sat[i], T) / P, 1.0);
+      f_moist += f[i];
+    }
+  f_dry = fmax(1.0 - f_moist, 1.0e-40);
+  for (int i = 0; i < d.ng; i++)
+    if (!d.cond[i]) f[i] = f_dry * d.f_i_dry[i];
+}
+
+// one component of root_fcn (:483-513): 0 = tropopause, i + 1 = gas i reaches saturation
+__device__ double root_component(const Col &d, double P, double T, int ind) {
+  if (ind == 0) return T - d.a->T_trop;
+  const int i = ind - 1;
+  if (d.cond[i]) return 1.0;
+  if (!d.a->has_sat[i]) return DBL_MAX;
+  double f[MAXG], f_dry;
+  mixing_ratios(d, P, T, f, f_dry);
+  return d.a->RH[i] * sat_pressure(d.a->sat[i], T) - f[i] * P;
+}
+
+// right_hand_side (:576-656): Eq. 1 of Graham et al. (2021) without condensate retention, and hydrostatics
+struct ProfileRhs {
+  Col *d;
+  __device__ void operator()(double P, const double *u, double *du) const {
+    Col &c = *d;
+    const AdiabatData &a = *c.a;
+    const double T = u[0], z = u[1];
+    const double Rgas_si = RGAS / 1.0e7;
+    double f[MAXG], f_dry;
+    mixing_ratios(c, P, T, f, f_dry);
+    double mubar = 0.0;
+    for (int i = 0; i < c.ng; i++) mubar += f[i] * a.mass[i];
+    double cp_dry = DBL_MIN, first = 0.0, second = 0.0;
+    for (int i = 0; i < c.ng; i++) {
+      double cp;
+      if (!heat_capacity(a, i, T, cp)) {
+        c.err = 6;
+        du[0] = du[1] = 0.0;
+        return;
+      }
+      if (c.cond[i]) {
+        const double L = latent_heat(a.sat[i], T) * a.mass[i] * 1.0e-7;  // J/mol
+        const double beta = L / (Rgas_si * T);
+        first += f[i] * (cp - Rgas_si * beta + Rgas_si * (beta * beta));
+        second += beta * f[i];
+      } else {
+        cp_dry += c.f_i_dry[i] * cp;
+      }
+    }
+    const double dlnT_dlnP = 1.0 / (f_dry * ((cp_dry * f_dry + first) / (Rgas_si * (f_dry + second))) + second);
+    du[0] = dlnT_dlnP * (T / P);
+    const double grav = gravity(a.planet_radius, a.planet_mass, z);
+    du[1] = -(RGAS * T) / (grav * P * mubar);
+    c.nfcn++;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// DOP853: the driver loop of dop853.f (step-size rule safe 0.9, fac1 0.333, fac2 6, beta 0; hinit; the error
+// is the 5th-order estimate damped by the 3rd-order one); dense output contd8.  The stiffness test (every 1000
+// accepted steps) is left out: these integrations take < 200 steps, and nmax stops a runaway one.
+// ---------------------------------------------------------------------------------------------------------
+template <int N>
+struct Dop {
+  double K[16][N];
+  double F[7][N];
+  double yold[N];
+  double xold, hout;
+  __device__ double contd8(int i, double xq) const {
+    const double s = (xq - xold) / hout, s1 = 1.0 - s;
+    const double conpar = F[3][i] + s * (F[4][i] + s1 * (F[5][i] + s * F[6][i]));
+    return yold[i] + s * (F[0][i] + s1 * (F[1][i] + s * (F[2][i] + s1 * conpar)));
+  }
+};
+
+template <int N, class Rhs>
+__device__ void dop_stage(Dop<N> &d, int s, double x, double h, const double *y, const Rhs &rhs) {
+  double y1[N];
+#pragma unroll
+  for (int i = 0; i < N; i++) {
+    double acc = 0.0;
+    for (int j = 0; j < s; j++) acc += dop853::A[s][j] * d.K[j][i];
+    y1[i] = y[i] + h * acc;
+  }
+  rhs(x + dop853::C[s] * h, y1, d.K[s]);
+}
+
+// -> idid: 1 reached xend, 2 stopped by solout, -2 more than nmax steps, -3 step size too small
+template <int N, class Rhs, class Solout>
+__device__ int dop_integrate(Dop<N> &d, double &x, double *y, double xend, double rtol, double atol,
+                             const Rhs &rhs, Solout &solout) {
+  const double safe = 0.9, fac1 = 0.333, fac2 = 6.0, uround = 2.220446049250313e-16;
+  const int nmax = 100000;
+  double facold = 1.0e-4;
+  const double expo1 = 1.0 / 8.0, facc1 = 1.0 / fac1, facc2 = 1.0 / fac2;
+  const double posneg = copysign(1.0, xend - x);
+  const double hmax = fabs(xend - x);
+  bool last = false, reject = false;
+  int nstep = 0, naccpt = 0;
+  rhs(x, y, d.K[0]);
+  double h;
+  {  // hinit
+    double dnf = 0.0, dny = 0.0, sk[N], y1[N], f1[N];
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+      sk[i] = atol + rtol * fabs(y[i]);
+      dnf += (d.K[0][i] / sk[i]) * (d.K[0][i] / sk[i]);
+      dny += (y[i] / sk[i]) * (y[i] / sk[i]);
+    }
+    h = (dnf <= 1.0e-10 || dny <= 1.0e-10) ? 1.0e-6 : sqrt(dny / dnf) * 0.01;
+    h = copysign(fmin(h, hmax), posneg);
+#pragma unroll
+    for (int i = 0; i < N; i++) y1[i] = y[i] + h * d.K[0][i];
+    rhs(x + h, y1, f1);
+    double der2 = 0.0;
+#pragma unroll
+    for (int i = 0; i < N; i++) der2 += ((f1[i] - d.K[0][i]) / sk[i]) * ((f1[i] - d.K[0][i]) / sk[i]);
+    der2 = sqrt(der2) / h;
+    const double der12 = fmax(fabs(der2), sqrt(dnf));
+    const double h1 = der12 <= 1.0e-15 ? fmax(1.0e-6, fabs(h) * 1.0e-3) : pow(0.01 / der12, 1.0 / 8.0);
+    h = copysign(fmin(fmin(100.0 * fabs(h), h1), hmax), posneg);
+  }
+  d.xold = x;
+  d.hout = 1.0;
+  if (solout(d, naccpt + 1, x, x, y) < 0) return 2;
+  for (;;) {
+    if (nstep > nmax) return -2;
+    if (0.1 * fabs(h) <= fabs(x) * uround) return -3;
+    if ((x + 1.01 * h - xend) * posneg > 0.0) {
+      h = xend - x;
+      last = true;
+    }
+    nstep++;
+    for (int s = 1; s < 12; s++) dop_stage<N>(d, s, x, h, y, rhs);
+    const double xph = x + h;
+    double ynew[N], err = 0.0, err2 = 0.0;
+#pragma unroll
+    for (int i = 0; i < N; i++) {
+      double k4 = 0.0, e5 = 0.0, e3 = 0.0;
+      for (int j = 0; j < 12; j++) {
+        k4 += dop853::B[j] * d.K[j][i];
+        e5 += dop853::E5[j] * d.K[j][i];
+        e3 += dop853::E3[j] * d.K[j][i];
+      }
+      ynew[i] = y[i] + h * k4;
+      const double sk = atol + rtol * fmax(fabs(y[i]), fabs(ynew[i]));
+      err += (e5 / sk) * (e5 / sk);
+      err2 += (e3 / sk) * (e3 / sk);
+    }
+    double deno = err + 0.01 * err2;
+    if (deno <= 0.0) deno = 1.0;
+    err = fabs(h) * err * sqrt(1.0 / (N * deno));
+    const double fac11 = pow(err, expo1);
+    const double fac = fmax(facc2, fmin(facc1, fac11 / safe));
+    double hnew = h / fac;
+    if (err <= 1.0) {
+      facold = fmax(err, 1.0e-4);
+      naccpt++;
+      rhs(xph, ynew, d.K[12]);
+      for (int s = 13; s < 16; s++) dop_stage<N>(d, s, x, h, y, rhs);
+#pragma unroll
+      for (int i = 0; i < N; i++) {
+        const double dy = ynew[i] - y[i];
+        d.F[0][i] = dy;
+        d.F[1][i] = h * d.K[0][i] - dy;
+        d.F[2][i] = 2.0 * dy - h * (d.K[12][i] + d.K[0][i]);
+        for (int r = 0; r < 4; r++) {
+          double acc = 0.0;
+          for (int j = 0; j < 16; j++) acc += dop853::D[r][j] * d.K[j][i];
+          d.F[3 + r][i] = h * acc;
+        }
+        d.yold[i] = y[i];
+        d.K[0][i] = d.K[12][i];
+        y[i] = ynew[i];
+      }
+      d.hout = h;
+      d.xold = x;
+      x = xph;
+      if (solout(d, naccpt + 1, d.xold, x, y) < 0) return 2;
+      if (last) return 1;
+      if (fabs(hnew) > hmax) hnew = posneg * hmax;
+      if (reject) hnew = posneg * fmin(fabs(hnew), fabs(h));
+      reject = false;
+    } else {
+      hnew = h / fmin(facc1, fac11 / safe);
+      reject = true;
+      last = false;
+    }
+    h = hnew;
+  }
+  (void)facold;
+}
+
+// Brent's zeroin (futils brent_class%find_zero); info -1 when f(ax) and f(bx) have one sign
+template <class Fn>
+__device__ double zeroin(const Fn &f, double ax, double bx, double tol, int &info) {
+  const double eps = 2.220446049250313e-16;
+  double a = ax, b = bx, fa = f(a), fb = f(b);
+  info = 0;
+  if (fa * fb > 0.0) {
+    info = -1;
+    return b;
+  }
+  double c = a, fc = fa, dd = b - a, e = dd;
+  for (;;) {
+    if ((fb > 0.0 && fc > 0.0) || (fb < 0.0 && fc < 0.0)) {
+      c = a;
+      fc = fa;
+      dd = e = b - a;
+    }
+    if (fabs(fc) < fabs(fb)) {
+      a = b; b = c; c = a;
+      fa = fb; fb = fc; fc = fa;
+    }
+    const double tol1 = 2.0 * eps * fabs(b) + 0.5 * tol;
+    const double xm = 0.5 * (c - b);
+    if (fabs(xm) <= tol1 || fb == 0.0) return b;
+    if (fabs(e) >= tol1 && fabs(fa) > fabs(fb)) {
+      double p, q, s = fb / fa;
+      if (a == c) {
+        p = 2.0 * xm * s;
+        q = 1.0 - s;
+      } else {
+        q = fa / fc;
+        const double r = fb / fc;
+        p = s * (2.0 * xm * q * (q - r) - (b - a) * (r - 1.0));
+        q = (q - 1.0) * (r - 1.0) * (s - 1.0);
+      }
+      if (p > 0.0) q = -q; else p = -p;
+      if (2.0 * p < fmin(3.0 * xm * q - fabs(tol1 * q), fabs(e * q))) {
+        e = dd;
+        dd = p / q;
+      } else {
+        dd = e = xm;
+      }
+    } else {
+      dd = e = xm;
+    }
+    a = b;
+    fa = fb;
+    b += fabs(dd) > tol1 ? dd : copysign(tol1, xm);
+    fb = f(b);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// solout_dop (:355-449): event search on the step just accepted, then the samples on the pressure grid
+// ---------------------------------------------------------------------------------------------------------
+struct ProfileSolout {
+  Col *col;
+  // the log-spaced edge grid P_e(0 .. ne-1) (:256-260), generated on the fly
+  int ne, j;
+  double l0, range, P_surf, Pj;
+  double gout_old[MAXG + 1];
+  int reason;  // 0 reached P_top, 1 tropopause, 2 a gas reached saturation
+  int ind_sat;
+  double P_root, u_root[2];
+  bool z_negative;
+  // model-grid outputs of this column: layer i is edge 2 i + 1
+  double *T_m, *f_m;  // T_m[i], f_m[i + nz * g]
+  int nz;
+
+  __device__ double P_edge(int k) const {
+    if (k == 0) return P_surf;
+    if (k == ne - 1) return col->a->P_top;
+    return pow(10.0, l0 + range * k / (ne - 1));
+  }
+  __device__ void sample(int k, double T, double z, const double *f) {
+    if (z < 0.0 && k < ne - 1) z_negative = true;
+    if (k & 1) {
+      const int i = k >> 1;
+      T_m[i] = T;
+      for (int g = 0; g < col->ng; g++) f_m[i + (size_t)nz * g] = f[g];
+    }
+  }
+  __device__ int operator()(const Dop<2> &dop, int nr, double P_old, double P_cur, const double *y) {
+    Col &d = *col;
+    if (d.err) return -10;
+    int irtrn = 1;
+    double gout[MAXG + 1];
+    for (int i = 0; i <= d.ng; i++) gout[i] = root_component(d, P_cur, y[0], i);
+    if (nr == 1)
+      for (int i = 0; i <= d.ng; i++) gout_old[i] = gout[i];
+    double best = 0.0;
+    int ind_root = -1;
+    for (int i = 0; i <= d.ng; i++) {
+      if ((gout_old[i] < 0.0 && gout[i] > 0.0) || (gout_old[i] > 0.0 && gout[i] < 0.0)) {
+        int info;
+        const double r = zeroin([&](double x) { return root_component(d, x, dop.contd8(0, x), i); }, P_old,
+                                P_cur, 1.0e-8, info);
+        if (info != 0) {
+          d.err = 5;
+          return -10;
+        }
+        if (ind_root < 0 || r > best) {  // the highest-pressure root, the first one on a tie (maxloc)
+          best = r;
+          ind_root = i;
+        }
+      }
+    }
+    if (ind_root >= 0) {
+      irtrn = -1;
+      P_root = best;
+      u_root[0] = dop.contd8(0, P_root);
+      u_root[1] = dop.contd8(1, P_root);
+      if (ind_root == 0) {
+        reason = 1;
+      } else {
+        reason = 2;
+        ind_sat = ind_root - 1;
+      }
+    }
+    for (int i = 0; i <= d.ng; i++) gout_old[i] = gout[i];
+    if (j < ne) {
+      const double PP = irtrn == -1 ? P_root : P_cur;
+      if (Pj <= P_old && Pj >= PP) {
+        while (Pj >= PP) {
+          const double T = dop.contd8(0, Pj), z = dop.contd8(1, Pj);
+          double f[MAXG], f_dry;
+          mixing_ratios(d, Pj, T, f, f_dry);
+          sample(j, T, z, f);
+          j++;
+          if (j >= ne) break;
+          Pj = P_edge(j);
+        }
+      }
+    }
+    return irtrn;
+  }
+};
+
+__device__ double altitude_vs_P(double P, double T, double mubar, double P0, double z0, double planet_mass,
+                                double planet_radius) {  // :659-669
+  const double G_grav_cgs = 6.67e-8;
+  return 1.0 / ((N_AVO * K_BOLTZ * T) / (G_grav_cgs * planet_mass * mubar) * log(P / P0) + 1.0 / (planet_radius + z0)) -
+         planet_radius;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// compute_altitude (clima_adiabat_altitude.f90, reference_pressure <= 0): hydrostatics over T and mubar
+// interpolated linearly in log10 P between the surface and the layer centres
+// ---------------------------------------------------------------------------------------------------------
+struct AltitudeRhs {
+  // descending in pressure (ground first): lp[0 .. nz], Tg, mg of this column
+  const double *lp, *Tg, *mg;
+  int nz;
+  double planet_mass, planet_radius;
+  // linear_interp_1d%evaluate on the ascending grid xg(a) = lp[nz - a]: the bracketing interval, the end
+  // intervals outside the grid
+  __device__ void interp(double x, double &T, double &m) const {
+    const int n = nz + 1;
+    const double x0 = lp[nz], x1 = lp[0];
+    int a = (int)floor((x - x0) / (x1 - x0) * (n - 1));
+    a = min(max(a, 0), n - 2);
+    while (a > 0 && x < lp[nz - a]) a--;
+    while (a < n - 2 && x >= lp[nz - a - 1]) a++;
+    const double xa = lp[nz - a], xb = lp[nz - a - 1];
+    const double q = (x - xa) / (xb - xa), p = 1.0 - q;
+    T = p * Tg[nz - a] + q * Tg[nz - a - 1];
+    m = p * mg[nz - a] + q * mg[nz - a - 1];
+  }
+  __device__ void operator()(double P, const double *u, double *du) const {
+    double T, m;
+    interp(log10(P), T, m);
+    du[0] = -(RGAS * T) / (gravity(planet_radius, planet_mass, u[0]) * P * m);
+  }
+};
+
+// solout_dop853_solveivp (clima_useful.f90:216-236): dense-output samples at the requested pressures
+struct AltitudeSolout {
+  const double *x_eval;  // P_e2[1 .. m]
+  double *y_eval;
+  int m, j;
+  double xtol;
+  __device__ int operator()(const Dop<1> &dop, int nr, double xold, double x, const double *y) {
+    const double x_lo = fmin(xold, x) - xtol, x_hi = fmax(xold, x) + xtol;
+    while (j < m) {
+      const double xe = x_eval[j];
+      if (xe < x_lo || xe > x_hi) break;
+      y_eval[j] = dop.contd8(0, xe);
+      j++;
+    }
+    return 1;
+  }
+};
+
+// One column per thread.  Model-grid outputs are (nz, ncol) / (nz, ng, ncol) with nz fastest; the radiative
+// grid (nzr = 2 nz + 2 when doubled, else nz) likewise.  `work` holds, per column, lp / Tg / mg (nz + 1 each),
+// the second edge grid and its altitudes (2 nz + 1 each).
+__global__ void __launch_bounds__(ADIABAT_THREADS)
+make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, const double *__restrict__ T_surf_in,
+                    const double *__restrict__ P_i_surf, AdiabatOut o, double *__restrict__ work) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= ncol) return;
+  const AdiabatData &a = *ap;
+  const int ng = a.ng, nz = a.nz, ne = 2 * nz + 1;
+  const double T_surf = T_surf_in[c];
+  const double *Pin = P_i_surf + (size_t)ng * c;
+  double *T_m = o.T + (size_t)nz * c, *P_m = o.P + (size_t)nz * c, *z_m = o.z + (size_t)nz * c,
+         *dz_m = o.dz + (size_t)nz * c, *f_m = o.f_i + (size_t)nz * ng * c;
+  double *N_surface = o.N_surface + (size_t)ng * c;
+  int status = 0;
+  Col col;
+  col.a = ap;
+  col.ng = ng;
+  col.err = 0;
+  col.nfcn = 0;
+  o.P_trop[c] = -1.0;
+  o.P_surf[c] = 0.0;
+
+  // input checks (:124-139)
+  if (T_surf < a.T_trop) status = 1;
+  for (int i = 0; i < ng; i++)
+    if (Pin[i] < 0.0 && !status) status = 2;
+  if (a.T_trop < 0.0 && !status) status = 10;
+  if (status) {
+    o.status[c] = status;
+    return;
+  }
+
+  // which gases condense at the surface (:199-224), the surface reservoir of those that do
+  const double grav0 = gravity(a.planet_radius, a.planet_mass, 0.0);
+  double f_cur[MAXG], P_surf = 0.0;
+  for (int i = 0; i < ng; i++) {
+    const double P_sat = a.has_sat[i] ? a.RH[i] * sat_pressure(a.sat[i], T_surf) : DBL_MAX;
+    if (Pin[i] > P_sat) {
+      f_cur[i] = P_sat;
+      N_surface[i] = (Pin[i] - P_sat) / (a.mass[i] * grav0);
+      col.cond[i] = 1;
+    } else {
+      f_cur[i] = Pin[i];
+      N_surface[i] = 0.0;
+      col.cond[i] = 0;
+    }
+    P_surf += f_cur[i];
+  }
+  o.P_surf[c] = P_surf;
+  if (a.P_top > P_surf) {
+    o.status[c] = 3;
+    return;
+  }
+  for (int i = 0; i < ng; i++) f_cur[i] /= P_surf;
+  update_f_i_dry(col, P_surf, f_cur);
+  for (int i = 0; i < ng; i++) o.f_i_surf[(size_t)ng * c + i] = f_cur[i];
+
+  ProfileSolout so;
+  so.col = &col;
+  so.ne = ne;
+  so.j = 1;
+  so.l0 = log10(P_surf);
+  so.range = log10(a.P_top) - so.l0;
+  so.P_surf = P_surf;
+  so.Pj = so.P_edge(1);
+  so.reason = 0;
+  so.z_negative = false;
+  so.T_m = T_m;
+  so.f_m = f_m;
+  so.nz = nz;
+  for (int i = 0; i < nz; i++) P_m[i] = so.P_edge(2 * i + 1);
+
+  // integrate (:274-353): restart after every "gas reached saturation" event with that gas condensing
+  {
+    Dop<2> dop;
+    ProfileRhs rhs{&col};
+    double u[2] = {T_surf, 0.0}, Pn = P_surf;
+    for (;;) {
+      so.reason = 0;
+      const int idid = dop_integrate<2>(dop, Pn, u, a.P_top, a.rtol, a.atol, rhs, so);
+      if (col.err) {
+        status = col.err;
+        break;
+      }
+      if (idid < 0) {
+        status = 4;
+        break;
+      }
+      if (so.reason != 2) break;
+      Pn = so.P_root;
+      u[0] = so.u_root[0];
+      u[1] = so.u_root[1];
+      double f_dry;
+      mixing_ratios(col, Pn, u[0], f_cur, f_dry);
+      col.cond[so.ind_sat] = 1;
+      update_f_i_dry(col, Pn, f_cur);
+    }
+  }
+  if (!status && so.reason == 1) {  // isothermal stratosphere above the tropopause (:331-351)
+    double f_dry;
+    mixing_ratios(col, so.P_root, so.u_root[0], f_cur, f_dry);
+    o.P_trop[c] = so.P_root;
+    double mubar = 0.0;
+    for (int i = 0; i < ng; i++) mubar += f_cur[i] * a.mass[i];
+    for (int k = so.j; k < ne; k++)
+      so.sample(k, a.T_trop,
+                altitude_vs_P(so.P_edge(k), a.T_trop, mubar, so.P_root, so.u_root[1], a.planet_mass, a.planet_radius),
+                f_cur);
+  }
+  if (!status && so.z_negative) status = 7;
+  o.nfcn[c] = col.nfcn;
+  if (status) {
+    o.status[c] = status;
+    return;
+  }
+
+  // compute_altitude (clima_adiabat_altitude.f90:41-193)
+  double *lp = work + (size_t)c * (3 * (nz + 1) + 2 * ne), *Tg = lp + nz + 1, *mg = Tg + nz + 1, *P_e2 = mg + nz + 1,
+         *z_e = P_e2 + ne;
+  lp[0] = log10(P_surf);
+  Tg[0] = T_surf;
+  {
+    double m0 = 0.0;
+    for (int g = 0; g < ng; g++) m0 += o.f_i_surf[(size_t)ng * c + g] * a.mass[g];
+    mg[0] = m0;
+  }
+  P_e2[0] = P_surf;
+  for (int i = 0; i < nz; i++) {
+    lp[i + 1] = log10(P_m[i]);
+    Tg[i + 1] = T_m[i];
+    double m = 0.0;
+    for (int g = 0; g < ng; g++) m += f_m[i + (size_t)nz * g] * a.mass[g];
+    mg[i + 1] = m;
+    P_e2[2 * i + 1] = P_m[i];
+    if (i < nz - 1) P_e2[2 * i + 2] = sqrt(P_m[i] * P_m[i + 1]);
+  }
+  P_e2[2 * nz] = a.P_top;
+  {
+    double dmin = DBL_MAX;
+    for (int k = 0; k < 2 * nz; k++) dmin = fmin(dmin, P_e2[k] - P_e2[k + 1]);
+    const double ulp = nextafter(P_surf, DBL_MAX) - P_surf;  // spacing(P_e(1))
+    if (dmin <= 10.0 * ulp) status = 9;
+  }
+  if (!status) {
+    Dop<1> dop;
+    AltitudeRhs rhs{lp, Tg, mg, nz, a.planet_mass, a.planet_radius};
+    AltitudeSolout as;
+    as.x_eval = P_e2 + 1;
+    as.y_eval = z_e + 1;
+    as.m = 2 * nz - 1;
+    as.j = 0;
+    const double big = fmax(1.0, P_surf);
+    as.xtol = fmax(1.0e-12 * big, 10.0 * (nextafter(big, DBL_MAX) - big));
+    z_e[0] = 0.0;
+    double x = P_surf, y[1] = {0.0};
+    const int idid = dop_integrate<1>(dop, x, y, P_e2[2 * nz - 1], a.rtol, a.atol, rhs, as);
+    if (idid < 0 || as.j < as.m) status = 8;
+    z_e[2 * nz] = z_e[2 * nz - 1] + (z_e[2 * nz - 1] - z_e[2 * nz - 2]);
+  }
+  o.status[c] = status;
+  if (status) return;
+  for (int i = 0; i < nz; i++) {
+    z_m[i] = z_e[2 * i + 1];
+    dz_m[i] = z_e[2 * i + 2] - z_e[2 * i];
+  }
+
+  // densities (clima_adiabat.f90:446-449) and copy_atm_to_radiative_grid (:729-773), pressures in bars
+  if (o.T_r) {
+    const int nzr = a.double_radiative_grid ? 2 * nz + 2 : nz;
+    double *T_r = o.T_r + (size_t)nzr * c, *P_r = o.P_r + (size_t)nzr * c, *dz_r = o.dz_r + (size_t)nzr * c,
+           *dens_r = o.dens_r + (size_t)nzr * ng * c;
+    for (int i = 0; i < nz; i++) {
+      const double density = P_m[i] / (K_BOLTZ * T_m[i]);
+      const int reps = a.double_radiative_grid ? (i == nz - 1 ? 4 : 2) : 1;
+      const int j0 = a.double_radiative_grid ? 2 * i : i;
+      const double dzr = a.double_radiative_grid ? 0.5 * dz_m[i] : dz_m[i];
+      for (int r = 0; r < reps; r++) {
+        T_r[j0 + r] = T_m[i];
+        P_r[j0 + r] = P_m[i] / 1.0e6;
+        dz_r[j0 + r] = dzr;
+        for (int g = 0; g < ng; g++) dens_r[j0 + r + (size_t)nzr * g] = f_m[i + (size_t)nz * g] * density;
+      }
+    }
+    o.Tsurf_r[c] = T_surf;
+  }
+}
+
+}  // namespace adiabat
+
+size_t rt_adiabat_work_doubles(int nz, int ncol) { return (size_t)ncol * (3 * (nz + 1) + 2 * (2 * nz + 1)); }
+
+void rt_launch_make_profile(const AdiabatData *a, int ncol, const double *T_surf, const double *P_i_surf,
+                            const AdiabatOut &o, double *work, cudaStream_t st) {
+  const int blocks = (ncol + ADIABAT_THREADS - 1) / ADIABAT_THREADS;
+  adiabat::make_profile_kernel<<<blocks, ADIABAT_THREADS, 0, st>>>(a, ncol, T_surf, P_i_surf, o, work);
+}

@@ -109,6 +109,16 @@ struct Handle {
   int jac_delta = 1;  // CLIMA_RT_JAC=full: every column through the full IR solve (the round-1 path)
   int64_t jac_delta_calls = 0, jac_full_calls = 0;
 
+  // N4 (adiabat_profile.cu): the adiabat description on the device, per-call column buffers
+  AdiabatData *d_adiabat = nullptr;
+  AdiabatData adiabat{};
+  bool adiabat_set = false;
+  std::vector<void *> adiabat_allocs;
+  size_t adiabat_cap_cols = 0;
+  double *d_aTs = nullptr, *d_aPi = nullptr, *d_awork = nullptr;
+  AdiabatOut aout{};
+  int64_t adiabat_calls = 0;
+
   // introspection
   int64_t launches = 0;
   int last_unit_order = 0;  // RORR unit order of the last chunk: 0 column-grouped, 1 slot-fastest
@@ -879,6 +889,93 @@ void comm_buffers(Handle &h, size_t block) {
 }  // namespace
 
 // =============================================================================================
+/* ---- N4: batched make_profile (adiabat_profile.cu) ------------------------------------------------ */
+static const char *profile_message(int status) {
+  switch (status) {  // the reference's own strings
+    case 1: return "make_profile: Input \"T_surf\" is less than input \"T_trop\"";
+    case 2: return "make_profile: Surface pressures (input \"P_i_surf\") must be positive";
+    case 3: return "make_profile: \"P_top\" is bigger than the surface pressure";
+    case 4: return "dop853 integration failed";
+    case 5: return "brent failed in \"find_root\"";
+    case 6: return "Failed to compute heat capacity";
+    case 7: return "\"make_profile\" yielded negative altitudes. This may be caused by the lack of a hydrostatic solution to the entered atmosphere.";
+    case 8: return "compute_altitude: altitude segment integration failed.";
+    case 9: return "compute_altitude: pressure grid is not strictly decreasing.";
+    case 10: return "make_profile: Input \"T_trop\" is less than 0";
+  }
+  return "make_profile failed";
+}
+
+static void adiabat_ensure(Handle &h, size_t ncol) {
+  if (ncol <= h.adiabat_cap_cols) return;
+  CK(cudaStreamSynchronize(h.st));
+  for (void *q : h.adiabat_allocs) cudaFree(q);
+  h.adiabat_allocs.clear();
+  h.adiabat_cap_cols = 0;
+  const size_t nz = h.adiabat.nz, ng = h.adiabat.ng;
+  const size_t nzr = h.adiabat.double_radiative_grid ? 2 * nz + 2 : nz;
+  auto dalloc = [&](size_t n) {
+    double *d = nullptr;
+    CK(cudaMalloc(&d, std::max<size_t>(n, 1) * sizeof(double)));
+    h.adiabat_allocs.push_back(d);
+    return d;
+  };
+  AdiabatOut &o = h.aout;
+  h.d_aTs = dalloc(ncol);
+  h.d_aPi = dalloc(ng * ncol);
+  h.d_awork = dalloc(rt_adiabat_work_doubles((int)nz, (int)ncol));
+  o.P = dalloc(nz * ncol); o.T = dalloc(nz * ncol); o.z = dalloc(nz * ncol); o.dz = dalloc(nz * ncol);
+  o.f_i = dalloc(nz * ng * ncol);
+  o.f_i_surf = dalloc(ng * ncol); o.N_surface = dalloc(ng * ncol);
+  o.P_surf = dalloc(ncol); o.P_trop = dalloc(ncol);
+  o.status = reinterpret_cast<int *>(dalloc(ncol)); o.nfcn = reinterpret_cast<int *>(dalloc(ncol));
+  o.T_r = dalloc(nzr * ncol); o.P_r = dalloc(nzr * ncol); o.dz_r = dalloc(nzr * ncol);
+  o.dens_r = dalloc(nzr * ng * ncol); o.Tsurf_r = dalloc(ncol);
+  h.adiabat_cap_cols = ncol;
+}
+
+// make_profile for every column on the device; copies what `prof` asks for back to the host.  Returns the
+// first failed column (-1: none) and its status.
+static int make_profile_impl(Handle &h, int ncol, const double *T_surf, const double *P_i_surf,
+                             const clima_rt_profile_out *prof, int *first_status) {
+  CK(cudaSetDevice(h.device));
+  if (!h.adiabat_set) throw CudaError{"clima_rt_adiabat_set has not been called on this handle"};
+  if (ncol < 1) throw CudaError{"ncol must be >= 1"};
+  if (!T_surf || !P_i_surf) throw CudaError{"clima_rt: null argument"};
+  adiabat_ensure(h, (size_t)ncol);
+  const size_t nz = h.adiabat.nz, ng = h.adiabat.ng, n = (size_t)ncol;
+  NvtxRange r("make_profile");
+  CK(cudaMemcpyAsync(h.d_aTs, T_surf, n * 8, cudaMemcpyHostToDevice, h.st));
+  CK(cudaMemcpyAsync(h.d_aPi, P_i_surf, n * ng * 8, cudaMemcpyHostToDevice, h.st));
+  rt_launch_make_profile(h.d_adiabat, ncol, h.d_aTs, h.d_aPi, h.aout, h.d_awork, h.st);
+  CK(cudaGetLastError());
+  h.launches++;
+  h.adiabat_calls++;
+  std::vector<int> status(n);
+  CK(cudaMemcpyAsync(status.data(), h.aout.status, n * sizeof(int), cudaMemcpyDeviceToHost, h.st));
+  if (prof) {
+    auto back = [&](void *dst, const void *src, size_t bytes) {
+      if (dst) CK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, h.st));
+    };
+    const AdiabatOut &o = h.aout;
+    back(prof->P, o.P, nz * n * 8); back(prof->T, o.T, nz * n * 8); back(prof->z, o.z, nz * n * 8);
+    back(prof->dz, o.dz, nz * n * 8); back(prof->f_i, o.f_i, nz * ng * n * 8);
+    back(prof->f_i_surf, o.f_i_surf, ng * n * 8); back(prof->N_surface, o.N_surface, ng * n * 8);
+    back(prof->P_surf, o.P_surf, n * 8); back(prof->P_trop, o.P_trop, n * 8);
+    back(prof->nfcn, o.nfcn, n * sizeof(int));
+  }
+  CK(cudaStreamSynchronize(h.st));
+  int first = -1;
+  for (size_t c = 0; c < n; c++) {
+    if (prof && prof->status) prof->status[c] = status[c];
+    if (status[c] && first < 0) {
+      first = (int)c;
+      *first_status = status[c];
+    }
+  }
+  return first;
+}
+
 extern "C" {
 
 void clima_rt_create(const clima_rt_tables *tables, const clima_rt_params *params,
@@ -952,6 +1049,8 @@ void clima_rt_destroy(void *handle) {
   for (double *p : {h->d_baseT, h->d_basef, h->d_factor, h->d_jTm, h->d_jTs, h->d_jpartial, h->d_jout}) if (p) cudaFree(p);
   if (h->d_jwin) cudaFree(h->d_jwin);
   if (h->d_jflag) cudaFree(h->d_jflag);
+  for (void *q : h->adiabat_allocs) cudaFree(q);
+  if (h->d_adiabat) cudaFree(h->d_adiabat);
   free_chunk(*h);
   for (void *p : h->table_allocs) cudaFree(p);
   for (auto &p : h->d_custom) if (p) cudaFree(p);
@@ -1157,6 +1256,93 @@ void clima_rt_radiate_batch_sharded(void *handle, const int32_t *ncol, const int
       }
     }
     CK(cudaStreamSynchronize(h.st));
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_adiabat_set(void *handle, const clima_rt_adiabat *ad, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle) throw CudaError{"clima_rt: NULL handle"};
+    Handle &h = *static_cast<Handle *>(handle);
+    CK(cudaSetDevice(h.device));
+    if (!ad || !ad->mass || !ad->thermo_model || !ad->thermo_ntemps || !ad->thermo_temps || !ad->thermo_data ||
+        !ad->has_sat || !ad->sat || !ad->RH)
+      throw CudaError{"clima_rt_adiabat_set: null argument"};
+    if (ad->ng != h.tb.ng) throw CudaError{"clima_rt_adiabat_set: \"ng\" differs from the radiative tables"};
+    if (ad->ng > ADIABAT_MAXG) throw CudaError{"clima_rt_adiabat_set: more than 16 gases"};
+    if (ad->nz < 2) throw CudaError{"compute_altitude requires nz >= 2"};
+    if (h.tb.np > 0) throw CudaError{"clima_rt_adiabat_set: tables with particles are not supported on this path"};
+    if (!(ad->rtol > 0.0) || !(ad->atol > 0.0) || !(ad->P_top > 0.0))
+      throw CudaError{"clima_rt_adiabat_set: rtol, atol and P_top must be positive"};
+    AdiabatData a{};
+    a.ng = ad->ng;
+    a.nz = ad->nz;
+    a.double_radiative_grid = ad->double_radiative_grid != 0;
+    for (int i = 0; i < a.ng; i++) {
+      a.mass[i] = ad->mass[i];
+      a.model[i] = ad->thermo_model[i];
+      a.ntemps[i] = ad->thermo_ntemps[i];
+      if (a.model[i] != 1 && a.model[i] != 2) throw CudaError{"clima_rt_adiabat_set: thermo model must be 1 (Shomate) or 2 (NASA-9)"};
+      if (a.ntemps[i] < 1 || a.ntemps[i] > ADIABAT_MAXT) throw CudaError{"clima_rt_adiabat_set: 1 to 4 temperature ranges per gas"};
+      for (int k = 0; k <= ADIABAT_MAXT; k++) a.temps[i][k] = ad->thermo_temps[(size_t)i * (ADIABAT_MAXT + 1) + k];
+      for (int k = 0; k < ADIABAT_MAXT; k++)
+        for (int q = 0; q < 9; q++) a.coef[i][k][q] = ad->thermo_data[((size_t)i * ADIABAT_MAXT + k) * 9 + q];
+      a.has_sat[i] = ad->has_sat[i] != 0;
+      for (int q = 0; q < 11; q++) a.sat[i][q] = ad->sat[(size_t)i * 11 + q];
+      a.RH[i] = ad->RH[i];
+    }
+    a.planet_mass = ad->planet_mass;
+    a.planet_radius = ad->planet_radius;
+    a.P_top = ad->P_top;
+    a.T_trop = ad->T_trop;
+    a.rtol = ad->rtol;
+    a.atol = ad->atol;
+    CK(cudaStreamSynchronize(h.st));
+    if (h.adiabat_set && (a.nz != h.adiabat.nz || a.double_radiative_grid != h.adiabat.double_radiative_grid)) {
+      for (void *q : h.adiabat_allocs) cudaFree(q);  // buffers are sized by nz
+      h.adiabat_allocs.clear();
+      h.adiabat_cap_cols = 0;
+    }
+    if (!h.d_adiabat) CK(cudaMalloc(&h.d_adiabat, sizeof(AdiabatData)));
+    CK(cudaMemcpy(h.d_adiabat, &a, sizeof(AdiabatData), cudaMemcpyHostToDevice));
+    h.adiabat = a;
+    h.adiabat_set = true;
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_make_profile_batch(void *handle, const int32_t *ncol, const double *T_surf,
+                                 const double *P_i_surf, const clima_rt_profile_out *profile, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle) throw CudaError{"clima_rt: NULL handle"};
+    if (!ncol) throw CudaError{"clima_rt: null argument"};
+    int st = 0;
+    const int bad = make_profile_impl(*static_cast<Handle *>(handle), *ncol, T_surf, P_i_surf, profile, &st);
+    if (bad >= 0) set_err(err, "column " + std::to_string(bad) + ": " + profile_message(st));
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_adiabat_toa_fluxes_batch(void *handle, const int32_t *ncol, const double *T_surf,
+                                       const double *P_i_surf, const clima_rt_profile_out *profile,
+                                       const clima_rt_out *out, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle) throw CudaError{"clima_rt: NULL handle"};
+    if (!ncol) throw CudaError{"clima_rt: null argument"};
+    Handle &h = *static_cast<Handle *>(handle);
+    int st = 0;
+    const int bad = make_profile_impl(h, *ncol, T_surf, P_i_surf, profile, &st);
+    if (bad >= 0) throw CudaError{"column " + std::to_string(bad) + ": " + profile_message(st)};
+    const AdiabatOut &o = h.aout;
+    const int nzr = h.adiabat.double_radiative_grid ? 2 * h.adiabat.nz + 2 : h.adiabat.nz;
+    HostIn in{o.Tsurf_r, o.T_r, o.P_r, o.dens_r, o.dz_r, nullptr, nullptr};
+    radiate_batch_impl(h, true, *ncol, nzr, h.adiabat.ng, 0, in, true, true, out, 0);
   } catch (const CudaError &e) {
     set_err(err, e.msg);
   }

@@ -52,3 +52,35 @@ void rt_launch_jac_reduce(const double *partial, const double *basef, double *ou
                           cudaStream_t st);
 // fp64_peak.cu
 double rt_measure_fp64_tflops(int device, cudaStream_t st);
+
+// adiabat_profile.cu (N4: batched AdiabatClimate%make_profile)
+#ifndef ADIABAT_MAXG
+#define ADIABAT_MAXG 16  // gases
+#endif
+#define ADIABAT_MAXT 4   // temperature ranges of a heat-capacity polynomial
+#ifndef ADIABAT_THREADS
+#define ADIABAT_THREADS 32  // one column per thread; small blocks spread a batch over the SMs
+#endif
+struct AdiabatData {  // device copy of what make_profile reads from the AdiabatClimate object
+  int ng, nz, double_radiative_grid;
+  double mass[ADIABAT_MAXG];
+  int model[ADIABAT_MAXG];   // 1 Shomate, 2 NASA-9
+  int ntemps[ADIABAT_MAXG];
+  double temps[ADIABAT_MAXG][ADIABAT_MAXT + 1];
+  double coef[ADIABAT_MAXG][ADIABAT_MAXT][9];
+  int has_sat[ADIABAT_MAXG];
+  double sat[ADIABAT_MAXG][11];  // mu, T_ref, P_ref, T_triple, T_critical, a_v, b_v, a_s, b_s, a_c, b_c
+  double RH[ADIABAT_MAXG];
+  double planet_mass, planet_radius, P_top, T_trop, rtol, atol;
+};
+struct AdiabatOut {  // device pointers
+  double *P, *T, *z, *dz;            // (nz, ncol)
+  double *f_i;                       // (nz, ng, ncol)
+  double *f_i_surf, *N_surface;      // (ng, ncol)
+  double *P_surf, *P_trop;           // (ncol)
+  int *status, *nfcn;                // (ncol)
+  double *T_r, *P_r, *dz_r, *dens_r, *Tsurf_r;  // radiative grid (nullptr: not wanted)
+};
+size_t rt_adiabat_work_doubles(int nz, int ncol);
+void rt_launch_make_profile(const AdiabatData *a, int ncol, const double *T_surf, const double *P_i_surf,
+                            const AdiabatOut &o, double *work, cudaStream_t st);

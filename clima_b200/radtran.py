@@ -31,7 +31,8 @@ EXPORTS = ["clima_rt_create", "clima_rt_destroy", "clima_rt_set_params",
            "clima_rt_get_launch_count", "clima_rt_get_stage_ms", "clima_rt_get_stream", "clima_rt_get_rorr_stats", "clima_rt_get_rorr_cut_stats", "clima_rt_measure_fp64_peak",
            "clima_rt_version_get",
            "clima_rt_comm_unique_id", "clima_rt_comm_init", "clima_rt_comm_destroy", "clima_rt_allgather_device",
-           "clima_rt_radiate_batch_sharded"]
+           "clima_rt_radiate_batch_sharded",
+           "clima_rt_adiabat_set", "clima_rt_make_profile_batch", "clima_rt_adiabat_toa_fluxes_batch"]
 COMM_ID_BYTES = 128
 
 

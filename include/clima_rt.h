@@ -257,6 +257,81 @@ void clima_rt_radiate_batch_sharded(void *handle, const int32_t *ncol, const int
 void clima_rt_jacobian_batch(void *handle, const int32_t *ncol, const int32_t *nz,
                              const double *T_surface, const double *T, double *f_total, char *err);
 
+/* ---- N4: `AdiabatClimate%make_profile` for a batch of (T_surf, P_i_surf) pairs, built on
+   the device, and the batched `AdiabatClimate%TOA_fluxes` on top of it.
+
+   clima_rt_adiabat is what make_profile reads from the AdiabatClimate object
+   (src/adiabat/clima_adiabat.f90:13-135): the gases of species.yaml in the order of the radiative
+   tables (mass, heat-capacity polynomial, optional LinearLatentHeat saturation data:
+   src/clima_types.f90 `Gas`, src/clima_saturationdata.f90:16-28), RH, P_top, T_trop, the planet,
+   rtol / atol and the number of model layers.  Not carried: ocean solubility functions (host
+   callbacks; N_ocean is zero without them), particles, reference_pressure > 0, CustomDrySpecies. */
+#define CLIMA_RT_ADIABAT_MAX_GASES 16
+#define CLIMA_RT_ADIABAT_MAX_TEMPS 4
+typedef struct clima_rt_adiabat {
+  int32_t ng;                    /* gases, = the ng of the radiative tables */
+  int32_t nz;                    /* model layers (AdiabatClimate%nz) */
+  int32_t double_radiative_grid; /* default 1: nz_r = 2 nz + 2 (clima_adiabat.f90:729-762) */
+  const double *mass;            /* (ng) g/mol */
+  const int32_t *thermo_model;   /* (ng) 1 = Shomate, 2 = NASA-9 (clima_eqns.f90:82-103) */
+  const int32_t *thermo_ntemps;  /* (ng) temperature ranges, <= CLIMA_RT_ADIABAT_MAX_TEMPS */
+  const double *thermo_temps;    /* (MAX_TEMPS + 1, ng) range bounds [K] */
+  const double *thermo_data;     /* (9, MAX_TEMPS, ng) polynomial coefficients (7 used by Shomate) */
+  const int32_t *has_sat;        /* (ng) 1 when the gas has saturation data */
+  const double *sat;             /* (11, ng) mu, T-ref, P-ref, T-triple, T-critical, a_v, b_v, a_s, b_s, a_c, b_c */
+  const double *RH;              /* (ng) relative humidity, default 1 */
+  double planet_mass, planet_radius; /* g, cm */
+  double P_top;                  /* dynes/cm^2, default 1 */
+  double T_trop;                 /* K, default 180 */
+  double rtol, atol;             /* defaults 1e-9, 1e-12 (clima_adiabat.f90:133-135) */
+} clima_rt_adiabat;
+
+/* What make_profile leaves in the object, per column (HOST pointers; any may be NULL): */
+typedef struct clima_rt_profile_out {
+  double *P;         /* (nz,ncol) dynes/cm^2, layer centres */
+  double *T;         /* (nz,ncol) K */
+  double *z;         /* (nz,ncol) cm */
+  double *dz;        /* (nz,ncol) cm */
+  double *f_i;       /* (nz,ng,ncol) mixing ratios */
+  double *f_i_surf;  /* (ng,ncol) */
+  double *N_surface; /* (ng,ncol) mol/cm^2 condensed at the surface */
+  double *P_surf;    /* (ncol) dynes/cm^2 */
+  double *P_trop;    /* (ncol) dynes/cm^2, negative when no tropopause was found */
+  int32_t *status;   /* (ncol) CLIMA_RT_PROFILE_* */
+  int32_t *nfcn;     /* (ncol) right-hand-side evaluations of the adiabat integration */
+} clima_rt_profile_out;
+/* per-column status: the `err` strings of make_profile / compute_altitude */
+#define CLIMA_RT_PROFILE_OK 0
+#define CLIMA_RT_PROFILE_TSURF_BELOW_TTROP 1   /* clima_adiabat_general.f90:124-127 */
+#define CLIMA_RT_PROFILE_NEGATIVE_PRESSURE 2   /* :128-131 */
+#define CLIMA_RT_PROFILE_PTOP_ABOVE_SURFACE 3  /* :249-252 */
+#define CLIMA_RT_PROFILE_DOP853_FAILED 4       /* :306-310 */
+#define CLIMA_RT_PROFILE_BRENT_FAILED 5        /* :468-471 */
+#define CLIMA_RT_PROFILE_HEAT_CAPACITY 6       /* :618-621 */
+#define CLIMA_RT_PROFILE_NEGATIVE_ALTITUDE 7   /* :266-270 */
+#define CLIMA_RT_PROFILE_ALTITUDE_FAILED 8     /* clima_adiabat_altitude.f90:215-220 */
+#define CLIMA_RT_PROFILE_PRESSURE_GRID 9       /* clima_adiabat_altitude.f90:52-55 */
+#define CLIMA_RT_PROFILE_NEGATIVE_TTROP 10     /* clima_adiabat_general.f90:136-139 */
+
+/* Give the handle the adiabat description (copied to the device; call again after changing RH, T_trop, ...:
+   the setters of clima/fortran/AdiabatClimate.f90). */
+void clima_rt_adiabat_set(void *handle, const clima_rt_adiabat *adiabat, char *err);
+
+/* `AdiabatClimate%make_profile` (src/adiabat/clima_adiabat.f90:401-472) for ncol columns:
+   T_surf(ncol) [K], P_i_surf(ng,ncol) [dynes/cm^2], HOST pointers.  A column that fails gets its status
+   code; `err` names the first such column with the reference's message, the others are still computed. */
+void clima_rt_make_profile_batch(void *handle, const int32_t *ncol, const double *T_surf,
+                                 const double *P_i_surf, const clima_rt_profile_out *profile, char *err);
+
+/* `AdiabatClimate%TOA_fluxes` (src/adiabat/clima_adiabat.f90:776-799) for ncol columns in ONE call:
+   make_profile on the device, copy_atm_to_radiative_grid written straight into the arrays the RT kernels
+   read, then the radiate path.  `profile` may be NULL.  `out` as for clima_rt_radiate_batch with
+   nz_r = 2 nz + 2 (nz when double_radiative_grid = 0) levels.  Any failed column fails the call (err set,
+   `out` untouched), as the reference's loop would stop there.  Needs tables without particles. */
+void clima_rt_adiabat_toa_fluxes_batch(void *handle, const int32_t *ncol, const double *T_surf,
+                                       const double *P_i_surf, const clima_rt_profile_out *profile,
+                                       const clima_rt_out *out, char *err);
+
 /* Copy the retained opacity of column `*icol` (0-based) of the last chunk to the host:
    tau(nz,ngauss,nw), w0(nz,ngauss,nw), g(nz,nw), tau_band(nz,nw), all TOP-first exactly like
    `type OpticalPropertiesResult` (clima_radtran_types.f90:242-247).  Test/debug hook. */

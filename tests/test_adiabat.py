@@ -1,0 +1,317 @@
+"""Row N4: batched `AdiabatClimate%make_profile` / `TOA_fluxes` (clima_b200/csrc/adiabat_profile.cu behind
+clima_rt_make_profile_batch / clima_rt_adiabat_toa_fluxes_batch) against the numpy restatement of the reference
+(oracle/adiabat_np.py, parity unpinned: see its header).  Inputs are the cases of the reference's own
+tests/test_adiabat.f90 (which holds no numbers) on the reference's species data (tests/golden/adiabat_species.json).
+Tolerances: see PROFILE_TOL / TIGHT_TOL below (the integration error of the reference's default settings bounds
+what any two builds can agree on); 1e-9 on ISR / OLR like the rest of the path, on converged profiles."""
+import json
+import math
+import os
+import sys
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(os.path.dirname(HERE), "oracle"))
+import adiabat_np as A  # noqa: E402
+
+EARTH_MASS, EARTH_RADIUS = 5.972e27, 6.371e8  # templates/AdiabatClimate/Earth/settings.yaml
+BAR = 1.0e6
+# tests/test_adiabat.f90:31, :99: [H2O, CO2, N2, H2, CH4, CO, O2] in bars
+P_I_OCEAN = np.array([270.0, 400e-6, 1.0, 1e-10, 1e-10, 1e-10, 1e-10]) * BAR
+P_I_CO2 = np.array([270.0, 10.0, 1.0, 1e-10, 1e-10, 1e-10, 1e-10]) * BAR
+
+
+def species():
+    with open(os.path.join(HERE, "golden", "adiabat_species.json")) as f:
+        return json.load(f)
+
+
+def one_gas(cp=29.0, mass=28.0):
+    """A single non-condensing gas with a constant heat capacity (Shomate, only the A coefficient)."""
+    return dict(names=["X"], mass=[mass], sat=[None],
+                thermo=[dict(model="Shomate", temps=[0.0, 6000.0], data=[[cp, 0, 0, 0, 0, 0, 0]])])
+
+
+# ------------------------------------------------------------------------------------------------------------
+# the oracle against closed forms and an independent integrator (CPU)
+# ------------------------------------------------------------------------------------------------------------
+def test_zeroin_finds_roots_to_the_tolerance():
+    r, fr, info = A.zeroin(lambda x: x ** 3 - 2.0 * x - 5.0, 2.0, 3.0, 1e-12)
+    assert info == 0 and abs(r - 2.0945514815423265) < 1e-11
+    r, _, info = A.zeroin(lambda x: math.cos(x) - x, 1.0, 0.0, 1e-10)  # descending bracket, as find_root uses it
+    assert info == 0 and abs(r - 0.7390851332151607) < 1e-9
+    assert A.zeroin(lambda x: x * x + 1.0, -1.0, 1.0, 1e-8)[2] == -1
+
+
+def test_dop853_against_scipy_and_a_closed_form():
+    from scipy.integrate import solve_ivp
+    f = lambda x, y: np.array([y[1], -y[0]])  # noqa: E731
+    d = A.Dop853(f, 2)
+    x, y, idid = d.integrate(0.0, np.array([0.0, 1.0]), 10.0, 1e-11, 1e-13)
+    assert idid == 1 and x == 10.0
+    assert abs(y[0] - math.sin(10.0)) < 1e-9 and abs(y[1] - math.cos(10.0)) < 1e-9
+    assert abs(d.contd8(0, 9.9) - math.sin(9.9)) < 1e-8          # dense output inside the last step
+    s = solve_ivp(f, (0.0, 10.0), [0.0, 1.0], method="DOP853", rtol=1e-11, atol=1e-13)
+    assert np.max(np.abs(s.y[:, -1] - y)) < 1e-9
+    # backward integration (pressure decreases along the adiabat) and a solout that stops it
+    stop = dict(n=0)
+
+    def solout(nr, xo, xn, yn):
+        stop["n"] = nr
+        return -1 if xn < 5.0 else 1
+    d2 = A.Dop853(lambda x, y: np.array([y[0] / x]), 1, solout)   # y = x
+    x, y, idid = d2.integrate(10.0, np.array([10.0]), 1.0, 1e-10, 1e-12)
+    assert idid == 2 and x < 5.0 and abs(y[0] - x) < 1e-8 and stop["n"] > 1
+
+
+def test_dry_adiabat_of_a_constant_cp_gas():
+    """T = T_s (P / P_s)^(R / cp) below the tropopause, T_trop above it; P_trop from the same law."""
+    cp, nz, Ts, Ps, Tt = 29.0, 40, 300.0, 1.0e6, 200.0
+    e = A.make_profile(Ts, [Ps], one_gas(cp), nz, EARTH_MASS, EARTH_RADIUS, 1.0, Tt, [1.0], 1e-11, 1e-13)
+    kappa = (A.RGAS / 1e7) / cp
+    want = np.maximum(Ts * (e["P"] / Ps) ** kappa, Tt)
+    assert np.max(np.abs(e["T"][:-1] / want[:-1] - 1.0)) < 1e-9
+    assert abs(e["P_trop"] / (Ps * (Tt / Ts) ** (1.0 / kappa)) - 1.0) < 1e-8
+    assert np.all(np.diff(e["z"][:-1]) > 0.0) and np.all(e["f_i"] == 1.0)
+    assert e["P"][0] == Ps and e["P"][-1] == 1.0 and np.allclose(np.diff(np.log10(e["P"])), -6.0 / (2 * nz))
+
+
+def test_condensing_gases_follow_their_saturation_curve():
+    sp = species()
+    c = A.adiabat_column(280.0, P_I_CO2, sp, 30, EARTH_MASS, EARTH_RADIUS, T_trop=150.0)
+    e = c["edges"]
+    assert list(e["sp_type"][:3]) == [1, 1, 0]          # H2O from the surface, CO2 aloft (tests/test_adiabat.f90:95)
+    assert c["N_surface"][0] > 0.0 and c["N_surface"][1] == 0.0
+    below = c["P"] > c["P_trop"]
+    for i in np.where(below)[0]:
+        assert abs(c["f_i"][i, 0] * c["P"][i] / A.sat_pressure(sp["sat"][0], c["T"][i]) - 1.0) < 1e-12
+    assert np.allclose(c["f_i"].sum(axis=1), 1.0, rtol=0, atol=1e-12)
+    # CO2 is dry at the surface (its mixing ratio relative to N2 is the surface one) and saturated higher up
+    assert abs(c["f_i"][0, 1] / c["f_i"][0, 2] - 10.0) < 1e-9
+    top = np.where(below)[0][-1]
+    assert abs(c["f_i"][top, 1] * c["P"][top] / A.sat_pressure(sp["sat"][1], c["T"][top]) - 1.0) < 1e-12
+    assert 150.0 <= c["T"].min() and c["T"][-1] == 150.0 and c["P_trop"] > 0.0
+    assert np.all(c["dz"] > 0.0) and np.all(np.diff(c["z"]) > 0.0)
+
+
+def test_compute_altitude_isothermal_closed_form():
+    """Constant T and mubar: 1/(R+z) = 1/R + (Rgas T)/(G M mubar) ln(P/P0) with the G of `gravity`."""
+    nz, T0, mu = 20, 250.0, 28.0
+    P = np.logspace(5.9, 0.2, nz)
+    z, dz = A.compute_altitude(1.0e6, T0, [1.0], P, np.full(nz, T0), np.ones((nz, 1)), [mu], 1.0, EARTH_MASS,
+                               EARTH_RADIUS, 1e-11, 1e-13)
+    GM = A.G_GRAV * 1.0e3 * EARTH_MASS   # cm^3/s^2
+    want = 1.0 / (1.0 / EARTH_RADIUS + (A.RGAS * T0) / (GM * mu) * np.log(P / 1.0e6)) - EARTH_RADIUS
+    assert np.max(np.abs(z / want - 1.0)) < 1e-9
+    assert np.all(dz > 0.0) and abs(dz.sum() / (2.0 * z[-1] - z[-2] + 0.5 * (z[-1] - z[-2])) - 1.0) < 0.2
+
+
+def test_make_profile_input_errors():
+    sp = species()
+    with pytest.raises(A.AdiabatError, match="less than input"):
+        A.make_profile(150.0, P_I_OCEAN, sp, 10, EARTH_MASS, EARTH_RADIUS, 1.0, 180.0, np.ones(7))
+    with pytest.raises(A.AdiabatError, match="must be positive"):
+        A.make_profile(300.0, -P_I_OCEAN, sp, 10, EARTH_MASS, EARTH_RADIUS, 1.0, 180.0, np.ones(7))
+    with pytest.raises(A.AdiabatError, match="bigger than the surface"):
+        A.make_profile(300.0, P_I_OCEAN * 1e-12, sp, 10, EARTH_MASS, EARTH_RADIUS, 1.0, 180.0, np.ones(7))
+    with pytest.raises(A.AdiabatError, match="wrong shape"):
+        A.make_profile(300.0, P_I_OCEAN[:3], sp, 10, EARTH_MASS, EARTH_RADIUS, 1.0, 180.0, np.ones(7))
+
+
+def test_species_file_reader_on_the_reference_template():
+    from clima_b200.adiabat import species_from_yaml
+    path = "/root/reference/templates/AdiabatClimate/species.yaml"
+    if not os.path.exists(path):
+        pytest.skip("the reference tree is not on this machine")
+    sp = species_from_yaml(path)
+    assert sp == species()
+    assert sp["names"][:3] == ["H2O", "CO2", "N2"] and abs(sp["mass"][0] - 18.01534) < 1e-12
+    assert sp["sat"][2] is None and sp["sat"][0]["T_critical"] == 647.0 and sp["sat"][0]["P_ref"] == 1.0142e6
+    sub = species_from_yaml(path, ["N2", "H2O"])
+    assert sub["names"] == ["N2", "H2O"] and sub["sat"][0] is None
+
+
+# ------------------------------------------------------------------------------------------------------------
+# the device path against the oracle
+# ------------------------------------------------------------------------------------------------------------
+def sweep(n, seed=0):
+    """Columns around the reference's test cases: warm oceans, the CO2-condensing case, dry thin atmospheres."""
+    rng = np.random.default_rng(seed)
+    T = rng.uniform(240.0, 360.0, n)
+    P = np.empty((7, n), order="F")
+    for c in range(n):
+        base = (P_I_OCEAN, P_I_CO2, np.array([1e-4, 0.05, 0.8, 1e-3, 1e-6, 1e-7, 0.2]) * BAR)[c % 3]
+        P[:, c] = base * rng.uniform(0.5, 2.0, 7)
+    return T, P
+
+
+def gpu_model(nz=24, **kw):
+    from cases import small_case
+    from clima_b200.adiabat import AdiabatClimate
+    from clima_b200.radtran import Radtran
+    tb, pr, _ = small_case(G=16, nw=10, nz=4, ncol=1, nzen=2)
+    ac = AdiabatClimate(Radtran(tb, pr), species(), nz, EARTH_MASS, EARTH_RADIUS, **kw)
+    return tb, pr, ac
+
+
+def oracle_column(ac, T, Pi):
+    return A.adiabat_column(T, Pi, ac.sp, ac.nz, ac.planet_mass, ac.planet_radius, ac.P_top, ac.T_trop, ac.RH,
+                            ac.rtol, ac.atol)
+
+
+# Default tolerances of the reference (rtol 1e-9, atol 1e-12 on T [K] and z [cm]): the oracle at these settings is
+# itself 4e-8 (T), 4e-7 (z), 4e-6 (dz) away from the converged solution (rtol 1e-13), because z starts at 0 with
+# an absolute tolerance of 1e-12 cm, where the error estimate is rounding noise and accept/reject decisions differ
+# between any two builds.  Device and oracle must agree within that accuracy at the default settings and to 1e-9
+# once the tolerance is tightened (test_make_profile_tight_tolerance_and_knobs) -- on T and the mixing ratios.  The
+# altitudes keep a floor of about 1e-8 at any rtol: compute_altitude integrates over T and mubar interpolated
+# LINEARLY in log10 P, the step that straddles a kink of that interpolant picks up an error its estimator does
+# not see (4e-3 cm of 4e5 was measured at rtol 1e-12), and which step straddles it is again build-dependent.
+PROFILE_TOL = dict(T=2e-7, z=2e-6, dz=2e-5, f=1e-6)
+TIGHT_TOL = dict(T=1e-9, z=5e-8, dz=5e-8, f=1e-9)
+
+
+def same_profile(p, c, o, tol=PROFILE_TOL):
+    assert np.max(np.abs(p["P"][:, c] / o["P"] - 1.0)) < 1e-14
+    for k in ("T", "z", "dz"):
+        assert np.max(np.abs(p[k][:, c] / o[k] - 1.0)) < tol[k], k
+    assert np.max(np.abs(p["f_i"][:, :, c] - o["f_i"])) < tol["f"]
+    assert np.max(np.abs(p["densities"][:, :, c] - o["densities"]) / o["densities"].max()) < tol["f"]
+    assert abs(p["P_surf"][c] / o["P_surf"] - 1.0) < 1e-13
+    assert (p["P_trop"][c] < 0) == (o["P_trop"] < 0)
+    if o["P_trop"] > 0:
+        assert abs(p["P_trop"][c] / o["P_trop"] - 1.0) < 10 * tol["T"]
+    assert np.allclose(p["N_surface"][:, c], o["N_surface"], rtol=1e-12, atol=0)
+    assert np.allclose(p["N_atmos"][:, c], o["N_atmos"], rtol=tol["dz"], atol=0)
+
+
+@pytest.mark.gpu
+def test_make_profile_batch_matches_the_oracle():
+    _, _, ac = gpu_model(nz=24)
+    ac.T_trop = 150.0
+    T, P = sweep(12)
+    T[1], P[:, 1] = 280.0, P_I_CO2        # tests/test_adiabat.f90:95-104 exactly
+    p = ac.make_profile_batch(T, P)
+    assert not p["status"].any() and np.all(p["nfcn"] > 50)
+    for c in range(T.shape[0]):
+        same_profile(p, c, oracle_column(ac, T[c], P[:, c]))
+    assert (p["P_trop"] > 0).any()
+
+
+@pytest.mark.gpu
+def test_make_profile_tight_tolerance_and_knobs():
+    """rtol 1e-12: device and oracle agree to 1e-9 however their steps fall; RH, T_trop, P_top reach the device."""
+    _, _, ac = gpu_model(nz=16)
+    ac.rtol, ac.T_trop, ac.P_top = 1e-12, 200.0, 10.0
+    ac.RH = np.array([0.6, 1.0, 1.0, 1.0, 1.0, 1.0, 1.0])
+    T, P = sweep(6, seed=3)
+    p = ac.make_profile_batch(T, P)
+    for c in range(6):
+        o = oracle_column(ac, T[c], P[:, c])
+        same_profile(p, c, o, tol=TIGHT_TOL)
+        assert o["P"][-1] > 10.0 and p["T"][:, c].min() >= 200.0
+    q = ac.make_profile_batch(T, P)
+    ac.RH = np.ones(7)
+    r = ac.make_profile_batch(T, P)
+    assert np.array_equal(p["T"], q["T"]) and not np.array_equal(p["T"], r["T"])
+
+
+@pytest.mark.gpu
+def test_make_profile_column_does_not_depend_on_the_batch():
+    _, _, ac = gpu_model(nz=20)
+    T, P = sweep(70, seed=5)
+    p = ac.make_profile_batch(T, P)
+    for c in (0, 33, 69):
+        ac.make_profile(T[c], P[:, c])
+        assert np.array_equal(ac.T, p["T"][:, c]) and np.array_equal(ac.dz, p["dz"][:, c])
+        assert np.array_equal(ac.f_i, p["f_i"][:, :, c]) and ac.P_trop == p["P_trop"][c]
+        assert ac.lapse_rate.shape == (20,) and ac.convecting_with_below.dtype == bool
+
+
+@pytest.mark.gpu
+def test_make_profile_failures_are_reported_per_column():
+    from clima_b200.radtran import ClimaException
+    _, _, ac = gpu_model(nz=12)
+    T, P = sweep(5, seed=2)
+    T[1] = 100.0                       # below T_trop
+    P[2, 2] = -1.0                     # negative pressure
+    P[:, 3] = 1e-9                     # surface pressure below P_top
+    p = ac.make_profile_batch(T, P, check=False)
+    assert list(p["status"]) == [0, 1, 2, 3, 0]
+    same_profile(p, 4, oracle_column(ac, T[4], P[:, 4]))
+    with pytest.raises(ClimaException, match='column 1: make_profile: Input "T_surf" is less than input "T_trop"'):
+        ac.make_profile_batch(T, P)
+    with pytest.raises(ClimaException, match="column 1"):
+        ac.TOA_fluxes_batch(T, P)
+    with pytest.raises(ClimaException, match="inconsistent dimensions"):
+        ac.TOA_fluxes_batch(T[:2], P)
+    # a heat capacity outside its temperature ranges (clima_adiabat_general.f90:618-621)
+    sp = species()
+    sp["thermo"][2]["temps"] = [0.0, 250.0]
+    from clima_b200.adiabat import AdiabatClimate
+    bad = AdiabatClimate(ac.rad, sp, 12, EARTH_MASS, EARTH_RADIUS)
+    with pytest.raises(ClimaException, match="Failed to compute heat capacity"):
+        bad.make_profile_batch(T[:1], P[:, :1])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("doubled", [True, False])
+def test_adiabat_toa_fluxes_batch_matches_the_per_column_reference_loop(doubled):
+    """AdiabatClimate%TOA_fluxes per column (make_profile, copy_atm_to_radiative_grid, rad%TOA_fluxes) restated
+    with the oracles, against the one device call."""
+    from clima_b200.adiabat import copy_atm_to_radiative_grid
+    from oracle_lib import OracleRadtran
+    tb, pr, ac = gpu_model(nz=14, double_radiative_grid=doubled)
+    ac.T_trop = 160.0
+    ac.rtol = 1e-12                       # converged profiles on both sides, so that 1e-9 on the fluxes is meaningful
+    T, P = sweep(9, seed=7)
+    r = ac.TOA_fluxes_batch(T, P, full=True)
+    o = OracleRadtran(tb, pr)
+    nzr = 2 * 14 + 2 if doubled else 14
+    assert r["f_total"].shape == (nzr + 1, 9)
+    pg = r["profile"]
+    for c in range(9):
+        col = oracle_column(ac, T[c], P[:, c])
+        same_profile(pg, c, col, tol=TIGHT_TOL)
+        # (a) the RT on the column the device built: the 1e-9 bar of the path
+        # (b) the whole chain restated on the CPU: bounded by the altitude floor above
+        dev = dict(T=pg["T"][:, c], P=pg["P"][:, c], densities=pg["densities"][:, :, c], dz=pg["dz"][:, c])
+        for src, tol in ((dev, 1e-9), (col, 1e-7)):
+            if doubled:
+                g = copy_atm_to_radiative_grid(src["T"], src["P"] / 1.0e6, src["densities"], src["dz"])
+            else:
+                g = dict(T=src["T"], P=src["P"] / 1.0e6, densities=src["densities"], dz=src["dz"])
+            cols = dict(nz=nzr, ng=7, np=0, ncol=1, T_surface=np.array([T[c]]))
+            for k in ("T", "P", "dz"):
+                cols[k] = np.asfortranarray(g[k][:, None])
+            cols["densities"] = np.asfortranarray(g["densities"][:, :, None])
+            ro = o.radiate(cols, 0, spectral=False)
+            assert abs(r["ISR"][c] / ro["ISR"][0] - 1.0) < tol and abs(r["OLR"][c] / ro["OLR"][0] - 1.0) < tol
+            assert np.max(np.abs(r["f_total"][:, c] - ro["f_total"][:, 0])) < tol * np.max(np.abs(ro["f_total"]))
+    isr, olr = ac.TOA_fluxes(T[3], P[:, 3])
+    assert isr == r["ISR"][3] or abs(isr / r["ISR"][3] - 1.0) < 1e-12
+    assert abs(olr / r["OLR"][3] - 1.0) < 1e-12
+
+
+@pytest.mark.gpu
+def test_adiabat_needs_matching_tables():
+    from cases import small_case
+    from clima_b200.adiabat import AdiabatClimate
+    from clima_b200.radtran import ClimaException, Radtran
+    tb, pr, _ = small_case(G=16, nw=10, nz=4, ncol=1, nzen=2)
+    sp = species()
+    few = {k: v[:3] for k, v in sp.items()}
+    with pytest.raises(ClimaException, match="differs from the radiative tables"):
+        AdiabatClimate(Radtran(tb, pr), few, 10, EARTH_MASS, EARTH_RADIUS).make_profile_batch([300.0], P_I_OCEAN[:3, None])
+    g = Radtran(tb, pr)
+    with pytest.raises(ClimaException, match="clima_rt_adiabat_set has not been called"):
+        import ctypes as C
+        from clima_b200._abi import ERR_LEN
+        from clima_b200.radtran import _check, _i
+        err = C.create_string_buffer(ERR_LEN + 1)
+        z = np.zeros(8)
+        g._lib.clima_rt_make_profile_batch(g._h, _i(1), z.ctypes.data_as(C.POINTER(C.c_double)),
+                                           z.ctypes.data_as(C.POINTER(C.c_double)), None, err)
+        _check(err)

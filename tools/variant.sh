@@ -6,7 +6,7 @@ cd "$(dirname "$0")/.."
 name=$1; src=$2; shift 2
 mkdir -p experiments/variants
 objs=""
-for s in capi prep optics_rorr optics_rorr_fast optics_rorr_exact optics_rorr_cut jacobian_delta twostream fp64_peak; do
+for s in capi prep optics_rorr optics_rorr_fast optics_rorr_exact optics_rorr_cut jacobian_delta adiabat_profile twostream fp64_peak; do
   if [ "$s.cu" == "$src" ]; then
     nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -std=c++17 -Xcompiler -fPIC --expt-relaxed-constexpr --extended-lambda "$@" -c clima_b200/csrc/$s.cu -o experiments/variants/$name.$s.o
     objs="$objs experiments/variants/$name.$s.o"
