@@ -302,3 +302,9 @@ class AdiabatClimate:
     def TOA_fluxes(self, T_surf: float, P_i_surf):
         isr, olr = self.TOA_fluxes_batch([T_surf], np.asarray(P_i_surf, dtype=np.float64)[:, None])
         return float(isr[0]), float(olr[0])
+
+    def kernel_ms(self) -> float:
+        """Device time of the last make_profile kernel (CUDA events on the handle's stream)."""
+        st = (C.c_double * 2)()
+        self.rad._lib.clima_rt_get_adiabat_stats(self.rad._h, st)
+        return float(st[0])

@@ -13,11 +13,35 @@
 // 1.2.0) and the root finder (futils 0.1.14 brent_class) are dependencies that are not in the reference tree:
 // both are restated from the published algorithms (Hairer, Norsett, Wanner II.5 / dop853.f; Brent 1973).
 // The step sequence of a column depends only on that column, so a thread's result does not depend on the batch.
+// Lanes of a warp sit at different places of the integrator most of the time, so the code is kept SMALL (the
+// right-hand side, the stages, the event search and the dense output are __noinline__, loops over stages are not
+// unrolled): fully inlined it was 429 KB of SASS and the warps stalled on instruction fetch.
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 
 #include "dop853_tables.h"
 #include "rt_kernels.h"
+
+#ifndef ADIABAT_NOINLINE
+#define ADIABAT_NOINLINE __noinline__
+#endif
+
+#ifndef NI_MATH
+#define NI_MATH ADIABAT_NOINLINE
+#endif
+#ifndef NI_RHS
+#define NI_RHS ADIABAT_NOINLINE
+#endif
+#ifndef NI_STAGE
+#define NI_STAGE ADIABAT_NOINLINE
+#endif
+#ifndef NI_SOL
+#define NI_SOL ADIABAT_NOINLINE
+#endif
+#ifndef NI_MISC
+#define NI_MISC ADIABAT_NOINLINE
+#endif
 
 namespace adiabat {
 
@@ -32,21 +56,27 @@ __device__ __forceinline__ double gravity(double radius, double mass, double z) 
   return G_GRAV * (mass / 1.0e3) / (r * r) * 1.0e2;
 }
 
-__device__ __forceinline__ double integral_fcn(double A, double B, double T) { return -A / T + B * log(T); }
+// one copy of each libm routine in the code (see the note on code size above)
+__device__ NI_MATH double nlog(double x) { return log(x); }
+__device__ NI_MATH double nexp(double x) { return exp(x); }
+__device__ NI_MATH double nlog10(double x) { return log10(x); }
+__device__ NI_MATH double npow(double x, double y) { return pow(x, y); }
+
+__device__ __forceinline__ double integral_fcn(double A, double B, double T) { return -A / T + B * nlog(T); }
 
 // SaturationData%sat_pressure (clima_saturationdata.f90:97-155); s = mu, T_ref, P_ref, T_triple, T_critical,
-// a_v, b_v, a_s, b_s, a_c, b_c
-__device__ double sat_pressure(const double *s, double T) {
+// a_v, b_v, a_s, b_s, a_c, b_c, then the temperature-independent terms of the three branches (filled by
+// clima_rt_adiabat_set in the order the reference adds them): [11] I_v(T_ref), [12] I_v(T_critical) - I_v(T_ref),
+// [13] I_c(T_critical), [14] I_v(T_triple) - I_v(T_ref), [15] I_s(T_triple), with I_x(T) = -a_x / T + b_x log T.
+__device__ NI_MISC double sat_pressure(const double *s, double T) {
   double tmp;
   if (T >= s[4])
-    tmp = (integral_fcn(s[5], s[6], s[4]) - integral_fcn(s[5], s[6], s[1])) +
-          (integral_fcn(s[9], s[10], T) - integral_fcn(s[9], s[10], s[4]));
+    tmp = s[12] + (integral_fcn(s[9], s[10], T) - s[13]);
   else if (T > s[3])
-    tmp = integral_fcn(s[5], s[6], T) - integral_fcn(s[5], s[6], s[1]);
+    tmp = integral_fcn(s[5], s[6], T) - s[11];
   else
-    tmp = (integral_fcn(s[5], s[6], s[3]) - integral_fcn(s[5], s[6], s[1])) +
-          (integral_fcn(s[7], s[8], T) - integral_fcn(s[7], s[8], s[3]));
-  return s[2] * exp((s[0] / RGAS) * tmp);
+    tmp = s[14] + (integral_fcn(s[7], s[8], T) - s[15]);
+  return s[2] * nexp((s[0] / RGAS) * tmp);
 }
 
 __device__ __forceinline__ double latent_heat(const double *s, double T) {  // :56-91 [erg/g]
@@ -55,19 +85,31 @@ __device__ __forceinline__ double latent_heat(const double *s, double T) {  // :
   return s[7] + s[8] * T;
 }
 
-// heat_capacity_eval (clima_eqns.f90:105-133) [J/(mol K)]; false when T is outside every range
-__device__ bool heat_capacity(const AdiabatData &a, int i, double T, double &cp) {
+// heat_capacity_eval (clima_eqns.f90:105-133) [J/(mol K)]; false when T is outside every range.  The powers of
+// T (Shomate: of T / 1000) are the same for every gas and are computed once per right-hand side.
+struct TPowers {
+  double T, TT, TT2, TT3, rTT2, T2, T3, T4, rT, rT2;
+  __device__ explicit TPowers(double T_) : T(T_) {
+    TT = T / 1000.0;
+    TT2 = TT * TT;
+    TT3 = TT * TT * TT;
+    rTT2 = 1.0 / TT2;
+    T2 = T * T;
+    T3 = T2 * T;
+    T4 = T2 * T2;
+    rT = 1.0 / T;
+    rT2 = 1.0 / T2;
+  }
+};
+__device__ bool heat_capacity(const AdiabatData &a, int i, const TPowers &t, double &cp) {
   for (int k = 0; k < a.ntemps[i]; k++) {
-    if (T >= a.temps[i][k] && T < a.temps[i][k + 1]) {
+    if (t.T >= a.temps[i][k] && t.T < a.temps[i][k + 1]) {
       const double *c = a.coef[i][k];
-      if (a.model[i] == 1) {
-        const double TT = T / 1000.0;
-        cp = c[0] + c[1] * TT + c[2] * (TT * TT) + c[3] * (TT * TT * TT) + c[4] / (TT * TT);
-      } else {
-        const double T2 = T * T;
+      if (a.model[i] == 1)
+        cp = c[0] + c[1] * t.TT + c[2] * t.TT2 + c[3] * t.TT3 + c[4] * t.rTT2;
+      else
         cp = 8.31446261815324 *
-             (c[0] / T2 + c[1] / T + c[2] + c[3] * T + c[4] * T2 + c[5] * (T2 * T) + c[6] * (T2 * T2));
-      }
+             (c[0] * t.rT2 + c[1] * t.rT + c[2] + c[3] * t.T + c[4] * t.T2 + c[5] * t.T3 + c[6] * t.T4);
       return true;
     }
   }
@@ -91,7 +133,8 @@ __device__ void update_f_i_dry(Col &d, double P, const double *f_layer) {  // :5
   for (int i = 0; i < d.ng; i++) d.f_i_dry[i] = (f_layer[i] * P) / P_dry;
 }
 
-__device__ void mixing_ratios(const Col &d, double P, double T, double *f, double &f_dry) {  // :548-574
+// returns f_dry (by value: with the function out of line, an unused reference result was given the address of f[0])
+__device__ NI_MISC double mixing_ratios(const Col &d, double P, double T, double *f) {  // :548-574
   const AdiabatData &a = *d.a;
   double f_moist = 0.0;
   for (int i = 0; i < d.ng; i++)
@@ -99,45 +142,48 @@ __device__ void mixing_ratios(const Col &d, double P, double T, double *f, doubl
       f[i] = fmin(a.RH[i] * sat_pressure(a.sat[i], T) / P, 1.0);
       f_moist += f[i];
     }
-  f_dry = fmax(1.0 - f_moist, 1.0e-40);
+  const double f_dry = fmax(1.0 - f_moist, 1.0e-40);
   for (int i = 0; i < d.ng; i++)
     if (!d.cond[i]) f[i] = f_dry * d.f_i_dry[i];
+  return f_dry;
 }
 
 // one component of root_fcn (:483-513): 0 = tropopause, i + 1 = gas i reaches saturation
-__device__ double root_component(const Col &d, double P, double T, int ind) {
+__device__ NI_MISC double root_component(const Col &d, double P, double T, int ind) {
   if (ind == 0) return T - d.a->T_trop;
   const int i = ind - 1;
   if (d.cond[i]) return 1.0;
   if (!d.a->has_sat[i]) return DBL_MAX;
-  double f[MAXG], f_dry;
-  mixing_ratios(d, P, T, f, f_dry);
+  double f[MAXG];
+  mixing_ratios(d, P, T, f);
   return d.a->RH[i] * sat_pressure(d.a->sat[i], T) - f[i] * P;
 }
 
 // right_hand_side (:576-656): Eq. 1 of Graham et al. (2021) without condensate retention, and hydrostatics
 struct ProfileRhs {
   Col *d;
-  __device__ void operator()(double P, const double *u, double *du) const {
+  __device__ NI_RHS void operator()(double P, const double *u, double *du) const {
     Col &c = *d;
     const AdiabatData &a = *c.a;
     const double T = u[0], z = u[1];
     const double Rgas_si = RGAS / 1.0e7;
-    double f[MAXG], f_dry;
-    mixing_ratios(c, P, T, f, f_dry);
+    double f[MAXG];
+    const double f_dry = mixing_ratios(c, P, T, f);
     double mubar = 0.0;
     for (int i = 0; i < c.ng; i++) mubar += f[i] * a.mass[i];
     double cp_dry = DBL_MIN, first = 0.0, second = 0.0;
+    const TPowers tp(T);
+    const double rRT = 1.0 / (Rgas_si * T);
     for (int i = 0; i < c.ng; i++) {
       double cp;
-      if (!heat_capacity(a, i, T, cp)) {
+      if (!heat_capacity(a, i, tp, cp)) {
         c.err = 6;
         du[0] = du[1] = 0.0;
         return;
       }
       if (c.cond[i]) {
         const double L = latent_heat(a.sat[i], T) * a.mass[i] * 1.0e-7;  // J/mol
-        const double beta = L / (Rgas_si * T);
+        const double beta = L * rRT;
         first += f[i] * (cp - Rgas_si * beta + Rgas_si * (beta * beta));
         second += beta * f[i];
       } else {
@@ -163,7 +209,7 @@ struct Dop {
   double F[7][N];
   double yold[N];
   double xold, hout;
-  __device__ double contd8(int i, double xq) const {
+  __device__ NI_SOL double contd8(int i, double xq) const {
     const double s = (xq - xold) / hout, s1 = 1.0 - s;
     const double conpar = F[3][i] + s * (F[4][i] + s1 * (F[5][i] + s * F[6][i]));
     return yold[i] + s * (F[0][i] + s1 * (F[1][i] + s * (F[2][i] + s1 * conpar)));
@@ -171,7 +217,7 @@ struct Dop {
 };
 
 template <int N, class Rhs>
-__device__ void dop_stage(Dop<N> &d, int s, double x, double h, const double *y, const Rhs &rhs) {
+__device__ NI_STAGE void dop_stage(Dop<N> &d, int s, double x, double h, const double *y, const Rhs &rhs) {
   double y1[N];
 #pragma unroll
   for (int i = 0; i < N; i++) {
@@ -214,7 +260,7 @@ __device__ int dop_integrate(Dop<N> &d, double &x, double *y, double xend, doubl
     for (int i = 0; i < N; i++) der2 += ((f1[i] - d.K[0][i]) / sk[i]) * ((f1[i] - d.K[0][i]) / sk[i]);
     der2 = sqrt(der2) / h;
     const double der12 = fmax(fabs(der2), sqrt(dnf));
-    const double h1 = der12 <= 1.0e-15 ? fmax(1.0e-6, fabs(h) * 1.0e-3) : pow(0.01 / der12, 1.0 / 8.0);
+    const double h1 = der12 <= 1.0e-15 ? fmax(1.0e-6, fabs(h) * 1.0e-3) : npow(0.01 / der12, 1.0 / 8.0);
     h = copysign(fmin(fmin(100.0 * fabs(h), h1), hmax), posneg);
   }
   d.xold = x;
@@ -228,6 +274,7 @@ __device__ int dop_integrate(Dop<N> &d, double &x, double *y, double xend, doubl
       last = true;
     }
     nstep++;
+#pragma unroll 1
     for (int s = 1; s < 12; s++) dop_stage<N>(d, s, x, h, y, rhs);
     const double xph = x + h;
     double ynew[N], err = 0.0, err2 = 0.0;
@@ -247,13 +294,14 @@ __device__ int dop_integrate(Dop<N> &d, double &x, double *y, double xend, doubl
     double deno = err + 0.01 * err2;
     if (deno <= 0.0) deno = 1.0;
     err = fabs(h) * err * sqrt(1.0 / (N * deno));
-    const double fac11 = pow(err, expo1);
+    const double fac11 = npow(err, expo1);
     const double fac = fmax(facc2, fmin(facc1, fac11 / safe));
     double hnew = h / fac;
     if (err <= 1.0) {
       facold = fmax(err, 1.0e-4);
       naccpt++;
       rhs(xph, ynew, d.K[12]);
+#pragma unroll 1
       for (int s = 13; s < 16; s++) dop_stage<N>(d, s, x, h, y, rhs);
 #pragma unroll
       for (int i = 0; i < N; i++) {
@@ -290,7 +338,7 @@ __device__ int dop_integrate(Dop<N> &d, double &x, double *y, double xend, doubl
 
 // Brent's zeroin (futils brent_class%find_zero); info -1 when f(ax) and f(bx) have one sign
 template <class Fn>
-__device__ double zeroin(const Fn &f, double ax, double bx, double tol, int &info) {
+__device__ NI_MISC double zeroin(const Fn &f, double ax, double bx, double tol, int &info) {
   const double eps = 2.220446049250313e-16;
   double a = ax, b = bx, fa = f(a), fb = f(b);
   info = 0;
@@ -357,10 +405,10 @@ struct ProfileSolout {
   double *T_m, *f_m;  // T_m[i], f_m[i + nz * g]
   int nz;
 
-  __device__ double P_edge(int k) const {
+  __device__ NI_SOL double P_edge(int k) const {
     if (k == 0) return P_surf;
     if (k == ne - 1) return col->a->P_top;
-    return pow(10.0, l0 + range * k / (ne - 1));
+    return npow(10.0, l0 + range * k / (ne - 1));
   }
   __device__ void sample(int k, double T, double z, const double *f) {
     if (z < 0.0 && k < ne - 1) z_negative = true;
@@ -370,7 +418,7 @@ struct ProfileSolout {
       for (int g = 0; g < col->ng; g++) f_m[i + (size_t)nz * g] = f[g];
     }
   }
-  __device__ int operator()(const Dop<2> &dop, int nr, double P_old, double P_cur, const double *y) {
+  __device__ NI_SOL int operator()(const Dop<2> &dop, int nr, double P_old, double P_cur, const double *y) {
     Col &d = *col;
     if (d.err) return -10;
     int irtrn = 1;
@@ -413,8 +461,8 @@ struct ProfileSolout {
       if (Pj <= P_old && Pj >= PP) {
         while (Pj >= PP) {
           const double T = dop.contd8(0, Pj), z = dop.contd8(1, Pj);
-          double f[MAXG], f_dry;
-          mixing_ratios(d, Pj, T, f, f_dry);
+          double f[MAXG];
+          mixing_ratios(d, Pj, T, f);
           sample(j, T, z, f);
           j++;
           if (j >= ne) break;
@@ -429,7 +477,7 @@ struct ProfileSolout {
 __device__ double altitude_vs_P(double P, double T, double mubar, double P0, double z0, double planet_mass,
                                 double planet_radius) {  // :659-669
   const double G_grav_cgs = 6.67e-8;
-  return 1.0 / ((N_AVO * K_BOLTZ * T) / (G_grav_cgs * planet_mass * mubar) * log(P / P0) + 1.0 / (planet_radius + z0)) -
+  return 1.0 / ((N_AVO * K_BOLTZ * T) / (G_grav_cgs * planet_mass * mubar) * nlog(P / P0) + 1.0 / (planet_radius + z0)) -
          planet_radius;
 }
 
@@ -456,9 +504,9 @@ struct AltitudeRhs {
     T = p * Tg[nz - a] + q * Tg[nz - a - 1];
     m = p * mg[nz - a] + q * mg[nz - a - 1];
   }
-  __device__ void operator()(double P, const double *u, double *du) const {
+  __device__ NI_RHS void operator()(double P, const double *u, double *du) const {
     double T, m;
-    interp(log10(P), T, m);
+    interp(nlog10(P), T, m);
     du[0] = -(RGAS * T) / (gravity(planet_radius, planet_mass, u[0]) * P * m);
   }
 };
@@ -469,7 +517,7 @@ struct AltitudeSolout {
   double *y_eval;
   int m, j;
   double xtol;
-  __device__ int operator()(const Dop<1> &dop, int nr, double xold, double x, const double *y) {
+  __device__ NI_SOL int operator()(const Dop<1> &dop, int nr, double xold, double x, const double *y) {
     const double x_lo = fmin(xold, x) - xtol, x_hi = fmax(xold, x) + xtol;
     while (j < m) {
       const double xe = x_eval[j];
@@ -485,9 +533,13 @@ struct AltitudeSolout {
 // grid (nzr = 2 nz + 2 when doubled, else nz) likewise.  `work` holds, per column, lp / Tg / mg (nz + 1 each),
 // the second edge grid and its altitudes (2 nz + 1 each).
 __global__ void __launch_bounds__(ADIABAT_THREADS)
-make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, const double *__restrict__ T_surf_in,
+make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, int lanes, const double *__restrict__ T_surf_in,
                     const double *__restrict__ P_i_surf, AdiabatOut o, double *__restrict__ work) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  // `lanes` columns per warp (a power of two): a warp runs as long as its slowest column and a small batch
+  // fills only a few of the 592 warp schedulers, so small batches spread their columns over more warps
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if ((t & 31) >= lanes) return;
+  const int c = (t >> 5) * lanes + (t & 31);
   if (c >= ncol) return;
   const AdiabatData &a = *ap;
   const int ng = a.ng, nz = a.nz, ne = 2 * nz + 1;
@@ -544,8 +596,8 @@ make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, const double *
   so.col = &col;
   so.ne = ne;
   so.j = 1;
-  so.l0 = log10(P_surf);
-  so.range = log10(a.P_top) - so.l0;
+  so.l0 = nlog10(P_surf);
+  so.range = nlog10(a.P_top) - so.l0;
   so.P_surf = P_surf;
   so.Pj = so.P_edge(1);
   so.reason = 0;
@@ -575,15 +627,13 @@ make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, const double *
       Pn = so.P_root;
       u[0] = so.u_root[0];
       u[1] = so.u_root[1];
-      double f_dry;
-      mixing_ratios(col, Pn, u[0], f_cur, f_dry);
+      mixing_ratios(col, Pn, u[0], f_cur);
       col.cond[so.ind_sat] = 1;
       update_f_i_dry(col, Pn, f_cur);
     }
   }
   if (!status && so.reason == 1) {  // isothermal stratosphere above the tropopause (:331-351)
-    double f_dry;
-    mixing_ratios(col, so.P_root, so.u_root[0], f_cur, f_dry);
+    mixing_ratios(col, so.P_root, so.u_root[0], f_cur);
     o.P_trop[c] = so.P_root;
     double mubar = 0.0;
     for (int i = 0; i < ng; i++) mubar += f_cur[i] * a.mass[i];
@@ -602,7 +652,7 @@ make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, const double *
   // compute_altitude (clima_adiabat_altitude.f90:41-193)
   double *lp = work + (size_t)c * (3 * (nz + 1) + 2 * ne), *Tg = lp + nz + 1, *mg = Tg + nz + 1, *P_e2 = mg + nz + 1,
          *z_e = P_e2 + ne;
-  lp[0] = log10(P_surf);
+  lp[0] = nlog10(P_surf);
   Tg[0] = T_surf;
   {
     double m0 = 0.0;
@@ -611,7 +661,7 @@ make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, const double *
   }
   P_e2[0] = P_surf;
   for (int i = 0; i < nz; i++) {
-    lp[i + 1] = log10(P_m[i]);
+    lp[i + 1] = nlog10(P_m[i]);
     Tg[i + 1] = T_m[i];
     double m = 0.0;
     for (int g = 0; g < ng; g++) m += f_m[i + (size_t)nz * g] * a.mass[g];
@@ -674,8 +724,21 @@ make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, const double *
 
 size_t rt_adiabat_work_doubles(int nz, int ncol) { return (size_t)ncol * (3 * (nz + 1) + 2 * (2 * nz + 1)); }
 
-void rt_launch_make_profile(const AdiabatData *a, int ncol, const double *T_surf, const double *P_i_surf,
-                            const AdiabatOut &o, double *work, cudaStream_t st) {
-  const int blocks = (ncol + ADIABAT_THREADS - 1) / ADIABAT_THREADS;
-  adiabat::make_profile_kernel<<<blocks, ADIABAT_THREADS, 0, st>>>(a, ncol, T_surf, P_i_surf, o, work);
+void rt_launch_make_profile(const AdiabatData *a, int ncol, int num_sms, const double *T_surf,
+                            const double *P_i_surf, const AdiabatOut &o, double *work, cudaStream_t st) {
+  // Columns of a warp diverge (each has its own step sequence; ncu: 2.3 of 4 lanes active on average) and the
+  // kernel is bound by the latency of one column's chain of steps (12 ms for a 2000-evaluation column), so a
+  // small batch spreads over more warps: a warp takes 1, 2, 4 ... 32 columns as the batch grows beyond
+  // ADIABAT_WARPS_PER_SM warps per SM.  Measured at 4096 columns: 27.1 ms with 4 (4 columns per warp),
+  // 28.7 with 1 (16 per warp), 40.8 with 16 (1 per warp: 4096 warps run in two waves of 16 per SM).
+  static const int wps = [] {
+    const char *e = getenv("CLIMA_RT_ADIABAT_WARPS_PER_SM");
+    return e && atoi(e) > 0 ? atoi(e) : ADIABAT_WARPS_PER_SM;
+  }();
+  int lanes = 32;
+  while (lanes > 1 && (size_t)ncol < (size_t)wps * num_sms * lanes) lanes >>= 1;
+  const int warps = (ncol + lanes - 1) / lanes;
+  const int wpb = ADIABAT_THREADS / 32;
+  adiabat::make_profile_kernel<<<(warps + wpb - 1) / wpb, ADIABAT_THREADS, 0, st>>>(a, ncol, lanes, T_surf, P_i_surf, o,
+                                                                                  work);
 }

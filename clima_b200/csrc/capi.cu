@@ -118,6 +118,8 @@ struct Handle {
   double *d_aTs = nullptr, *d_aPi = nullptr, *d_awork = nullptr;
   AdiabatOut aout{};
   int64_t adiabat_calls = 0;
+  cudaEvent_t adiabat_ev[2] = {nullptr, nullptr};
+  double adiabat_ms = 0.0;
 
   // introspection
   int64_t launches = 0;
@@ -947,8 +949,14 @@ static int make_profile_impl(Handle &h, int ncol, const double *T_surf, const do
   NvtxRange r("make_profile");
   CK(cudaMemcpyAsync(h.d_aTs, T_surf, n * 8, cudaMemcpyHostToDevice, h.st));
   CK(cudaMemcpyAsync(h.d_aPi, P_i_surf, n * ng * 8, cudaMemcpyHostToDevice, h.st));
-  rt_launch_make_profile(h.d_adiabat, ncol, h.d_aTs, h.d_aPi, h.aout, h.d_awork, h.st);
+  if (!h.adiabat_ev[0]) {
+    CK(cudaEventCreate(&h.adiabat_ev[0]));
+    CK(cudaEventCreate(&h.adiabat_ev[1]));
+  }
+  CK(cudaEventRecord(h.adiabat_ev[0], h.st));
+  rt_launch_make_profile(h.d_adiabat, ncol, h.num_sms, h.d_aTs, h.d_aPi, h.aout, h.d_awork, h.st);
   CK(cudaGetLastError());
+  CK(cudaEventRecord(h.adiabat_ev[1], h.st));
   h.launches++;
   h.adiabat_calls++;
   std::vector<int> status(n);
@@ -965,6 +973,11 @@ static int make_profile_impl(Handle &h, int ncol, const double *T_surf, const do
     back(prof->nfcn, o.nfcn, n * sizeof(int));
   }
   CK(cudaStreamSynchronize(h.st));
+  {
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, h.adiabat_ev[0], h.adiabat_ev[1]));
+    h.adiabat_ms = ms;
+  }
   int first = -1;
   for (size_t c = 0; c < n; c++) {
     if (prof && prof->status) prof->status[c] = status[c];
@@ -1051,6 +1064,7 @@ void clima_rt_destroy(void *handle) {
   if (h->d_jflag) cudaFree(h->d_jflag);
   for (void *q : h->adiabat_allocs) cudaFree(q);
   if (h->d_adiabat) cudaFree(h->d_adiabat);
+  for (auto &e : h->adiabat_ev) if (e) cudaEventDestroy(e);
   free_chunk(*h);
   for (void *p : h->table_allocs) cudaFree(p);
   for (auto &p : h->d_custom) if (p) cudaFree(p);
@@ -1291,6 +1305,15 @@ void clima_rt_adiabat_set(void *handle, const clima_rt_adiabat *ad, char *err) {
         for (int q = 0; q < 9; q++) a.coef[i][k][q] = ad->thermo_data[((size_t)i * ADIABAT_MAXT + k) * 9 + q];
       a.has_sat[i] = ad->has_sat[i] != 0;
       for (int q = 0; q < 11; q++) a.sat[i][q] = ad->sat[(size_t)i * 11 + q];
+      if (a.has_sat[i]) {  // temperature-independent terms of sat_pressure (clima_saturationdata.f90:106-137)
+        const double *q = a.sat[i];
+        auto I = [](double A, double B, double T) { return -A / T + B * std::log(T); };
+        a.sat[i][11] = I(q[5], q[6], q[1]);
+        a.sat[i][12] = I(q[5], q[6], q[4]) - I(q[5], q[6], q[1]);
+        a.sat[i][13] = I(q[9], q[10], q[4]);
+        a.sat[i][14] = I(q[5], q[6], q[3]) - I(q[5], q[6], q[1]);
+        a.sat[i][15] = I(q[7], q[8], q[3]);
+      }
       a.RH[i] = ad->RH[i];
     }
     a.planet_mass = ad->planet_mass;
@@ -1411,6 +1434,13 @@ void clima_rt_get_rorr_cut_stats(void *handle, int64_t *stats8) {
   for (int i = 0; i < 8; i++) stats8[i] = (int64_t)v[i];
   stats8[5] = h.last_rorr_kernel;
   stats8[7] = h.jac_delta_calls;
+}
+
+void clima_rt_get_adiabat_stats(void *handle, double *stats2) {
+  if (!handle || !stats2) return;
+  Handle &h = *static_cast<Handle *>(handle);
+  stats2[0] = h.adiabat_ms;
+  stats2[1] = (double)h.adiabat_calls;
 }
 
 void clima_rt_get_stream(void *handle, void **stream) {

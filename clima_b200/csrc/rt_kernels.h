@@ -59,7 +59,10 @@ double rt_measure_fp64_tflops(int device, cudaStream_t st);
 #endif
 #define ADIABAT_MAXT 4   // temperature ranges of a heat-capacity polynomial
 #ifndef ADIABAT_THREADS
-#define ADIABAT_THREADS 32  // one column per thread; small blocks spread a batch over the SMs
+#define ADIABAT_THREADS 32  // one warp per block: a batch spreads over the SMs
+#endif
+#ifndef ADIABAT_WARPS_PER_SM
+#define ADIABAT_WARPS_PER_SM 4  // a warp takes more than one column only beyond this many warps per SM
 #endif
 struct AdiabatData {  // device copy of what make_profile reads from the AdiabatClimate object
   int ng, nz, double_radiative_grid;
@@ -69,7 +72,7 @@ struct AdiabatData {  // device copy of what make_profile reads from the Adiabat
   double temps[ADIABAT_MAXG][ADIABAT_MAXT + 1];
   double coef[ADIABAT_MAXG][ADIABAT_MAXT][9];
   int has_sat[ADIABAT_MAXG];
-  double sat[ADIABAT_MAXG][11];  // mu, T_ref, P_ref, T_triple, T_critical, a_v, b_v, a_s, b_s, a_c, b_c
+  double sat[ADIABAT_MAXG][16];  // mu, T_ref, P_ref, T_triple, T_critical, a_v, b_v, a_s, b_s, a_c, b_c + 5 derived
   double RH[ADIABAT_MAXG];
   double planet_mass, planet_radius, P_top, T_trop, rtol, atol;
 };
@@ -82,5 +85,5 @@ struct AdiabatOut {  // device pointers
   double *T_r, *P_r, *dz_r, *dens_r, *Tsurf_r;  // radiative grid (nullptr: not wanted)
 };
 size_t rt_adiabat_work_doubles(int nz, int ncol);
-void rt_launch_make_profile(const AdiabatData *a, int ncol, const double *T_surf, const double *P_i_surf,
-                            const AdiabatOut &o, double *work, cudaStream_t st);
+void rt_launch_make_profile(const AdiabatData *a, int ncol, int num_sms, const double *T_surf,
+                            const double *P_i_surf, const AdiabatOut &o, double *work, cudaStream_t st);

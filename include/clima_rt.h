@@ -332,6 +332,10 @@ void clima_rt_adiabat_toa_fluxes_batch(void *handle, const int32_t *ncol, const 
                                        const double *P_i_surf, const clima_rt_profile_out *profile,
                                        const clima_rt_out *out, char *err);
 
+/* N4 bookkeeping: [0] device time (ms, CUDA events on the handle's stream) of the last make_profile kernel,
+   [1] make_profile launches since the handle was created. */
+void clima_rt_get_adiabat_stats(void *handle, double *stats2);
+
 /* Copy the retained opacity of column `*icol` (0-based) of the last chunk to the host:
    tau(nz,ngauss,nw), w0(nz,ngauss,nw), g(nz,nw), tau_band(nz,nw), all TOP-first exactly like
    `type OpticalPropertiesResult` (clima_radtran_types.f90:242-247).  Test/debug hook. */

@@ -161,16 +161,19 @@ def oracle_column(ac, T, Pi):
                             ac.rtol, ac.atol)
 
 
-# Default tolerances of the reference (rtol 1e-9, atol 1e-12 on T [K] and z [cm]): the oracle at these settings is
-# itself 4e-8 (T), 4e-7 (z), 4e-6 (dz) away from the converged solution (rtol 1e-13), because z starts at 0 with
-# an absolute tolerance of 1e-12 cm, where the error estimate is rounding noise and accept/reject decisions differ
-# between any two builds.  Device and oracle must agree within that accuracy at the default settings and to 1e-9
-# once the tolerance is tightened (test_make_profile_tight_tolerance_and_knobs) -- on T and the mixing ratios.  The
-# altitudes keep a floor of about 1e-8 at any rtol: compute_altitude integrates over T and mubar interpolated
-# LINEARLY in log10 P, the step that straddles a kink of that interpolant picks up an error its estimator does
-# not see (4e-3 cm of 4e5 was measured at rtol 1e-12), and which step straddles it is again build-dependent.
-PROFILE_TOL = dict(T=2e-7, z=2e-6, dz=2e-5, f=1e-6)
-TIGHT_TOL = dict(T=1e-9, z=5e-8, dz=5e-8, f=1e-9)
+# What two builds of this algorithm can agree on.  At the reference's default tolerances (rtol 1e-9, atol 1e-12 on
+# T [K] and z [cm]) the oracle is itself 4e-8 (T), 4e-7 (z), 4e-6 (dz) away from its converged solution (rtol
+# 1e-13) on these columns: z starts at 0 with an absolute tolerance of 1e-12 cm, where the error estimate is
+# rounding noise, so accept/reject decisions -- and from there the whole step sequence -- differ between any two
+# builds (two compilations of the device code differ from each other by as much).  compute_altitude adds a floor
+# that no rtol removes: it integrates over T and mubar interpolated LINEARLY in log10 P, the step that straddles a
+# kink of the interpolant picks up an error its estimator does not see (4e-3 cm of 4e5 at rtol 1e-12; 1.3e-7
+# relative was seen), and which step straddles it is again build-dependent (experiments/adiabat_noise.py: a 1e-13
+# perturbation of T_surf moves the oracle's own altitude error between 1e-9 and 2e-6).  So: at the default settings
+# device and oracle must agree within that band (test_make_profile_batch_matches_the_oracle also measures both
+# against the converged solution), and within 1e-9 on T and the mixing ratios / 5e-7 on the altitudes at rtol 1e-12.
+PROFILE_TOL = dict(T=1e-6, z=1e-5, dz=1e-4, f=1e-6)
+TIGHT_TOL = dict(T=1e-9, z=5e-7, dz=5e-7, f=1e-9)
 
 
 def same_profile(p, c, o, tol=PROFILE_TOL):
@@ -195,8 +198,21 @@ def test_make_profile_batch_matches_the_oracle():
     T[1], P[:, 1] = 280.0, P_I_CO2        # tests/test_adiabat.f90:95-104 exactly
     p = ac.make_profile_batch(T, P)
     assert not p["status"].any() and np.all(p["nfcn"] > 50)
+    e_dev = dict(T=0.0, z=0.0, dz=0.0)
+    e_ora = dict(T=0.0, z=0.0, dz=0.0)
     for c in range(T.shape[0]):
-        same_profile(p, c, oracle_column(ac, T[c], P[:, c]))
+        o = oracle_column(ac, T[c], P[:, c])
+        same_profile(p, c, o)
+        conv = A.adiabat_column(T[c], P[:, c], ac.sp, ac.nz, ac.planet_mass, ac.planet_radius, ac.P_top, ac.T_trop,
+                                ac.RH, 1e-13, ac.atol)
+        for k in e_dev:
+            e_dev[k] = max(e_dev[k], float(np.max(np.abs(p[k][:, c] / conv[k] - 1.0))))
+            e_ora[k] = max(e_ora[k], float(np.max(np.abs(o[k] / conv[k] - 1.0))))
+    # the device is as close to the converged solution as the reference's algorithm is: on T directly, on the
+    # altitudes within the band that a 1e-13 perturbation of the input moves the oracle itself through
+    # (experiments/adiabat_noise.py: 1e-9 ... 2e-6 on z)
+    assert e_dev["T"] < 5.0 * e_ora["T"] + 1e-9, (e_dev, e_ora)
+    assert e_dev["z"] < 1e-5 and e_dev["dz"] < 1e-4, (e_dev, e_ora)
     assert (p["P_trop"] > 0).any()
 
 
