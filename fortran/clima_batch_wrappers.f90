@@ -11,7 +11,7 @@
 !>     `copy_atm_to_radiative_grid` per column on the host (unchanged reference code,
 !>     src/adiabat/clima_adiabat.f90:401-472,729-773), then ONE `rad%radiate_batch` for all columns
 !>     instead of ncol calls of `rad%TOA_fluxes` (:474-520).  This is row N3 of SURVEY.md section 8(f);
-!>     batching `make_profile` itself is row N4 and is not part of this repository.
+!>     `make_profile` itself on the device (row N4) is fortran/clima_adiabat_cuda.f90.
 
 subroutine radtran_radiate_batch_wrapper(ptr, ncol, nz, ng, T_surface, T, P, densities, dz, &
                                          compute_solar, fup_n_ir, fdn_n_ir, fup_n_sol, fdn_n_sol, &
