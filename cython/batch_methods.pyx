@@ -73,3 +73,21 @@
     if len(err.strip()) > 0:
       raise ClimaException(err.decode("utf-8").strip())
     return ISR, OLR
+
+  def TOA_fluxes_batch_device(self, ndarray[double, ndim=1] T_surf, ndarray[double, ndim=2] P_i_surf):
+    """Same result, with `make_profile` itself on the GPU (row N4: fortran/clima_adiabat_cuda.f90,
+    `AdiabatClimate%TOA_fluxes_batch_device`).  Not for objects with ocean solubility functions, particles,
+    `reference_pressure > 0` or a temperature-dependent albedo: those raise and `TOA_fluxes_batch` applies.
+    pxd addition: the wrapper below with the argument list of adiabatclimate_toa_fluxes_batch_wrapper."""
+    cdef int ng = P_i_surf.shape[0], ncol = P_i_surf.shape[1]
+    if T_surf.shape[0] != ncol:
+      raise ClimaException('"T_surf" and "P_i_surf" have inconsistent dimensions')
+    if not P_i_surf.flags.f_contiguous:
+      raise ClimaException('"P_i_surf" must be Fortran ordered')
+    cdef char err[ERR_LEN+1]
+    cdef ndarray[double, ndim=1] ISR = np.empty(ncol, np.double), OLR = np.empty(ncol, np.double)
+    wa_pxd.adiabatclimate_toa_fluxes_batch_device_wrapper(self._ptr, &ncol, <double *>T_surf.data, &ng,
+        <double *>P_i_surf.data, <double *>ISR.data, <double *>OLR.data, err)
+    if len(err.strip()) > 0:
+      raise ClimaException(err.decode("utf-8").strip())
+    return ISR, OLR

@@ -108,3 +108,25 @@ subroutine adiabatclimate_toa_fluxes_batch_wrapper(ptr, ncol, T_surf, ng, P_i_su
     call copy_string_ftoc(err_f, err)
   endif
 end subroutine
+
+!> Row N4: same signature, `make_profile` on the device (fortran/clima_adiabat_cuda.f90).
+subroutine adiabatclimate_toa_fluxes_batch_device_wrapper(ptr, ncol, T_surf, ng, P_i_surf, ISR, OLR, err) bind(c)
+  use clima, only: AdiabatClimate
+  type(c_ptr), value, intent(in) :: ptr
+  integer(c_int), intent(in) :: ncol
+  real(c_double), intent(in) :: T_surf(ncol)
+  integer(c_int), intent(in) :: ng
+  real(c_double), intent(in) :: P_i_surf(ng,ncol)
+  real(c_double), intent(out) :: ISR(ncol), OLR(ncol)
+  character(c_char), intent(out) :: err(err_len+1)
+
+  character(:), allocatable :: err_f
+  type(AdiabatClimate), pointer :: c
+
+  call c_f_pointer(ptr, c)
+  call c%TOA_fluxes_batch_device(T_surf, P_i_surf, ISR, OLR, err_f)
+  err(1) = c_null_char
+  if (allocated(err_f)) then
+    call copy_string_ftoc(err_f, err)
+  endif
+end subroutine
