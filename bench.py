@@ -368,6 +368,15 @@ def run_ours(args):
                                "value": tot / (mss * 1e-3), "unit": UNIT, "ms_per_step": mss, "steps": xs, "warmup": xw,
                                "stage_ms_per_step": {"optics_rorr": sts[0], "kernels_total": sts[4], "prep": sts[5]}}
 
+    # ---- N = 1: row N4, the batched AdiabatClimate%TOA_fluxes (make_profile on the device + the RT) on an
+    # OLR-versus-T_surf sweep at fixed composition (the loop of examples/EarlyMars.ipynb cell 7), host inputs and
+    # host results, after the headline legs so that it cannot disturb them
+    if world == 1 and not args.no_extra and cfg == "cfg2":
+        try:
+            extra["adiabat_toa_fluxes"] = adiabat_leg(rt, ncol)
+        except Exception as e:  # reported, never fatal for the headline line
+            extra["adiabat_toa_fluxes"] = {"error": str(e)[:300]}
+
     if rank == 0:
         d = roofline.dims_of(tb, pr, cols)
         ops = roofline.stage_ops(d)
@@ -455,6 +464,32 @@ def _emit(line: dict):
 _REAL_STDOUT = 1
 
 
+def adiabat_leg(rt, ncol, nz=50, reps=2):
+    """Row N4 on the bench handle: `ncol` surface temperatures 250..400 K over a 270-bar ocean inventory, 400 ppm
+    CO2, 1 bar N2 (tests/test_adiabat.f90:31), the gases of the reference's species.yaml."""
+    import torch
+    from clima_b200.adiabat import AdiabatClimate
+    with open(os.path.join(ROOT, "tests", "golden", "adiabat_species.json")) as f:
+        sp = json.load(f)
+    ac = AdiabatClimate(rt, sp, nz, 5.972e27, 6.371e8)
+    T = np.linspace(250.0, 400.0, ncol)
+    P = np.asfortranarray(np.repeat((np.array([270.0, 400e-6, 1.0, 1e-10, 1e-10, 1e-10, 1e-10]) * 1e6)[:, None], ncol, 1))
+    ac.TOA_fluxes_batch(T[:64], P[:, :64])
+    best, kern, stage = 1e30, 0.0, None
+    for _ in range(reps):
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        isr, olr = ac.TOA_fluxes_batch(T, P)
+        dt = time.perf_counter() - t0
+        if dt < best:
+            best, kern, stage = dt, ac.kernel_ms(), rt.stage_ms()
+    return {"workload": f"{ncol} columns, T_surf 250..400 K at fixed surface inventory, nz={nz} (nz_r={2 * nz + 2}), 7 gases",
+            "value": ncol / best, "unit": UNIT, "ms_per_call": best * 1e3, "make_profile_kernel_ms": kern,
+            "rt_kernels_ms": stage[4], "rorr_kernel": rt.rorr_cut_stats()["last_kernel"],
+            "olr_min_max": [float(olr.min()), float(olr.max())],
+            "timing": "host clock around the public call, host inputs and host results (an e2e number)"}
+
+
 def main():
     global _REAL_STDOUT
     sys.stdout.flush()
@@ -467,7 +502,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--ncol", type=int, default=0, help="columns per GPU (default: the config's)")
     ap.add_argument("--config", default="cfg2", choices=sorted(CONFIGS), help="workload (BASELINE.json configs)")
-    ap.add_argument("--no-extra", action="store_true", help="N>1: skip the cfg5 / strong-scaling legs")
+    ap.add_argument("--no-extra", action="store_true", help="skip the extra legs (N>1: cfg5 / strong scaling; N=1: the batched AdiabatClimate TOA_fluxes)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     if args.impl == "reference":
