@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libclima_rt.so")
 SOURCES = ["capi.cu", "prep.cu", "optics_rorr.cu", "optics_rorr_fast.cu", "optics_rorr_exact.cu", "optics_rorr_cut.cu", "jacobian_delta.cu", "adiabat_profile.cu", "twostream.cu", "fp64_peak.cu"]
-HEADERS = ["rt_device.cuh", "rt_kernels.h", "rorr_impl.cuh", "dop853_tables.h", os.path.join("..", "..", "include", "clima_rt.h")]
+HEADERS = ["rt_device.cuh", "rt_kernels.h", "rorr_impl.cuh", "dop853_tables.h", "adiabat_group.cuh", os.path.join("..", "..", "include", "clima_rt.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
          "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr", "--extended-lambda"]

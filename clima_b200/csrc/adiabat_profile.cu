@@ -19,6 +19,7 @@
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
+#include <cstring>
 
 #include "dop853_tables.h"
 #include "rt_kernels.h"
@@ -529,6 +530,32 @@ struct AltitudeSolout {
   }
 };
 
+// compute_altitude (clima_adiabat_altitude.f90:52-55, 180-243) on the prepared tables: the strictly-decreasing
+// check of the second edge grid, the integration of z from the surface with samples at every edge, the
+// extrapolated top edge.  Returns the column status (0, 8 or 9).
+__device__ NI_SOL int altitude_profile(const AdiabatData &a, int nz, double P_surf, const double *lp, const double *Tg,
+                                       const double *mg, const double *P_e2, double *z_e) {
+  double dmin = DBL_MAX;
+  for (int k = 0; k < 2 * nz; k++) dmin = fmin(dmin, P_e2[k] - P_e2[k + 1]);
+  const double ulp = nextafter(P_surf, DBL_MAX) - P_surf;  // spacing(P_e(1))
+  if (dmin <= 10.0 * ulp) return 9;
+  Dop<1> dop;
+  AltitudeRhs rhs{lp, Tg, mg, nz, a.planet_mass, a.planet_radius};
+  AltitudeSolout as;
+  as.x_eval = P_e2 + 1;
+  as.y_eval = z_e + 1;
+  as.m = 2 * nz - 1;
+  as.j = 0;
+  const double big = fmax(1.0, P_surf);
+  as.xtol = fmax(1.0e-12 * big, 10.0 * (nextafter(big, DBL_MAX) - big));
+  z_e[0] = 0.0;
+  double x = P_surf, y[1] = {0.0};
+  const int idid = dop_integrate<1>(dop, x, y, P_e2[2 * nz - 1], a.rtol, a.atol, rhs, as);
+  if (idid < 0 || as.j < as.m) return 8;
+  z_e[2 * nz] = z_e[2 * nz - 1] + (z_e[2 * nz - 1] - z_e[2 * nz - 2]);
+  return 0;
+}
+
 // One column per thread.  Model-grid outputs are (nz, ncol) / (nz, ng, ncol) with nz fastest; the radiative
 // grid (nzr = 2 nz + 2 when doubled, else nz) likewise.  `work` holds, per column, lp / Tg / mg (nz + 1 each),
 // the second edge grid and its altitudes (2 nz + 1 each).
@@ -670,28 +697,7 @@ make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, int lanes, con
     if (i < nz - 1) P_e2[2 * i + 2] = sqrt(P_m[i] * P_m[i + 1]);
   }
   P_e2[2 * nz] = a.P_top;
-  {
-    double dmin = DBL_MAX;
-    for (int k = 0; k < 2 * nz; k++) dmin = fmin(dmin, P_e2[k] - P_e2[k + 1]);
-    const double ulp = nextafter(P_surf, DBL_MAX) - P_surf;  // spacing(P_e(1))
-    if (dmin <= 10.0 * ulp) status = 9;
-  }
-  if (!status) {
-    Dop<1> dop;
-    AltitudeRhs rhs{lp, Tg, mg, nz, a.planet_mass, a.planet_radius};
-    AltitudeSolout as;
-    as.x_eval = P_e2 + 1;
-    as.y_eval = z_e + 1;
-    as.m = 2 * nz - 1;
-    as.j = 0;
-    const double big = fmax(1.0, P_surf);
-    as.xtol = fmax(1.0e-12 * big, 10.0 * (nextafter(big, DBL_MAX) - big));
-    z_e[0] = 0.0;
-    double x = P_surf, y[1] = {0.0};
-    const int idid = dop_integrate<1>(dop, x, y, P_e2[2 * nz - 1], a.rtol, a.atol, rhs, as);
-    if (idid < 0 || as.j < as.m) status = 8;
-    z_e[2 * nz] = z_e[2 * nz - 1] + (z_e[2 * nz - 1] - z_e[2 * nz - 2]);
-  }
+  status = altitude_profile(a, nz, P_surf, lp, Tg, mg, P_e2, z_e);
   o.status[c] = status;
   if (status) return;
   for (int i = 0; i < nz; i++) {
@@ -720,25 +726,43 @@ make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, int lanes, con
   }
 }
 
+#include "adiabat_group.cuh"
+
 }  // namespace adiabat
 
 size_t rt_adiabat_work_doubles(int nz, int ncol) { return (size_t)ncol * (3 * (nz + 1) + 2 * (2 * nz + 1)); }
 
-void rt_launch_make_profile(const AdiabatData *a, int ncol, int num_sms, const double *T_surf,
+void rt_launch_make_profile(const AdiabatData *a, int ng, int ncol, int num_sms, const double *T_surf,
                             const double *P_i_surf, const AdiabatOut &o, double *work, cudaStream_t st) {
-  // Columns of a warp diverge (each has its own step sequence; ncu: 2.3 of 4 lanes active on average) and the
-  // kernel is bound by the latency of one column's chain of steps (12 ms for a 2000-evaluation column), so a
-  // small batch spreads over more warps: a warp takes 1, 2, 4 ... 32 columns as the batch grows beyond
-  // ADIABAT_WARPS_PER_SM warps per SM.  Measured at 4096 columns: 27.1 ms with 4 (4 columns per warp),
-  // 28.7 with 1 (16 per warp), 40.8 with 16 (1 per warp: 4096 warps run in two waves of 16 per SM).
-  static const int wps = [] {
-    const char *e = getenv("CLIMA_RT_ADIABAT_WARPS_PER_SM");
-    return e && atoi(e) > 0 ? atoi(e) : ADIABAT_WARPS_PER_SM;
-  }();
-  int lanes = 32;
-  while (lanes > 1 && (size_t)ncol < (size_t)wps * num_sms * lanes) lanes >>= 1;
-  const int warps = (ncol + lanes - 1) / lanes;
+  // Both kernels are bound by the latency of one column's chain of steps, and columns of a warp sit at different
+  // places of the integrator (ncu: 2.3 of 4 active), so a small batch spreads over more warps: a warp takes more
+  // columns only as the batch grows beyond ADIABAT_WARPS_PER_SM warps per SM.
+  const char *e = getenv("CLIMA_RT_ADIABAT_WARPS_PER_SM");
+  const int wps = e && atoi(e) > 0 ? atoi(e) : ADIABAT_WARPS_PER_SM;
+  // Which kernel: one lane per gas shortens a column's chain (4096 columns: 17.8 against 27.1 ms; 256: 10.2 against
+  // 15.8) but occupies 8 lanes per column, so beyond about 64 columns per SM the one-thread-per-column kernel
+  // wins on throughput (16384 columns: 31.6 against 42.9 ms; the crossover was measured near 10 000 columns).
+  // CLIMA_RT_ADIABAT=thread|group forces one (read per call: the tests run both in one process).
+  const char *m = getenv("CLIMA_RT_ADIABAT");
+  const bool per_thread = m && (!strcmp(m, "thread") || !strcmp(m, "group")) ? !strcmp(m, "thread")
+                                                                             : ncol > ADIABAT_GROUP_MAX_COLS_PER_SM * num_sms;
   const int wpb = ADIABAT_THREADS / 32;
-  adiabat::make_profile_kernel<<<(warps + wpb - 1) / wpb, ADIABAT_THREADS, 0, st>>>(a, ncol, lanes, T_surf, P_i_surf, o,
-                                                                                  work);
+  if (per_thread) {  // one thread per column
+    int lanes = 32;
+    while (lanes > 1 && (size_t)ncol < (size_t)wps * num_sms * lanes) lanes >>= 1;
+    const int warps = (ncol + lanes - 1) / lanes;
+    adiabat::make_profile_kernel<<<(warps + wpb - 1) / wpb, ADIABAT_THREADS, 0, st>>>(a, ncol, lanes, T_surf, P_i_surf,
+                                                                                    o, work);
+    return;
+  }
+  // one lane per gas: 8 lanes per column up to 8 gases (4 columns per warp at most), 16 beyond
+  const int gs = ng <= 8 ? 8 : 16;
+  int gpw = 32 / gs;
+  while (gpw > 1 && (size_t)ncol < (size_t)wps * num_sms * gpw) gpw >>= 1;
+  const int warps = (ncol + gpw - 1) / gpw;
+  const int blocks = (warps + wpb - 1) / wpb;
+  if (gs == 8)
+    adiabat::make_profile_group_kernel<8><<<blocks, ADIABAT_THREADS, 0, st>>>(a, ncol, gpw, T_surf, P_i_surf, o, work);
+  else
+    adiabat::make_profile_group_kernel<16><<<blocks, ADIABAT_THREADS, 0, st>>>(a, ncol, gpw, T_surf, P_i_surf, o, work);
 }

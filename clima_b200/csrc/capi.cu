@@ -954,7 +954,7 @@ static int make_profile_impl(Handle &h, int ncol, const double *T_surf, const do
     CK(cudaEventCreate(&h.adiabat_ev[1]));
   }
   CK(cudaEventRecord(h.adiabat_ev[0], h.st));
-  rt_launch_make_profile(h.d_adiabat, ncol, h.num_sms, h.d_aTs, h.d_aPi, h.aout, h.d_awork, h.st);
+  rt_launch_make_profile(h.d_adiabat, h.adiabat.ng, ncol, h.num_sms, h.d_aTs, h.d_aPi, h.aout, h.d_awork, h.st);
   CK(cudaGetLastError());
   CK(cudaEventRecord(h.adiabat_ev[1], h.st));
   h.launches++;

@@ -57,6 +57,9 @@ double rt_measure_fp64_tflops(int device, cudaStream_t st);
 #ifndef ADIABAT_MAXG
 #define ADIABAT_MAXG 16  // gases
 #endif
+#ifndef ADIABAT_GROUP_MAX_COLS_PER_SM
+#define ADIABAT_GROUP_MAX_COLS_PER_SM 64  // larger batches take the one-thread-per-column kernel
+#endif
 #define ADIABAT_MAXT 4   // temperature ranges of a heat-capacity polynomial
 #ifndef ADIABAT_THREADS
 #define ADIABAT_THREADS 32  // one warp per block: a batch spreads over the SMs
@@ -85,5 +88,5 @@ struct AdiabatOut {  // device pointers
   double *T_r, *P_r, *dz_r, *dens_r, *Tsurf_r;  // radiative grid (nullptr: not wanted)
 };
 size_t rt_adiabat_work_doubles(int nz, int ncol);
-void rt_launch_make_profile(const AdiabatData *a, int ncol, int num_sms, const double *T_surf,
+void rt_launch_make_profile(const AdiabatData *a, int ng, int ncol, int num_sms, const double *T_surf,
                             const double *P_i_surf, const AdiabatOut &o, double *work, cudaStream_t st);

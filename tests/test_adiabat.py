@@ -247,6 +247,37 @@ def test_make_profile_column_does_not_depend_on_the_batch():
 
 
 @pytest.mark.gpu
+def test_both_make_profile_kernels_agree(monkeypatch):
+    """One lane per gas (default up to 64 columns per SM) and one thread per column (beyond) restate the same
+    algorithm: same status, same tropopause, profiles within the reproducibility band of the default tolerances and
+    1e-9 / 5e-7 at rtol 1e-12; each against the oracle as well."""
+    _, _, ac = gpu_model(nz=20)
+    ac.T_trop = 150.0
+    T, P = sweep(40, seed=9)
+    T[3] = 100.0
+    res = {}
+    for rtol, tol in ((1e-9, PROFILE_TOL), (1e-12, TIGHT_TOL)):
+        ac.rtol = rtol
+        for mode in ("group", "thread"):
+            monkeypatch.setenv("CLIMA_RT_ADIABAT", mode)
+            res[mode] = ac.make_profile_batch(T, P, check=False)
+        a, b = res["group"], res["thread"]
+        assert np.array_equal(a["status"], b["status"]) and a["status"][3] == 1 and a["status"].sum() == 1
+        ok = a["status"] == 0
+        # the surface pressure is a sum over the gases: a butterfly over the lanes against a running sum
+        assert np.max(np.abs(a["P"][:, ok] / b["P"][:, ok] - 1.0)) < 1e-14
+        assert np.array_equal(a["N_surface"][:, ok], b["N_surface"][:, ok])
+        for k in ("T", "z", "dz"):
+            assert np.max(np.abs(a[k][:, ok] / b[k][:, ok] - 1.0)) < tol[k], (k, rtol)
+        assert np.max(np.abs(a["f_i"][:, :, ok] - b["f_i"][:, :, ok])) < tol["f"]
+        assert np.array_equal(a["P_trop"] > 0, b["P_trop"] > 0)
+        for c in (0, 17, 39):
+            o = oracle_column(ac, T[c], P[:, c])
+            same_profile(a, c, o, tol)
+            same_profile(b, c, o, tol)
+
+
+@pytest.mark.gpu
 def test_make_profile_failures_are_reported_per_column():
     from clima_b200.radtran import ClimaException
     _, _, ac = gpu_model(nz=12)
