@@ -308,3 +308,24 @@ class AdiabatClimate:
         st = (C.c_double * 2)()
         self.rad._lib.clima_rt_get_adiabat_stats(self.rad._h, st)
         return float(st[0])
+
+    NOALLOC_MAX_WORK_DOUBLES = 2 * 1024 * 1024  # CLIMA_RT_NOALLOC_MAX_WORK_DOUBLES of include/clima_rt.h
+
+    def make_profile_batch_noalloc(self, ncol: int, T_surf_ptr: int, P_i_surf_ptr: int, out_ptrs: Dict[str, int]):
+        """`clima_rt_make_profile_batch_noalloc`: the same kernel with its work arrays in the library's static
+        device array; every argument is a raw DEVICE address of the caller (`tensor.data_ptr()`): T_surf (ncol),
+        P_i_surf (ng, ncol) and, in `out_ptrs`, P, T, z, dz (nz, ncol), f_i (nz, ng, ncol), f_i_surf, N_surface
+        (ng, ncol), P_surf, P_trop (ncol) as float64 and status, nfcn (ncol) as int32.  The call allocates nothing;
+        per-column failures stay in `status`.  `_sync()` (clima_rt_adiabat_set, which allocates) must have run:
+        any make_profile / TOA_fluxes call, or call it first."""
+        self._sync()
+        o = CProfileOut()
+        for k in PROFILE_FIELDS:
+            setattr(o, k, C.cast(C.c_void_p(out_ptrs.get(k, 0) or None), c_double_p))
+        o.status = C.cast(C.c_void_p(out_ptrs.get("status", 0) or None), c_int32_p)
+        o.nfcn = C.cast(C.c_void_p(out_ptrs.get("nfcn", 0) or None), c_int32_p)
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self.rad._lib.clima_rt_make_profile_batch_noalloc(
+            self.rad._h, _i(ncol), C.cast(C.c_void_p(T_surf_ptr or None), c_double_p),
+            C.cast(C.c_void_p(P_i_surf_ptr or None), c_double_p), C.byref(o), err)
+        _check(err)

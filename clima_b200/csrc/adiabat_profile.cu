@@ -20,6 +20,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 
 #include "dop853_tables.h"
 #include "rt_kernels.h"
@@ -765,4 +766,52 @@ void rt_launch_make_profile(const AdiabatData *a, int ng, int ncol, int num_sms,
     adiabat::make_profile_group_kernel<8><<<blocks, ADIABAT_THREADS, 0, st>>>(a, ncol, gpw, T_surf, P_i_surf, o, work);
   else
     adiabat::make_profile_group_kernel<16><<<blocks, ADIABAT_THREADS, 0, st>>>(a, ncol, gpw, T_surf, P_i_surf, o, work);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// make_profile with its per-column work arrays in a STATIC device array instead of a cudaMalloc'ed buffer
+// (clima_rt_make_profile_batch_noalloc: for callers that may not allocate -- CUDA graph capture, serving loops).
+// The array is held by every GPU that loads the library until the process exits; every call shares it, so calls
+// that overlap on the GPU race.  Nothing in it has to start at zero: a column writes lp / Tg / mg / P_e2 / z_e
+// before it reads them.
+// ---------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_noalloc_work[RT_NOALLOC_MAX_WORK_DOUBLES];
+
+size_t rt_noalloc_max_work_doubles() { return (size_t)RT_NOALLOC_MAX_WORK_DOUBLES; }
+
+// In host code `g_noalloc_work` is a host-side stand-in, not a device address: the address the kernel gets comes
+// from cudaGetSymbolAddress, once per device, with that device current.  Returns nullptr and sets *why on failure.
+static double *noalloc_work_ptr(const char **why) {
+  static double *ptr[64] = {};
+  static std::mutex mu;
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) {
+    *why = "make_profile (no-alloc): cudaGetDevice failed";
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptr[dev]) {
+    double *p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void **)&p, g_noalloc_work);
+    if (e != cudaSuccess || !p) {
+      *why = "make_profile (no-alloc): cudaGetSymbolAddress of the static scratch array failed";
+      return nullptr;
+    }
+    ptr[dev] = p;
+  }
+  return ptr[dev];
+}
+
+// 0 = launched; otherwise *why says what is wrong (nothing was launched).  The current device must be the one the
+// pointers live on.
+int rt_launch_make_profile_noalloc(const AdiabatData *a, int ng, int nz, int ncol, int num_sms, const double *T_surf,
+                                   const double *P_i_surf, const AdiabatOut &o, cudaStream_t st, const char **why) {
+  if (rt_adiabat_work_doubles(nz, ncol) > rt_noalloc_max_work_doubles()) {
+    *why = "make_profile (no-alloc): ncol * (7 nz + 5) exceeds the static scratch array";
+    return 1;
+  }
+  double *work = noalloc_work_ptr(why);
+  if (!work) return 2;
+  rt_launch_make_profile(a, ng, ncol, num_sms, T_surf, P_i_surf, o, work, st);
+  return 0;
 }

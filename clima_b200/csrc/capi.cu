@@ -1351,6 +1351,48 @@ void clima_rt_make_profile_batch(void *handle, const int32_t *ncol, const double
   }
 }
 
+static_assert(CLIMA_RT_NOALLOC_MAX_WORK_DOUBLES == RT_NOALLOC_MAX_WORK_DOUBLES, "include/clima_rt.h and rt_kernels.h disagree");
+
+void clima_rt_make_profile_batch_noalloc(void *handle, const int32_t *ncol, const double *T_surf,
+                                         const double *P_i_surf, const clima_rt_profile_out *profile, char *err) {
+  // No cudaMalloc / cudaFree / cudaEventCreate on this path: inputs and outputs are the caller's device buffers, the
+  // adiabat description was uploaded by clima_rt_adiabat_set, the work arrays are the static device array of
+  // adiabat_profile.cu.
+  set_err(err, "");
+  try {
+    if (!handle) throw CudaError{"clima_rt: NULL handle"};
+    Handle &h = *static_cast<Handle *>(handle);
+    CK(cudaSetDevice(h.device));
+    if (!h.adiabat_set) throw CudaError{"clima_rt_adiabat_set has not been called on this handle"};
+    if (!ncol || !T_surf || !P_i_surf || !profile) throw CudaError{"clima_rt: null argument"};
+    if (*ncol < 1) throw CudaError{"ncol must be >= 1"};
+    const clima_rt_profile_out &p = *profile;
+    if (!p.P || !p.T || !p.z || !p.dz || !p.f_i || !p.f_i_surf || !p.N_surface || !p.P_surf || !p.P_trop ||
+        !p.status || !p.nfcn)
+      throw CudaError{"clima_rt_make_profile_batch_noalloc: every member of `profile` must be a device buffer"};
+    const size_t need = rt_adiabat_work_doubles(h.adiabat.nz, *ncol);
+    if (need > rt_noalloc_max_work_doubles())
+      throw CudaError{"clima_rt_make_profile_batch_noalloc: ncol * (7 nz + 5) = " + std::to_string(need) +
+                      " doubles of scratch exceed the static maximum of " +
+                      std::to_string(rt_noalloc_max_work_doubles()) + " (CLIMA_RT_NOALLOC_MAX_WORK_DOUBLES); use " +
+                      "clima_rt_make_profile_batch or split the batch"};
+    AdiabatOut o{};
+    o.P = p.P; o.T = p.T; o.z = p.z; o.dz = p.dz; o.f_i = p.f_i;
+    o.f_i_surf = p.f_i_surf; o.N_surface = p.N_surface; o.P_surf = p.P_surf; o.P_trop = p.P_trop;
+    o.status = p.status; o.nfcn = p.nfcn;  // the radiative-grid members stay NULL: not written
+    const char *why = "";
+    if (rt_launch_make_profile_noalloc(h.d_adiabat, h.adiabat.ng, h.adiabat.nz, *ncol, h.num_sms, T_surf, P_i_surf, o,
+                                       h.st, &why))
+      throw CudaError{why};
+    CK(cudaGetLastError());
+    h.launches++;
+    h.adiabat_calls++;
+    CK(cudaStreamSynchronize(h.st));
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
 void clima_rt_adiabat_toa_fluxes_batch(void *handle, const int32_t *ncol, const double *T_surf,
                                        const double *P_i_surf, const clima_rt_profile_out *profile,
                                        const clima_rt_out *out, char *err) {

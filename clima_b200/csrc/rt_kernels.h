@@ -90,3 +90,12 @@ struct AdiabatOut {  // device pointers
 size_t rt_adiabat_work_doubles(int nz, int ncol);
 void rt_launch_make_profile(const AdiabatData *a, int ng, int ncol, int num_sms, const double *T_surf,
                             const double *P_i_surf, const AdiabatOut &o, double *work, cudaStream_t st);
+
+// the same launch with the per-column work arrays in a file-scope static __device__ array (no allocation anywhere);
+// RT_NOALLOC_MAX_WORK_DOUBLES doubles = 16 MiB held by every GPU that loads the library
+#ifndef RT_NOALLOC_MAX_WORK_DOUBLES
+#define RT_NOALLOC_MAX_WORK_DOUBLES (2 * 1024 * 1024)
+#endif
+size_t rt_noalloc_max_work_doubles();
+int rt_launch_make_profile_noalloc(const AdiabatData *a, int ng, int nz, int ncol, int num_sms, const double *T_surf,
+                                   const double *P_i_surf, const AdiabatOut &o, cudaStream_t st, const char **why);

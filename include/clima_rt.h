@@ -332,6 +332,27 @@ void clima_rt_adiabat_toa_fluxes_batch(void *handle, const int32_t *ncol, const 
                                        const double *P_i_surf, const clima_rt_profile_out *profile,
                                        const clima_rt_out *out, char *err);
 
+/* clima_rt_make_profile_batch for callers that may not allocate (code under CUDA graph capture, tight serving
+   loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+   Same kernel and same results as clima_rt_make_profile_batch, but
+     * every pointer is a DEVICE pointer of the caller on the handle's device: T_surf(ncol), P_i_surf(ng,ncol)
+       and ALL eleven members of `profile` (none may be NULL; status / nfcn are int32 (ncol));
+     * the kernel's per-column work arrays live in a file-scope static __device__ array of
+       CLIMA_RT_NOALLOC_MAX_WORK_DOUBLES doubles (16 MiB, held by every GPU that loads the library until the
+       process exits) instead of a cudaMalloc'ed buffer; a call needs ncol * (7 nz + 5) of them (nz = 50: at
+       most 5907 columns) and is rejected with a clear error beyond that;
+     * the call itself issues no cudaMalloc / cudaFree / event creation: the handle and clima_rt_adiabat_set
+       (which do allocate) are set-up and come first;
+     * per-column failures are left in `profile->status` (CLIMA_RT_PROFILE_*) for the caller to read; `err` is
+       set only for argument, size and launch errors.
+   The work is enqueued on the handle's stream and the call returns after a stream synchronisation.  Every call
+   (from every handle on that GPU) shares the one array, which keeps the last call's contents -- nothing in it
+   has to start at zero, each column writes its work arrays before reading them -- so calls that OVERLAP on the
+   GPU (two handles, two host threads) race; serialise them. */
+#define CLIMA_RT_NOALLOC_MAX_WORK_DOUBLES (2 * 1024 * 1024)
+void clima_rt_make_profile_batch_noalloc(void *handle, const int32_t *ncol, const double *T_surf,
+                                         const double *P_i_surf, const clima_rt_profile_out *profile, char *err);
+
 /* N4 bookkeeping: [0] device time (ms, CUDA events on the handle's stream) of the last make_profile kernel,
    [1] make_profile launches since the handle was created. */
 void clima_rt_get_adiabat_stats(void *handle, double *stats2);
