@@ -4,7 +4,8 @@ TEST INFRASTRUCTURE ONLY: imported by tests/ (and nothing in clima_b200/).  PARI
 cannot be compiled in this image (Fortran + fypp + CPM-fetched dependencies, DESIGN.md "Oracle") and its
 own test of this path (tests/test_adiabat.f90) holds no numbers, only "runs without error" cases; those
 cases are reused as inputs (tests/test_adiabat.py), and the restatement is checked against closed forms
-(dry adiabat with constant cp, saturated mixing ratios, isothermal hydrostatic altitude).
+(dry adiabat with constant cp, saturated mixing ratios, isothermal hydrostatic altitude) and against an independent
+scipy integration of the same equations with its own step control and event location (1e-9).
 
 What is restated, with the reference lines each function follows:
   * Dop853          -- the integrator is a third-party dependency that is NOT in /root/reference:

@@ -108,6 +108,80 @@ def test_compute_altitude_isothermal_closed_form():
     assert np.all(dz > 0.0) and abs(dz.sum() / (2.0 * z[-1] - z[-2] + 0.5 * (z[-1] - z[-2])) - 1.0) < 0.2
 
 
+def test_converged_oracle_against_an_independent_integration():
+    """The pseudo-adiabat of the reference's CO2-condensing case (tests/test_adiabat.f90:95-104) integrated a second
+    way: scipy's DOP853 with its own step control and its own event location (terminal events for "CO2 reaches
+    saturation" and "T reaches T_trop"), the right-hand side written from Graham et al. (2021) eq. 1 with numpy
+    vectors instead of the oracle's loops.  Both at tight tolerance: T, z and the tropopause agree to 1e-9."""
+    from scipy.integrate import solve_ivp
+    sp = species()
+    nz, T_surf, T_trop = 30, 280.0, 150.0
+    e = A.make_profile(T_surf, P_I_CO2, sp, nz, EARTH_MASS, EARTH_RADIUS, 1.0, T_trop, np.ones(7), 1e-13, 1e-12)
+    mass = np.array(sp["mass"])
+    R = A.RGAS / 1.0e7
+    psat = [(lambda T, q=q: A.sat_pressure(q, T)) if q is not None else None for q in sp["sat"]]
+    cond = np.zeros(7, bool)
+    P_i = P_I_CO2.copy()
+    for i in range(7):
+        if psat[i] is not None and P_i[i] > psat[i](T_surf):
+            P_i[i], cond[i] = psat[i](T_surf), True
+    P0 = P_i.sum()
+    assert abs(P0 / e["P"][0] - 1.0) < 1e-14
+    f_dry_share = np.where(cond, 0.0, P_i) / P_i[~cond].sum()
+
+    def mixing(P, T):
+        f = np.zeros(7)
+        for i in np.where(cond)[0]:
+            f[i] = min(psat[i](T) / P, 1.0)
+        fd = max(1.0 - f.sum(), 1e-40)
+        f[~cond] = fd * f_dry_share[~cond]
+        return f, fd
+
+    def rhs(P, u):
+        T, z = u
+        f, fd = mixing(P, T)
+        cp = np.array([A.heat_capacity(t, T) for t in sp["thermo"]])
+        L = np.array([A.latent_heat(sp["sat"][i], T) * mass[i] * 1e-7 if cond[i] else 0.0 for i in range(7)])
+        beta = L / (R * T)
+        s1 = np.sum(f[cond] * (cp[cond] - R * beta[cond] + R * beta[cond] ** 2))
+        s2 = np.sum(beta[cond] * f[cond])
+        cpd = np.sum(f_dry_share[~cond] * cp[~cond])
+        dlnT = 1.0 / (fd * ((cpd * fd + s1) / (R * (fd + s2))) + s2)
+        g = A.gravity(EARTH_RADIUS, EARTH_MASS, z)
+        return [dlnT * T / P, -(A.RGAS * T) / (g * P * np.dot(f, mass))]
+
+    def ev_trop(P, u):
+        return u[0] - T_trop
+
+    def ev_co2(P, u):
+        return psat[1](u[0]) - mixing(P, u[0])[0][1] * P if not cond[1] else 1.0
+    ev_trop.terminal = ev_co2.terminal = True
+    P_start, u = P0, [T_surf, 0.0]
+    pieces = []
+    for _ in range(3):
+        s = solve_ivp(rhs, (P_start, 1.0), u, method="DOP853", rtol=1e-12, atol=1e-10, dense_output=True,
+                      events=[ev_trop, ev_co2])
+        pieces.append((P_start, s.t[-1], s.sol))
+        if s.status != 1:
+            break
+        if s.t_events[0].size:             # tropopause
+            P_trop = float(s.t_events[0][0])
+            break
+        f, _ = mixing(s.t[-1], s.y[0, -1])  # CO2 starts to condense: restart with it on its saturation curve
+        cond[1] = True
+        Pd = f * s.t[-1]
+        f_dry_share = np.where(cond, 0.0, Pd) / Pd[~cond].sum()
+        P_start, u = float(s.t[-1]), [float(s.y[0, -1]), float(s.y[1, -1])]
+    assert cond[1] and abs(P_trop / e["P_trop"] - 1.0) < 1e-9
+    for k, Pk in enumerate(e["P"][:-1]):
+        if Pk < P_trop:
+            assert e["T"][k] == T_trop
+            continue
+        hi, lo, sol = next(p for p in pieces if p[0] >= Pk >= p[1])
+        T, z = sol(Pk)
+        assert abs(T / e["T"][k] - 1.0) < 1e-9 and abs(z - e["z"][k]) < 1e-9 * max(e["z"][k], 1e5)
+
+
 def test_make_profile_input_errors():
     sp = species()
     with pytest.raises(A.AdiabatError, match="less than input"):
