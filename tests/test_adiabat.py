@@ -352,6 +352,56 @@ def test_both_make_profile_kernels_agree(monkeypatch):
 
 
 @pytest.mark.gpu
+def test_eleven_gases_nasa9_and_three_condensers(monkeypatch):
+    """More than 8 gases (groups of 16 lanes per column), NASA-9 heat capacities (clima_eqns.f90:94-103) next to
+    Shomate ones, and a third condensable: both kernels against the oracle."""
+    import copy
+    from clima_b200 import synth
+    from clima_b200.adiabat import AdiabatClimate
+    from clima_b200.radtran import Radtran
+    sp = species()
+    extra = ["NH3", "He", "Ar", "SO2"]
+    for k, (n, m) in enumerate(zip(extra, (17.03, 4.0026, 39.948, 64.06))):
+        sp["names"].append(n)
+        sp["mass"].append(m)
+        # cp / R = a3 + a4 T + a5 T^2 (+ a1 / T^2 for the last range): two temperature ranges
+        sp["thermo"].append(dict(model="Nasa9", temps=[0.0, 400.0, 6000.0],
+                                 data=[[0.0, 0.0, 3.5 + 0.2 * k, 1.0e-3, -2.0e-7, 0.0, 0.0, 0.0, 0.0],
+                                       [1.0e3, 0.0, 3.6 + 0.2 * k, 8.0e-4, -1.0e-7, 0.0, 0.0, 0.0, 0.0]]))
+        sp["sat"].append(None)
+    nh3 = copy.deepcopy(sp["sat"][1])       # an NH3-like condensable from CO2's fit: lower vapour pressure
+    nh3.update(mu=17.03, P_ref=nh3["P_ref"] * 0.05)
+    sp["sat"][7] = nh3
+    names = sp["names"]
+    tb = synth.make_tables(nw=10, G=16, nk=3, ncia=6, nray=3, npxs=2, cont=True, npress=8, ntemp=6, n_sol=6, ir_start=3,
+                           seed=1, species=names)
+    assert tb.ng == 11
+    ac = AdiabatClimate(Radtran(tb, synth.default_params(tb, nzenith=2)), sp, 18, EARTH_MASS, EARTH_RADIUS)
+    ac.T_trop, ac.rtol = 140.0, 1e-12
+    rng = np.random.default_rng(4)
+    n = 10
+    T = rng.uniform(250.0, 330.0, n)
+    P = np.empty((11, n), order="F")
+    for c in range(n):
+        P[:7, c] = (P_I_OCEAN, P_I_CO2)[c % 2] * rng.uniform(0.5, 2.0, 7)
+        P[7:, c] = np.array([0.3, 1e-3, 0.01, 1e-5]) * BAR * rng.uniform(0.5, 2.0, 4)
+    got = {}
+    for mode in ("group", "thread"):
+        monkeypatch.setenv("CLIMA_RT_ADIABAT", mode)
+        got[mode] = ac.make_profile_batch(T, P)
+    cond_nh3 = 0
+    for c in range(n):
+        o = oracle_column(ac, T[c], P[:, c])
+        cond_nh3 += int(o["edges"]["sp_type"][7] == 1)
+        for mode in got:
+            same_profile(got[mode], c, o, tol=TIGHT_TOL)
+    assert cond_nh3 > 0                       # the third condensable did condense somewhere
+    monkeypatch.delenv("CLIMA_RT_ADIABAT")
+    isr, olr = ac.TOA_fluxes_batch(T, P)      # and the columns go through the RT with 11 gases
+    assert np.all(np.isfinite(olr)) and np.all(olr > 0.0) and np.all(isr > 0.0)
+
+
+@pytest.mark.gpu
 def test_make_profile_failures_are_reported_per_column():
     from clima_b200.radtran import ClimaException
     _, _, ac = gpu_model(nz=12)
