@@ -1,11 +1,21 @@
 """CPU oracle for row N4: `AdiabatClimate.make_profile`, restated in numpy.
 
-TEST INFRASTRUCTURE ONLY: imported by tests/ (and nothing in clima_b200/).  PARITY UNPINNED: the reference
-cannot be compiled in this image (Fortran + fypp + CPM-fetched dependencies, DESIGN.md "Oracle") and its
-own test of this path (tests/test_adiabat.f90) holds no numbers, only "runs without error" cases; those
-cases are reused as inputs (tests/test_adiabat.py), and the restatement is checked against closed forms
-(dry adiabat with constant cp, saturated mixing ratios, isothermal hydrostatic altitude) and against an independent
-scipy integration of the same equations with its own step control and event location (1e-9).
+TEST INFRASTRUCTURE ONLY: imported by tests/ (and nothing in clima_b200/).
+
+PARITY: PINNED FOR make_profile, UNPINNED FOR compute_altitude.  The reference cannot be compiled in this image
+(Fortran + fypp + CPM-fetched dependencies, DESIGN.md "Oracle") and its own test of this path (tests/test_adiabat.f90)
+holds no numbers -- but its tutorial notebook (examples/Tutorial_AdiabatClimate.ipynb, cells 6, 10, 11, 14) stores what
+the real code printed for `c.make_profile(280 K, [260, 10, 1, 1e-10 ...] bar)`, P_top = 1e-2, T_trop = 150:
+P_surf = 11.010013835789936 bar (reproduced to all 17 digits), N_surface(H2O) = 14696.15911658 mol/cm^2 (all 13
+digits) and N_atmos of the seven gases to 9 digits (reproduced to 2e-9 at rtol 1e-12 and to 1e-7 at the default rtol,
+with dz taken from make_profile's own z(P), as the notebook's version of the reference did).  N_atmos integrates T(P),
+z(P), the mixing ratios, the CO2 saturation event and the tropopause over the whole column.  Fixture and generator:
+tests/golden/tutorial_adiabat_outputs.json, tests/golden/make_tutorial_outputs.py; test:
+tests/test_adiabat.py::test_oracle_against_the_outputs_the_reference_printed.  `compute_altitude` (added to the reference
+after that notebook was run; it moves N_atmos by 3e-4) has no published numbers: it is checked against closed forms only.
+Further checks of the restatement: closed forms (dry adiabat with constant cp, saturated mixing ratios, isothermal
+hydrostatic altitude) and an independent scipy integration of the same equations with its own step control and event
+location (1e-9).
 
 What is restated, with the reference lines each function follows:
   * Dop853          -- the integrator is a third-party dependency that is NOT in /root/reference:

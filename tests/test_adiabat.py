@@ -1,6 +1,6 @@
 """Row N4: batched `AdiabatClimate%make_profile` / `TOA_fluxes` (clima_b200/csrc/adiabat_profile.cu behind
 clima_rt_make_profile_batch / clima_rt_adiabat_toa_fluxes_batch) against the numpy restatement of the reference
-(oracle/adiabat_np.py, parity unpinned: see its header).  Inputs are the cases of the reference's own
+(oracle/adiabat_np.py: pinned for make_profile against outputs the reference printed, see its header).  Inputs are the cases of the reference's own
 tests/test_adiabat.f90 (which holds no numbers) on the reference's species data (tests/golden/adiabat_species.json).
 Tolerances: see PROFILE_TOL / TIGHT_TOL below (the integration error of the reference's default settings bounds
 what any two builds can agree on); 1e-9 on ISR / OLR like the rest of the path, on converged profiles."""
@@ -106,6 +106,44 @@ def test_compute_altitude_isothermal_closed_form():
     want = 1.0 / (1.0 / EARTH_RADIUS + (A.RGAS * T0) / (GM * mu) * np.log(P / 1.0e6)) - EARTH_RADIUS
     assert np.max(np.abs(z / want - 1.0)) < 1e-9
     assert np.all(dz > 0.0) and abs(dz.sum() / (2.0 * z[-1] - z[-2] + 0.5 * (z[-1] - z[-2])) - 1.0) < 0.2
+
+
+def tutorial_case():
+    with open(os.path.join(HERE, "golden", "tutorial_adiabat_outputs.json")) as f:
+        ref = json.load(f)
+    i = ref["inputs"]
+    return ref, i["T_surf"], np.array(i["P_i_bar"]) * BAR, i
+
+
+def test_oracle_against_the_outputs_the_reference_printed():
+    """THE PIN of this path: examples/Tutorial_AdiabatClimate.ipynb stores what the reference printed after
+    `c.make_profile(280, [260, 10, 1, ...] bar)` with P_top = 1e-2, T_trop = 150 (fixture + generator in tests/golden).
+      * P_surf = 11.010013835789936 bar: all 17 digits (saturation pressure of H2O at 280 K + the dry gases);
+      * N_surface(H2O) = 14696.15911658 mol/cm^2: all 13 printed digits (masses, gravity);
+      * N_atmos (9 printed digits): sum of density * f_i * dz / N_avo over the layers, i.e. T(P), z(P), the mixing
+        ratios, the CO2 saturation event and the tropopause of the pseudo-adiabat.  The notebook's version of the
+        reference took dz from make_profile's own z; today's takes it from `compute_altitude` (interpolating T and mubar
+        linearly in log10 P between the layer centres), which moves N_atmos by 3e-4 -- so the printed numbers pin the
+        adiabat integration (checked with dz from its own z) and not compute_altitude."""
+    ref, T_surf, P_i, inp = tutorial_case()
+    sp = species()
+    want = np.array(ref["N_atmos"])
+    for rtol, tol in ((1e-9, 1e-7), (1e-12, 2e-9)):
+        c = A.adiabat_column(T_surf, P_i, sp, inp["nz"], inp["planet_mass"], inp["planet_radius"], P_top=inp["P_top"],
+                             T_trop=inp["T_trop"], rtol=rtol)
+        assert repr(c["P_surf"] / 1e6) == ref["P_surf_text"]
+        assert "%.8f" % c["N_surface"][0] == ref["N_surface_text"].split()[0].lstrip("[") and not c["N_surface"][1:].any()
+        ze = c["edges"]["z"]
+        dz_own = ze[2::2] - ze[0:-1:2]
+        dens = c["P"] / (A.K_BOLTZ * c["T"])
+        N_own = np.array([np.sum(dens * c["f_i"][:, i] * dz_own) / A.N_AVO for i in range(7)])
+        assert np.max(np.abs(N_own / want - 1.0)) < tol, (rtol, N_own / want - 1.0)
+        # today's dz (compute_altitude): a different discretisation of the same column, 3e-4 away
+        assert 1e-5 < np.max(np.abs(c["N_atmos"] / want - 1.0)) < 1e-3
+    assert c["edges"]["sp_type"][1] == 1 and c["P_trop"] > 0        # "CO2 condensation starts at about 3 bars"
+    k = int(np.argmax(c["f_i"][:, 1] < c["f_i"][0, 1] * 0.999))
+    assert 2.0e6 < c["P"][k] < 4.0e6
+    assert abs(c["P_trop"] / 1e6 / 1e-2 - 1.0) < 0.5                # "the tropopause is at 1e-2 bars"
 
 
 def test_converged_oracle_against_an_independent_integration():
@@ -288,6 +326,28 @@ def test_make_profile_batch_matches_the_oracle():
     assert e_dev["T"] < 5.0 * e_ora["T"] + 1e-9, (e_dev, e_ora)
     assert e_dev["z"] < 1e-5 and e_dev["dz"] < 1e-4, (e_dev, e_ora)
     assert (p["P_trop"] > 0).any()
+
+
+@pytest.mark.gpu
+def test_device_on_the_tutorial_case_of_the_reference():
+    """The column the reference's notebook printed numbers for (the oracle is pinned against them above): device against
+    oracle at nz = 100, P_top = 1e-2, both kernels, and the printed P_surf / N_surface directly."""
+    ref, T_surf, P_i, inp = tutorial_case()
+    _, _, ac = gpu_model(nz=inp["nz"])
+    ac.T_trop, ac.P_top, ac.rtol = inp["T_trop"], inp["P_top"], 1e-12
+    o = oracle_column(ac, T_surf, P_i)
+    for mode in ("group", "thread"):
+        os.environ["CLIMA_RT_ADIABAT"] = mode
+        try:
+            p = ac.make_profile_batch([T_surf], P_i[:, None])
+        finally:
+            del os.environ["CLIMA_RT_ADIABAT"]
+        same_profile(p, 0, o, tol=TIGHT_TOL)
+        assert abs(p["P_surf"][0] / 1e6 / ref["P_surf_bar"] - 1.0) < 1e-15
+        assert abs(p["N_surface"][0, 0] / ref["N_surface"][0] - 1.0) < 1e-12
+        # N_atmos with today's dz is 3e-4 from the printed numbers (see the oracle test); the mixing ratios and T that
+        # enter it are the pinned ones
+        assert np.max(np.abs(p["N_atmos"][:, 0] / np.array(ref["N_atmos"]) - 1.0)) < 1e-3
 
 
 @pytest.mark.gpu
