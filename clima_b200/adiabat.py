@@ -303,6 +303,27 @@ class AdiabatClimate:
         isr, olr = self.TOA_fluxes_batch([T_surf], np.asarray(P_i_surf, dtype=np.float64)[:, None])
         return float(isr[0]), float(olr[0])
 
+    def set_particle_density_and_radii(self, P, pdensities, pradii):
+        """`AdiabatClimate%set_particle_density_and_radii` (clima_adiabat.f90:1047-1123): P (n) [dynes/cm^2, strictly
+        decreasing], pdensities (n, np) [particles/cm^3], pradii (n, np) [cm]; make_profile interpolates them onto its
+        pressure grid (log-log, end values held) and TOA_fluxes passes them to the RT."""
+        P = np.ascontiguousarray(P, dtype=np.float64).reshape(-1)
+        pd = np.asfortranarray(pdensities, dtype=np.float64)
+        pr = np.asfortranarray(pradii, dtype=np.float64)
+        npart = len(self.rad.tables.particle_names)
+        if P.shape[0] != pd.shape[0]:
+            raise ClimaException("`P` and `pdensities` have incompatible shapes")
+        if P.shape[0] != pr.shape[0]:
+            raise ClimaException("`P` and `pradii` have incompatible shapes")
+        if pd.ndim != 2 or pd.shape[1] != npart:
+            raise ClimaException("The second dimension of `pdensities` does not match the number of particles")
+        if pr.ndim != 2 or pr.shape[1] != npart:
+            raise ClimaException("The second dimension of `pradii` does not match the number of particles")
+        err = C.create_string_buffer(ERR_LEN + 1)
+        self.rad._lib.clima_rt_adiabat_set_particles(self.rad._h, _i(P.shape[0]), P.ctypes.data_as(c_double_p),
+                                                     pd.ctypes.data_as(c_double_p), pr.ctypes.data_as(c_double_p), err)
+        _check(err)
+
     def kernel_ms(self) -> float:
         """Device time of the last make_profile kernel (CUDA events on the handle's stream)."""
         st = (C.c_double * 2)()

@@ -383,5 +383,6 @@ make_profile_group_kernel(const AdiabatData *__restrict__ ap, int ncol, int gpw,
       }
     }
     if (lane == 0) o.Tsurf_r[c] = T_surf;
+    write_particles(a, o, c, P_m, lane, GS);
   }
 }

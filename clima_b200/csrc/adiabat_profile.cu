@@ -557,6 +557,38 @@ __device__ NI_SOL int altitude_profile(const AdiabatData &a, int nz, double P_su
   return 0;
 }
 
+// AdiabatClimate_interpolate_particles (clima_adiabat.f90:1022-1044) + the particle part of
+// copy_atm_to_radiative_grid (:745-750, :760-761) for the layers first, first + stride, ... of column c: densities and
+// radii are 10 ** (linear interpolation in log10 P of the log10 values given to set_particle_density_and_radii,
+// :1095-1121, whose table ends at log10(tiny) and log10(huge): every pressure is inside it).
+__device__ void write_particles(const AdiabatData &a, const AdiabatOut &o, const int c, const double *P_m, const int first,
+                                const int stride) {
+  if (a.np <= 0 || !o.pd_r) return;
+  const int nz = a.nz, n = a.npl;
+  const bool dbl = a.double_radiative_grid != 0;
+  const int nzr = dbl ? 2 * nz + 2 : nz;
+  double *pd = o.pd_r + (size_t)nzr * a.np * c, *rd = o.rd_r + (size_t)nzr * a.np * c;
+  for (int i = first; i < nz; i += stride) {
+    const double x = nlog10(P_m[i]);
+    int lo = 0, hi = n - 1;  // bracketing interval of the ascending grid (dintrv)
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (x >= a.part_x[mid]) lo = mid; else hi = mid;
+    }
+    const double q = (x - a.part_x[lo]) / (a.part_x[lo + 1] - a.part_x[lo]), p1 = 1.0 - q;
+    const int reps = dbl ? (i == nz - 1 ? 4 : 2) : 1;
+    const int j0 = dbl ? 2 * i : i;
+    for (int k = 0; k < a.np; k++) {
+      const double d = npow(10.0, p1 * a.part_d[lo + (size_t)n * k] + q * a.part_d[lo + 1 + (size_t)n * k]);
+      const double r = npow(10.0, p1 * a.part_r[lo + (size_t)n * k] + q * a.part_r[lo + 1 + (size_t)n * k]);
+      for (int t = 0; t < reps; t++) {
+        pd[j0 + t + (size_t)nzr * k] = d;
+        rd[j0 + t + (size_t)nzr * k] = r;
+      }
+    }
+  }
+}
+
 // One column per thread.  Model-grid outputs are (nz, ncol) / (nz, ng, ncol) with nz fastest; the radiative
 // grid (nzr = 2 nz + 2 when doubled, else nz) likewise.  `work` holds, per column, lp / Tg / mg (nz + 1 each),
 // the second edge grid and its altitudes (2 nz + 1 each).
@@ -724,6 +756,7 @@ make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, int lanes, con
       }
     }
     o.Tsurf_r[c] = T_surf;
+    write_particles(a, o, c, P_m, 0, 1);
   }
 }
 

@@ -9,6 +9,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <limits>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -118,6 +119,8 @@ struct Handle {
   double *d_aTs = nullptr, *d_aPi = nullptr, *d_awork = nullptr;
   AdiabatOut aout{};
   int64_t adiabat_calls = 0;
+  double *d_part[3] = {nullptr, nullptr, nullptr};  // particle tables: log10 P (npl), log10 density / radius (npl, np)
+  int part_npl = 0;
   cudaEvent_t adiabat_ev[2] = {nullptr, nullptr};
   double adiabat_ms = 0.0;
 
@@ -933,6 +936,9 @@ static void adiabat_ensure(Handle &h, size_t ncol) {
   o.status = reinterpret_cast<int *>(dalloc(ncol)); o.nfcn = reinterpret_cast<int *>(dalloc(ncol));
   o.T_r = dalloc(nzr * ncol); o.P_r = dalloc(nzr * ncol); o.dz_r = dalloc(nzr * ncol);
   o.dens_r = dalloc(nzr * ng * ncol); o.Tsurf_r = dalloc(ncol);
+  const size_t npp = (size_t)std::max(h.tb.np, 0);
+  o.pd_r = npp ? dalloc(nzr * npp * ncol) : nullptr;
+  o.rd_r = npp ? dalloc(nzr * npp * ncol) : nullptr;
   h.adiabat_cap_cols = ncol;
 }
 
@@ -1064,6 +1070,7 @@ void clima_rt_destroy(void *handle) {
   if (h->d_jflag) cudaFree(h->d_jflag);
   for (void *q : h->adiabat_allocs) cudaFree(q);
   if (h->d_adiabat) cudaFree(h->d_adiabat);
+  for (double *q : h->d_part) if (q) cudaFree(q);
   for (auto &e : h->adiabat_ev) if (e) cudaEventDestroy(e);
   free_chunk(*h);
   for (void *p : h->table_allocs) cudaFree(p);
@@ -1275,6 +1282,69 @@ void clima_rt_radiate_batch_sharded(void *handle, const int32_t *ncol, const int
   }
 }
 
+// `AdiabatClimate%set_particle_density_and_radii` (clima_adiabat.f90:1047-1123): the interpolation tables of
+// interpolate_particles, i.e. log10 of the values on log10 P, the pressures extended by `huge` and `tiny` with the end
+// values repeated, everything reversed to ascending log10 P.
+static void set_particle_tables(Handle &h, int n, const double *P, const double *pd, const double *pr) {
+  const int np = h.tb.np;
+  if (n < 1) throw CudaError{"`P` must have a length greater than zero"};
+  for (int j = 0; j < n; j++)
+    if (!(P[j] > 0.0)) throw CudaError{"All elements of `P` must be larger than zero"};
+  for (size_t j = 0; j < (size_t)n * np; j++) {
+    if (pd[j] < 0.0) throw CudaError{"All elements of `pdensities` must be larger than zero"};
+    if (pr[j] < 0.0) throw CudaError{"All elements of `pradii` must be larger than zero"};
+  }
+  const int npl = n + 2;
+  const double tiny = std::numeric_limits<double>::min(), huge = std::numeric_limits<double>::max();
+  std::vector<double> x(npl), d((size_t)npl * np), r((size_t)npl * np);
+  for (int a = 0; a < npl; a++) {  // ascending position a <- descending position npl - 1 - a of [huge, P, tiny]
+    const int q = npl - 1 - a;
+    const int j = q == 0 ? 0 : (q == npl - 1 ? n - 1 : q - 1);  // row of the inputs (end values repeated)
+    x[a] = std::log10(q == 0 ? huge : (q == npl - 1 ? tiny : P[j]));
+    for (int k = 0; k < np; k++) {
+      d[a + (size_t)npl * k] = std::log10(std::max(pd[j + (size_t)n * k], tiny));
+      r[a + (size_t)npl * k] = std::log10(std::max(pr[j + (size_t)n * k], tiny));
+    }
+  }
+  for (int a = 1; a < npl; a++)  // linear_interp_1d%initialize wants a strictly increasing grid
+    if (!(x[a] > x[a - 1])) throw CudaError{"Interpolation initialization in `set_particle_density_and_radii` failed"};
+  CK(cudaStreamSynchronize(h.st));
+  for (double *&q : h.d_part) {
+    if (q) cudaFree(q);
+    q = nullptr;
+  }
+  CK(cudaMalloc(&h.d_part[0], x.size() * 8));
+  CK(cudaMalloc(&h.d_part[1], std::max<size_t>(d.size(), 1) * 8));
+  CK(cudaMalloc(&h.d_part[2], std::max<size_t>(r.size(), 1) * 8));
+  CK(cudaMemcpy(h.d_part[0], x.data(), x.size() * 8, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(h.d_part[1], d.data(), d.size() * 8, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(h.d_part[2], r.data(), r.size() * 8, cudaMemcpyHostToDevice));
+  h.part_npl = npl;
+  if (h.adiabat_set) {
+    h.adiabat.np = np;
+    h.adiabat.npl = npl;
+    h.adiabat.part_x = h.d_part[0];
+    h.adiabat.part_d = h.d_part[1];
+    h.adiabat.part_r = h.d_part[2];
+    CK(cudaMemcpy(h.d_adiabat, &h.adiabat, sizeof(AdiabatData), cudaMemcpyHostToDevice));
+  }
+}
+
+void clima_rt_adiabat_set_particles(void *handle, const int32_t *n, const double *P, const double *pdensities,
+                                    const double *pradii, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle) throw CudaError{"clima_rt: NULL handle"};
+    Handle &h = *static_cast<Handle *>(handle);
+    CK(cudaSetDevice(h.device));
+    if (h.tb.np <= 0) throw CudaError{"clima_rt_adiabat_set_particles: the radiative tables have no particles"};
+    if (!n || !P || !pdensities || !pradii) throw CudaError{"clima_rt: null argument"};
+    set_particle_tables(h, *n, P, pdensities, pradii);
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
 void clima_rt_adiabat_set(void *handle, const clima_rt_adiabat *ad, char *err) {
   set_err(err, "");
   try {
@@ -1287,7 +1357,6 @@ void clima_rt_adiabat_set(void *handle, const clima_rt_adiabat *ad, char *err) {
     if (ad->ng != h.tb.ng) throw CudaError{"clima_rt_adiabat_set: \"ng\" differs from the radiative tables"};
     if (ad->ng > ADIABAT_MAXG) throw CudaError{"clima_rt_adiabat_set: more than 16 gases"};
     if (ad->nz < 2) throw CudaError{"compute_altitude requires nz >= 2"};
-    if (h.tb.np > 0) throw CudaError{"clima_rt_adiabat_set: tables with particles are not supported on this path"};
     if (!(ad->rtol > 0.0) || !(ad->atol > 0.0) || !(ad->P_top > 0.0))
       throw CudaError{"clima_rt_adiabat_set: rtol, atol and P_top must be positive"};
     AdiabatData a{};
@@ -1322,6 +1391,16 @@ void clima_rt_adiabat_set(void *handle, const clima_rt_adiabat *ad, char *err) {
     a.T_trop = ad->T_trop;
     a.rtol = ad->rtol;
     a.atol = ad->atol;
+    if (h.tb.np > 0 && !h.d_part[0]) {  // the constructor's default (clima_adiabat.f90:387-389): no particles, 1 micron
+      std::vector<double> zero((size_t)h.tb.np, 0.0), micron((size_t)h.tb.np, 1.0e-4);
+      const double one = 1.0e6;
+      set_particle_tables(h, 1, &one, zero.data(), micron.data());
+    }
+    a.np = std::max(h.tb.np, 0);
+    a.npl = h.part_npl;
+    a.part_x = h.d_part[0];
+    a.part_d = h.d_part[1];
+    a.part_r = h.d_part[2];
     CK(cudaStreamSynchronize(h.st));
     if (h.adiabat_set && (a.nz != h.adiabat.nz || a.double_radiative_grid != h.adiabat.double_radiative_grid)) {
       for (void *q : h.adiabat_allocs) cudaFree(q);  // buffers are sized by nz
@@ -1406,8 +1485,8 @@ void clima_rt_adiabat_toa_fluxes_batch(void *handle, const int32_t *ncol, const 
     if (bad >= 0) throw CudaError{"column " + std::to_string(bad) + ": " + profile_message(st)};
     const AdiabatOut &o = h.aout;
     const int nzr = h.adiabat.double_radiative_grid ? 2 * h.adiabat.nz + 2 : h.adiabat.nz;
-    HostIn in{o.Tsurf_r, o.T_r, o.P_r, o.dens_r, o.dz_r, nullptr, nullptr};
-    radiate_batch_impl(h, true, *ncol, nzr, h.adiabat.ng, 0, in, true, true, out, 0);
+    HostIn in{o.Tsurf_r, o.T_r, o.P_r, o.dens_r, o.dz_r, o.pd_r, o.rd_r};
+    radiate_batch_impl(h, true, *ncol, nzr, h.adiabat.ng, std::max(h.tb.np, 0), in, true, true, out, 0);
   } catch (const CudaError &e) {
     set_err(err, e.msg);
   }

@@ -78,6 +78,10 @@ struct AdiabatData {  // device copy of what make_profile reads from the Adiabat
   double sat[ADIABAT_MAXG][16];  // mu, T_ref, P_ref, T_triple, T_critical, a_v, b_v, a_s, b_s, a_c, b_c + 5 derived
   double RH[ADIABAT_MAXG];
   double planet_mass, planet_radius, P_top, T_trop, rtol, atol;
+  // particles (AdiabatClimate%set_particle_density_and_radii): np species, npl table levels = the given pressures
+  // plus the two end points; device arrays part_x (npl) ascending log10 P, part_d / part_r (npl, np) log10 values
+  int np, npl;
+  const double *part_x, *part_d, *part_r;
 };
 struct AdiabatOut {  // device pointers
   double *P, *T, *z, *dz;            // (nz, ncol)
@@ -86,6 +90,7 @@ struct AdiabatOut {  // device pointers
   double *P_surf, *P_trop;           // (ncol)
   int *status, *nfcn;                // (ncol)
   double *T_r, *P_r, *dz_r, *dens_r, *Tsurf_r;  // radiative grid (nullptr: not wanted)
+  double *pd_r, *rd_r;               // (nz_r, np, ncol) particle densities / radii (np > 0 only)
 };
 size_t rt_adiabat_work_doubles(int nz, int ncol);
 void rt_launch_make_profile(const AdiabatData *a, int ng, int ncol, int num_sms, const double *T_surf,

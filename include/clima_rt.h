@@ -265,7 +265,8 @@ void clima_rt_jacobian_batch(void *handle, const int32_t *ncol, const int32_t *n
    tables (mass, heat-capacity polynomial, optional LinearLatentHeat saturation data:
    src/clima_types.f90 `Gas`, src/clima_saturationdata.f90:16-28), RH, P_top, T_trop, the planet,
    rtol / atol and the number of model layers.  Not carried: ocean solubility functions (host
-   callbacks; N_ocean is zero without them), particles, reference_pressure > 0, CustomDrySpecies. */
+   callbacks; N_ocean is zero without them), reference_pressure > 0, CustomDrySpecies.  Particle profiles:
+   clima_rt_adiabat_set_particles below. */
 #define CLIMA_RT_ADIABAT_MAX_GASES 16
 #define CLIMA_RT_ADIABAT_MAX_TEMPS 4
 typedef struct clima_rt_adiabat {
@@ -317,6 +318,15 @@ typedef struct clima_rt_profile_out {
    the setters of clima/fortran/AdiabatClimate.f90). */
 void clima_rt_adiabat_set(void *handle, const clima_rt_adiabat *adiabat, char *err);
 
+/* `AdiabatClimate%set_particle_density_and_radii` (src/adiabat/clima_adiabat.f90:1047-1123) for handles whose tables
+   have particles: P(n) [dynes/cm^2, strictly decreasing], pdensities(n,np) [particles/cm^3], pradii(n,np) [cm], HOST
+   pointers, same checks and messages.  make_profile then interpolates both onto its pressure grid like
+   `interpolate_particles` (:1022-1044: linear in log10 P of the log10 values, end values held) and the batched
+   TOA_fluxes passes them to the RT.  Without this call the constructor's default applies (:387-389: no particles,
+   radius 1 micron). */
+void clima_rt_adiabat_set_particles(void *handle, const int32_t *n, const double *P, const double *pdensities,
+                                    const double *pradii, char *err);
+
 /* `AdiabatClimate%make_profile` (src/adiabat/clima_adiabat.f90:401-472) for ncol columns:
    T_surf(ncol) [K], P_i_surf(ng,ncol) [dynes/cm^2], HOST pointers.  A column that fails gets its status
    code; `err` names the first such column with the reference's message, the others are still computed. */
@@ -327,7 +337,7 @@ void clima_rt_make_profile_batch(void *handle, const int32_t *ncol, const double
    make_profile on the device, copy_atm_to_radiative_grid written straight into the arrays the RT kernels
    read, then the radiate path.  `profile` may be NULL.  `out` as for clima_rt_radiate_batch with
    nz_r = 2 nz + 2 (nz when double_radiative_grid = 0) levels.  Any failed column fails the call (err set,
-   `out` untouched), as the reference's loop would stop there.  Needs tables without particles. */
+   `out` untouched), as the reference's loop would stop there. */
 void clima_rt_adiabat_toa_fluxes_batch(void *handle, const int32_t *ncol, const double *T_surf,
                                        const double *P_i_surf, const clima_rt_profile_out *profile,
                                        const clima_rt_out *out, char *err);

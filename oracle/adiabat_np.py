@@ -585,3 +585,26 @@ def adiabat_column(T_surf, P_i_surf, sp, nz, planet_mass, planet_radius, P_top=1
     return dict(P=P, T=T, f_i=f_i, densities=densities, z=z, dz=dz, P_surf=float(e["P"][0]),
                 P_trop=e["P_trop"], N_surface=e["N_surface"], N_atmos=N_atmos, f_i_surf=e["f_i"][0].copy(),
                 edges=e)
+
+
+# --------------------------------------------------------------------------------------------------
+# particles: set_particle_density_and_radii + interpolate_particles (clima_adiabat.f90:1022-1044, 1047-1123)
+# --------------------------------------------------------------------------------------------------
+def interpolate_particles(P_layers, P_set, pdensities, pradii):
+    """-> (pdensities, pradii) at the layer pressures, each (nz, np): 10 ** (linear interpolation in log10 P of the log10
+    of the values given at P_set (strictly decreasing), the table extended by `huge` / `tiny` with the end values held)."""
+    tiny, huge = 2.2250738585072014e-308, 1.7976931348623157e308
+    P_set = np.asarray(P_set, float)
+    x = np.log10(np.concatenate([[huge], P_set, [tiny]])[::-1])
+    if np.any(np.diff(x) <= 0.0):
+        raise AdiabatError("Interpolation initialization in `set_particle_density_and_radii` failed")
+    out = []
+    for vals in (np.asarray(pdensities, float), np.asarray(pradii, float)):
+        res = np.empty((len(P_layers), vals.shape[1]))
+        for k in range(vals.shape[1]):
+            tmp = np.concatenate([[vals[0, k]], vals[:, k], [vals[-1, k]]])
+            tmp = np.log10(np.maximum(tmp[::-1], tiny))
+            for j, Pj in enumerate(P_layers):
+                res[j, k] = 10.0 ** _interp_linear(x, tmp, math.log10(Pj))
+        out.append(res)
+    return out[0], out[1]

@@ -461,6 +461,68 @@ def test_eleven_gases_nasa9_and_three_condensers(monkeypatch):
     assert np.all(np.isfinite(olr)) and np.all(olr > 0.0) and np.all(isr > 0.0)
 
 
+def test_particle_interpolation_oracle():
+    """interpolate_particles: log-log between the given levels, end values held outside them, zero density -> tiny."""
+    Pset = np.array([1.0e6, 1.0e4, 1.0e2])
+    pd = np.array([[100.0], [1.0], [0.0]])
+    pr = np.array([[1.0e-4], [4.0e-4], [1.0e-5]])
+    d, r = A.interpolate_particles([1.0e7, 1.0e6, 1.0e5, 1.0e4, 1.0], Pset, pd, pr)
+    assert np.allclose(d[:4, 0], [100.0, 100.0, 10.0, 1.0], rtol=1e-13) and d[4, 0] < 1e-300
+    assert np.allclose(r[:, 0], [1.0e-4, 1.0e-4, 2.0e-4, 4.0e-4, 1.0e-5], rtol=1e-13)
+    with pytest.raises(A.AdiabatError, match="Interpolation initialization"):
+        A.interpolate_particles([1.0], Pset[::-1], pd, pr)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["group", "thread"])
+def test_adiabat_toa_fluxes_with_particles(mode, monkeypatch):
+    """Tables with two particle species: `set_particle_density_and_radii` + `interpolate_particles` on the device and
+    the particle arrays of copy_atm_to_radiative_grid, checked through the fluxes against the oracle chain; the
+    constructor's default (no particles, 1 micron) before any profile is set."""
+    from cases import small_case
+    from clima_b200.adiabat import AdiabatClimate, copy_atm_to_radiative_grid
+    from clima_b200.radtran import ClimaException, Radtran
+    from oracle_lib import OracleRadtran
+    monkeypatch.setenv("CLIMA_RT_ADIABAT", mode)
+    tb, pr, _ = small_case(G=16, nw=10, nz=4, ncol=1, nzen=2, npart=2)
+    nz = 12
+    ac = AdiabatClimate(Radtran(tb, pr), species(), nz, EARTH_MASS, EARTH_RADIUS)
+    ac.T_trop, ac.rtol = 160.0, 1e-12
+    T, P = sweep(5, seed=8)
+    o = OracleRadtran(tb, pr)
+    Pset = np.array([3.0e6, 1.0e5, 1.0e3, 10.0])
+    pdens = np.array([[50.0, 0.0], [20.0, 5.0], [1.0, 8.0], [0.0, 0.1]])
+    prad = np.array([[2.0e-4, 1.0e-5], [1.0e-4, 2.0e-5], [5.0e-5, 3.0e-5], [2.0e-5, 3.0e-5]])
+    for given in (False, True):
+        if given:
+            ac.set_particle_density_and_radii(Pset, pdens, prad)
+        r = ac.TOA_fluxes_batch(T, P, full=True)
+        for c in range(5):
+            col = oracle_column(ac, T[c], P[:, c])
+            if given:
+                pd_l, pr_l = A.interpolate_particles(col["P"], Pset, pdens, prad)
+            else:
+                pd_l, pr_l = np.full((nz, 2), 2.2250738585072014e-308), np.full((nz, 2), 1.0e-4)
+            g = copy_atm_to_radiative_grid(col["T"], col["P"] / 1.0e6, col["densities"], col["dz"], pd_l, pr_l)
+            cols = dict(nz=2 * nz + 2, ng=7, np=2, ncol=1, T_surface=np.array([T[c]]))
+            for k in ("T", "P", "dz"):
+                cols[k] = np.asfortranarray(g[k][:, None])
+            for k in ("densities", "pdensities", "radii"):
+                cols[k] = np.asfortranarray(g[k][:, :, None])
+            ro = o.radiate(cols, 0, spectral=False)
+            assert abs(r["ISR"][c] / ro["ISR"][0] - 1.0) < 1e-7 and abs(r["OLR"][c] / ro["OLR"][0] - 1.0) < 1e-7
+            assert np.max(np.abs(r["f_total"][:, c] - ro["f_total"][:, 0])) < 1e-7 * np.max(np.abs(ro["f_total"]))
+        if not given:
+            olr0 = r["OLR"].copy()
+    assert np.max(np.abs(r["OLR"] / olr0 - 1.0)) > 1e-3       # the particles do change the fluxes
+    with pytest.raises(ClimaException, match="Interpolation initialization"):
+        ac.set_particle_density_and_radii(Pset[::-1], pdens, prad)
+    with pytest.raises(ClimaException, match="`pradii` must be larger than zero"):
+        ac.set_particle_density_and_radii(Pset, pdens, -prad)
+    with pytest.raises(ClimaException, match="does not match the number of particles"):
+        ac.set_particle_density_and_radii(Pset, pdens[:, :1], prad[:, :1])
+
+
 @pytest.mark.gpu
 def test_make_profile_failures_are_reported_per_column():
     from clima_b200.radtran import ClimaException
