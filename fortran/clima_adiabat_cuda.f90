@@ -136,8 +136,10 @@ end module
 !> To be added to src/adiabat/clima_adiabat.f90 (`procedure :: TOA_fluxes_batch_device => ...`): the loop
 !>   do i = 1,ncol;  call c%TOA_fluxes(T_surf(i), P_i_surf(:,i), ISR(i), OLR(i), err);  enddo
 !> of a sweep (examples/EarlyMars.ipynb, cell 7) as ONE device call.  Not supported here, as in
-!> include/clima_rt.h: ocean solubility functions, particles, reference_pressure > 0, a T_surf-dependent
-!> albedo (the host-profile variant in fortran/clima_batch_wrappers.f90 covers the first three).
+!> include/clima_rt.h: ocean solubility functions, reference_pressure > 0, a T_surf-dependent albedo (the host-profile
+!> variant in fortran/clima_batch_wrappers.f90 covers the first two).  Particle profiles: forward the arguments of
+!> AdiabatClimate_set_particle_density_and_radii to clima_rt_adiabat_set_particles (same argument list + handle); objects
+!> with particles are refused below until that forwarding is added.
 subroutine AdiabatClimate_TOA_fluxes_batch_device(self, T_surf, P_i_surf, ISR, OLR, err)
   use iso_c_binding
   use clima_adiabat_cuda
