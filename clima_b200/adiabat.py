@@ -94,7 +94,8 @@ MAX_GASES, MAX_TEMPS = 16, 4
 SAT_KEYS = ("mu", "T_ref", "P_ref", "T_triple", "T_critical", "a_v", "b_v", "a_s", "b_s", "a_c", "b_c")
 PROFILE_STATUS = {1: "T_surf below T_trop", 2: "negative surface pressure", 3: "P_top above the surface pressure",
                   4: "dop853 failed", 5: "brent failed", 6: "heat capacity out of range", 7: "negative altitudes",
-                  8: "altitude integration failed", 9: "pressure grid not decreasing", 10: "negative T_trop"}
+                  8: "altitude integration failed", 9: "pressure grid not decreasing", 10: "negative T_trop",
+                  11: "reference_pressure outside the model domain"}
 
 
 def species_from_yaml(path_or_dict, names: Optional[Sequence[str]] = None) -> Dict:
@@ -143,7 +144,7 @@ class CAdiabat(C.Structure):
                 ("thermo_temps", c_double_p), ("thermo_data", c_double_p), ("has_sat", c_int32_p),
                 ("sat", c_double_p), ("RH", c_double_p),
                 ("planet_mass", C.c_double), ("planet_radius", C.c_double), ("P_top", C.c_double),
-                ("T_trop", C.c_double), ("rtol", C.c_double), ("atol", C.c_double)]
+                ("T_trop", C.c_double), ("rtol", C.c_double), ("atol", C.c_double), ("reference_pressure", C.c_double)]
 
 
 PROFILE_FIELDS = ("P", "T", "z", "dz", "f_i", "f_i_surf", "N_surface", "P_surf", "P_trop")
@@ -168,12 +169,14 @@ class AdiabatClimate:
         self.P_top, self.T_trop = 1.0, 180.0
         self.RH = np.ones(self.ng)
         self.rtol, self.atol = 1.0e-9, 1.0e-12
+        self.reference_pressure = -1.0  # > 0: the planet radius is at this pressure (clima_adiabat.f90:58-64)
         self._sent = None
+        self.ocean_fcns = [None] * self.ng  # per ocean-forming species: fcn(T_surf, ng, P_i [bar]) -> mol/kg (ng)
 
     # -- the adiabat description goes to the device whenever a public member has changed
     def _sync(self):
         key = (self.P_top, self.T_trop, tuple(np.asarray(self.RH, float)), self.rtol, self.atol,
-               self.double_radiative_grid, self.nz)
+               self.double_radiative_grid, self.nz, self.reference_pressure)
         if key == self._sent:
             return
         sp, ng = self.sp, self.ng
@@ -207,7 +210,7 @@ class AdiabatClimate:
                      temps.ctypes.data_as(c_double_p), data.ctypes.data_as(c_double_p),
                      has_sat.ctypes.data_as(c_int32_p), sat.ctypes.data_as(c_double_p), RH.ctypes.data_as(c_double_p),
                      self.planet_mass, self.planet_radius, float(self.P_top), float(self.T_trop), float(self.rtol),
-                     float(self.atol))
+                     float(self.atol), float(self.reference_pressure))
         err = C.create_string_buffer(ERR_LEN + 1)
         self.rad._lib.clima_rt_adiabat_set(self.rad._h, C.byref(a), err)
         _check(err)
@@ -264,7 +267,7 @@ class AdiabatClimate:
             _check(err)
         self._T_surf = T_surf
         with np.errstate(all="ignore"):
-            return self._derived(arrs)
+            return self._oceans(self._derived(arrs))
 
     def make_profile(self, T_surf: float, P_i_surf):
         """One column; leaves the reference's member names on the object."""
@@ -276,6 +279,7 @@ class AdiabatClimate:
             setattr(self, k, p[k][:, :, 0].copy())
         for k in ("f_i_surf", "N_surface", "N_atmos"):
             setattr(self, k, p[k][:, 0].copy())
+        self.N_ocean = p["N_ocean"][:, :, 0].copy()
         self.P_surf, self.P_trop = float(p["P_surf"][0]), float(p["P_trop"][0])
 
     def TOA_fluxes_batch(self, T_surf, P_i_surf, full: bool = False):
@@ -295,13 +299,37 @@ class AdiabatClimate:
         _check(err)
         if full:
             self._T_surf = T_surf
-            arrs["profile"] = self._derived(parrs)
+            arrs["profile"] = self._oceans(self._derived(parrs))
             return arrs
         return arrs["ISR"], arrs["OLR"]
 
     def TOA_fluxes(self, T_surf: float, P_i_surf):
         isr, olr = self.TOA_fluxes_batch([T_surf], np.asarray(P_i_surf, dtype=np.float64)[:, None])
         return float(isr[0]), float(olr[0])
+
+    def set_ocean_solubility_fcn(self, species: str, fcn):
+        """`AdiabatClimate%set_ocean_solubility_fcn` (clima_adiabat.f90:1125-1150): `fcn(T_surf, ng, P_i)` with P_i the
+        surface partial pressures in bars returns the mol/kg of every gas dissolved in an ocean of `species`; None
+        removes it.  The callbacks are host code and touch only N_ocean (clima_adiabat_general.f90:226-246), never the
+        profile, so they run on the host after the device call, per column, exactly as the reference calls them."""
+        if species not in self.sp["names"]:
+            raise ClimaException('Gas "%s" is not in the list of species' % species)
+        self.ocean_fcns[self.sp["names"].index(species)] = fcn
+
+    def _oceans(self, p: Dict) -> Dict:
+        ng, ncol = self.ng, p["P_surf"].shape[0]
+        N_ocean = np.zeros((ng, ng, ncol), order="F")
+        if any(f is not None for f in self.ocean_fcns):
+            P_i_cur = p["f_i_surf"] * p["P_surf"][None, :]
+            for c in np.where(p["status"] == 0)[0]:
+                for j, fcn in enumerate(self.ocean_fcns):
+                    if fcn is None:
+                        continue
+                    m_i = np.asarray(fcn(float(self._T_surf[c]), ng, P_i_cur[:, c] / 1.0e6), dtype=np.float64)
+                    N_ocean[:, j, c] = m_i * p["N_surface"][j, c] * (self.sp["mass"][j] / 1.0e3)
+                    N_ocean[j, j, c] = 0.0  # an ocean does not dissolve into itself
+        p["N_ocean"] = N_ocean
+        return p
 
     def set_particle_density_and_radii(self, P, pdensities, pradii):
         """`AdiabatClimate%set_particle_density_and_radii` (clima_adiabat.f90:1047-1123): P (n) [dynes/cm^2, strictly

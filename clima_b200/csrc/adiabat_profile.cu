@@ -515,45 +515,84 @@ struct AltitudeRhs {
 
 // solout_dop853_solveivp (clima_useful.f90:216-236): dense-output samples at the requested pressures
 struct AltitudeSolout {
-  const double *x_eval;  // P_e2[1 .. m]
+  const double *x_eval;  // first requested pressure; the j-th is x_eval[j * step]
   double *y_eval;
-  int m, j;
+  int m, j, step;
   double xtol;
   __device__ NI_SOL int operator()(const Dop<1> &dop, int nr, double xold, double x, const double *y) {
     const double x_lo = fmin(xold, x) - xtol, x_hi = fmax(xold, x) + xtol;
     while (j < m) {
-      const double xe = x_eval[j];
+      const double xe = x_eval[j * step];
       if (xe < x_lo || xe > x_hi) break;
-      y_eval[j] = dop.contd8(0, xe);
+      y_eval[j * step] = dop.contd8(0, xe);
       j++;
     }
     return 1;
   }
 };
 
-// compute_altitude (clima_adiabat_altitude.f90:52-55, 180-243) on the prepared tables: the strictly-decreasing
-// check of the second edge grid, the integration of z from the surface with samples at every edge, the
-// extrapolated top edge.  Returns the column status (0, 8 or 9).
+// integrate_altitude_segment (clima_adiabat_altitude.f90:195-243) through solve_ivp_dop853 (clima_useful.f90:97-236):
+// z = 0 at P_start, samples at the edges j_start, j_start + step, ..., j_end.  false = the integration failed.
+__device__ NI_SOL bool altitude_segment(const AdiabatData &a, const AltitudeRhs &rhs, double P_start, const double *P_e2,
+                                        double *z_e, int j_start, int j_end, int step) {
+  Dop<1> dop;
+  AltitudeSolout as;
+  as.x_eval = P_e2 + j_start;
+  as.y_eval = z_e + j_start;
+  as.m = (j_end > j_start ? j_end - j_start : j_start - j_end) + 1;
+  as.j = 0;
+  as.step = step;
+  const double big = fmax(1.0, fmax(P_start, fmax(P_e2[j_start], P_e2[j_end])));
+  as.xtol = fmax(1.0e-12 * big, 10.0 * (nextafter(big, DBL_MAX) - big));
+  while (as.j < as.m && fabs(as.x_eval[as.j * step] - P_start) <= as.xtol) {  // :155-159
+    as.y_eval[as.j * step] = 0.0;
+    as.j++;
+  }
+  if (as.j >= as.m) return true;
+  double x = P_start, y[1] = {0.0};
+  const int idid = dop_integrate<1>(dop, x, y, P_e2[j_end], a.rtol, a.atol, rhs, as);
+  return idid >= 0 && as.j >= as.m;
+}
+
+// compute_altitude (clima_adiabat_altitude.f90:52-55, 97-193) on the prepared tables: the strictly-decreasing check
+// of the second edge grid, then z at every edge -- from the surface upward (reference_pressure <= 0: the planet radius
+// is at the surface), or from the reference pressure upward and downward and shifted back to zero at the surface
+// (:107-169) -- and the extrapolated top edge.  Returns the column status (0, 8, 9 or 11).
 __device__ NI_SOL int altitude_profile(const AdiabatData &a, int nz, double P_surf, const double *lp, const double *Tg,
                                        const double *mg, const double *P_e2, double *z_e) {
   double dmin = DBL_MAX;
   for (int k = 0; k < 2 * nz; k++) dmin = fmin(dmin, P_e2[k] - P_e2[k + 1]);
   const double ulp = nextafter(P_surf, DBL_MAX) - P_surf;  // spacing(P_e(1))
   if (dmin <= 10.0 * ulp) return 9;
-  Dop<1> dop;
-  AltitudeRhs rhs{lp, Tg, mg, nz, a.planet_mass, a.planet_radius};
-  AltitudeSolout as;
-  as.x_eval = P_e2 + 1;
-  as.y_eval = z_e + 1;
-  as.m = 2 * nz - 1;
-  as.j = 0;
-  const double big = fmax(1.0, P_surf);
-  as.xtol = fmax(1.0e-12 * big, 10.0 * (nextafter(big, DBL_MAX) - big));
-  z_e[0] = 0.0;
-  double x = P_surf, y[1] = {0.0};
-  const int idid = dop_integrate<1>(dop, x, y, P_e2[2 * nz - 1], a.rtol, a.atol, rhs, as);
-  if (idid < 0 || as.j < as.m) return 8;
-  z_e[2 * nz] = z_e[2 * nz - 1] + (z_e[2 * nz - 1] - z_e[2 * nz - 2]);
+  const AltitudeRhs rhs{lp, Tg, mg, nz, a.planet_mass, a.planet_radius};
+  const int ne = 2 * nz + 1;
+  const double Pr = a.reference_pressure;
+  if (Pr <= 0.0) {
+    z_e[0] = 0.0;
+    if (!altitude_segment(a, rhs, P_surf, P_e2, z_e, 1, ne - 2, 1)) return 8;
+  } else {
+    if (Pr < a.P_top || Pr > P_surf) return 11;
+    int k = 0;
+    while (k < ne - 2 && !(Pr <= P_e2[k] && Pr >= P_e2[k + 1])) k++;
+    int top, bot;
+    if (Pr == P_e2[k]) {
+      z_e[k] = 0.0;
+      top = k + 1;
+      bot = k - 1;
+    } else if (Pr == P_e2[k + 1]) {
+      z_e[k + 1] = 0.0;
+      top = k + 2;
+      bot = k;
+    } else {
+      top = k + 1;
+      bot = k;
+    }
+    if (top <= ne - 2 && !altitude_segment(a, rhs, Pr, P_e2, z_e, top, ne - 2, 1)) return 8;
+    if (bot >= 0 && !altitude_segment(a, rhs, Pr, P_e2, z_e, bot, 0, -1)) return 8;
+    const double z_shift = z_e[0];  // keep the stored altitude surface-anchored (:164-166)
+    for (int j = 0; j < ne - 1; j++) z_e[j] -= z_shift;
+  }
+  z_e[ne - 1] = z_e[ne - 2] + (z_e[ne - 2] - z_e[ne - 3]);
   return 0;
 }
 

@@ -907,6 +907,7 @@ static const char *profile_message(int status) {
     case 8: return "compute_altitude: altitude segment integration failed.";
     case 9: return "compute_altitude: pressure grid is not strictly decreasing.";
     case 10: return "make_profile: Input \"T_trop\" is less than 0";
+    case 11: return "compute_altitude: reference_pressure outside model domain [P_top, P_surf]";
   }
   return "make_profile failed";
 }
@@ -1391,6 +1392,7 @@ void clima_rt_adiabat_set(void *handle, const clima_rt_adiabat *ad, char *err) {
     a.T_trop = ad->T_trop;
     a.rtol = ad->rtol;
     a.atol = ad->atol;
+    a.reference_pressure = ad->reference_pressure;
     if (h.tb.np > 0 && !h.d_part[0]) {  // the constructor's default (clima_adiabat.f90:387-389): no particles, 1 micron
       std::vector<double> zero((size_t)h.tb.np, 0.0), micron((size_t)h.tb.np, 1.0e-4);
       const double one = 1.0e6;

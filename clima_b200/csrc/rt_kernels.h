@@ -78,6 +78,7 @@ struct AdiabatData {  // device copy of what make_profile reads from the Adiabat
   double sat[ADIABAT_MAXG][16];  // mu, T_ref, P_ref, T_triple, T_critical, a_v, b_v, a_s, b_s, a_c, b_c + 5 derived
   double RH[ADIABAT_MAXG];
   double planet_mass, planet_radius, P_top, T_trop, rtol, atol;
+  double reference_pressure;  // <= 0: planet radius at the surface (clima_adiabat.f90:64)
   // particles (AdiabatClimate%set_particle_density_and_radii): np species, npl table levels = the given pressures
   // plus the two end points; device arrays part_x (npl) ascending log10 P, part_d / part_r (npl, np) log10 values
   int np, npl;

@@ -23,7 +23,7 @@ module clima_adiabat_cuda
   type, bind(c) :: clima_rt_adiabat
     integer(c_int32_t) :: ng, nz, double_radiative_grid
     type(c_ptr) :: mass, thermo_model, thermo_ntemps, thermo_temps, thermo_data, has_sat, sat, RH
-    real(c_double) :: planet_mass, planet_radius, P_top, T_trop, rtol, atol
+    real(c_double) :: planet_mass, planet_radius, P_top, T_trop, rtol, atol, reference_pressure
   end type
 
   type, bind(c) :: clima_rt_profile_out
@@ -64,13 +64,13 @@ contains
   !> Packs what make_profile reads from the object and hands it to the device.  Call after any change of
   !> RH, P_top, T_trop, rtol, atol (the setters of clima/fortran/AdiabatClimate.f90).
   subroutine adiabat_to_device(handle, sp, nz, double_radiative_grid, planet_mass, planet_radius, &
-                               P_top, T_trop, RH, rtol, atol, err)
+                               P_top, T_trop, RH, rtol, atol, reference_pressure, err)
     use clima_types, only: Species
     type(c_ptr), intent(in) :: handle
     type(Species), intent(in) :: sp
     integer, intent(in) :: nz
     logical, intent(in) :: double_radiative_grid
-    real(dp), intent(in) :: planet_mass, planet_radius, P_top, T_trop, RH(:), rtol, atol
+    real(dp), intent(in) :: planet_mass, planet_radius, P_top, T_trop, RH(:), rtol, atol, reference_pressure
     character(:), allocatable, intent(out) :: err
 
     type(clima_rt_adiabat) :: a
@@ -111,7 +111,7 @@ contains
     a%thermo_temps = c_loc(temps); a%thermo_data = c_loc(coef); a%has_sat = c_loc(has_sat)
     a%sat = c_loc(sat); a%RH = c_loc(RH_c)
     a%planet_mass = planet_mass; a%planet_radius = planet_radius
-    a%P_top = P_top; a%T_trop = T_trop; a%rtol = rtol; a%atol = atol
+    a%P_top = P_top; a%T_trop = T_trop; a%rtol = rtol; a%atol = atol; a%reference_pressure = reference_pressure
     call clima_rt_adiabat_set(handle, a, err_c)
     call err_from_c(err_c, err)
   end subroutine
@@ -136,8 +136,8 @@ end module
 !> To be added to src/adiabat/clima_adiabat.f90 (`procedure :: TOA_fluxes_batch_device => ...`): the loop
 !>   do i = 1,ncol;  call c%TOA_fluxes(T_surf(i), P_i_surf(:,i), ISR(i), OLR(i), err);  enddo
 !> of a sweep (examples/EarlyMars.ipynb, cell 7) as ONE device call.  Not supported here, as in
-!> include/clima_rt.h: ocean solubility functions, reference_pressure > 0, a T_surf-dependent albedo (the host-profile
-!> variant in fortran/clima_batch_wrappers.f90 covers the first two).  Particle profiles: forward the arguments of
+!> include/clima_rt.h: ocean solubility functions (they only fill N_ocean, which this entry does not return; the
+!> host-profile variant in fortran/clima_batch_wrappers.f90 keeps them) and a T_surf-dependent albedo.  Particle profiles: forward the arguments of
 !> AdiabatClimate_set_particle_density_and_radii to clima_rt_adiabat_set_particles (same argument list + handle); objects
 !> with particles are refused below until that forwarding is added.
 subroutine AdiabatClimate_TOA_fluxes_batch_device(self, T_surf, P_i_surf, ISR, OLR, err)
@@ -160,8 +160,8 @@ subroutine AdiabatClimate_TOA_fluxes_batch_device(self, T_surf, P_i_surf, ISR, O
     err = '"T_surf" and "P_i_surf" have inconsistent dimensions'
     return
   endif
-  if (associated(self%albedo_fcn) .or. self%reference_pressure > 0.0_dp .or. self%sp%np > 0) then
-    err = 'TOA_fluxes_batch_device: albedo_fcn, reference_pressure and particles need the host-profile variant'
+  if (associated(self%albedo_fcn) .or. self%sp%np > 0) then
+    err = 'TOA_fluxes_batch_device: albedo_fcn and particles need the host-profile variant'
     return
   endif
   do i = 1,self%sp%ng
@@ -171,7 +171,8 @@ subroutine AdiabatClimate_TOA_fluxes_batch_device(self, T_surf, P_i_surf, ISR, O
     endif
   enddo
   call adiabat_to_device(self%rad%cuda%handle, self%sp, self%nz, self%double_radiative_grid, self%planet_mass, &
-                         self%planet_radius, self%P_top, self%T_trop, self%RH, self%rtol, self%atol, err)
+                         self%planet_radius, self%P_top, self%T_trop, self%RH, self%rtol, self%atol, &
+                         self%reference_pressure, err)
   if (allocated(err)) return
   allocate(fup_ir(self%nz_r+1,ncol), fdn_ir(self%nz_r+1,ncol), fup_sol(self%nz_r+1,ncol), fdn_sol(self%nz_r+1,ncol))
   allocate(f_total(self%nz_r+1,ncol))

@@ -265,7 +265,8 @@ void clima_rt_jacobian_batch(void *handle, const int32_t *ncol, const int32_t *n
    tables (mass, heat-capacity polynomial, optional LinearLatentHeat saturation data:
    src/clima_types.f90 `Gas`, src/clima_saturationdata.f90:16-28), RH, P_top, T_trop, the planet,
    rtol / atol and the number of model layers.  Not carried: ocean solubility functions (host
-   callbacks; N_ocean is zero without them), reference_pressure > 0, CustomDrySpecies.  Particle profiles:
+   callbacks that only fill N_ocean: the caller runs them on N_surface and f_i_surf * P_surf, as
+   clima_b200/adiabat.py does), CustomDrySpecies.  Particle profiles:
    clima_rt_adiabat_set_particles below. */
 #define CLIMA_RT_ADIABAT_MAX_GASES 16
 #define CLIMA_RT_ADIABAT_MAX_TEMPS 4
@@ -285,6 +286,8 @@ typedef struct clima_rt_adiabat {
   double P_top;                  /* dynes/cm^2, default 1 */
   double T_trop;                 /* K, default 180 */
   double rtol, atol;             /* defaults 1e-9, 1e-12 (clima_adiabat.f90:133-135) */
+  double reference_pressure;     /* dynes/cm^2; <= 0 (default -1): the planet radius is at the surface, else at this
+                                    pressure (clima_adiabat.f90:58-64, clima_adiabat_altitude.f90:97-169) */
 } clima_rt_adiabat;
 
 /* What make_profile leaves in the object, per column (HOST pointers; any may be NULL): */
@@ -313,6 +316,7 @@ typedef struct clima_rt_profile_out {
 #define CLIMA_RT_PROFILE_ALTITUDE_FAILED 8     /* clima_adiabat_altitude.f90:215-220 */
 #define CLIMA_RT_PROFILE_PRESSURE_GRID 9       /* clima_adiabat_altitude.f90:52-55 */
 #define CLIMA_RT_PROFILE_NEGATIVE_TTROP 10     /* clima_adiabat_general.f90:136-139 */
+#define CLIMA_RT_PROFILE_REFERENCE_PRESSURE 11 /* clima_adiabat_altitude.f90:97-105 */
 
 /* Give the handle the adiabat description (copied to the device; call again after changing RH, T_trop, ...:
    the setters of clima/fortran/AdiabatClimate.f90). */

@@ -413,9 +413,8 @@ def altitude_vs_P(P, T, mubar, P0, z0, planet_mass, planet_radius):             
 
 def make_profile(T_surf: float, P_i_surf: Sequence[float], sp: Dict, nz: int, planet_mass: float,
                  planet_radius: float, P_top: float, T_trop: float, RH: Sequence[float],
-                 rtol: float = 1.0e-9, atol: float = 1.0e-12) -> Dict:
-    """-> dict(P, z, T (2 nz + 1), f_i (2 nz + 1, ng), P_trop, N_surface (ng), nfcn).  No ocean functions
-    (host callbacks of the reference; N_ocean is zero without them)."""
+                 rtol: float = 1.0e-9, atol: float = 1.0e-12, ocean_fcns: Optional[Sequence] = None) -> Dict:
+    """-> dict(P, z, T (2 nz + 1), f_i (2 nz + 1, ng), P_trop, N_surface (ng), N_ocean (ng, ng), nfcn)."""
     P_i_surf = np.asarray(P_i_surf, dtype=np.float64)
     ng = len(sp["mass"])
     if T_surf < T_trop:
@@ -439,6 +438,14 @@ def make_profile(T_surf: float, P_i_surf: Sequence[float], sp: Dict, nz: int, pl
         else:
             P_i_cur[i] = P_i_surf[i]
             d.sp_type[i] = DRY
+    # gases dissolved in oceans (:226-246): ocean_fcns[j](T_surf, ng, P_i [bar]) -> mol/kg of every gas in ocean j
+    N_ocean = np.zeros((ng, ng))
+    for j in range(ng):
+        if ocean_fcns is not None and ocean_fcns[j] is not None:
+            m_i = np.asarray(ocean_fcns[j](T_surf, ng, P_i_cur / 1.0e6), dtype=np.float64)
+            for i in range(ng):
+                if i != j:
+                    N_ocean[i, j] = m_i[i] * N_surface[j] * (sp["mass"][j] / 1.0e3)
     P_surf = 0.0
     for i in range(ng):
         P_surf += P_i_cur[i]
@@ -481,7 +488,7 @@ def make_profile(T_surf: float, P_i_surf: Sequence[float], sp: Dict, nz: int, pl
     if np.any(d.z[:ne - 1] < 0.0):
         raise AdiabatError('"make_profile" yielded negative altitudes. This may be caused by the lack of a '
                            'hydrostatic solution to the entered atmosphere.')
-    return dict(P=d.P, z=d.z, T=d.T, f_i=d.f_i, P_trop=d.P_trop, N_surface=N_surface, nfcn=d.nfcn,
+    return dict(P=d.P, z=d.z, T=d.T, f_i=d.f_i, P_trop=d.P_trop, N_surface=N_surface, N_ocean=N_ocean, nfcn=d.nfcn,
                 sp_type=d.sp_type.copy())
 
 
@@ -531,8 +538,11 @@ def solve_ivp_dop853(rhs: Callable, x_start: float, y_start: Sequence[float], x_
     return y_eval
 
 
-def compute_altitude(P_surf, T_surf, f_i_surf, P, T, f_i, mass, P_top, planet_mass, planet_radius, rtol, atol):
-    """-> (z (nz), dz (nz)) for reference_pressure <= 0 (the default, clima_adiabat.f90:64)."""
+def compute_altitude(P_surf, T_surf, f_i_surf, P, T, f_i, mass, P_top, planet_mass, planet_radius, rtol, atol,
+                     reference_pressure=-1.0):
+    """-> (z (nz), dz (nz)).  reference_pressure <= 0 (the default, clima_adiabat.f90:64): the planet radius is at the
+    surface and z is integrated upward from it.  reference_pressure > 0 (:97-169): the radius is at that pressure,
+    z is integrated from there upward and downward, then shifted so that it is again zero at the surface."""
     nz = P.shape[0]
     if nz < 2:
         raise AdiabatError("compute_altitude requires nz >= 2")
@@ -560,15 +570,35 @@ def compute_altitude(P_surf, T_surf, f_i_surf, P, T, f_i, mass, P_top, planet_ma
         grav = gravity(planet_radius, planet_mass, float(u[0]))
         return np.array([-(RGAS * Tq) / (grav * Pq * mq)])
     z_e = np.zeros(2 * nz + 1)
-    z_e[1:2 * nz] = solve_ivp_dop853(rhs, P_e[0], [0.0], P_e[1:2 * nz], rtol, atol)[0]
-    z_e[2 * nz] = z_e[2 * nz - 1] + (z_e[2 * nz - 1] - z_e[2 * nz - 2])
+    if reference_pressure <= 0.0:
+        z_e[1:2 * nz] = solve_ivp_dop853(rhs, P_e[0], [0.0], P_e[1:2 * nz], rtol, atol)[0]
+        z_e[2 * nz] = z_e[2 * nz - 1] + (z_e[2 * nz - 1] - z_e[2 * nz - 2])
+    else:
+        Pr = reference_pressure
+        if Pr < P_top or Pr > P_surf:
+            raise AdiabatError("compute_altitude: reference_pressure=%11.4E outside model domain [%11.4E, %11.4E]"
+                               % (Pr, P_top, P_surf))
+        ne = 2 * nz + 1
+        k = next(kk for kk in range(ne - 1) if P_e[kk] >= Pr >= P_e[kk + 1])   # 0-based bracket [k, k + 1]
+        if Pr == P_e[k]:
+            top, bot = k + 1, k - 1
+        elif Pr == P_e[k + 1]:
+            top, bot = k + 2, k
+        else:
+            top, bot = k + 1, k
+        if top <= ne - 2:   # upward, to the last edge but one
+            z_e[top:ne - 1] = solve_ivp_dop853(rhs, Pr, [0.0], P_e[top:ne - 1], rtol, atol)[0]
+        if bot >= 0:        # downward, to the surface
+            z_e[bot::-1] = solve_ivp_dop853(rhs, Pr, [0.0], P_e[bot::-1], rtol, atol)[0]
+        z_e[:ne - 1] -= z_e[0]
+        z_e[ne - 1] = z_e[ne - 2] + (z_e[ne - 2] - z_e[ne - 3])
     z = z_e[1:2 * nz:2].copy()
     dz = z_e[2:2 * nz + 1:2] - z_e[0:2 * nz - 1:2]
     return z, dz
 
 
 def adiabat_column(T_surf, P_i_surf, sp, nz, planet_mass, planet_radius, P_top=1.0, T_trop=180.0, RH=None,
-                   rtol=1.0e-9, atol=1.0e-12) -> Dict:
+                   rtol=1.0e-9, atol=1.0e-12, reference_pressure=-1.0) -> Dict:
     """What `AdiabatClimate%make_profile` leaves in the object: P, T (nz), f_i, densities (nz, ng), z, dz,
     P_surf, P_trop, N_surface, N_atmos -- the model-grid column that copy_atm_to_radiative_grid doubles."""
     ng = len(sp["mass"])
@@ -578,7 +608,7 @@ def adiabat_column(T_surf, P_i_surf, sp, nz, planet_mass, planet_radius, P_top=1
     T = e["T"][1:2 * nz:2].copy()
     f_i = e["f_i"][1:2 * nz:2].copy()
     z, dz = compute_altitude(e["P"][0], T_surf, e["f_i"][0], P, T, f_i, sp["mass"], P_top, planet_mass,
-                             planet_radius, rtol, atol)
+                             planet_radius, rtol, atol, reference_pressure)
     density = P / (K_BOLTZ * T)
     densities = f_i * density[:, None]
     N_atmos = np.array([np.sum(density * f_i[:, i] * dz) / N_AVO for i in range(ng)])

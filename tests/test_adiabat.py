@@ -270,7 +270,7 @@ def gpu_model(nz=24, **kw):
 
 def oracle_column(ac, T, Pi):
     return A.adiabat_column(T, Pi, ac.sp, ac.nz, ac.planet_mass, ac.planet_radius, ac.P_top, ac.T_trop, ac.RH,
-                            ac.rtol, ac.atol)
+                            ac.rtol, ac.atol, ac.reference_pressure)
 
 
 # What two builds of this algorithm can agree on.  At the reference's default tolerances (rtol 1e-9, atol 1e-12 on
@@ -521,6 +521,70 @@ def test_adiabat_toa_fluxes_with_particles(mode, monkeypatch):
         ac.set_particle_density_and_radii(Pset, pdens, -prad)
     with pytest.raises(ClimaException, match="does not match the number of particles"):
         ac.set_particle_density_and_radii(Pset, pdens[:, :1], prad[:, :1])
+
+
+def test_reference_pressure_oracle():
+    """reference_pressure at the surface pressure is the default case bit for bit; higher up the radius of the planet is
+    reached at lower pressure, gravity below it is stronger and the column is thinner."""
+    sp = species()
+    a = A.adiabat_column(300.0, P_I_OCEAN, sp, 20, EARTH_MASS, EARTH_RADIUS, T_trop=200.0)
+    b = A.adiabat_column(300.0, P_I_OCEAN, sp, 20, EARTH_MASS, EARTH_RADIUS, T_trop=200.0, reference_pressure=a["P_surf"])
+    assert np.array_equal(a["z"], b["z"]) and np.array_equal(a["dz"], b["dz"])
+    c = A.adiabat_column(300.0, P_I_OCEAN, sp, 20, EARTH_MASS, EARTH_RADIUS, T_trop=200.0, reference_pressure=50.0)
+    assert np.all(c["z"] < a["z"]) and 0.97 < c["z"][-1] / a["z"][-1] < 0.99 and np.array_equal(c["T"], a["T"])
+    with pytest.raises(A.AdiabatError, match="outside model domain"):
+        A.adiabat_column(300.0, P_I_OCEAN, sp, 20, EARTH_MASS, EARTH_RADIUS, T_trop=200.0, reference_pressure=0.5)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["group", "thread"])
+def test_reference_pressure_on_the_device(mode, monkeypatch):
+    """compute_altitude with reference_pressure > 0 (clima_adiabat_altitude.f90:97-169): between two edges, exactly on a
+    layer centre of one column (the is_on_k / is_on_kp1 branches), at the top; outside the domain = status 11."""
+    from clima_b200.radtran import ClimaException
+    monkeypatch.setenv("CLIMA_RT_ADIABAT", mode)
+    _, _, ac = gpu_model(nz=16)
+    ac.T_trop, ac.rtol = 170.0, 1e-12
+    T, P = sweep(5, seed=17)
+    base = ac.make_profile_batch(T, P)
+    for Pr in (1.0e3, float(base["P"][5, 2]), 1.0):
+        ac.reference_pressure = Pr
+        p = ac.make_profile_batch(T, P)
+        for c in range(5):
+            same_profile(p, c, oracle_column(ac, T[c], P[:, c]), tol=TIGHT_TOL)
+        assert np.all(p["z"] < base["z"]) and np.array_equal(p["T"], base["T"])
+    ac.reference_pressure = 1.0e9
+    q = ac.make_profile_batch(T, P, check=False)
+    assert np.all(q["status"] == 11)
+    with pytest.raises(ClimaException, match="reference_pressure outside model domain"):
+        ac.TOA_fluxes_batch(T, P)
+
+
+@pytest.mark.gpu
+def test_ocean_solubility_functions_fill_N_ocean():
+    """N_ocean (clima_adiabat_general.f90:226-246) from host callbacks after the device call, against the oracle; a
+    Henry's-law style function as in the reference's tutorial (cells 50-52)."""
+    _, _, ac = gpu_model(nz=10)
+
+    def henry(T_surf, ng, P_i):
+        k = np.array([0.0, 3.4e-2, 6.1e-4, 7.8e-4, 1.4e-3, 9.5e-4, 1.3e-3]) * np.exp(-(T_surf - 298.0) / 50.0)
+        return k * P_i
+    ac.set_ocean_solubility_fcn("H2O", henry)
+    T, P = sweep(6, seed=13)
+    p = ac.make_profile_batch(T, P)
+    assert p["N_ocean"].shape == (7, 7, 6) and (p["N_ocean"][:, 0, :] > 0).any()
+    for c in range(6):
+        e = A.make_profile(T[c], P[:, c], ac.sp, ac.nz, ac.planet_mass, ac.planet_radius, ac.P_top, ac.T_trop, ac.RH,
+                           ocean_fcns=[henry] + [None] * 6)
+        assert np.allclose(p["N_ocean"][:, :, c], e["N_ocean"], rtol=1e-12, atol=0.0)
+        assert p["N_ocean"][0, 0, c] == 0.0 and not p["N_ocean"][:, 1:, c].any()
+    ac.make_profile(T[0], P[:, 0])
+    assert np.array_equal(ac.N_ocean, p["N_ocean"][:, :, 0])
+    ac.set_ocean_solubility_fcn("H2O", None)
+    assert not ac.make_profile_batch(T, P)["N_ocean"].any()
+    from clima_b200.radtran import ClimaException
+    with pytest.raises(ClimaException, match="not in the list of species"):
+        ac.set_ocean_solubility_fcn("Xe", henry)
 
 
 @pytest.mark.gpu
