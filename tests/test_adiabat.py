@@ -284,7 +284,13 @@ def oracle_column(ac, T, Pi):
 # perturbation of T_surf moves the oracle's own altitude error between 1e-9 and 2e-6).  So: at the default settings
 # device and oracle must agree within that band (test_make_profile_batch_matches_the_oracle also measures both
 # against the converged solution), and within 1e-9 on T and the mixing ratios / 5e-7 on the altitudes at rtol 1e-12.
-PROFILE_TOL = dict(T=1e-6, z=1e-5, dz=1e-4, f=1e-6)
+# Full-size finding (4096 columns, test_full_size_sweep_properties_of_make_profile): 1.7 % of the columns differ between
+# two builds by more than 1e-4 in dz, up to 8e-4, always at the layers around the TROPOPAUSE, where T(log10 P) of the
+# altitude integration has its sharpest kink; the oracle does exactly the same under a 1e-13 perturbation of T_surf
+# (column 3672 of that sweep: dz error against the converged solution between 1.8e-6 and 8.0e-4 over 60 perturbations,
+# median 8.5e-6, experiments/adiabat_noise.py).  It is a property of the reference's algorithm at its default
+# tolerances, not of a build, hence the dz bound below.
+PROFILE_TOL = dict(T=1e-6, z=2e-5, dz=2e-3, f=1e-6)
 TIGHT_TOL = dict(T=1e-9, z=5e-7, dz=5e-7, f=1e-9)
 
 
@@ -324,7 +330,7 @@ def test_make_profile_batch_matches_the_oracle():
     # altitudes within the band that a 1e-13 perturbation of the input moves the oracle itself through
     # (experiments/adiabat_noise.py: 1e-9 ... 2e-6 on z)
     assert e_dev["T"] < 5.0 * e_ora["T"] + 1e-9, (e_dev, e_ora)
-    assert e_dev["z"] < 1e-5 and e_dev["dz"] < 1e-4, (e_dev, e_ora)
+    assert e_dev["z"] < PROFILE_TOL["z"] and e_dev["dz"] < PROFILE_TOL["dz"], (e_dev, e_ora)
     assert (p["P_trop"] > 0).any()
 
 
@@ -585,6 +591,52 @@ def test_ocean_solubility_functions_fill_N_ocean():
     from clima_b200.radtran import ClimaException
     with pytest.raises(ClimaException, match="not in the list of species"):
         ac.set_ocean_solubility_fcn("Xe", henry)
+
+
+@pytest.mark.gpu
+def test_full_size_sweep_properties_of_make_profile():
+    """BASELINE's sweep size (4096 columns, nz = 50), where the oracle is too slow to be the checker: size-independent
+    properties of every column, both kernels on the same batch, a subset bit-identical to the batch, 8 columns against
+    the oracle."""
+    _, _, ac = gpu_model(nz=50)
+    n = 4096
+    T, P = sweep(n, seed=31)
+    p = ac.make_profile_batch(T, P)                      # one lane per gas at this size
+    assert not p["status"].any() and np.all(np.isfinite(p["T"])) and np.all(np.isfinite(p["dz"]))
+    assert np.max(np.abs(p["f_i"].sum(axis=1) - 1.0)) < 1e-12            # mixing ratios sum to one
+    assert np.all(np.diff(p["z"], axis=0) > 0.0) and np.all(p["dz"] > 0.0)
+    assert np.all(np.diff(p["P"], axis=0) < 0.0) and np.all(p["P"][0] < p["P_surf"][None, :])
+    assert np.all(p["T"] >= ac.T_trop) and np.all(np.diff(p["T"], axis=0) <= 1e-9)  # cooling upward, then isothermal
+    strat = p["P"] < p["P_trop"][None, :]
+    assert np.all(p["T"][strat] == ac.T_trop) and (p["P_trop"] > 0).sum() > n // 2
+    # hydrostatic consistency: the column mass above the surface from densities * dz against P_surf / g
+    mass = np.array(ac.sp["mass"])
+    col_mass = np.einsum("zgc,g,zc->c", p["densities"], mass, p["dz"]) / 6.02214076e23
+    g0 = A.gravity(EARTH_RADIUS, EARTH_MASS, 0.0)
+    assert np.all(np.abs(col_mass * g0 / (p["P_surf"] - ac.P_top) - 1.0) < 0.03)   # layer-mean discretisation, g(z)
+    # a water-saturated column stays on the saturation curve
+    wet = np.where(p["N_surface"][0] > 0)[0][:50]
+    for c in wet:
+        k = int(np.argmax(~(p["P"][:, c] > p["P_trop"][c]))) or 50
+        f_sat = np.array([A.sat_pressure(ac.sp["sat"][0], t) for t in p["T"][:k, c]]) / p["P"][:k, c]
+        assert np.max(np.abs(p["f_i"][:k, 0, c] / np.minimum(f_sat, 1.0) - 1.0)) < 1e-12
+    sub = np.arange(0, n, 97)
+    q = ac.make_profile_batch(T[sub], np.asfortranarray(P[:, sub]))
+    for k in ("T", "z", "dz", "f_i", "P_trop"):
+        assert np.array_equal(q[k], p[k][..., sub]), k
+    os.environ["CLIMA_RT_ADIABAT"] = "thread"
+    try:
+        r = ac.make_profile_batch(T, P)
+    finally:
+        del os.environ["CLIMA_RT_ADIABAT"]
+    assert np.max(np.abs(r["T"] / p["T"] - 1.0)) < PROFILE_TOL["T"]
+    ddz = np.max(np.abs(r["dz"] / p["dz"] - 1.0), axis=0)       # per column: see the note at PROFILE_TOL
+    assert ddz.max() < PROFILE_TOL["dz"] and np.median(ddz) < 1e-5 and (ddz > 1e-4).mean() < 0.05
+    worst = int(np.argmax(ddz))
+    k = int(np.argmax(np.abs(r["dz"][:, worst] / p["dz"][:, worst] - 1.0)))
+    assert abs(np.log(p["P"][k, worst] / p["P_trop"][worst])) < 1.0      # ... and it sits at the tropopause
+    for c in range(0, n, 512):
+        same_profile(p, c, oracle_column(ac, T[c], P[:, c]))
 
 
 @pytest.mark.gpu
