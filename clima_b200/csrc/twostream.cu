@@ -37,9 +37,11 @@ constexpr int TS_THREADS = 128;
 #define TS_SOL_BLOCKS 3
 #endif
 // forward-sweep unroll (register renaming instead of the moves that rotate the layer state).
-// Measured r1r per 1024 columns: IR 4.08 (1) / 4.17 (2) ms; solar 5.64 (1) / 5.42 (2) / 5.67 (3) ms
+// Measured r1r per 1024 columns: IR 4.08 (1) / 4.17 (2) ms; solar 5.64 (1) / 5.42 (2) / 5.67 (3) ms.  Re-measured r2f
+// on the r1s kernels, per 4096 columns: IR 14.46 (1) / 13.63 (2) / 13.69 (3) / 13.66 (4) ms; solar 20.74 (1) / 19.57 (2) /
+// 20.01 (3) / 20.70 (4) ms
 #ifndef TS_FWD_UNROLL_IR
-#define TS_FWD_UNROLL_IR 1
+#define TS_FWD_UNROLL_IR 2
 #endif
 #ifndef TS_FWD_UNROLL_SOL
 #define TS_FWD_UNROLL_SOL 2
