@@ -53,7 +53,8 @@
 #define CUT_UNIT_PAD 0
 #endif
 #ifndef CUT_ROW_UNROLL
-#define CUT_ROW_UNROLL 1  // count words (4 rows) per trip of the pass loop: fully unrolled it needs 168 registers
+#define CUT_ROW_UNROLL 2  // count words (4 rows) per trip of the pass loop: fully unrolled it needs 168 registers.  r2g, 4096 cfg2
+                          // columns: 1 -> 85.1 ms, 2 -> 83.2 ms (150 bytes of spills at 80 registers), 4 -> 95-140 ms at 3-5 blocks per SM
 #endif
 
 namespace rorr_cut {
