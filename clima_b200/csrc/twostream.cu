@@ -83,8 +83,10 @@ constexpr int SOL_GITEMS = TS_SOL_PRESUM == 2 ? 4 : 1;  // group slots: (Au, Ad,
 
 // forward sweep: tau/w0 lines this many layers ahead into L2 (0 = off).  Measured r1q per 1024 columns:
 // IR 5.16 (0) / 5.21 (6) ms; solar 6.94 (0) / 6.75 (6) / 6.93 (12) ms
+// Re-measured r2g (IR forward sweep unrolled by 2), per 4096 columns: IR 13.71 (0) / 13.19 (2) / 13.19 (4) / 13.37 (6-8) /
+// 13.65 (12) ms; solar 21.42 (0) / 19.6 (6) / 20.82 (12) ms
 #ifndef TS_FWD_L2_PREFETCH_IR
-#define TS_FWD_L2_PREFETCH_IR 0
+#define TS_FWD_L2_PREFETCH_IR 4
 #endif
 #ifndef TS_FWD_L2_PREFETCH_SOL
 #define TS_FWD_L2_PREFETCH_SOL 6
