@@ -358,7 +358,7 @@ void ensure_chunk(Handle &h, int ncol, int nz) {
   ch.tband = calloc_dev<double>(h, (size_t)C * tb.nw * nz);
   ch.cont = calloc_dev<double>(h, (size_t)3 * C * tb.nw * nz);
   ch.status = calloc_dev<int>(h, C);
-  ch.dissim = calloc_dev<int>(h, 1);
+  ch.dissim = calloc_dev<int>(h, 2);
   ch.cut_stats = calloc_dev<unsigned long long>(h, 8);
   h.cut_prev[0] = h.cut_prev[1] = 0;  // the counters restart with the buffers
   h.cut_pending = false;
@@ -461,9 +461,9 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     h.launches += 2;  // prep + similarity
     // tight slot capacity: max number of unique layers over the chunk
     std::vector<int> ns(ncol);
-    int dissim = 0;
+    int dissim[2] = {0, 0};
     CK(cudaMemcpyAsync(ns.data(), ch.nslots, ncol * sizeof(int), cudaMemcpyDeviceToHost, h.st));
-    CK(cudaMemcpyAsync(&dissim, ch.dissim, sizeof(int), cudaMemcpyDeviceToHost, h.st));
+    CK(cudaMemcpyAsync(dissim, ch.dissim, 2 * sizeof(int), cudaMemcpyDeviceToHost, h.st));
     CK(cudaStreamSynchronize(h.st));
     ch.nslot_cap = *std::max_element(ns.begin(), ns.end());
     record(h, 5);
@@ -471,7 +471,8 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     // RORR unit order of this chunk (rorr_impl.cuh): 4 adjacent columns per warp when the columns of
     // a group are alike, 4 adjacent slots of one column otherwise; CLIMA_RT_RORR_GROUP forces either
     DevTables tbc = h.tb;
-    if (!(tbc.pad0 & (4 | 8)) && (long long)dissim * 64 > (long long)ncol) tbc.pad0 |= 4;
+    if (!(tbc.pad0 & (4 | 8)) && (long long)dissim[0] * 64 > (long long)ncol) tbc.pad0 |= 4;
+    const bool neighbours_far = (long long)dissim[1] * 64 > (long long)ncol;  // > 1/16 of the groups
     h.last_unit_order = (tbc.pad0 & 4) ? 1 : 0;
     // Which RORR kernel.  The sort-free staircase kernel (optics_rorr_cut.cu) carries its staircases
     // along chains of consecutive COLUMNS and needs ~1.15 passes per merge when neighbouring columns
@@ -479,7 +480,10 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     // at 2048 / 1024 / 512 / 256 columns over 200 K: 22.5 / 23.9 / 28.2 / 37.1 us per column against
     // 34 us sorted).  Unlike neighbours (randomised composition, cfg3's shuffled pCO2) keep the sorting
     // kernels: chains over the layer slots of a column need 2.3-2.5 passes per merge (cfg5: 48 vs 36 us).
-    // similarity_kernel's verdict (pad0 bit 2 = unlike) decides; CLIMA_RT_RORR_CHAIN forces a direction.
+    // similarity_kernel's second verdict (neighbouring columns within 25 % in their k-gas amounts) says whether the
+    // staircase kernel is tried at all; CLIMA_RT_RORR_CHAIN forces a direction.  (Until r2g the 10 % verdict of the
+    // unit order decided: a 512-column sweep over 200 K was sent to the sorting kernels, 17.7 ms, although the
+    // staircase kernel needs 1.33 passes per merge on it, 14.1 ms.)
     // The verdict is checked against what the kernel then reports: if the previous staircase chunk
     // needed more than 1.5 passes per merge (alike by column amounts, yet staircases that do not carry
     // over), the next 8 chunks take the sorting kernels before the staircase kernel is tried again.
@@ -495,7 +499,7 @@ void run_chunk(Handle &h, int ncol, int nz, bool compute_solar, bool compute_opa
     int cut_chain = -1;
     if (!exact && !h.rorr_sort && h.tb.rows_sorted) {
       if (h.rorr_chain_env >= 0) cut_chain = h.rorr_chain_env;
-      else if (!(tbc.pad0 & 4) && ncol >= h.rorr_cut_mincols) {
+      else if (!neighbours_far && ncol >= h.rorr_cut_mincols) {
         if (h.cut_backoff > 0) h.cut_backoff--;
         else cut_chain = 1;
       }

@@ -134,32 +134,38 @@ __global__ void prep_kernel(const DevTables tb, const DevChunk ch) {
 }
 
 // Are the 4 adjacent columns that share a RORR warp alike?  Thread per group of 4 columns: the
-// k-gas column amounts of the ground layer and of the middle layer must agree within 10 %.
+// k-gas column amounts of the ground layer and of the middle layer must agree within 10 % over the group
+// (dissim[0]: unit order of the sorting kernels) and within 25 % between NEIGHBOURS, the first column of the
+// next group included (dissim[1]: is the staircase kernel worth a try; what it then reports decides, capi.cu).
 __global__ void similarity_kernel(const DevTables tb, const DevChunk ch) {
   const int g4 = blockIdx.x * blockDim.x + threadIdx.x;
   const int c0 = g4 * 4;
   if (c0 >= ch.ncol) return;
   const int nz = ch.nz, ng = tb.ng;
-  bool alike = true;
+  bool alike = true, near = true;
   for (int jj = 0; jj < tb.nk; jj++) {
     const int sp = tb.k[jj].sp - 1;
     for (int kk = 0; kk < 2; kk++) {
       const int k = kk ? nz / 2 : 0;
-      double lo = 0.0, hi = 0.0;
-      for (int c = c0; c < c0 + 4 && c < ch.ncol; c++) {
+      double lo = 0.0, hi = 0.0, prev = 0.0;
+      for (int c = c0; c < c0 + 5 && c < ch.ncol; c++) {
         const double v = ch.dens[(size_t)c * nz * ng + k + (size_t)sp * nz] * ch.dz[(size_t)c * nz + k];
+        if (c > c0 && !(fmax(v, prev) <= 1.25 * fmin(v, prev))) near = false;
+        prev = v;
+        if (c == c0 + 4) break;
         if (c == c0) { lo = hi = v; } else { lo = fmin(lo, v); hi = fmax(hi, v); }
       }
       if (!(hi <= 1.1 * lo)) alike = false;
     }
   }
   if (!alike) atomicAdd(ch.dissim, 1);
+  if (!near) atomicAdd(ch.dissim + 1, 1);
 }
 
 }  // namespace
 
 void rt_launch_similarity(const DevTables &tb, const DevChunk &ch, cudaStream_t st) {
-  cudaMemsetAsync(ch.dissim, 0, sizeof(int), st);
+  cudaMemsetAsync(ch.dissim, 0, 2 * sizeof(int), st);
   const int groups = (ch.ncol + 3) / 4;
   similarity_kernel<<<(groups + 127) / 128, 128, 0, st>>>(tb, ch);
 }

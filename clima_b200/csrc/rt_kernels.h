@@ -20,7 +20,8 @@ struct DevFlux {
 
 // prep.cu
 void rt_launch_prep(const DevTables &tb, const DevChunk &ch, cudaStream_t st);
-// counts the groups of 4 adjacent columns with unlike k-gas amounts into ch.dissim (RORR unit order)
+// counts the groups of 4 adjacent columns with unlike k-gas amounts into ch.dissim[0] (RORR unit order) and those
+// with neighbours more than 25 % apart into ch.dissim[1] (staircase kernel or not)
 void rt_launch_similarity(const DevTables &tb, const DevChunk &ch, cudaStream_t st);
 // optics_rorr.cu
 void rt_launch_optics_rorr(const DevTables &tb, const DevChunk &ch, int *worklist, int *wcount,
