@@ -12,6 +12,8 @@ from __future__ import annotations
 
 from typing import Callable, Dict, Sequence, Tuple
 
+import math
+
 import numpy as np
 
 from .radtran import ClimaException, Radtran
@@ -351,6 +353,143 @@ class AdiabatClimate:
         self.rad._lib.clima_rt_adiabat_set_particles(self.rad._h, _i(P.shape[0]), P.ctypes.data_as(c_double_p),
                                                      pd.ctypes.data_as(c_double_p), pr.ctypes.data_as(c_double_p), err)
         _check(err)
+
+    # ---- the two other column builders of the reference as lock-step Newton iterations over the whole batch: every
+    # iteration evaluates the residuals of all columns and of all their finite-difference perturbations in ONE
+    # make_profile_batch call (the reference runs MINPACK hybrd1 per column, 20-40 make_profile calls each)
+    @staticmethod
+    def _newton_batch(X0, resid, tol, max_iter=60, h=1.0e-5):
+        """Solves F(X[:, c]) = 0 for every column c of X0 (n, ncol), X = log10 of the unknown pressures.
+        `resid(idx, X) -> (F (n, m), ok (m))` evaluates m trial columns, idx[j] = the column X[:, j] belongs to.
+        Damped Newton with forward differences; converged like hybrd1 (relative change of X below tol) or |F| < tol."""
+        n, ncol = X0.shape
+        X = X0.copy()
+        allc = np.arange(ncol)
+        F, ok = resid(allc, X)
+        done, failed = np.zeros(ncol, bool), ~ok
+        for _ in range(max_iter):
+            act = np.where(~done & ~failed)[0]
+            if act.size == 0:
+                break
+            m = act.size
+            Xp = np.repeat(X[:, act], n, axis=1)                      # block q holds the n perturbations of column act[q]
+            for k in range(n):
+                Xp[k, k::n] += h
+            Fp, okp = resid(np.repeat(act, n), Xp)
+            step = np.zeros((n, m))
+            live = np.ones(m, bool)
+            for q, c in enumerate(act):
+                J = (Fp[:, q * n:(q + 1) * n] - F[:, [c]]) / h        # J[i, k] = dF_i / dx_k
+                try:
+                    if not okp[q * n:(q + 1) * n].all() or not np.all(np.isfinite(J)):
+                        raise np.linalg.LinAlgError
+                    step[:, q] = np.linalg.solve(J, -F[:, c])
+                except np.linalg.LinAlgError:
+                    live[q] = False
+            step = np.clip(np.nan_to_num(step), -1.0, 1.0)            # at most a decade per iteration
+            lam = np.ones(m)
+            f0 = np.max(np.abs(F[:, act]), axis=0)
+            for _ls in range(10):                                      # halve the step until the residual drops
+                Xn = X[:, act] + lam[None, :] * step
+                Fn, okn = resid(act, Xn)
+                fn = np.max(np.abs(np.nan_to_num(Fn, nan=np.inf)), axis=0)
+                worse = live & (~okn | ~(fn < f0 + 10.0 * tol))
+                if not worse.any():
+                    break
+                lam[worse] *= 0.5
+            good = live & okn & (fn < f0 + 10.0 * tol)
+            idx = act[good]
+            dx = np.max(np.abs(lam[None, :] * step)[:, good] / np.maximum(np.abs(Xn[:, good]), 1.0), axis=0)
+            X[:, idx] = Xn[:, good]
+            F[:, idx] = Fn[:, good]
+            done[idx] = (dx < tol) | (fn[good] < tol)
+            failed[act[~good]] = True
+        return X, done
+
+    def make_column_batch(self, T_surf, N_i_surf, tol: float = 1.0e-8) -> Dict:
+        """`AdiabatClimate%make_column` (clima_adiabat.f90:476-574) for every (T_surf[c], N_i_surf[:, c]) [mol/cm^2]: the
+        surface pressures whose profile holds N_atmos + N_surface + sum(N_ocean) = N_i_surf.  Initial guesses as in the
+        reference (N m g times 1, 0.5, 2, 0.1, 5, 0.01, tried in turn for the columns that have not converged).
+        Returns the make_profile_batch dict of the solutions plus "P_i_surf" (ng, ncol)."""
+        T_surf = np.ascontiguousarray(T_surf, dtype=np.float64).reshape(-1)
+        N_t = np.asarray(N_i_surf, dtype=np.float64)
+        if N_t.ndim == 1:
+            N_t = N_t[:, None]
+        if N_t.shape != (self.ng, T_surf.shape[0]):
+            raise ClimaException("N_i_surf has the wrong dimension")
+        ncol = T_surf.shape[0]
+        grav = 6.67430e-11 * (self.planet_mass / 1.0e3) / (self.planet_radius / 1.0e2) ** 2.0 * 1.0e2
+        mass = np.asarray(self.sp["mass"], dtype=np.float64)
+        X = np.zeros((self.ng, ncol))
+        solved = np.zeros(ncol, bool)
+        tiny = math.sqrt(2.2250738585072014e-308)
+        for sf in (1.0, 0.5, 2.0, 0.1, 5.0, 0.01):
+            todo = np.where(~solved)[0]
+            if todo.size == 0:
+                break
+
+            def resid(idx, Xq, todo=todo):
+                cols = todo[idx]
+                with np.errstate(all="ignore"):
+                    p = self.make_profile_batch(T_surf[cols], np.asfortranarray(10.0 ** Xq), check=False)
+                    N = p["N_atmos"] + p["N_surface"] + p["N_ocean"].sum(axis=1)
+                    den = np.where(N_t[:, cols] > 0.0, N_t[:, cols], 1.0)   # a gas with no inventory: absolute residual
+                    return (N - N_t[:, cols]) / den, p["status"] == 0
+            X0 = np.log10(np.maximum(N_t[:, todo] * mass[:, None] * grav * sf, tiny))
+            Xs, done = self._newton_batch(X0, resid, tol)
+            X[:, todo[done]] = Xs[:, done]
+            solved[todo[done]] = True
+        if not solved.all():
+            raise ClimaException("column %d: hybrd1 root solve failed in make_column." % int(np.where(~solved)[0][0]))
+        P_i = np.asfortranarray(10.0 ** X)
+        p = self.make_profile_batch(T_surf, P_i)
+        p["P_i_surf"] = P_i
+        return p
+
+    def make_profile_bg_gas_batch(self, T_surf, P_i_surf, P_surf, bg_gas: str, tol: float = 1.0e-8) -> Dict:
+        """`AdiabatClimate%make_profile_bg_gas` (clima_adiabat.f90:579-650): the pressure of `bg_gas` is varied until the
+        surface pressure of the profile is P_surf (scalar or (ncol)); guesses P_surf times 1 and 0.1 as in the reference."""
+        T_surf, P_i = self._inputs(T_surf, P_i_surf)
+        ncol = T_surf.shape[0]
+        P_t = np.broadcast_to(np.asarray(P_surf, dtype=np.float64), (ncol,)).copy()
+        if np.any(P_t <= 0.0):
+            raise ClimaException("P_surf must be greater than zero.")
+        if bg_gas not in self.sp["names"]:
+            raise ClimaException('Gas "%s" is not in the list of species' % bg_gas)
+        ind = self.sp["names"].index(bg_gas)
+        X = np.zeros((1, ncol))
+        solved = np.zeros(ncol, bool)
+        for sf in (1.0, 0.1):
+            todo = np.where(~solved)[0]
+            if todo.size == 0:
+                break
+
+            def resid(idx, Xq, todo=todo):
+                cols = todo[idx]
+                Pq = np.asfortranarray(P_i[:, cols].copy())
+                Pq[ind] = 10.0 ** Xq[0]
+                with np.errstate(all="ignore"):
+                    p = self.make_profile_batch(T_surf[cols], Pq, check=False)
+                    return (p["P_surf"] / P_t[cols] - 1.0)[None, :], p["status"] == 0
+            Xs, done = self._newton_batch(np.log10(P_t[todo] * sf)[None, :], resid, tol)
+            X[:, todo[done]] = Xs[:, done]
+            solved[todo[done]] = True
+        if not solved.all():
+            raise ClimaException("column %d: hybrd1 root solve failed in make_profile_bg_gas." % int(np.where(~solved)[0][0]))
+        P_sol = np.asfortranarray(P_i.copy())
+        P_sol[ind] = 10.0 ** X[0]
+        p = self.make_profile_batch(T_surf, P_sol)
+        p["P_i_surf"] = P_sol
+        return p
+
+    def make_column(self, T_surf: float, N_i_surf):
+        """One column; leaves the reference's member names on the object (like make_profile)."""
+        p = self.make_column_batch([T_surf], np.asarray(N_i_surf, dtype=np.float64)[:, None])
+        self.make_profile(T_surf, p["P_i_surf"][:, 0])
+
+    def make_profile_bg_gas(self, T_surf: float, P_i_surf, P_surf: float, bg_gas: str):
+        p = self.make_profile_bg_gas_batch([T_surf], np.asarray(P_i_surf, dtype=np.float64)[:, None], P_surf, bg_gas)
+        self.make_profile(T_surf, p["P_i_surf"][:, 0])
 
     def kernel_ms(self) -> float:
         """Device time of the last make_profile kernel (CUDA events on the handle's stream)."""

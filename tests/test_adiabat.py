@@ -640,6 +640,60 @@ def test_full_size_sweep_properties_of_make_profile():
 
 
 @pytest.mark.gpu
+def test_make_column_and_bg_gas_batches():
+    """`make_column` / `make_profile_bg_gas` (clima_adiabat.f90:476-650) as lock-step Newton iterations over the batch:
+    the inventories / the surface pressure are met, one column agrees with MINPACK hybrd (scipy fsolve, the reference's
+    solver) run on the oracle, and the numbers the reference printed in its tutorial (cells 16-20) come out."""
+    from scipy.optimize import fsolve
+    _, _, ac = gpu_model(nz=12)
+    ac.T_trop = 200.0
+    rng = np.random.default_rng(5)
+    n = 7
+    T = rng.uniform(260.0, 330.0, n)
+    N_i = np.empty((7, n))
+    for c in range(n):
+        N_i[:, c] = np.array([15.0e3, 23.0, 36.0, 1e-10, 1e-10, 1e-10, 1e-10]) * rng.uniform(0.3, 3.0, 7)
+    N_i[0, 3] = 1.0e-3                                    # a column whose water does not condense at the surface
+    p = ac.make_column_batch(T, N_i)
+    tot = p["N_atmos"] + p["N_surface"] + p["N_ocean"].sum(axis=1)
+    assert np.max(np.abs(tot / N_i - 1.0)) < 1e-7 and p["N_surface"][0, 3] == 0.0 and (p["N_surface"][0] > 0).sum() == n - 1
+    # MINPACK hybrd (mode 2, unit scaling = hybrd1) on the oracle, same residual as the reference's fcn
+    c = 1
+    grav = A.gravity(EARTH_RADIUS, EARTH_MASS, 0.0)
+
+    def fcn(x):
+        col = A.adiabat_column(T[c], 10.0 ** x, ac.sp, ac.nz, ac.planet_mass, ac.planet_radius, ac.P_top, ac.T_trop)
+        return col["N_atmos"] + col["N_surface"] - N_i[:, c]
+    x0 = np.log10(N_i[:, c] * np.array(ac.sp["mass"]) * grav)
+    x, _, ier, _ = fsolve(fcn, x0, xtol=1e-8, diag=np.ones(7), full_output=True)
+    # hybrd's residual is absolute and its stopping test a norm over all unknowns, so it leaves the 1e-10 mol/cm^2 trace
+    # gases wherever they are once the three major inventories are met (H2 ends 95 % off here); the batch solver works
+    # on relative residuals and meets every inventory.  The major gases agree:
+    assert ier == 1 and np.max(np.abs(10.0 ** x[:3] / p["P_i_surf"][:3, c] - 1.0)) < 1e-6
+    assert np.max(np.abs(fcn(x)[3:] / N_i[3:, c])) > 1e-3 > 1e-6 > np.max(np.abs(tot[3:, c] / N_i[3:, c] - 1.0))
+    # background gas: the surface pressure is met, the other gases keep their pressures
+    T2, P2 = sweep(5, seed=19)
+    P2[0], P2[1] = 1.0e4, 1.0e5                            # little water and CO2, so that 2 bar are reachable with N2
+    q = ac.make_profile_bg_gas_batch(T2, P2, 2.0e6, "N2")
+    assert np.max(np.abs(q["P_surf"] / 2.0e6 - 1.0)) < 1e-8
+    assert np.array_equal(np.delete(q["P_i_surf"], 2, axis=0), np.delete(P2, 2, axis=0))
+    from clima_b200.radtran import ClimaException
+    with pytest.raises(ClimaException, match="not in the list of species"):
+        ac.make_profile_bg_gas_batch(T2, P2, 2.0e6, "Xe")
+    with pytest.raises(ClimaException, match="root solve failed in make_profile_bg_gas"):
+        ac.make_profile_bg_gas_batch(T2, P2 * 100.0, 2.0e6, "N2")   # the other gases alone exceed 2 bar
+    # the reference's tutorial: T_trop = 200, P_top = 1e-2, nz = 100; N_i = [15e3, 23, 36, 1e-10 ...]
+    _, _, tc = gpu_model(nz=100)
+    tc.T_trop, tc.P_top = 200.0, 1.0e-2
+    tc.make_column(280.0, np.array([15.0e3, 23.0, 36.0, 1e-10, 1e-10, 1e-10, 1e-10]))
+    assert abs(tc.N_surface[0] / 14999.93596532 - 1.0) < 1e-8          # cell 18: printed N_surface
+    assert abs(tc.N_atmos[0] / 6.40346849e-02 - 1.0) < 2e-3             # printed N_atmos (its dz predates compute_altitude)
+    assert np.max(np.abs((tc.N_atmos + tc.N_surface) / np.array([1.5e4, 23.0, 36.0, 1e-10, 1e-10, 1e-10, 1e-10]) - 1.0)) < 1e-7
+    tc.make_profile_bg_gas(280.0, np.array([260.0, 1.0, 1.0, 1e-10, 1e-10, 1e-10, 1e-10]) * BAR, 2.0e6, "N2")
+    assert abs(tc.P_surf / 2000000.0 - 1.0) < 1e-8                      # cell 20: printed P_surf
+
+
+@pytest.mark.gpu
 def test_make_profile_failures_are_reported_per_column():
     from clima_b200.radtran import ClimaException
     _, _, ac = gpu_model(nz=12)
