@@ -387,6 +387,14 @@ class AdiabatClimate:
                 except np.linalg.LinAlgError:
                     live[q] = False
             step = np.clip(np.nan_to_num(step), -1.0, 1.0)            # at most a decade per iteration
+            # hybrd's test: a Newton step below tol relative to x means x is the root to that accuracy (the residual
+            # itself bottoms out at the integration noise of make_profile, ~1e-7 at the default rtol)
+            small = live & (np.max(np.abs(step) / np.maximum(np.abs(X[:, act]), 1.0), axis=0) < tol)
+            X[:, act[small]] += step[:, small]                        # (the step is taken, as hybrd does)
+            done[act[small]] = True
+            live &= ~small
+            if not live.any():
+                continue
             lam = np.ones(m)
             f0 = np.max(np.abs(F[:, act]), axis=0)
             for _ls in range(10):                                      # halve the step until the residual drops
@@ -403,7 +411,7 @@ class AdiabatClimate:
             X[:, idx] = Xn[:, good]
             F[:, idx] = Fn[:, good]
             done[idx] = (dx < tol) | (fn[good] < tol)
-            failed[act[~good]] = True
+            failed[act[live & ~good]] = True
         return X, done
 
     def make_column_batch(self, T_surf, N_i_surf, tol: float = 1.0e-8) -> Dict:
@@ -490,6 +498,50 @@ class AdiabatClimate:
     def make_profile_bg_gas(self, T_surf: float, P_i_surf, P_surf: float, bg_gas: str):
         p = self.make_profile_bg_gas_batch([T_surf], np.asarray(P_i_surf, dtype=np.float64)[:, None], P_surf, bg_gas)
         self.make_profile(T_surf, p["P_i_surf"][:, 0])
+
+    def surface_temperature_batch(self, P_i_surf, T_guess=280.0, surface_heat_flow: float = 0.0, tol: float = 1.0e-8):
+        """`AdiabatClimate%surface_temperature` (clima_adiabat.f90:882-975, solve_for_T_trop = .false.) for every
+        composition P_i_surf[:, c]: the surface temperature at which ISR - OLR + surface_heat_flow = 0, unknown
+        x = log10(T_surf) as in the reference, every iteration ONE batched TOA_fluxes call over all columns and their
+        perturbations.  Returns (T_surf (ncol), ISR, OLR).  (T_trop is one value per handle, so the reference's
+        solve_for_T_trop = .true. variant, a second unknown per column, is not offered.)"""
+        P_i = np.asfortranarray(P_i_surf, dtype=np.float64)
+        if P_i.ndim == 1:
+            P_i = np.asfortranarray(P_i[:, None])
+        if P_i.shape[0] != self.ng:
+            raise ClimaException("P_i_surf has the wrong dimension")
+        ncol = P_i.shape[1]
+        X0 = np.log10(np.broadcast_to(np.asarray(T_guess, dtype=np.float64), (ncol,)))[None, :].copy()
+        last = {}
+
+        def resid(idx, Xq):
+            T = 10.0 ** Xq[0]
+            try:
+                isr, olr = self.TOA_fluxes_batch(T, np.asfortranarray(P_i[:, idx]))
+            except ClimaException:
+                # one failing column fails the batched call (like the reference's loop): find out which, column by column
+                isr, olr = np.full(T.shape, np.nan), np.full(T.shape, np.nan)
+                for j in range(T.shape[0]):
+                    try:
+                        a, b = self.TOA_fluxes_batch(T[j:j + 1], np.asfortranarray(P_i[:, idx[j:j + 1]]))
+                        isr[j], olr[j] = a[0], b[0]
+                    except ClimaException:
+                        pass
+            last["isr"], last["olr"], last["idx"] = isr, olr, idx
+            with np.errstate(all="ignore"):
+                F = (isr - olr + surface_heat_flow) / olr
+            return F[None, :], np.isfinite(F)
+        X, done = self._newton_batch(X0, resid, tol, h=1.0e-4)
+        if not done.all():
+            raise ClimaException("column %d: hybrd1 root solve failed." % int(np.where(~done)[0][0]))
+        T = 10.0 ** X[0]
+        isr, olr = self.TOA_fluxes_batch(T, P_i)
+        return T, isr, olr
+
+    def surface_temperature(self, P_i_surf, T_guess: float = 280.0) -> float:
+        T, _, _ = self.surface_temperature_batch(np.asarray(P_i_surf, dtype=np.float64)[:, None], T_guess)
+        self.make_profile(float(T[0]), P_i_surf)
+        return float(T[0])
 
     def kernel_ms(self) -> float:
         """Device time of the last make_profile kernel (CUDA events on the handle's stream)."""
