@@ -255,7 +255,18 @@ class AdiabatClimate:
         p["lapse_rate"] = np.diff(lnT, axis=0) / np.diff(lnP, axis=0)
         return p
 
-    def make_profile_batch(self, T_surf, P_i_surf, check: bool = True) -> Dict:
+    def _column_T_trop(self, T_trop):
+        """clima_rt_adiabat_set_column_T_trop: one tropopause temperature per column for the next batch calls
+        (None: back to self.T_trop)."""
+        err = C.create_string_buffer(ERR_LEN + 1)
+        if T_trop is None:
+            self.rad._lib.clima_rt_adiabat_set_column_T_trop(self.rad._h, _i(0), None, err)
+        else:
+            t = np.ascontiguousarray(T_trop, dtype=np.float64).reshape(-1)
+            self.rad._lib.clima_rt_adiabat_set_column_T_trop(self.rad._h, _i(t.shape[0]), t.ctypes.data_as(c_double_p), err)
+        _check(err)
+
+    def make_profile_batch(self, T_surf, P_i_surf, check: bool = True, T_trop=None) -> Dict:
         """`make_profile` for every (T_surf[c], P_i_surf[:, c]) -> dict of (nz, ncol) / (nz, ng, ncol) arrays
         (+ status, nfcn per column).  check=False returns the per-column status instead of raising."""
         self._sync()
@@ -263,8 +274,14 @@ class AdiabatClimate:
         ncol = T_surf.shape[0]
         o, arrs = self._profile_out(ncol)
         err = C.create_string_buffer(ERR_LEN + 1)
-        self.rad._lib.clima_rt_make_profile_batch(self.rad._h, _i(ncol), T_surf.ctypes.data_as(c_double_p),
-                                                  P_i.ctypes.data_as(c_double_p), C.byref(o), err)
+        if T_trop is not None:   # a tropopause temperature per column (the solvers with solve_for_T_trop)
+            self._column_T_trop(T_trop)
+        try:
+            self.rad._lib.clima_rt_make_profile_batch(self.rad._h, _i(ncol), T_surf.ctypes.data_as(c_double_p),
+                                                      P_i.ctypes.data_as(c_double_p), C.byref(o), err)
+        finally:
+            if T_trop is not None:
+                self._column_T_trop(None)
         if check or not arrs["status"].any():
             _check(err)
         self._T_surf = T_surf
@@ -284,7 +301,7 @@ class AdiabatClimate:
         self.N_ocean = p["N_ocean"][:, :, 0].copy()
         self.P_surf, self.P_trop = float(p["P_surf"][0]), float(p["P_trop"][0])
 
-    def TOA_fluxes_batch(self, T_surf, P_i_surf, full: bool = False):
+    def TOA_fluxes_batch(self, T_surf, P_i_surf, full: bool = False, T_trop=None):
         """(ISR, OLR) of every column: make_profile, the radiative grid and the RT in ONE device call
         (`AdiabatClimate%TOA_fluxes` per column in the reference).  full=True returns the whole result dict
         of `Radtran.radiate_batch` plus the profile arrays."""
@@ -295,9 +312,15 @@ class AdiabatClimate:
         o, arrs = alloc_out(nzr, ncol, self.rad.tables.nw_ir, self.rad.tables.nw_sol, False)
         po, parrs = self._profile_out(ncol) if full else (None, None)
         err = C.create_string_buffer(ERR_LEN + 1)
-        self.rad._lib.clima_rt_adiabat_toa_fluxes_batch(self.rad._h, _i(ncol), T_surf.ctypes.data_as(c_double_p),
-                                                        P_i.ctypes.data_as(c_double_p),
-                                                        C.byref(po) if full else None, C.byref(o), err)
+        if T_trop is not None:
+            self._column_T_trop(T_trop)
+        try:
+            self.rad._lib.clima_rt_adiabat_toa_fluxes_batch(self.rad._h, _i(ncol), T_surf.ctypes.data_as(c_double_p),
+                                                            P_i.ctypes.data_as(c_double_p),
+                                                            C.byref(po) if full else None, C.byref(o), err)
+        finally:
+            if T_trop is not None:
+                self._column_T_trop(None)
         _check(err)
         if full:
             self._T_surf = T_surf
@@ -499,42 +522,66 @@ class AdiabatClimate:
         p = self.make_profile_bg_gas_batch([T_surf], np.asarray(P_i_surf, dtype=np.float64)[:, None], P_surf, bg_gas)
         self.make_profile(T_surf, p["P_i_surf"][:, 0])
 
-    def surface_temperature_batch(self, P_i_surf, T_guess=280.0, surface_heat_flow: float = 0.0, tol: float = 1.0e-8):
-        """`AdiabatClimate%surface_temperature` (clima_adiabat.f90:882-975, solve_for_T_trop = .false.) for every
-        composition P_i_surf[:, c]: the surface temperature at which ISR - OLR + surface_heat_flow = 0, unknown
-        x = log10(T_surf) as in the reference, every iteration ONE batched TOA_fluxes call over all columns and their
-        perturbations.  Returns (T_surf (ncol), ISR, OLR).  (T_trop is one value per handle, so the reference's
-        solve_for_T_trop = .true. variant, a second unknown per column, is not offered.)"""
+    def surface_temperature_batch(self, P_i_surf, T_guess=280.0, surface_heat_flow: float = 0.0, tol: float = 1.0e-8,
+                                  solve_for_T_trop: bool = False):
+        """`AdiabatClimate%surface_temperature` (clima_adiabat.f90:882-975) for every composition P_i_surf[:, c]: the
+        surface temperature at which ISR - OLR + surface_heat_flow = 0, unknown x = log10(T_surf) as in the reference,
+        every iteration ONE batched TOA_fluxes call over all columns and their perturbations.  With solve_for_T_trop the
+        tropopause temperature of each column is a second unknown that must equal the skin temperature of its own bond
+        albedo (:953-959; initial guess self.T_trop).  Returns (T_surf (ncol), ISR, OLR) and, with solve_for_T_trop,
+        T_trop (ncol) as a fourth array."""
         P_i = np.asfortranarray(P_i_surf, dtype=np.float64)
         if P_i.ndim == 1:
             P_i = np.asfortranarray(P_i[:, None])
         if P_i.shape[0] != self.ng:
             raise ClimaException("P_i_surf has the wrong dimension")
         ncol = P_i.shape[1]
-        X0 = np.log10(np.broadcast_to(np.asarray(T_guess, dtype=np.float64), (ncol,)))[None, :].copy()
-        last = {}
+        nun = 2 if solve_for_T_trop else 1
+        X0 = np.empty((nun, ncol))
+        X0[0] = np.log10(np.broadcast_to(np.asarray(T_guess, dtype=np.float64), (ncol,)))
+        if solve_for_T_trop:
+            X0[1] = math.log10(self.T_trop)
+        S = self.rad.bolometric_flux()   # W/m^2
+        sigma_si = 5.670374419e-8
+
+        def fluxes(T, cols, Tt):
+            r = self.TOA_fluxes_batch(T, np.asfortranarray(P_i[:, cols]), full=solve_for_T_trop, T_trop=Tt)
+            if not solve_for_T_trop:
+                return r[0], r[1], None
+            return r["ISR"], r["OLR"], r["fup_n_sol"][-1] / r["fdn_n_sol"][-1]   # bond albedo at the top (:955)
 
         def resid(idx, Xq):
             T = 10.0 ** Xq[0]
+            Tt = 10.0 ** Xq[1] if solve_for_T_trop else None
+            m = T.shape[0]
             try:
-                isr, olr = self.TOA_fluxes_batch(T, np.asfortranarray(P_i[:, idx]))
+                isr, olr, alb = fluxes(T, idx, Tt)
             except ClimaException:
                 # one failing column fails the batched call (like the reference's loop): find out which, column by column
-                isr, olr = np.full(T.shape, np.nan), np.full(T.shape, np.nan)
-                for j in range(T.shape[0]):
+                isr, olr, alb = np.full(m, np.nan), np.full(m, np.nan), np.full(m, np.nan)
+                for j in range(m):
                     try:
-                        a, b = self.TOA_fluxes_batch(T[j:j + 1], np.asfortranarray(P_i[:, idx[j:j + 1]]))
+                        a, b, c = fluxes(T[j:j + 1], idx[j:j + 1], None if Tt is None else Tt[j:j + 1])
                         isr[j], olr[j] = a[0], b[0]
+                        if c is not None:
+                            alb[j] = c[0]
                     except ClimaException:
                         pass
-            last["isr"], last["olr"], last["idx"] = isr, olr, idx
             with np.errstate(all="ignore"):
-                F = (isr - olr + surface_heat_flow) / olr
-            return F[None, :], np.isfinite(F)
+                F = np.empty((nun, m))
+                F[0] = (isr - olr + surface_heat_flow) / olr
+                if solve_for_T_trop:
+                    skin = ((S * (1.0 - alb)) / (4.0 * sigma_si)) ** 0.25 * 0.5 ** 0.25   # clima_eqns.f90:248-261
+                    F[1] = skin / Tt - 1.0
+            return F, np.all(np.isfinite(F), axis=0)
         X, done = self._newton_batch(X0, resid, tol, h=1.0e-4)
         if not done.all():
             raise ClimaException("column %d: hybrd1 root solve failed." % int(np.where(~done)[0][0]))
         T = 10.0 ** X[0]
+        if solve_for_T_trop:
+            Tt = 10.0 ** X[1]
+            isr, olr = self.TOA_fluxes_batch(T, P_i, T_trop=Tt)
+            return T, isr, olr, Tt
         isr, olr = self.TOA_fluxes_batch(T, P_i)
         return T, isr, olr
 

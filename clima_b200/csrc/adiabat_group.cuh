@@ -35,6 +35,7 @@ struct GCol {
   bool has_sat;
   double f_i_dry;  // this gas's share of the dry gas
   double mass, RH;
+  double T_trop;   // of this column (AdiabatOut::T_trop_in) or the object's
   const double *sat;
   int err, nfcn;
 };
@@ -136,7 +137,7 @@ struct GProfileSolout {  // solout_dop (:355-449)
     GCol<GS> &d = *col;
     if (d.err) return -10;
     int irtrn = 1;
-    const double g0 = y[0] - d.a->T_trop;
+    const double g0 = y[0] - d.T_trop;
     const double gl = g_root_lane(d, P_cur, y[0]);
     if (nr == 1) {
       g0_old = g0;
@@ -147,7 +148,7 @@ struct GProfileSolout {  // solout_dop (:355-449)
     double best = 0.0;
     int ind_root = -1, info = 0;
     if (chg0) {
-      const double T_trop = d.a->T_trop;
+      const double T_trop = d.T_trop;
       best = zeroin([&](double x) { return dop.contd8(0, x) - T_trop; }, P_old, P_cur, 1.0e-8, info);
       ind_root = 0;
       if (info != 0) d.err = 5;
@@ -238,9 +239,11 @@ make_profile_group_kernel(const AdiabatData *__restrict__ ap, int ncol, int gpw,
     o.nfcn[c] = 0;
   }
   // input checks (:124-139)
-  if (T_surf < a.T_trop) status = 1;
+  const double T_trop = o.T_trop_in ? o.T_trop_in[c] : a.T_trop;
+  col.T_trop = T_trop;
+  if (T_surf < T_trop) status = 1;
   if (!status && col.g.any(Pin < 0.0)) status = 2;
-  if (!status && a.T_trop < 0.0) status = 10;
+  if (!status && T_trop < 0.0) status = 10;
   if (status) {
     if (lane == 0) o.status[c] = status;
     return;
@@ -318,8 +321,8 @@ make_profile_group_kernel(const AdiabatData *__restrict__ ap, int ncol, int gpw,
     if (lane == 0) o.P_trop[c] = so.P_root;
     const double mubar = col.g.sum(f_cur * col.mass);
     for (int k = so.j; k < ne; k++)
-      so.sample(k, a.T_trop,
-                altitude_vs_P(so.P_edge(k), a.T_trop, mubar, so.P_root, so.u_root[1], a.planet_mass, a.planet_radius),
+      so.sample(k, T_trop,
+                altitude_vs_P(so.P_edge(k), T_trop, mubar, so.P_root, so.u_root[1], a.planet_mass, a.planet_radius),
                 f_cur);
   }
   if (!status && so.z_negative) status = 7;

@@ -122,6 +122,7 @@ __device__ bool heat_capacity(const AdiabatData &a, int i, const TPowers &t, dou
 struct Col {
   const AdiabatData *a;
   int ng;
+  double T_trop;           // of this column (AdiabatOut::T_trop_in) or the object's
   signed char cond[MAXG];  // 1 = CondensingSpeciesType, 0 = DrySpeciesType
   double f_i_dry[MAXG];
   int err;
@@ -152,7 +153,7 @@ __device__ NI_MISC double mixing_ratios(const Col &d, double P, double T, double
 
 // one component of root_fcn (:483-513): 0 = tropopause, i + 1 = gas i reaches saturation
 __device__ NI_MISC double root_component(const Col &d, double P, double T, int ind) {
-  if (ind == 0) return T - d.a->T_trop;
+  if (ind == 0) return T - d.T_trop;
   const int i = ind - 1;
   if (d.cond[i]) return 1.0;
   if (!d.a->has_sat[i]) return DBL_MAX;
@@ -657,10 +658,12 @@ make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, int lanes, con
   o.P_surf[c] = 0.0;
 
   // input checks (:124-139)
-  if (T_surf < a.T_trop) status = 1;
+  const double T_trop = o.T_trop_in ? o.T_trop_in[c] : a.T_trop;
+  col.T_trop = T_trop;
+  if (T_surf < T_trop) status = 1;
   for (int i = 0; i < ng; i++)
     if (Pin[i] < 0.0 && !status) status = 2;
-  if (a.T_trop < 0.0 && !status) status = 10;
+  if (T_trop < 0.0 && !status) status = 10;
   if (status) {
     o.status[c] = status;
     return;
@@ -737,8 +740,8 @@ make_profile_kernel(const AdiabatData *__restrict__ ap, int ncol, int lanes, con
     double mubar = 0.0;
     for (int i = 0; i < ng; i++) mubar += f_cur[i] * a.mass[i];
     for (int k = so.j; k < ne; k++)
-      so.sample(k, a.T_trop,
-                altitude_vs_P(so.P_edge(k), a.T_trop, mubar, so.P_root, so.u_root[1], a.planet_mass, a.planet_radius),
+      so.sample(k, T_trop,
+                altitude_vs_P(so.P_edge(k), T_trop, mubar, so.P_root, so.u_root[1], a.planet_mass, a.planet_radius),
                 f_cur);
   }
   if (!status && so.z_negative) status = 7;

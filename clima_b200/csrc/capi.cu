@@ -121,6 +121,8 @@ struct Handle {
   int64_t adiabat_calls = 0;
   double *d_part[3] = {nullptr, nullptr, nullptr};  // particle tables: log10 P (npl), log10 density / radius (npl, np)
   int part_npl = 0;
+  double *d_aTtrop = nullptr;  // per-column tropopause temperatures (clima_rt_adiabat_set_column_T_trop), n of them
+  int aTtrop_n = 0, aTtrop_cap = 0;
   cudaEvent_t adiabat_ev[2] = {nullptr, nullptr};
   double adiabat_ms = 0.0;
 
@@ -956,6 +958,10 @@ static int make_profile_impl(Handle &h, int ncol, const double *T_surf, const do
   if (ncol < 1) throw CudaError{"ncol must be >= 1"};
   if (!T_surf || !P_i_surf) throw CudaError{"clima_rt: null argument"};
   adiabat_ensure(h, (size_t)ncol);
+  if (h.aTtrop_n > 0 && h.aTtrop_n != ncol)
+    throw CudaError{"clima_rt_adiabat_set_column_T_trop holds " + std::to_string(h.aTtrop_n) + " tropopause temperatures, the batch has " +
+                    std::to_string(ncol) + " columns"};
+  h.aout.T_trop_in = h.aTtrop_n > 0 ? h.d_aTtrop : nullptr;
   const size_t nz = h.adiabat.nz, ng = h.adiabat.ng, n = (size_t)ncol;
   NvtxRange r("make_profile");
   CK(cudaMemcpyAsync(h.d_aTs, T_surf, n * 8, cudaMemcpyHostToDevice, h.st));
@@ -1076,6 +1082,7 @@ void clima_rt_destroy(void *handle) {
   for (void *q : h->adiabat_allocs) cudaFree(q);
   if (h->d_adiabat) cudaFree(h->d_adiabat);
   for (double *q : h->d_part) if (q) cudaFree(q);
+  if (h->d_aTtrop) cudaFree(h->d_aTtrop);
   for (auto &e : h->adiabat_ev) if (e) cudaEventDestroy(e);
   free_chunk(*h);
   for (void *p : h->table_allocs) cudaFree(p);
@@ -1345,6 +1352,28 @@ void clima_rt_adiabat_set_particles(void *handle, const int32_t *n, const double
     if (h.tb.np <= 0) throw CudaError{"clima_rt_adiabat_set_particles: the radiative tables have no particles"};
     if (!n || !P || !pdensities || !pradii) throw CudaError{"clima_rt: null argument"};
     set_particle_tables(h, *n, P, pdensities, pradii);
+  } catch (const CudaError &e) {
+    set_err(err, e.msg);
+  }
+}
+
+void clima_rt_adiabat_set_column_T_trop(void *handle, const int32_t *n, const double *T_trop, char *err) {
+  set_err(err, "");
+  try {
+    if (!handle) throw CudaError{"clima_rt: NULL handle"};
+    Handle &h = *static_cast<Handle *>(handle);
+    CK(cudaSetDevice(h.device));
+    if (!n || *n < 0 || (*n > 0 && !T_trop)) throw CudaError{"clima_rt: null argument"};
+    CK(cudaStreamSynchronize(h.st));
+    if (*n > h.aTtrop_cap) {
+      if (h.d_aTtrop) cudaFree(h.d_aTtrop);
+      h.d_aTtrop = nullptr;
+      h.aTtrop_cap = 0;
+      CK(cudaMalloc(&h.d_aTtrop, (size_t)*n * sizeof(double)));
+      h.aTtrop_cap = *n;
+    }
+    if (*n > 0) CK(cudaMemcpy(h.d_aTtrop, T_trop, (size_t)*n * sizeof(double), cudaMemcpyHostToDevice));
+    h.aTtrop_n = *n;
   } catch (const CudaError &e) {
     set_err(err, e.msg);
   }

@@ -93,6 +93,7 @@ struct AdiabatOut {  // device pointers
   int *status, *nfcn;                // (ncol)
   double *T_r, *P_r, *dz_r, *dens_r, *Tsurf_r;  // radiative grid (nullptr: not wanted)
   double *pd_r, *rd_r;               // (nz_r, np, ncol) particle densities / radii (np > 0 only)
+  const double *T_trop_in;           // (ncol) tropopause temperature per column, or nullptr: AdiabatData::T_trop
 };
 size_t rt_adiabat_work_doubles(int nz, int ncol);
 void rt_launch_make_profile(const AdiabatData *a, int ng, int ncol, int num_sms, const double *T_surf,

@@ -33,7 +33,8 @@ EXPORTS = ["clima_rt_create", "clima_rt_destroy", "clima_rt_set_params",
            "clima_rt_comm_unique_id", "clima_rt_comm_init", "clima_rt_comm_destroy", "clima_rt_allgather_device",
            "clima_rt_radiate_batch_sharded",
            "clima_rt_adiabat_set", "clima_rt_make_profile_batch", "clima_rt_adiabat_toa_fluxes_batch", "clima_rt_get_adiabat_stats",
-           "clima_rt_make_profile_batch_noalloc", "clima_rt_adiabat_set_particles"]
+           "clima_rt_make_profile_batch_noalloc", "clima_rt_adiabat_set_particles",
+           "clima_rt_adiabat_set_column_T_trop"]
 COMM_ID_BYTES = 128
 
 

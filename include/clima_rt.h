@@ -331,6 +331,12 @@ void clima_rt_adiabat_set(void *handle, const clima_rt_adiabat *adiabat, char *e
 void clima_rt_adiabat_set_particles(void *handle, const int32_t *n, const double *P, const double *pdensities,
                                     const double *pradii, char *err);
 
+/* One tropopause temperature PER COLUMN for the following batch calls (which must then have ncol = *n), instead of
+   clima_rt_adiabat::T_trop; *n = 0 returns to the single value.  The reference sets self%T_trop before each
+   make_profile of its solvers when solve_for_T_trop is on (src/adiabat/clima_adiabat.f90:926-1000): in a batch every
+   column has its own iterate. */
+void clima_rt_adiabat_set_column_T_trop(void *handle, const int32_t *n, const double *T_trop, char *err);
+
 /* `AdiabatClimate%make_profile` (src/adiabat/clima_adiabat.f90:401-472) for ncol columns:
    T_surf(ncol) [K], P_i_surf(ng,ncol) [dynes/cm^2], HOST pointers.  A column that fails gets its status
    code; `err` names the first such column with the reference's message, the others are still computed. */

@@ -737,6 +737,44 @@ def test_surface_temperature_batch():
 
 
 @pytest.mark.gpu
+def test_per_column_T_trop_and_solve_for_T_trop():
+    """A tropopause temperature per column (clima_rt_adiabat_set_column_T_trop): each column equals the single-value
+    call with its own T_trop; then the reference's solve_for_T_trop (clima_adiabat.f90:926-959, on in its own
+    tests/test_adiabat.f90:27): T_trop of every column ends at the skin temperature of that column's bond albedo."""
+    import dataclasses
+    from clima_b200.radtran import ClimaException
+    _, _, ac = gpu_model(nz=14)
+    T, P = sweep(6, seed=23)
+    Tt = np.array([150.0, 165.0, 180.0, 195.0, 210.0, 160.0])
+    p = ac.make_profile_batch(T, P, T_trop=Tt)
+    r = ac.TOA_fluxes_batch(T, P, T_trop=Tt)
+    for c in range(6):
+        ac.T_trop = float(Tt[c])
+        q = ac.make_profile_batch(T[c:c + 1], P[:, c:c + 1])
+        for k in ("T", "z", "dz", "f_i", "P_trop"):
+            assert np.array_equal(q[k][..., 0], p[k][..., c]), k
+        assert ac.TOA_fluxes(T[c], P[:, c])[1] == r[1][c]
+        assert p["T"][:, c].min() == Tt[c] or p["P_trop"][c] < 0
+    ac.T_trop = 180.0
+    assert np.array_equal(ac.make_profile_batch(T, P)["T"], ac.make_profile_batch(T, P, T_trop=np.full(6, 180.0))["T"])
+    with pytest.raises(ClimaException, match="tropopause temperatures, the batch has"):
+        ac.make_profile_batch(T, P, T_trop=Tt[:4])
+    # solve_for_T_trop
+    ac.rad.params = dataclasses.replace(ac.rad.params, photon_scale_factor=0.3)
+    n = 4
+    Pc = np.asfortranarray(np.repeat(P_I_OCEAN[:, None], n, 1))
+    Pc[1] = np.logspace(-3, 0, n) * BAR
+    Ts, isr, olr, Tts = ac.surface_temperature_batch(Pc, T_guess=300.0, solve_for_T_trop=True)
+    assert np.max(np.abs(isr / olr - 1.0)) < 1e-6 and np.all((Tts > 100.0) & (Tts < Ts))
+    full = ac.TOA_fluxes_batch(Ts, Pc, full=True, T_trop=Tts)
+    alb = full["fup_n_sol"][-1] / full["fdn_n_sol"][-1]
+    skin = np.array([ac.rad.skin_temperature(a) for a in alb])
+    assert np.max(np.abs(skin / Tts - 1.0)) < 1e-6
+    has = full["profile"]["P_trop"] > 0            # a hot column may reach P_top before it cools to its T_trop
+    assert has.any() and np.all(np.abs(full["profile"]["T"].min(axis=0)[has] / Tts[has] - 1.0) < 1e-12)
+
+
+@pytest.mark.gpu
 def test_make_profile_failures_are_reported_per_column():
     from clima_b200.radtran import ClimaException
     _, _, ac = gpu_model(nz=12)
