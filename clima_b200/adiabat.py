@@ -585,6 +585,90 @@ class AdiabatClimate:
         isr, olr = self.TOA_fluxes_batch(T, P_i)
         return T, isr, olr
 
+    def TOA_fluxes_column_batch(self, T_surf, N_i_surf):
+        """`AdiabatClimate%TOA_fluxes_column` (clima_adiabat.f90:802-825): make_column, then the RT -> (ISR, OLR)."""
+        sol = self.make_column_batch(T_surf, N_i_surf)
+        return self.TOA_fluxes_batch(T_surf, sol["P_i_surf"])
+
+    def TOA_fluxes_bg_gas_batch(self, T_surf, P_i_surf, P_surf, bg_gas: str):
+        """`AdiabatClimate%TOA_fluxes_bg_gas` (clima_adiabat.f90:828-853): make_profile_bg_gas, then the RT."""
+        sol = self.make_profile_bg_gas_batch(T_surf, P_i_surf, P_surf, bg_gas)
+        return self.TOA_fluxes_batch(T_surf, sol["P_i_surf"])
+
+    def _joint_solve(self, X0, cols_of, extra_residuals, surface_heat_flow, tol):
+        """Energy balance plus column-builder constraints as ONE Newton system per column (the reference nests a
+        hybrd1 of the column builder inside a hybrd1 for T_surf; the root is the same).  X = [log10 T_surf; log10 of
+        the unknown pressures]; cols_of(X, idx) -> P_i_surf (ng, m); extra_residuals(profile, idx) -> (n - 1, m)."""
+        def resid(idx, Xq):
+            m = Xq.shape[1]
+            T = 10.0 ** Xq[0]
+            P = np.asfortranarray(cols_of(Xq, idx))
+            F = np.full((Xq.shape[0], m), np.nan)
+            try:
+                r = self.TOA_fluxes_batch(T, P, full=True)
+                with np.errstate(all="ignore"):
+                    F[0] = (r["ISR"] - r["OLR"] + surface_heat_flow) / r["OLR"]
+                    F[1:] = extra_residuals(r["profile"], idx)
+            except ClimaException:
+                for j in range(m):
+                    try:
+                        r = self.TOA_fluxes_batch(T[j:j + 1], P[:, j:j + 1], full=True)
+                        with np.errstate(all="ignore"):
+                            F[0, j] = (r["ISR"][0] - r["OLR"][0] + surface_heat_flow) / r["OLR"][0]
+                            F[1:, j] = extra_residuals(r["profile"], idx[j:j + 1])[:, 0]
+                    except ClimaException:
+                        pass
+            return F, np.all(np.isfinite(F), axis=0)
+        X, done = self._newton_batch(X0, resid, tol, h=1.0e-4)
+        if not done.all():
+            raise ClimaException("column %d: hybrd1 root solve failed." % int(np.where(~done)[0][0]))
+        return X
+
+    def surface_temperature_column_batch(self, N_i_surf, T_guess=280.0, surface_heat_flow: float = 0.0,
+                                         tol: float = 1.0e-8):
+        """`AdiabatClimate%surface_temperature_column` (clima_adiabat.f90:977-992): ISR = OLR with the atmosphere built
+        from column inventories N_i_surf (ng, ncol) [mol/cm^2].  Returns (T_surf, ISR, OLR, P_i_surf)."""
+        N_t = np.asarray(N_i_surf, dtype=np.float64)
+        if N_t.ndim == 1:
+            N_t = N_t[:, None]
+        ncol = N_t.shape[1]
+        Tg = np.broadcast_to(np.asarray(T_guess, dtype=np.float64), (ncol,)).copy()
+        start = self.make_column_batch(Tg, N_t)                       # pressures that hold the inventories at T_guess
+        X0 = np.vstack([np.log10(Tg)[None, :], np.log10(start["P_i_surf"])])
+        den = np.where(N_t > 0.0, N_t, 1.0)
+
+        def extra(p, idx):
+            N = p["N_atmos"] + p["N_surface"] + p["N_ocean"].sum(axis=1)
+            return (N - N_t[:, idx]) / den[:, idx]
+        X = self._joint_solve(X0, lambda Xq, idx: 10.0 ** Xq[1:], extra, surface_heat_flow, tol)
+        T, P_i = 10.0 ** X[0], np.asfortranarray(10.0 ** X[1:])
+        isr, olr = self.TOA_fluxes_batch(T, P_i)
+        return T, isr, olr, P_i
+
+    def surface_temperature_bg_gas_batch(self, P_i_surf, P_surf, bg_gas: str, T_guess=280.0,
+                                         surface_heat_flow: float = 0.0, tol: float = 1.0e-8):
+        """`AdiabatClimate%surface_temperature_bg_gas` (clima_adiabat.f90:996-1020): ISR = OLR with the pressure of
+        `bg_gas` adjusted so that the surface pressure is P_surf.  Returns (T_surf, ISR, OLR, P_i_surf)."""
+        P_i = np.asfortranarray(P_i_surf, dtype=np.float64)
+        if P_i.ndim == 1:
+            P_i = np.asfortranarray(P_i[:, None])
+        ncol = P_i.shape[1]
+        P_t = np.broadcast_to(np.asarray(P_surf, dtype=np.float64), (ncol,)).copy()
+        Tg = np.broadcast_to(np.asarray(T_guess, dtype=np.float64), (ncol,)).copy()
+        start = self.make_profile_bg_gas_batch(Tg, P_i, P_t, bg_gas)
+        ind = self.sp["names"].index(bg_gas)
+        X0 = np.vstack([np.log10(Tg)[None, :], np.log10(start["P_i_surf"][ind])[None, :]])
+
+        def cols_of(Xq, idx):
+            Pq = P_i[:, idx].copy()
+            Pq[ind] = 10.0 ** Xq[1]
+            return Pq
+        X = self._joint_solve(X0, cols_of, lambda p, idx: (p["P_surf"] / P_t[idx] - 1.0)[None, :], surface_heat_flow, tol)
+        T = 10.0 ** X[0]
+        P_sol = np.asfortranarray(cols_of(X, np.arange(ncol)))
+        isr, olr = self.TOA_fluxes_batch(T, P_sol)
+        return T, isr, olr, P_sol
+
     def surface_temperature(self, P_i_surf, T_guess: float = 280.0) -> float:
         T, _, _ = self.surface_temperature_batch(np.asarray(P_i_surf, dtype=np.float64)[:, None], T_guess)
         self.make_profile(float(T[0]), P_i_surf)

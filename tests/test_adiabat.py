@@ -775,6 +775,35 @@ def test_per_column_T_trop_and_solve_for_T_trop():
 
 
 @pytest.mark.gpu
+def test_surface_temperature_column_and_bg_gas_batches():
+    """The two other climate solves of the reference (clima_adiabat.f90:977-1020): energy balance together with the
+    inventories / with a background gas at a fixed surface pressure.  At the solution all constraints hold, and the
+    answer equals the nested route (column builder inside, energy balance outside) the reference takes."""
+    import dataclasses
+    _, _, ac = gpu_model(nz=12)
+    ac.T_trop = 160.0
+    ac.rad.params = dataclasses.replace(ac.rad.params, photon_scale_factor=0.3)
+    n = 3
+    N_i = np.repeat(np.array([15.0e3, 1.0, 36.0, 1e-10, 1e-10, 1e-10, 1e-10])[:, None], n, 1)
+    N_i[1] = [0.1, 1.0, 10.0]                                           # CO2 inventories
+    T, isr, olr, P_i = ac.surface_temperature_column_batch(N_i, T_guess=310.0)
+    assert np.max(np.abs(isr / olr - 1.0)) < 1e-6 and np.all(np.diff(T) > 0.0)
+    p = ac.make_profile_batch(T, P_i)
+    tot = p["N_atmos"] + p["N_surface"] + p["N_ocean"].sum(axis=1)
+    assert np.max(np.abs(tot / N_i - 1.0)) < 1e-6
+    a, b = ac.TOA_fluxes_column_batch(T, N_i)                            # nested: make_column at the answer, then the RT
+    assert np.max(np.abs(a / isr - 1.0)) < 1e-6 and np.max(np.abs(b / olr - 1.0)) < 1e-6
+    Pg = np.asfortranarray(np.repeat(P_I_OCEAN[:, None], n, 1))
+    Pg[0], Pg[1] = 1.0e4, [1.0e3, 1.0e4, 1.0e5]                          # a dry-ish atmosphere topped up with N2 to 1.5 bar
+    T2, isr2, olr2, P2 = ac.surface_temperature_bg_gas_batch(Pg, 1.5e6, "N2", T_guess=300.0)
+    assert np.max(np.abs(isr2 / olr2 - 1.0)) < 1e-6
+    q = ac.make_profile_batch(T2, P2)
+    assert np.max(np.abs(q["P_surf"] / 1.5e6 - 1.0)) < 1e-6 and np.array_equal(np.delete(P2, 2, 0), np.delete(Pg, 2, 0))
+    a2, b2 = ac.TOA_fluxes_bg_gas_batch(T2, Pg, 1.5e6, "N2")
+    assert np.max(np.abs(a2 / isr2 - 1.0)) < 1e-6 and np.max(np.abs(b2 / olr2 - 1.0)) < 1e-6
+
+
+@pytest.mark.gpu
 def test_make_profile_failures_are_reported_per_column():
     from clima_b200.radtran import ClimaException
     _, _, ac = gpu_model(nz=12)
