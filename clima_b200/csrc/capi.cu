@@ -1494,6 +1494,10 @@ void clima_rt_make_profile_batch_noalloc(void *handle, const int32_t *ncol, cons
     o.P = p.P; o.T = p.T; o.z = p.z; o.dz = p.dz; o.f_i = p.f_i;
     o.f_i_surf = p.f_i_surf; o.N_surface = p.N_surface; o.P_surf = p.P_surf; o.P_trop = p.P_trop;
     o.status = p.status; o.nfcn = p.nfcn;  // the radiative-grid members stay NULL: not written
+    if (h.aTtrop_n > 0 && h.aTtrop_n != *ncol)
+      throw CudaError{"clima_rt_adiabat_set_column_T_trop holds " + std::to_string(h.aTtrop_n) + " tropopause temperatures, the batch has " +
+                      std::to_string(*ncol) + " columns"};
+    o.T_trop_in = h.aTtrop_n > 0 ? h.d_aTtrop : nullptr;
     const char *why = "";
     if (rt_launch_make_profile_noalloc(h.d_adiabat, h.adiabat.ng, h.adiabat.nz, *ncol, h.num_sms, T_surf, P_i_surf, o,
                                        h.st, &why))

@@ -364,7 +364,8 @@ void clima_rt_adiabat_toa_fluxes_batch(void *handle, const int32_t *ncol, const 
      * the call itself issues no cudaMalloc / cudaFree / event creation: the handle and clima_rt_adiabat_set
        (which do allocate) are set-up and come first;
      * per-column failures are left in `profile->status` (CLIMA_RT_PROFILE_*) for the caller to read; `err` is
-       set only for argument, size and launch errors.
+       set only for argument, size and launch errors;
+     * a per-column tropopause temperature (clima_rt_adiabat_set_column_T_trop) applies as in the other calls.
    The work is enqueued on the handle's stream and the call returns after a stream synchronisation.  Every call
    (from every handle on that GPU) shares the one array, which keeps the last call's contents -- nothing in it
    has to start at zero, each column writes its work arrays before reading them -- so calls that OVERLAP on the

@@ -521,6 +521,11 @@ def test_adiabat_toa_fluxes_with_particles(mode, monkeypatch):
         if not given:
             olr0 = r["OLR"].copy()
     assert np.max(np.abs(r["OLR"] / olr0 - 1.0)) > 1e-3       # the particles do change the fluxes
+    # the particle profile may also be set before the first profile call of a fresh handle
+    ac2 = AdiabatClimate(Radtran(tb, pr), species(), nz, EARTH_MASS, EARTH_RADIUS)
+    ac2.T_trop, ac2.rtol = 160.0, 1e-12
+    ac2.set_particle_density_and_radii(Pset, pdens, prad)
+    assert np.array_equal(ac2.TOA_fluxes_batch(T, P)[1], r["OLR"])
     with pytest.raises(ClimaException, match="Interpolation initialization"):
         ac.set_particle_density_and_radii(Pset[::-1], pdens, prad)
     with pytest.raises(ClimaException, match="`pradii` must be larger than zero"):
